@@ -1,0 +1,436 @@
+// K2/K3: persistent warp-specialised tcgen05 GEMM for sm_100a.
+//
+//   C[M,N] = alpha * ( op(A)[M,K] · op(B)[K,N]  +  A2[M,K2] · op(B2)[K2,N] ) (+ R) (+ C)
+//
+// * Operands are 16-bit (bf16 or fp16), staged global->shared by TMA with the 128-byte
+//   swizzle, multiplied by tcgen05.mma (kind::f16) issued from ONE thread, accumulated in
+//   fp32 in tensor memory (TMEM, two accumulator stages so the epilogue of tile i overlaps
+//   the MMAs of tile i+1), read back with tcgen05.ld by four epilogue warps.
+// * "K-extension": a second operand pair (A2,B2) is streamed after the main K loop into the
+//   SAME TMEM tile. This is how LoRA is fused: with A2 = (dropout(x)·A^T)
+//   padded to 64 columns and B2 = (alpha/r)·B padded to 64 columns the kernel produces
+//   W·x + (alpha/r)·B·(A·x) with one extra 64-deep K block instead of 4 extra kernels
+//   (the reference path is PEFT lora.Linear: base GEMM + dropout + 2 GEMMs + scale + add,
+//   reference call site training/train_baseline.py:131-140).
+// * Operand majorness is a template switch, so forward (x·W^T: B is K-major), input-gradient
+//   (dy·W: B is MN-major, read from the SAME weight buffer, no transposed copy) and
+//   weight-gradient (dy^T·x: both MN-major, split-K with fp32 atomics) all run here.
+// * Roles: warp 0 = TMA producer, warp 1 = TMEM allocator + MMA issuer, warps 2..5 = epilogue.
+//
+// Replaces cuBLAS/cuBLASLt GEMM calls made by torch.nn.functional.linear in the reference
+// stack.
+#include "common.cuh"
+
+#include <mutex>
+#include <unordered_map>
+#include <string>
+#include <cstring>
+#include <cstdio>
+
+namespace {
+
+constexpr int BM = 128;
+constexpr int BK = 64;
+constexpr int UMMA_K = 16;
+constexpr int NUM_THREADS = 192;
+
+template <int BN>
+struct Cfg {
+  static constexpr int A_BYTES = BM * BK * 2;
+  static constexpr int B_BYTES = BN * BK * 2;
+  static constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
+  static constexpr int STAGES = (BN == 256) ? 4 : (BN == 128 ? 6 : 8);
+  static constexpr int TMEM_COLS = 2 * BN;
+  static constexpr int BAR_BYTES = 256;
+  static constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + BAR_BYTES + 1024;
+};
+
+struct GemmParams {
+  int M, N;
+  int nmb, nnb;           // tile counts
+  int nkb_main, nkb_ext;  // 64-deep K blocks in the main and extension operands
+  int split_k, kb_per_split;
+  void* C;
+  const void* R;
+  long long ldc, ldr;
+  int out_dtype;   // DltiDtype
+  int in_dtype;    // DltiDtype (16-bit)
+  int accumulate;  // fp32 output only: C += result
+  int atomic_out;  // fp32 output only: red.add (split-K)
+  int vec_ok;      // 16-byte vector stores allowed
+  float alpha;
+  uint32_t idesc;
+};
+
+template <int BN, bool A_MN, bool B_MN>
+__global__ void __launch_bounds__(NUM_THREADS, 1)
+gemm_tcgen05_kernel(const GemmParams p, const __grid_constant__ CUtensorMap tmA,
+                    const __grid_constant__ CUtensorMap tmB,
+                    const __grid_constant__ CUtensorMap tmA2,
+                    const __grid_constant__ CUtensorMap tmB2) {
+  using C_ = Cfg<BN>;
+  extern __shared__ uint8_t smem_raw[];
+  const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;
+  const uint32_t bar_base = smem_base + C_::STAGES * C_::STAGE_BYTES;
+  auto full_bar = [&](int s) { return bar_base + 8u * s; };
+  auto empty_bar = [&](int s) { return bar_base + 8u * (C_::STAGES + s); };
+  auto tfull_bar = [&](int s) { return bar_base + 8u * (2 * C_::STAGES + s); };
+  auto tempty_bar = [&](int s) { return bar_base + 8u * (2 * C_::STAGES + 2 + s); };
+  const uint32_t tmem_slot = bar_base + 8u * (2 * C_::STAGES + 4);
+  // generic pointer to the TMEM base slot
+  volatile uint32_t* tmem_slot_ptr =
+      reinterpret_cast<volatile uint32_t*>(smem_raw + (tmem_slot - smem_u32(smem_raw)));
+
+  const int warp = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
+  const int tiles_mn = p.nmb * p.nnb;
+  const int total_tiles = tiles_mn * p.split_k;
+  const int nkb_total = p.nkb_main + p.nkb_ext;
+
+  if (warp == 0 && lane == 0) {
+    tma_prefetch_desc(&tmA);
+    tma_prefetch_desc(&tmB);
+    if (p.nkb_ext > 0) {
+      tma_prefetch_desc(&tmA2);
+      tma_prefetch_desc(&tmB2);
+    }
+    for (int s = 0; s < C_::STAGES; ++s) {
+      mbar_init(full_bar(s), 1);
+      mbar_init(empty_bar(s), 1);
+    }
+    for (int s = 0; s < 2; ++s) {
+      mbar_init(tfull_bar(s), 1);
+      mbar_init(tempty_bar(s), 4);
+    }
+    mbar_fence_init();
+  }
+  if (warp == 1) {
+    tmem_alloc(tmem_slot, C_::TMEM_COLS);
+    tmem_relinquish();
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot_ptr;
+
+  if (warp == 0) {
+    // ===================== TMA producer =====================
+    if (lane == 0) {
+      int stage = 0;
+      uint32_t phase = 0;
+      for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
+        const int split = tile / tiles_mn;
+        const int rem = tile - split * tiles_mn;
+        const int n_blk = rem / p.nmb;
+        const int m_blk = rem - n_blk * p.nmb;
+        const int m0 = m_blk * BM, n0 = n_blk * BN;
+        const int kb0 = split * p.kb_per_split;
+        const int kb1 = min(nkb_total, kb0 + p.kb_per_split);
+        for (int kb = kb0; kb < kb1; ++kb) {
+          mbar_wait(empty_bar(stage), phase ^ 1u);
+          const uint32_t sa = smem_base + stage * C_::STAGE_BYTES;
+          const uint32_t sb = sa + C_::A_BYTES;
+          const uint32_t fb = full_bar(stage);
+          mbar_expect_tx(fb, C_::STAGE_BYTES);
+          const bool ext = kb >= p.nkb_main;
+          const CUtensorMap* ma = ext ? &tmA2 : &tmA;
+          const CUtensorMap* mb = ext ? &tmB2 : &tmB;
+          const int k0 = (ext ? kb - p.nkb_main : kb) * BK;
+          if constexpr (!A_MN) {
+            tma_load_2d(sa, ma, fb, k0, m0);
+          } else {
+#pragma unroll
+            for (int j = 0; j < BM / 64; ++j) tma_load_2d(sa + j * (BK * 128), ma, fb, m0 + 64 * j, k0);
+          }
+          if constexpr (!B_MN) {
+            tma_load_2d(sb, mb, fb, k0, n0);
+          } else {
+#pragma unroll
+            for (int j = 0; j < BN / 64; ++j) tma_load_2d(sb + j * (BK * 128), mb, fb, n0 + 64 * j, k0);
+          }
+          if (++stage == C_::STAGES) { stage = 0; phase ^= 1u; }
+        }
+      }
+    }
+  } else if (warp == 1) {
+    // ===================== MMA issuer (single thread) =====================
+    if (lane == 0) {
+      int stage = 0;
+      uint32_t phase = 0;
+      int acc = 0;
+      uint32_t acc_phase = 0;
+      for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
+        const int split = tile / tiles_mn;
+        const int kb0 = split * p.kb_per_split;
+        const int kb1 = min(nkb_total, kb0 + p.kb_per_split);
+        mbar_wait(tempty_bar(acc), acc_phase ^ 1u);
+        tc_fence_after();
+        const uint32_t d_tmem = tmem_base + (uint32_t)(acc * BN);
+        for (int kb = kb0; kb < kb1; ++kb) {
+          mbar_wait(full_bar(stage), phase);
+          tc_fence_after();
+          const uint32_t sa = smem_base + stage * C_::STAGE_BYTES;
+          const uint32_t sb = sa + C_::A_BYTES;
+#pragma unroll
+          for (int k = 0; k < BK / UMMA_K; ++k) {
+            uint64_t ad, bd;
+            if constexpr (!A_MN) ad = umma_smem_desc(sa + k * (UMMA_K * 2), 0, 1024);
+            else                 ad = umma_smem_desc(sa + k * (UMMA_K * 128), BK * 128, 1024);
+            if constexpr (!B_MN) bd = umma_smem_desc(sb + k * (UMMA_K * 2), 0, 1024);
+            else                 bd = umma_smem_desc(sb + k * (UMMA_K * 128), BK * 128, 1024);
+            umma_f16_ss(d_tmem, ad, bd, p.idesc, (kb > kb0 || k > 0) ? 1u : 0u);
+          }
+          umma_commit(empty_bar(stage));  // frees the smem slot once these MMAs retire
+          if (kb == kb1 - 1) umma_commit(tfull_bar(acc));
+          if (++stage == C_::STAGES) { stage = 0; phase ^= 1u; }
+        }
+        if (++acc == 2) { acc = 0; acc_phase ^= 1u; }
+      }
+    }
+  } else {
+    // ===================== epilogue (4 warps; warp w owns TMEM lanes 32*(w%4)..) =============
+    const int quarter = warp & 3;
+    int acc = 0;
+    uint32_t acc_phase = 0;
+    for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
+      const int split = tile / tiles_mn;
+      const int rem = tile - split * tiles_mn;
+      const int n_blk = rem / p.nmb;
+      const int m_blk = rem - n_blk * p.nmb;
+      const int row = m_blk * BM + quarter * 32 + lane;
+      const int n0 = n_blk * BN;
+      mbar_wait(tfull_bar(acc), acc_phase);
+      tc_fence_after();
+      const uint32_t t_row = tmem_base + ((uint32_t)(quarter * 32) << 16) + (uint32_t)(acc * BN);
+#pragma unroll 1
+      for (int c = 0; c < BN / 32; ++c) {
+        const int col0 = n0 + c * 32;
+        if (col0 >= p.N) break;  // warp-uniform
+        uint32_t v[32];
+        tmem_ld_32x32b_x32(t_row + c * 32, v);
+        tmem_wait_ld();
+        if (row < p.M) {
+          float f[32];
+#pragma unroll
+          for (int i = 0; i < 32; ++i) f[i] = __uint_as_float(v[i]) * p.alpha;
+          const bool full = (col0 + 32 <= p.N) && p.vec_ok;
+          if (p.out_dtype == DLTI_FP32) {
+            float* crow = reinterpret_cast<float*>(p.C) + (long long)row * p.ldc + col0;
+            if (p.atomic_out) {
+              for (int i = 0; i < 32; ++i)
+                if (col0 + i < p.N) atomicAdd(crow + i, f[i]);
+            } else if (full) {
+#pragma unroll
+              for (int i = 0; i < 8; ++i) {
+                float4 o = make_float4(f[4 * i], f[4 * i + 1], f[4 * i + 2], f[4 * i + 3]);
+                float4* dst = reinterpret_cast<float4*>(crow) + i;
+                if (p.accumulate) {
+                  float4 old = *dst;
+                  o.x += old.x; o.y += old.y; o.z += old.z; o.w += old.w;
+                }
+                *dst = o;
+              }
+            } else {
+              for (int i = 0; i < 32; ++i)
+                if (col0 + i < p.N) crow[i] = p.accumulate ? crow[i] + f[i] : f[i];
+            }
+          } else {
+            uint16_t* crow = reinterpret_cast<uint16_t*>(p.C) + (long long)row * p.ldc + col0;
+            const uint16_t* rrow =
+                p.R ? reinterpret_cast<const uint16_t*>(p.R) + (long long)row * p.ldr + col0 : nullptr;
+            const bool bf = p.out_dtype == DLTI_BF16;
+            if (full) {
+              if (rrow) {
+#pragma unroll
+                for (int i = 0; i < 4; ++i) {
+                  int4 rv = *(reinterpret_cast<const int4*>(rrow) + i);
+                  const uint32_t* ru = reinterpret_cast<const uint32_t*>(&rv);
+#pragma unroll
+                  for (int j = 0; j < 4; ++j) {
+                    float2 r2 = bf ? Cvt<__nv_bfloat16>::unpack2(ru[j]) : Cvt<__half>::unpack2(ru[j]);
+                    f[8 * i + 2 * j] += r2.x;
+                    f[8 * i + 2 * j + 1] += r2.y;
+                  }
+                }
+              }
+#pragma unroll
+              for (int i = 0; i < 4; ++i) {
+                int4 o;
+                uint32_t* ou = reinterpret_cast<uint32_t*>(&o);
+#pragma unroll
+                for (int j = 0; j < 4; ++j)
+                  ou[j] = bf ? Cvt<__nv_bfloat16>::pack2(f[8 * i + 2 * j], f[8 * i + 2 * j + 1])
+                             : Cvt<__half>::pack2(f[8 * i + 2 * j], f[8 * i + 2 * j + 1]);
+                *(reinterpret_cast<int4*>(crow) + i) = o;
+              }
+            } else {
+              for (int i = 0; i < 32; ++i) {
+                if (col0 + i < p.N) {
+                  float x = f[i];
+                  if (rrow) {
+                    x += bf ? __bfloat162float(*reinterpret_cast<const __nv_bfloat16*>(rrow + i))
+                            : __half2float(*reinterpret_cast<const __half*>(rrow + i));
+                  }
+                  if (bf) *reinterpret_cast<__nv_bfloat16*>(crow + i) = __float2bfloat16_rn(x);
+                  else    *reinterpret_cast<__half*>(crow + i) = __float2half_rn(x);
+                }
+              }
+            }
+          }
+        }
+      }
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(tempty_bar(acc));
+      if (++acc == 2) { acc = 0; acc_phase ^= 1u; }
+    }
+  }
+
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 1) {
+    tc_fence_after();
+    tmem_dealloc(tmem_base, C_::TMEM_COLS);
+  }
+}
+
+// ---------------------------------------------------------------------------
+// Host side
+// ---------------------------------------------------------------------------
+struct TmapKey {
+  const void* base;
+  uint64_t inner, outer, ld;
+  uint32_t bi, bo;
+  bool operator==(const TmapKey& o) const {
+    return base == o.base && inner == o.inner && outer == o.outer && ld == o.ld && bi == o.bi &&
+           bo == o.bo;
+  }
+};
+struct TmapKeyHash {
+  size_t operator()(const TmapKey& k) const {
+    size_t h = reinterpret_cast<size_t>(k.base);
+    auto mix = [&](uint64_t v) { h ^= v + 0x9e3779b97f4a7c15ull + (h << 6) + (h >> 2); };
+    mix(k.inner); mix(k.outer); mix(k.ld); mix(((uint64_t)k.bi << 32) | k.bo);
+    return h;
+  }
+};
+std::mutex g_tm_mu;
+std::unordered_map<TmapKey, CUtensorMap, TmapKeyHash> g_tm_cache;
+
+int get_tmap(CUtensorMap* out, const void* base, uint64_t inner, uint64_t outer, uint64_t ld,
+             uint32_t bi, uint32_t bo) {
+  TmapKey key{base, inner, outer, ld, bi, bo};
+  {
+    std::lock_guard<std::mutex> g(g_tm_mu);
+    auto it = g_tm_cache.find(key);
+    if (it != g_tm_cache.end()) {
+      *out = it->second;
+      return 0;
+    }
+  }
+  int rc = dlti_make_tmap_2d(out, base, inner, outer, ld, bi, bo, 2, 128);
+  if (rc) return rc;
+  std::lock_guard<std::mutex> g(g_tm_mu);
+  if (g_tm_cache.size() > 65536) g_tm_cache.clear();
+  g_tm_cache.emplace(key, *out);
+  return 0;
+}
+
+template <int BN, bool A_MN, bool B_MN>
+int launch(const GemmParams& p, const CUtensorMap& a, const CUtensorMap& b, const CUtensorMap& a2,
+           const CUtensorMap& b2, int grid, cudaStream_t stream) {
+  using C_ = Cfg<BN>;
+  static bool configured[64] = {false};
+  int dev = 0;
+  cudaGetDevice(&dev);
+  if (!configured[dev & 63]) {
+    DLTI_CUDA_CHECK(cudaFuncSetAttribute(gemm_tcgen05_kernel<BN, A_MN, B_MN>,
+                                         cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                         C_::SMEM_BYTES));
+    configured[dev & 63] = true;
+  }
+  gemm_tcgen05_kernel<BN, A_MN, B_MN><<<grid, NUM_THREADS, C_::SMEM_BYTES, stream>>>(p, a, b, a2, b2);
+  dlti_count_launch();
+  return (int)cudaGetLastError();
+}
+
+}  // namespace
+
+// See include/dlti_b200.h for the contract.
+DLTI_API int dlti_gemm(const void* A, const void* B, void* C, const void* R, int M, int N, int K,
+                       long long lda, long long ldb, long long ldc, long long ldr, int a_mn,
+                       int b_mn, const void* A2, const void* B2, int K2, long long lda2,
+                       long long ldb2, int in_dtype, int out_dtype, float alpha, int accumulate,
+                       int split_k, int block_n, int max_ctas, cudaStream_t stream) {
+  if (M <= 0 || N <= 0 || K < 0 || (K == 0 && K2 == 0)) return DLTI_ERR_BAD_ARG;
+  if (in_dtype != DLTI_BF16 && in_dtype != DLTI_FP16) return DLTI_ERR_UNSUPPORTED;
+  if (K2 % BK) { dlti_set_error("K2 must be a multiple of 64"); return DLTI_ERR_BAD_ARG; }
+  if (out_dtype != DLTI_FP32 && accumulate) { dlti_set_error("accumulate needs fp32 output"); return DLTI_ERR_BAD_ARG; }
+  if (a_mn && !b_mn) return DLTI_ERR_UNSUPPORTED;
+  int bn = block_n;
+  if (bn == 0) bn = (N <= 64) ? 64 : (N <= 128 ? 128 : 256);
+  if (a_mn && bn == 256) bn = 128;
+  if (bn != 64 && bn != 128 && bn != 256) return DLTI_ERR_BAD_ARG;
+
+  GemmParams p{};
+  p.M = M; p.N = N;
+  p.nmb = (M + BM - 1) / BM;
+  p.nnb = (N + bn - 1) / bn;
+  p.nkb_main = (K + BK - 1) / BK;
+  p.nkb_ext = (A2 && B2) ? K2 / BK : 0;
+  const int nkb_total = p.nkb_main + p.nkb_ext;
+  if (split_k < 1) split_k = 1;
+  if (split_k > nkb_total) split_k = nkb_total;
+  p.kb_per_split = (nkb_total + split_k - 1) / split_k;
+  p.split_k = (nkb_total + p.kb_per_split - 1) / p.kb_per_split;
+  if (p.split_k > 1 && !(out_dtype == DLTI_FP32 && accumulate)) {
+    dlti_set_error("split_k > 1 requires fp32 output with accumulate=1 (atomic adds into C)");
+    return DLTI_ERR_BAD_ARG;
+  }
+  p.C = C; p.R = R; p.ldc = ldc; p.ldr = ldr;
+  p.out_dtype = out_dtype; p.in_dtype = in_dtype;
+  p.accumulate = accumulate;
+  p.atomic_out = p.split_k > 1;
+  const int ob = out_dtype == DLTI_FP32 ? 4 : 2;
+  p.vec_ok = ((reinterpret_cast<uintptr_t>(C) & 15) == 0) && ((ldc * ob) % 16 == 0) &&
+             (!R || (((reinterpret_cast<uintptr_t>(R) & 15) == 0) && ((ldr * 2) % 16 == 0)));
+  p.alpha = alpha;
+  p.idesc = umma_idesc_f16(in_dtype, BM, bn, a_mn != 0, b_mn != 0);
+
+  CUtensorMap ta, tb, ta2, tb2;
+  int rc;
+  if (p.nkb_main > 0) {
+    rc = a_mn ? get_tmap(&ta, A, M, K, lda, 64, 64) : get_tmap(&ta, A, K, M, lda, 64, BM);
+    if (rc) return rc;
+    rc = b_mn ? get_tmap(&tb, B, N, K, ldb, 64, 64) : get_tmap(&tb, B, K, N, ldb, 64, bn);
+    if (rc) return rc;
+  }
+  if (p.nkb_ext > 0) {
+    rc = a_mn ? get_tmap(&ta2, A2, M, K2, lda2, 64, 64) : get_tmap(&ta2, A2, K2, M, lda2, 64, BM);
+    if (rc) return rc;
+    rc = b_mn ? get_tmap(&tb2, B2, N, K2, ldb2, 64, 64) : get_tmap(&tb2, B2, K2, N, ldb2, 64, bn);
+    if (rc) return rc;
+    if (p.nkb_main == 0) { ta = ta2; tb = tb2; }
+  } else {
+    ta2 = ta; tb2 = tb;
+  }
+
+  const int total = p.nmb * p.nnb * p.split_k;
+  int grid = dlti_num_sms();
+  if (max_ctas > 0 && max_ctas < grid) grid = max_ctas;
+  if (total < grid) grid = total;
+
+#define DLTI_GEMM_CASE(BN_, AM_, BM_) \
+  if (bn == BN_ && (a_mn != 0) == AM_ && (b_mn != 0) == BM_) \
+    return launch<BN_, AM_, BM_>(p, ta, tb, ta2, tb2, grid, stream);
+  DLTI_GEMM_CASE(256, false, false)
+  DLTI_GEMM_CASE(128, false, false)
+  DLTI_GEMM_CASE(64, false, false)
+  DLTI_GEMM_CASE(256, false, true)
+  DLTI_GEMM_CASE(128, false, true)
+  DLTI_GEMM_CASE(64, false, true)
+  DLTI_GEMM_CASE(128, true, true)
+  DLTI_GEMM_CASE(64, true, true)
+#undef DLTI_GEMM_CASE
+  return DLTI_ERR_UNSUPPORTED;
+}

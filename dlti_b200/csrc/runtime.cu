@@ -1,0 +1,99 @@
+// Host runtime shared by all kernels: launch accounting, error strings, device
+// properties and TMA tensor-map encoding (driver entry point fetched at run time so
+// the library links without libcuda on the build box).
+// No reference counterpart (the reference has no native code).
+#include "common.cuh"
+
+#include <atomic>
+#include <cstdio>
+#include <cstring>
+#include <mutex>
+
+#include <cudaTypedefs.h>
+
+static std::atomic<long long> g_launches{0};
+static char g_error[512] = {0};
+
+void dlti_count_launch(int n) { g_launches.fetch_add(n, std::memory_order_relaxed); }
+void dlti_set_error(const char* msg) {
+  std::strncpy(g_error, msg, sizeof(g_error) - 1);
+  g_error[sizeof(g_error) - 1] = 0;
+}
+
+DLTI_API long long dlti_launch_count() { return g_launches.load(std::memory_order_relaxed); }
+DLTI_API void dlti_reset_launch_count() { g_launches.store(0); }
+DLTI_API const char* dlti_last_error() { return g_error; }
+DLTI_API const char* dlti_error_string(int code) {
+  switch (code) {
+    case 0: return "success";
+    case DLTI_ERR_BAD_ARG: return "dlti: bad argument";
+    case DLTI_ERR_UNSUPPORTED: return "dlti: unsupported configuration";
+    case DLTI_ERR_DRIVER: return "dlti: CUDA driver entry point unavailable";
+    case DLTI_ERR_TOO_LARGE: return "dlti: size exceeds the compiled-in maximum";
+    default: return code > 0 ? cudaGetErrorString((cudaError_t)code) : "dlti: unknown error";
+  }
+}
+DLTI_API int dlti_version() { return 100; }
+
+int dlti_num_sms() {
+  static int sms[64] = {0};
+  int dev = 0;
+  if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) return 148;
+  if (sms[dev] == 0) {
+    int v = 0;
+    if (cudaDeviceGetAttribute(&v, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || v <= 0)
+      v = 148;
+    sms[dev] = v;
+  }
+  return sms[dev];
+}
+DLTI_API int dlti_sm_count() { return dlti_num_sms(); }
+
+static PFN_cuTensorMapEncodeTiled_v12000 g_encode = nullptr;
+static std::once_flag g_encode_once;
+
+static void load_encode() {
+  void* fn = nullptr;
+  cudaDriverEntryPointQueryResult q;
+  if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &fn, cudaEnableDefault, &q) == cudaSuccess &&
+      q == cudaDriverEntryPointSuccess)
+    g_encode = reinterpret_cast<PFN_cuTensorMapEncodeTiled_v12000>(fn);
+}
+
+int dlti_make_tmap_2d(CUtensorMap* out, const void* base, uint64_t inner, uint64_t outer,
+                      uint64_t ld_elems, uint32_t box_inner, uint32_t box_outer, int elem_bytes,
+                      int swizzle_bytes) {
+  std::call_once(g_encode_once, load_encode);
+  if (!g_encode) {
+    dlti_set_error("cuTensorMapEncodeTiled not available");
+    return DLTI_ERR_DRIVER;
+  }
+  if ((reinterpret_cast<uintptr_t>(base) & 15) || ((ld_elems * elem_bytes) & 15)) {
+    dlti_set_error("TMA operand must be 16-byte aligned with a 16-byte-multiple row pitch");
+    return DLTI_ERR_BAD_ARG;
+  }
+  CUtensorMapDataType dt = elem_bytes == 2 ? CU_TENSOR_MAP_DATA_TYPE_BFLOAT16
+                           : elem_bytes == 4 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT32
+                                             : CU_TENSOR_MAP_DATA_TYPE_UINT8;
+  cuuint64_t gdim[2] = {inner, outer};
+  cuuint64_t gstride[1] = {ld_elems * (uint64_t)elem_bytes};
+  cuuint32_t box[2] = {box_inner, box_outer};
+  cuuint32_t estr[2] = {1, 1};
+  CUtensorMapSwizzle sw = swizzle_bytes == 128  ? CU_TENSOR_MAP_SWIZZLE_128B
+                          : swizzle_bytes == 64 ? CU_TENSOR_MAP_SWIZZLE_64B
+                          : swizzle_bytes == 32 ? CU_TENSOR_MAP_SWIZZLE_32B
+                                                : CU_TENSOR_MAP_SWIZZLE_NONE;
+  CUresult r = g_encode(out, dt, 2, const_cast<void*>(base), gdim, gstride, box, estr,
+                        CU_TENSOR_MAP_INTERLEAVE_NONE, sw, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                        CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) {
+    char buf[256];
+    std::snprintf(buf, sizeof(buf),
+                  "cuTensorMapEncodeTiled failed (%d): base=%p inner=%llu outer=%llu ld=%llu box=%ux%u",
+                  (int)r, base, (unsigned long long)inner, (unsigned long long)outer,
+                  (unsigned long long)ld_elems, box_inner, box_outer);
+    dlti_set_error(buf);
+    return DLTI_ERR_DRIVER;
+  }
+  return 0;
+}

@@ -1,0 +1,84 @@
+"""GEMM op: tcgen05/TMEM/TMA kernel on CUDA (csrc/gemm.cu), fp32 PyTorch oracle on CPU.
+
+    C = alpha * (op(A)·op(B) + A2·op(B2)) [+ R]      (16-bit output)
+    C (+)= alpha * (...)                              (fp32 output)
+
+Operand conventions (match the C ABI, include/dlti_b200.h):
+    a_mn=False: A is [M,K];  a_mn=True: A is stored [K,M]   (contraction dim outermost)
+    b_mn=False: B is [N,K] (y = x·W^T, the nn.Linear layout);  b_mn=True: B is stored [K,N]
+
+Replaces torch.nn.functional.linear / cuBLAS in the reference stack.
+"""
+from __future__ import annotations
+
+import ctypes as C
+
+import torch
+
+from . import _lib
+
+
+def gemm_ref(a, b, *, a_mn=False, b_mn=False, a2=None, b2=None, residual=None, out=None,
+             out_dtype=None, alpha=1.0, accumulate=False):
+    """fp32 oracle with identical semantics (used on CPU and by the GPU numerics tests)."""
+    A = a.float().t() if a_mn else a.float()
+    Bm = b.float() if b_mn else b.float().t()
+    acc = A @ Bm
+    if a2 is not None:
+        A2 = a2.float().t() if a_mn else a2.float()
+        B2 = b2.float() if b_mn else b2.float().t()
+        acc = acc + A2 @ B2
+    acc = acc * alpha
+    out_dtype = out_dtype or (out.dtype if out is not None else a.dtype)
+    if residual is not None:
+        acc = acc + residual.float()
+    if out is not None:
+        if accumulate:
+            out.add_(acc.to(out.dtype))
+        else:
+            out.copy_(acc.to(out.dtype))
+        return out
+    return acc.to(out_dtype)
+
+
+def _gemm_fn():
+    return _lib.fn("dlti_gemm", [
+        C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int,
+        C.c_longlong, C.c_longlong, C.c_longlong, C.c_longlong, C.c_int, C.c_int,
+        C.c_void_p, C.c_void_p, C.c_int, C.c_longlong, C.c_longlong,
+        C.c_int, C.c_int, C.c_float, C.c_int, C.c_int, C.c_int, C.c_int, C.c_void_p])
+
+
+def gemm(a: torch.Tensor, b: torch.Tensor, *, a_mn: bool = False, b_mn: bool = False,
+         a2: torch.Tensor | None = None, b2: torch.Tensor | None = None,
+         residual: torch.Tensor | None = None, out: torch.Tensor | None = None,
+         out_dtype: torch.dtype | None = None, alpha: float = 1.0, accumulate: bool = False,
+         split_k: int = 1, block_n: int = 0, max_ctas: int = 0) -> torch.Tensor:
+    if not _lib.use_native(a, b):
+        return gemm_ref(a, b, a_mn=a_mn, b_mn=b_mn, a2=a2, b2=b2, residual=residual, out=out,
+                        out_dtype=out_dtype, alpha=alpha, accumulate=accumulate)
+    assert a.dim() == 2 and b.dim() == 2 and a.dtype == b.dtype
+    assert a.stride(1) == 1 and b.stride(1) == 1, "operands must have unit inner stride"
+    M, K = (a.shape[1], a.shape[0]) if a_mn else a.shape
+    N, Kb = (b.shape[1], b.shape[0]) if b_mn else b.shape
+    assert K == Kb, f"K mismatch {K} vs {Kb}"
+    K2 = 0
+    if a2 is not None:
+        assert b2 is not None and a2.stride(1) == 1 and b2.stride(1) == 1 and a2.dtype == a.dtype
+        K2 = a2.shape[0] if a_mn else a2.shape[1]
+    out_dtype = out_dtype or (out.dtype if out is not None else a.dtype)
+    if out is None:
+        assert not accumulate
+        out = torch.empty((M, N), dtype=out_dtype, device=a.device)
+    assert out.shape == (M, N) and out.stride(1) == 1 and out.dtype == out_dtype
+    if residual is not None:
+        assert residual.shape == (M, N) and residual.stride(1) == 1 and residual.dtype == out.dtype
+    rc = _gemm_fn()(
+        _lib.ptr(a), _lib.ptr(b), _lib.ptr(out), _lib.ptr(residual), M, N, K,
+        a.stride(0), b.stride(0), out.stride(0), residual.stride(0) if residual is not None else 0,
+        int(a_mn), int(b_mn), _lib.ptr(a2), _lib.ptr(b2), K2,
+        a2.stride(0) if a2 is not None else 0, b2.stride(0) if b2 is not None else 0,
+        _lib.dtype_code(a.dtype), _lib.dtype_code(out_dtype), float(alpha), int(accumulate),
+        int(split_k), int(block_n), int(max_ctas), _lib.stream_ptr())
+    _lib.check(rc, "dlti_gemm")
+    return out

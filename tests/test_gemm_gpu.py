@@ -1,0 +1,92 @@
+"""K2/K3 tcgen05 GEMM vs fp32 PyTorch oracle (GPU tier)."""
+import pytest
+import torch
+
+from dlti_b200.ops.gemm import gemm, gemm_ref
+
+pytestmark = pytest.mark.gpu
+
+
+def _check(out, ref, scale_tol=1.2e-2):
+    out = out.float()
+    ref = ref.float()
+    denom = ref.abs().max().clamp_min(1e-6)
+    err = (out - ref).abs().max() / denom
+    assert torch.isfinite(out).all()
+    assert err.item() < scale_tol, f"max rel-to-max err {err.item():.4e}"
+
+
+@pytest.mark.parametrize("dtype", [torch.bfloat16, torch.float16])
+@pytest.mark.parametrize("M,N,K,bn", [
+    (128, 256, 64, 0), (128, 256, 256, 0), (256, 512, 512, 0), (384, 768, 1024, 128),
+    (200, 300, 520, 0), (64, 64, 128, 0), (1, 4096, 4096, 0), (4096, 4096, 4096, 0),
+    (1000, 1000, 1000, 64), (512, 11008, 4096, 256),
+])
+def test_gemm_nt(M, N, K, bn, dtype):
+    torch.manual_seed(0)
+    a = torch.randn(M, K, device="cuda", dtype=dtype)
+    # pitch must be a multiple of 8 elements for TMA
+    Kp = (K + 7) // 8 * 8
+    a = torch.randn(M, Kp, device="cuda", dtype=dtype)[:, :K]
+    b = torch.randn(N, Kp, device="cuda", dtype=dtype)[:, :K]
+    out = gemm(a, b, block_n=bn)
+    _check(out, gemm_ref(a, b, out_dtype=torch.float32))
+
+
+@pytest.mark.parametrize("M,N,K,bn", [(128, 256, 64, 0), (256, 512, 512, 0), (384, 704, 1000, 128),
+                                      (4096, 4096, 4096, 0), (130, 72, 264, 64)])
+def test_gemm_nn(M, N, K, bn):
+    torch.manual_seed(1)
+    a = torch.randn(M, K, device="cuda", dtype=torch.bfloat16)
+    b = torch.randn(K, N, device="cuda", dtype=torch.bfloat16)
+    out = gemm(a, b, b_mn=True, block_n=bn)
+    _check(out, gemm_ref(a, b, b_mn=True, out_dtype=torch.float32))
+
+
+@pytest.mark.parametrize("M,N,K,bn,split", [(128, 64, 64, 0, 1), (256, 128, 512, 0, 1),
+                                            (4096, 64, 4096, 64, 8), (4096, 128, 2048, 128, 4),
+                                            (264, 72, 1000, 64, 3)])
+def test_gemm_tn_splitk(M, N, K, bn, split):
+    """Weight-gradient form: both operands stored with the contraction dim outermost."""
+    torch.manual_seed(2)
+    a = torch.randn(K, M, device="cuda", dtype=torch.bfloat16)
+    b = torch.randn(K, N, device="cuda", dtype=torch.bfloat16)
+    out = torch.zeros(M, N, device="cuda", dtype=torch.float32)
+    base = torch.randn(M, N, device="cuda", dtype=torch.float32)
+    out.copy_(base)
+    gemm(a, b, a_mn=True, b_mn=True, out=out, accumulate=True, split_k=split, block_n=bn)
+    ref = base + gemm_ref(a, b, a_mn=True, b_mn=True, out_dtype=torch.float32)
+    _check(out, ref)
+
+
+@pytest.mark.parametrize("b_mn", [False, True])
+def test_gemm_k_extension_lora(b_mn):
+    """W·x + B·(A·x) via one extra 64-deep K block (rank padded to 64)."""
+    torch.manual_seed(3)
+    M, N, K, r = 512, 768, 1024, 16
+    x = torch.randn(M, K, device="cuda", dtype=torch.bfloat16)
+    w = (torch.randn(K, N, device="cuda", dtype=torch.bfloat16) if b_mn
+         else torch.randn(N, K, device="cuda", dtype=torch.bfloat16))
+    t = torch.zeros(M, 64, device="cuda", dtype=torch.bfloat16)
+    t[:, :r] = torch.randn(M, r, device="cuda")
+    if b_mn:
+        bl = torch.zeros(64, N, device="cuda", dtype=torch.bfloat16)
+        bl[:r] = torch.randn(r, N, device="cuda")
+    else:
+        bl = torch.zeros(N, 64, device="cuda", dtype=torch.bfloat16)
+        bl[:, :r] = torch.randn(N, r, device="cuda")
+    res = torch.randn(M, N, device="cuda", dtype=torch.bfloat16)
+    out = gemm(x, w, b_mn=b_mn, a2=t, b2=bl, residual=res, alpha=0.5)
+    ref = gemm_ref(x, w, b_mn=b_mn, a2=t, b2=bl, residual=res, alpha=0.5, out_dtype=torch.float32)
+    _check(out, ref)
+
+
+def test_gemm_fp32_out_and_strided():
+    torch.manual_seed(4)
+    big = torch.randn(300, 2048, device="cuda", dtype=torch.bfloat16)
+    a = big[:, 512:1536]  # strided view, pitch 2048
+    b = torch.randn(640, 1024, device="cuda", dtype=torch.bfloat16)
+    cbuf = torch.zeros(300, 1024, device="cuda", dtype=torch.float32)
+    out = gemm(a, b, out=cbuf[:, 128:768], out_dtype=torch.float32)
+    _check(out, gemm_ref(a, b, out_dtype=torch.float32))
+    assert cbuf[:, :128].abs().max().item() == 0 and cbuf[:, 768:].abs().max().item() == 0

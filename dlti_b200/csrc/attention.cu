@@ -1,0 +1,651 @@
+// K6: causal flash attention for sm_100a — forward, and a two-kernel backward (dK/dV and dQ) —
+// on tcgen05 tensor cores with TMEM accumulators and TMA-fed, 128B-swizzled shared tiles.
+//
+// Layout: activations are token-major. `qkv` is [T, (H + 2*KV) * 128] (q heads | k heads | v heads
+// per token row, RoPE already applied), sequences are concatenated and described by cu_seqlens
+// (varlen: the same kernels serve training batches and serving prefill). head_dim is 128.
+// GQA: query head h reads kv head h / (H / KV).
+//
+// Forward (one CTA = 128 query rows of one head):
+//   warp 0: TMA producer (Q once; K/V blocks of 128 keys, 2 stages)
+//   warp 1: MMA issuer:  S_j = Q·K_j^T  -> TMEM (double-buffered);  PV_j = P_j·V_j -> TMEM
+//   warps 2-5: softmax, one thread per query row (no cross-thread reductions): S from TMEM via
+//     tcgen05.ld, online max/sum in the exp2 domain, P written as bf16 into a swizzled smem tile
+//     (the A operand of the PV MMA), O kept in registers (o = o*alpha + PV_j).
+//   The tensor core computes S_{j+1} while the softmax warps work on S_j.
+//
+// Backward uses the stored log-sum-exp and D = rowsum(dO*O):
+//   dK/dV kernel (one CTA = 128 keys of one kv head; loops over the q heads of the group and over
+//   64-row query blocks): computes S^T = K·Q^T and dP^T = V·dO^T so that one thread owns one KEY
+//   row, writes P^T and dS^T as bf16 smem tiles, and accumulates dV += P^T·dO, dK += dS^T·Q in TMEM
+//   across the whole loop (no rescaling needed in the backward).
+//   dQ kernel (one CTA = 128 query rows of one head; loops over 64-key blocks): S = Q·K^T,
+//   dP = dO·V^T, dS -> smem, dQ += dS·K in TMEM. Deterministic: no atomics anywhere.
+//
+// Replaces PyTorch SDPA (mem-efficient / math kernels on the reference's V100; FlashAttention-2
+// mma.sync code elsewhere) — SURVEY.md N5, O6, S5.
+#include "common.cuh"
+
+#include <mutex>
+#include <unordered_map>
+
+namespace {
+
+constexpr int HD = 128;           // head dim
+constexpr int AT_THREADS = 192;   // producer, mma, 4 softmax warps
+constexpr float LOG2E = 1.4426950408889634f;
+constexpr float LN2 = 0.6931471805599453f;
+
+struct AttnParams {
+  const int* cu_seqlens;
+  int H, KV;
+  int W;                 // qkv row width in elements = (H + 2 KV) * 128
+  void* O;               // fwd out [T, H*128]
+  long long ldo;
+  float* lse;            // [H, T_total] natural-log LSE
+  const float* D;        // [H, T_total] rowsum(dO * O) (backward)
+  void* dqkv;            // backward out [T, W]
+  long long T_total;
+  float scale;           // 1/sqrt(hd)
+  int dtype;
+};
+
+__device__ __forceinline__ uint32_t swz_off(int row, int chunk16) {
+  // byte offset inside a [rows x 128 B] 128B-swizzled tile
+  return (uint32_t)(row * 128 + ((chunk16 ^ (row & 7)) << 4));
+}
+
+template <typename T>
+__device__ __forceinline__ void store_row32(uint32_t tile_base, int row, int chunk16_base,
+                                            const float (&f)[32]) {
+#pragma unroll
+  for (int k = 0; k < 4; ++k) {
+    uint32_t u0 = Cvt<T>::pack2(f[8 * k + 0], f[8 * k + 1]);
+    uint32_t u1 = Cvt<T>::pack2(f[8 * k + 2], f[8 * k + 3]);
+    uint32_t u2 = Cvt<T>::pack2(f[8 * k + 4], f[8 * k + 5]);
+    uint32_t u3 = Cvt<T>::pack2(f[8 * k + 6], f[8 * k + 7]);
+    const uint32_t addr = tile_base + swz_off(row, chunk16_base + k);
+    asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(addr), "r"(u0), "r"(u1), "r"(u2),
+                 "r"(u3)
+                 : "memory");
+  }
+}
+
+// K-major operand [rows x 128 elements] stored as two [rows x 64] swizzled chunks
+// (chunk pitch = rows*128 B). Descriptor for k-step kk (16 elements each) of a K=128 operand.
+__device__ __forceinline__ uint64_t desc_kmajor(uint32_t base, int rows, int kk) {
+  return umma_smem_desc(base + (kk >> 2) * (rows * 128) + (kk & 3) * 32, 0, 1024);
+}
+// K-major operand with K = 64 (single chunk).
+__device__ __forceinline__ uint64_t desc_kmajor64(uint32_t base, int kk) {
+  return umma_smem_desc(base + kk * 32, 0, 1024);
+}
+// MN-major operand: tile [krows x 128 elements] as two [krows x 64] chunks; N (=128) contiguous,
+// K = krows. k-step kk covers rows 16kk..16kk+15.
+__device__ __forceinline__ uint64_t desc_mnmajor(uint32_t base, int krows, int kk) {
+  return umma_smem_desc(base + kk * 2048, krows * 128, 1024);
+}
+
+// =============================================================================================
+// Forward
+// =============================================================================================
+template <typename T>
+__global__ void __launch_bounds__(AT_THREADS, 1)
+attn_fwd_kernel(const AttnParams p, const __grid_constant__ CUtensorMap tm128) {
+  const int b = blockIdx.z, h = blockIdx.y;
+  const int row0 = p.cu_seqlens[b];
+  const int seqlen = p.cu_seqlens[b + 1] - row0;
+  const int nqb = (seqlen + 127) >> 7;
+  const int qb = nqb - 1 - (int)blockIdx.x;   // heavy (late) query blocks first
+  if (qb < 0) return;
+  const int kvh = h / (p.H / p.KV);
+  const int nkv = qb + 1;
+
+  extern __shared__ uint8_t smem_raw[];
+  const uint32_t base = (smem_u32(smem_raw) + 1023u) & ~1023u;
+  const uint32_t sQ = base, sK = base + 32768, sV = base + 3 * 32768, sP = base + 5 * 32768;
+  const uint32_t bars = base + 6 * 32768;
+  const uint32_t q_full = bars, k_full = bars + 8, v_full = bars + 24, kv_empty = bars + 40,
+                 s_full = bars + 56, s_free = bars + 72, p_full = bars + 88, pv_full = bars + 96,
+                 tmem_slot = bars + 104;
+  volatile uint32_t* tmem_slot_ptr =
+      reinterpret_cast<volatile uint32_t*>(smem_raw + (tmem_slot - smem_u32(smem_raw)));
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+
+  if (warp == 0 && lane == 0) {
+    tma_prefetch_desc(&tm128);
+    mbar_init(q_full, 1);
+    for (int s = 0; s < 2; ++s) {
+      mbar_init(k_full + 8 * s, 1);
+      mbar_init(v_full + 8 * s, 1);
+      mbar_init(kv_empty + 8 * s, 1);
+      mbar_init(s_full + 8 * s, 1);
+      mbar_init(s_free + 8 * s, 4);
+    }
+    mbar_init(p_full, 4);
+    mbar_init(pv_full, 1);
+    mbar_fence_init();
+  }
+  if (warp == 1) {
+    tmem_alloc(tmem_slot, 512);
+    tmem_relinquish();
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem = *tmem_slot_ptr;
+  const uint32_t TS0 = 0, TPV = 256;  // S buffers at columns 0 and 128, PV at 256
+
+  if (warp == 0) {
+    if (lane == 0) {
+      const int qcol = h * HD, kcol = p.H * HD + kvh * HD, vcol = (p.H + p.KV) * HD + kvh * HD;
+      mbar_expect_tx(q_full, 32768);
+      tma_load_2d(sQ, &tm128, q_full, qcol, row0 + qb * 128);
+      tma_load_2d(sQ + 16384, &tm128, q_full, qcol + 64, row0 + qb * 128);
+      for (int j = 0; j < nkv; ++j) {
+        const int s = j & 1;
+        if (j >= 2) mbar_wait(kv_empty + 8 * s, ((j >> 1) - 1) & 1);
+        const int r = row0 + j * 128;
+        mbar_expect_tx(k_full + 8 * s, 32768);
+        tma_load_2d(sK + s * 32768, &tm128, k_full + 8 * s, kcol, r);
+        tma_load_2d(sK + s * 32768 + 16384, &tm128, k_full + 8 * s, kcol + 64, r);
+        mbar_expect_tx(v_full + 8 * s, 32768);
+        tma_load_2d(sV + s * 32768, &tm128, v_full + 8 * s, vcol, r);
+        tma_load_2d(sV + s * 32768 + 16384, &tm128, v_full + 8 * s, vcol + 64, r);
+      }
+    }
+  } else if (warp == 1) {
+    if (lane == 0) {
+      const uint32_t idesc_s = umma_idesc_f16(p.dtype, 128, 128, false, false);
+      const uint32_t idesc_pv = umma_idesc_f16(p.dtype, 128, 128, false, true);
+      auto issue_s = [&](int j) {
+        const int s = j & 1;
+        mbar_wait(k_full + 8 * s, (j >> 1) & 1);
+        if (j >= 2) mbar_wait(s_free + 8 * s, ((j >> 1) - 1) & 1);
+        tc_fence_after();
+#pragma unroll
+        for (int kk = 0; kk < 8; ++kk)
+          umma_f16_ss(tmem + TS0 + s * 128, desc_kmajor(sQ, 128, kk),
+                      desc_kmajor(sK + s * 32768, 128, kk), idesc_s, kk > 0);
+        umma_commit(s_full + 8 * s);
+      };
+      mbar_wait(q_full, 0);
+      issue_s(0);
+      for (int j = 0; j < nkv; ++j) {
+        if (j + 1 < nkv) issue_s(j + 1);
+        mbar_wait(p_full, j & 1);
+        mbar_wait(v_full + 8 * (j & 1), (j >> 1) & 1);
+        tc_fence_after();
+#pragma unroll
+        for (int kk = 0; kk < 8; ++kk)
+          umma_f16_ss(tmem + TPV, desc_kmajor(sP, 128, kk),
+                      desc_mnmajor(sV + (j & 1) * 32768, 128, kk), idesc_pv, kk > 0);
+        umma_commit(pv_full);
+        umma_commit(kv_empty + 8 * (j & 1));
+      }
+    }
+  } else {
+    const int quarter = warp & 3;
+    const int r = quarter * 32 + lane;          // query row inside the tile
+    const uint32_t trow = tmem + ((uint32_t)(quarter * 32) << 16);
+    const float sl2 = p.scale * LOG2E;
+    float o[128];
+#pragma unroll
+    for (int i = 0; i < 128; ++i) o[i] = 0.f;
+    float m = -INFINITY, l = 0.f;
+    for (int j = 0; j < nkv; ++j) {
+      const int s = j & 1;
+      const bool diag = (j == qb);
+      mbar_wait(s_full + 8 * s, (j >> 1) & 1);
+      tc_fence_after();
+      float mx = m;
+#pragma unroll 1
+      for (int c = 0; c < 4; ++c) {
+        uint32_t v[32];
+        tmem_ld_32x32b_x32(trow + TS0 + s * 128 + c * 32, v);
+        tmem_wait_ld();
+#pragma unroll
+        for (int i = 0; i < 32; ++i) {
+          float sv = __uint_as_float(v[i]) * sl2;
+          if (diag && (c * 32 + i > r)) sv = -INFINITY;
+          mx = fmaxf(mx, sv);
+        }
+      }
+      const float alpha = exp2f(m - mx);
+      if (j > 0) {
+        mbar_wait(pv_full, (j - 1) & 1);
+        tc_fence_after();
+#pragma unroll
+        for (int c = 0; c < 4; ++c) {
+          uint32_t v[32];
+          tmem_ld_32x32b_x32(trow + TPV + c * 32, v);
+          tmem_wait_ld();
+#pragma unroll
+          for (int i = 0; i < 32; ++i) o[c * 32 + i] = (o[c * 32 + i] + __uint_as_float(v[i])) * alpha;
+        }
+      }
+      l *= alpha;
+#pragma unroll 1
+      for (int c = 0; c < 4; ++c) {
+        uint32_t v[32];
+        tmem_ld_32x32b_x32(trow + TS0 + s * 128 + c * 32, v);
+        tmem_wait_ld();
+        float pr[32];
+#pragma unroll
+        for (int i = 0; i < 32; ++i) {
+          float pv = exp2f(__uint_as_float(v[i]) * sl2 - mx);
+          if (diag && (c * 32 + i > r)) pv = 0.f;
+          // sum the bf16-rounded probabilities the PV MMA will actually use
+          pv = Cvt<T>::to_f(Cvt<T>::from_f(pv));
+          l += pv;
+          pr[i] = pv;
+        }
+        store_row32<T>(sP + (c >> 1) * 16384, r, (c & 1) * 4, pr);
+      }
+      tc_fence_before();
+      fence_proxy_async_smem();
+      __syncwarp();
+      if (lane == 0) {
+        mbar_arrive(s_free + 8 * s);
+        mbar_arrive(p_full);
+      }
+      m = mx;
+    }
+    mbar_wait(pv_full, (nkv - 1) & 1);
+    tc_fence_after();
+    const float inv = 1.f / l;
+    const int qi = qb * 128 + r;
+    T* orow = reinterpret_cast<T*>(p.O) + (long long)(row0 + qi) * p.ldo + h * HD;
+#pragma unroll
+    for (int c = 0; c < 4; ++c) {
+      uint32_t v[32];
+      tmem_ld_32x32b_x32(trow + TPV + c * 32, v);
+      tmem_wait_ld();
+      if (qi < seqlen) {
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+          int4 ov;
+          uint32_t* ou = reinterpret_cast<uint32_t*>(&ov);
+#pragma unroll
+          for (int q = 0; q < 4; ++q) {
+            const int i = 8 * k + 2 * q;
+            ou[q] = Cvt<T>::pack2((o[c * 32 + i] + __uint_as_float(v[i])) * inv,
+                                  (o[c * 32 + i + 1] + __uint_as_float(v[i + 1])) * inv);
+          }
+          *reinterpret_cast<int4*>(orow + c * 32 + 8 * k) = ov;
+        }
+      }
+    }
+    if (qi < seqlen && p.lse) p.lse[(long long)h * p.T_total + row0 + qi] = (m + log2f(l)) * LN2;
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 1) {
+    tc_fence_after();
+    tmem_dealloc(tmem, 512);
+  }
+}
+
+// =============================================================================================
+// Backward preprocess: D[h, t] = sum_d dO[t, h, d] * O[t, h, d].  One warp per (t, h).
+// =============================================================================================
+template <typename T>
+__global__ void attn_bwd_prep_kernel(const T* __restrict__ dO, const T* __restrict__ O, float* __restrict__ D,
+                                     long long T_total, int H, long long ld) {
+  const long long w = ((long long)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  const int lane = threadIdx.x & 31;
+  if (w >= T_total * H) return;
+  const long long t = w / H;
+  const int h = (int)(w - t * H);
+  const uint2 a = *reinterpret_cast<const uint2*>(dO + t * ld + h * HD + lane * 4);
+  const uint2 c = *reinterpret_cast<const uint2*>(O + t * ld + h * HD + lane * 4);
+  float2 a0 = Cvt<T>::unpack2(a.x), a1 = Cvt<T>::unpack2(a.y);
+  float2 c0 = Cvt<T>::unpack2(c.x), c1 = Cvt<T>::unpack2(c.y);
+  float acc = a0.x * c0.x + a0.y * c0.y + a1.x * c1.x + a1.y * c1.y;
+  acc = warp_sum(acc);
+  if (lane == 0) D[(long long)h * T_total + t] = acc;
+}
+
+// =============================================================================================
+// Backward main kernels. One template:
+//   DKDV = true : stationary X1 = K_j, X2 = V_j (128 keys); streamed Y1 = Q_i, Y2 = dO_i (64 rows),
+//                 looping over the q heads of the GQA group and the causal range of q blocks.
+//                 thread = key row. acc1 (dV) += P^T·dO, acc2 (dK) += dS^T·Q.
+//   DKDV = false: stationary X1 = Q_i, X2 = dO_i (128 query rows); streamed Y1 = K_j, Y2 = V_j
+//                 (64 keys). thread = query row. acc2 (dQ) += dS·K.
+// In both, tile A = X1·Y1^T (scores) and tile B = X2·Y2^T (dP) are [128 x 64] fp32 in TMEM,
+// double-buffered; P / dS go to smem as K-major [128 x 64] 16-bit tiles.
+// =============================================================================================
+template <typename T, bool DKDV>
+__global__ void __launch_bounds__(AT_THREADS, 1)
+attn_bwd_kernel(const AttnParams p, const __grid_constant__ CUtensorMap tmQKV128,
+                const __grid_constant__ CUtensorMap tmQKV64,
+                const __grid_constant__ CUtensorMap tmDO128,
+                const __grid_constant__ CUtensorMap tmDO64) {
+  const int b = blockIdx.z;
+  const int row0 = p.cu_seqlens[b];
+  const int seqlen = p.cu_seqlens[b + 1] - row0;
+  const int G = p.H / p.KV;
+  const int n64 = (seqlen + 63) >> 6;
+  const int blk = (int)blockIdx.x;          // stationary 128-row block index
+  if (blk * 128 >= seqlen) return;
+  const int head = blockIdx.y;              // DKDV: kv head; else: q head
+  // streamed block range and iteration count
+  int y0, ny, iters;
+  if (DKDV) {
+    y0 = 2 * blk; ny = n64 - y0; iters = ny * G;
+  } else {
+    y0 = 0; ny = min(2 * blk + 2, n64); iters = ny;
+  }
+
+  extern __shared__ uint8_t smem_raw[];
+  const uint32_t base = (smem_u32(smem_raw) + 1023u) & ~1023u;
+  const uint32_t sX1 = base, sX2 = base + 32768;
+  const uint32_t sY1 = base + 65536;            // 2 stages x 16 KB
+  const uint32_t sY2 = base + 65536 + 32768;    // 2 stages x 16 KB
+  const uint32_t sP = base + 131072;            // 16 KB
+  const uint32_t sDS = base + 131072 + 16384;   // 16 KB
+  const uint32_t sStat = base + 163840;         // 2 stages x (64 lse + 64 D) floats = 1 KB
+  const uint32_t bars = base + 163840 + 1024;
+  const uint32_t x_full = bars, y_full = bars + 8, y_empty = bars + 24, ab_full = bars + 40,
+                 ab_free = bars + 56, pds_full = bars + 72, pds_free = bars + 80,
+                 tmem_slot = bars + 88;
+  volatile uint32_t* tmem_slot_ptr =
+      reinterpret_cast<volatile uint32_t*>(smem_raw + (tmem_slot - smem_u32(smem_raw)));
+  float* stat = reinterpret_cast<float*>(smem_raw + (sStat - smem_u32(smem_raw)));
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+
+  if (warp == 0 && lane == 0) {
+    mbar_init(x_full, 1);
+    for (int s = 0; s < 2; ++s) {
+      mbar_init(y_full + 8 * s, 1);
+      mbar_init(y_empty + 8 * s, 1);
+      mbar_init(ab_full + 8 * s, 1);
+      mbar_init(ab_free + 8 * s, 4);
+    }
+    mbar_init(pds_full, 4);
+    mbar_init(pds_free, 1);
+    mbar_fence_init();
+  }
+  if (warp == 1) {
+    tmem_alloc(tmem_slot, 512);
+    tmem_relinquish();
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem = *tmem_slot_ptr;
+  // TMEM columns: A tiles at 0/64, B tiles at 128/192, acc1 at 256, acc2 at 384
+  const uint32_t TA = 0, TB = 128, TACC1 = 256, TACC2 = 384;
+
+  const int kcol_base = p.H * HD, vcol_base = (p.H + p.KV) * HD;
+
+  if (warp == 0) {
+    if (lane == 0) {
+      mbar_expect_tx(x_full, 65536);
+      if (DKDV) {
+        const int kc = kcol_base + head * HD, vc = vcol_base + head * HD, r = row0 + blk * 128;
+        tma_load_2d(sX1, &tmQKV128, x_full, kc, r);
+        tma_load_2d(sX1 + 16384, &tmQKV128, x_full, kc + 64, r);
+        tma_load_2d(sX2, &tmQKV128, x_full, vc, r);
+        tma_load_2d(sX2 + 16384, &tmQKV128, x_full, vc + 64, r);
+      } else {
+        const int qc = head * HD, r = row0 + blk * 128;
+        tma_load_2d(sX1, &tmQKV128, x_full, qc, r);
+        tma_load_2d(sX1 + 16384, &tmQKV128, x_full, qc + 64, r);
+        tma_load_2d(sX2, &tmDO128, x_full, qc, r);
+        tma_load_2d(sX2 + 16384, &tmDO128, x_full, qc + 64, r);
+      }
+      for (int it = 0; it < iters; ++it) {
+        const int s = it & 1;
+        if (it >= 2) mbar_wait(y_empty + 8 * s, ((it >> 1) - 1) & 1);
+        mbar_expect_tx(y_full + 8 * s, 32768);
+        if (DKDV) {
+          const int g = it / ny, i = y0 + (it - g * ny);
+          const int qc = (head * G + g) * HD, r = row0 + i * 64;
+          tma_load_2d(sY1 + s * 16384, &tmQKV64, y_full + 8 * s, qc, r);
+          tma_load_2d(sY1 + s * 16384 + 8192, &tmQKV64, y_full + 8 * s, qc + 64, r);
+          tma_load_2d(sY2 + s * 16384, &tmDO64, y_full + 8 * s, qc, r);
+          tma_load_2d(sY2 + s * 16384 + 8192, &tmDO64, y_full + 8 * s, qc + 64, r);
+        } else {
+          const int kvh = head / G;
+          const int kc = kcol_base + kvh * HD, vc = vcol_base + kvh * HD, r = row0 + (y0 + it) * 64;
+          tma_load_2d(sY1 + s * 16384, &tmQKV64, y_full + 8 * s, kc, r);
+          tma_load_2d(sY1 + s * 16384 + 8192, &tmQKV64, y_full + 8 * s, kc + 64, r);
+          tma_load_2d(sY2 + s * 16384, &tmQKV64, y_full + 8 * s, vc, r);
+          tma_load_2d(sY2 + s * 16384 + 8192, &tmQKV64, y_full + 8 * s, vc + 64, r);
+        }
+      }
+    }
+  } else if (warp == 1) {
+    if (lane == 0) {
+      const uint32_t idesc_ab = umma_idesc_f16(p.dtype, 128, 64, false, false);
+      const uint32_t idesc_acc = umma_idesc_f16(p.dtype, 128, 128, false, true);
+      auto issue_ab = [&](int it) {
+        const int s = it & 1;
+        mbar_wait(y_full + 8 * s, (it >> 1) & 1);
+        if (it >= 2) mbar_wait(ab_free + 8 * s, ((it >> 1) - 1) & 1);
+        tc_fence_after();
+#pragma unroll
+        for (int kk = 0; kk < 8; ++kk)
+          umma_f16_ss(tmem + TA + s * 64, desc_kmajor(sX1, 128, kk),
+                      desc_kmajor(sY1 + s * 16384, 64, kk), idesc_ab, kk > 0);
+#pragma unroll
+        for (int kk = 0; kk < 8; ++kk)
+          umma_f16_ss(tmem + TB + s * 64, desc_kmajor(sX2, 128, kk),
+                      desc_kmajor(sY2 + s * 16384, 64, kk), idesc_ab, kk > 0);
+        umma_commit(ab_full + 8 * s);
+      };
+      mbar_wait(x_full, 0);
+      issue_ab(0);
+      for (int it = 0; it < iters; ++it) {
+        const int s = it & 1;
+        if (it + 1 < iters) issue_ab(it + 1);
+        mbar_wait(pds_full, it & 1);
+        tc_fence_after();
+        if (DKDV) {
+#pragma unroll
+          for (int kk = 0; kk < 4; ++kk)   // dV += P^T · dO
+            umma_f16_ss(tmem + TACC1, desc_kmajor64(sP, kk), desc_mnmajor(sY2 + s * 16384, 64, kk),
+                        idesc_acc, (it > 0 || kk > 0));
+        }
+#pragma unroll
+        for (int kk = 0; kk < 4; ++kk)     // dK += dS^T · Q   /   dQ += dS · K
+          umma_f16_ss(tmem + TACC2, desc_kmajor64(sDS, kk), desc_mnmajor(sY1 + s * 16384, 64, kk),
+                      idesc_acc, (it > 0 || kk > 0));
+        umma_commit(y_empty + 8 * s);
+        umma_commit(pds_free);
+      }
+    }
+  } else {
+    const int quarter = warp & 3;
+    const int r = quarter * 32 + lane;
+    const int sidx = blk * 128 + r;            // key index (DKDV) or query index (!DKDV)
+    const uint32_t trow = tmem + ((uint32_t)(quarter * 32) << 16);
+    const float sl2 = p.scale * LOG2E;
+    const int tid128 = threadIdx.x - 64;
+    float my_lse = 0.f, my_D = 0.f;
+    if (!DKDV && sidx < seqlen) {
+      my_lse = p.lse[(long long)head * p.T_total + row0 + sidx] * LOG2E;
+      my_D = p.D[(long long)head * p.T_total + row0 + sidx];
+    }
+    for (int it = 0; it < iters; ++it) {
+      const int s = it & 1;
+      int yb;                                   // streamed 64-block index
+      if (DKDV) {
+        const int g = it / ny;
+        yb = y0 + (it - g * ny);
+        // stage this q block's lse / D (64 values each) into smem
+        const int qh = head * G + g;
+        const int q = yb * 64 + (tid128 & 63);
+        float val = 0.f;
+        if (q < seqlen) {
+          const long long off = (long long)qh * p.T_total + row0 + q;
+          val = (tid128 < 64) ? p.lse[off] * LOG2E : p.D[off];
+        }
+        stat[s * 128 + tid128] = val;
+        asm volatile("bar.sync 1, 128;" ::: "memory");
+      } else {
+        yb = y0 + it;
+      }
+      mbar_wait(ab_full + 8 * s, (it >> 1) & 1);
+      tc_fence_after();
+#pragma unroll 1
+      for (int c = 0; c < 2; ++c) {
+        uint32_t sv[32], dv[32];
+        tmem_ld_32x32b_x32(trow + TA + s * 64 + c * 32, sv);
+        tmem_ld_32x32b_x32(trow + TB + s * 64 + c * 32, dv);
+        tmem_wait_ld();
+        float pr[32], ds[32];
+#pragma unroll
+        for (int i = 0; i < 32; ++i) {
+          const int yi = yb * 64 + c * 32 + i;  // query index (DKDV) or key index (!DKDV)
+          float lse_v, D_v;
+          bool valid;
+          if (DKDV) {
+            lse_v = stat[s * 128 + c * 32 + i];
+            D_v = stat[s * 128 + 64 + c * 32 + i];
+            valid = (yi < seqlen) && (yi >= sidx);
+          } else {
+            lse_v = my_lse; D_v = my_D;
+            valid = (sidx < seqlen) && (yi <= sidx);
+          }
+          float pv = exp2f(__uint_as_float(sv[i]) * sl2 - lse_v);
+          pr[i] = valid ? pv : 0.f;
+          ds[i] = valid ? pv * (__uint_as_float(dv[i]) - D_v) * p.scale : 0.f;
+        }
+        if (c == 0 && it > 0) mbar_wait(pds_free, (it - 1) & 1);
+        if (DKDV) store_row32<T>(sP, r, c * 4, pr);
+        store_row32<T>(sDS, r, c * 4, ds);
+      }
+      tc_fence_before();
+      fence_proxy_async_smem();
+      __syncwarp();
+      if (lane == 0) {
+        mbar_arrive(ab_free + 8 * s);
+        mbar_arrive(pds_full);
+      }
+    }
+    mbar_wait(pds_free, (iters - 1) & 1);
+    tc_fence_after();
+    // write the accumulators
+    T* outbase = reinterpret_cast<T*>(p.dqkv) + (long long)(row0 + sidx) * p.W;
+    const int nacc = DKDV ? 2 : 1;
+    for (int a = 0; a < nacc; ++a) {
+      const uint32_t tacc = (DKDV && a == 0) ? TACC1 : TACC2;
+      int col;
+      if (DKDV) col = (a == 0) ? (vcol_base + head * HD) : (kcol_base + head * HD);
+      else col = head * HD;
+#pragma unroll
+      for (int c = 0; c < 4; ++c) {
+        uint32_t v[32];
+        tmem_ld_32x32b_x32(trow + tacc + c * 32, v);
+        tmem_wait_ld();
+        if (sidx < seqlen) {
+#pragma unroll
+          for (int k = 0; k < 4; ++k) {
+            int4 ov;
+            uint32_t* ou = reinterpret_cast<uint32_t*>(&ov);
+#pragma unroll
+            for (int q = 0; q < 4; ++q)
+              ou[q] = Cvt<T>::pack2(__uint_as_float(v[8 * k + 2 * q]), __uint_as_float(v[8 * k + 2 * q + 1]));
+            *reinterpret_cast<int4*>(outbase + col + c * 32 + 8 * k) = ov;
+          }
+        }
+      }
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 1) {
+    tc_fence_after();
+    tmem_dealloc(tmem, 512);
+  }
+}
+
+constexpr int FWD_SMEM = 6 * 32768 + 256 + 1024;
+constexpr int BWD_SMEM = 163840 + 1024 + 256 + 1024;
+
+int make_map(CUtensorMap* m, const void* base, long long T_total, long long width, int box_rows) {
+  return dlti_make_tmap_2d(m, base, (uint64_t)width, (uint64_t)T_total, (uint64_t)width, 64,
+                           (uint32_t)box_rows, 2, 128);
+}
+
+}  // namespace
+
+// qkv [T, (H+2KV)*128]; out [T, H*128]; lse [H, T] fp32 (may be NULL for inference).
+DLTI_API int dlti_attn_fwd(const void* qkv, void* out, float* lse, const int* cu_seqlens, int batch,
+                           int max_seqlen, long long T_total, int H, int KV, int hd, float scale,
+                           int dtype, cudaStream_t st) {
+  if (hd != HD) { dlti_set_error("attention: head_dim must be 128"); return DLTI_ERR_UNSUPPORTED; }
+  if (H % KV) return DLTI_ERR_BAD_ARG;
+  if (batch <= 0 || T_total <= 0) return 0;
+  AttnParams p{};
+  p.cu_seqlens = cu_seqlens; p.H = H; p.KV = KV; p.W = (H + 2 * KV) * HD;
+  p.O = out; p.ldo = (long long)H * HD; p.lse = lse; p.T_total = T_total; p.scale = scale; p.dtype = dtype;
+  CUtensorMap tm;
+  int rc = make_map(&tm, qkv, T_total, p.W, 128);
+  if (rc) return rc;
+  dim3 grid((max_seqlen + 127) / 128, H, batch);
+  static bool cfg[2] = {false, false};
+  if (dtype == DLTI_BF16) {
+    if (!cfg[0]) { DLTI_CUDA_CHECK(cudaFuncSetAttribute(attn_fwd_kernel<__nv_bfloat16>, cudaFuncAttributeMaxDynamicSharedMemorySize, FWD_SMEM)); cfg[0] = true; }
+    attn_fwd_kernel<__nv_bfloat16><<<grid, AT_THREADS, FWD_SMEM, st>>>(p, tm);
+  } else if (dtype == DLTI_FP16) {
+    if (!cfg[1]) { DLTI_CUDA_CHECK(cudaFuncSetAttribute(attn_fwd_kernel<__half>, cudaFuncAttributeMaxDynamicSharedMemorySize, FWD_SMEM)); cfg[1] = true; }
+    attn_fwd_kernel<__half><<<grid, AT_THREADS, FWD_SMEM, st>>>(p, tm);
+  } else {
+    return DLTI_ERR_UNSUPPORTED;
+  }
+  dlti_count_launch();
+  return (int)cudaGetLastError();
+}
+
+// dqkv [T, (H+2KV)*128] receives dq | dk | dv. D_scratch: [H, T] fp32 workspace.
+DLTI_API int dlti_attn_bwd(const void* dout, const void* qkv, const void* out, const float* lse,
+                           float* D_scratch, void* dqkv, const int* cu_seqlens, int batch,
+                           int max_seqlen, long long T_total, int H, int KV, int hd, float scale,
+                           int dtype, cudaStream_t st) {
+  if (hd != HD) { dlti_set_error("attention: head_dim must be 128"); return DLTI_ERR_UNSUPPORTED; }
+  if (H % KV) return DLTI_ERR_BAD_ARG;
+  if (batch <= 0 || T_total <= 0) return 0;
+  AttnParams p{};
+  p.cu_seqlens = cu_seqlens; p.H = H; p.KV = KV; p.W = (H + 2 * KV) * HD;
+  p.lse = const_cast<float*>(lse); p.D = D_scratch; p.dqkv = dqkv; p.T_total = T_total;
+  p.scale = scale; p.dtype = dtype; p.ldo = (long long)H * HD;
+  CUtensorMap q128, q64, d128, d64;
+  int rc;
+  if ((rc = make_map(&q128, qkv, T_total, p.W, 128))) return rc;
+  if ((rc = make_map(&q64, qkv, T_total, p.W, 64))) return rc;
+  if ((rc = make_map(&d128, dout, T_total, (long long)H * HD, 128))) return rc;
+  if ((rc = make_map(&d64, dout, T_total, (long long)H * HD, 64))) return rc;
+  const long long warps = T_total * H;
+  const int prep_blocks = (int)((warps * 32 + 255) / 256);
+  dim3 g_kv((max_seqlen + 127) / 128, KV, batch), g_q((max_seqlen + 127) / 128, H, batch);
+  static bool cfg[2] = {false, false};
+  if (dtype == DLTI_BF16) {
+    using T = __nv_bfloat16;
+    if (!cfg[0]) {
+      DLTI_CUDA_CHECK(cudaFuncSetAttribute(attn_bwd_kernel<T, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, BWD_SMEM));
+      DLTI_CUDA_CHECK(cudaFuncSetAttribute(attn_bwd_kernel<T, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, BWD_SMEM));
+      cfg[0] = true;
+    }
+    attn_bwd_prep_kernel<T><<<prep_blocks, 256, 0, st>>>((const T*)dout, (const T*)out, D_scratch, T_total, H, p.ldo);
+    attn_bwd_kernel<T, true><<<g_kv, AT_THREADS, BWD_SMEM, st>>>(p, q128, q64, d128, d64);
+    attn_bwd_kernel<T, false><<<g_q, AT_THREADS, BWD_SMEM, st>>>(p, q128, q64, d128, d64);
+  } else if (dtype == DLTI_FP16) {
+    using T = __half;
+    if (!cfg[1]) {
+      DLTI_CUDA_CHECK(cudaFuncSetAttribute(attn_bwd_kernel<T, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, BWD_SMEM));
+      DLTI_CUDA_CHECK(cudaFuncSetAttribute(attn_bwd_kernel<T, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, BWD_SMEM));
+      cfg[1] = true;
+    }
+    attn_bwd_prep_kernel<T><<<prep_blocks, 256, 0, st>>>((const T*)dout, (const T*)out, D_scratch, T_total, H, p.ldo);
+    attn_bwd_kernel<T, true><<<g_kv, AT_THREADS, BWD_SMEM, st>>>(p, q128, q64, d128, d64);
+    attn_bwd_kernel<T, false><<<g_q, AT_THREADS, BWD_SMEM, st>>>(p, q128, q64, d128, d64);
+  } else {
+    return DLTI_ERR_UNSUPPORTED;
+  }
+  dlti_count_launch(3);
+  return (int)cudaGetLastError();
+}

@@ -25,7 +25,9 @@ OBJDIR = PKG.parent / "build" / "obj"
 INCLUDE = PKG.parent / "include"
 
 NVCC = os.environ.get("NVCC") or shutil.which("nvcc") or "/usr/local/cuda/bin/nvcc"
-CXX = os.environ.get("CXX") or shutil.which("g++") or "g++"
+# the image exports CXX=/opt/gcc/bin/g++, a trimmed toolchain without libgomp: prefer the distro g++
+CXX = (os.environ.get("DLTI_CXX") or ("/usr/bin/g++" if os.path.exists("/usr/bin/g++") else None)
+       or os.environ.get("CXX") or shutil.which("g++") or "g++")
 
 NVCC_FLAGS = [
     "-gencode", "arch=compute_100a,code=sm_100a",
@@ -34,7 +36,7 @@ NVCC_FLAGS = [
     "-Xcompiler", "-fPIC,-fvisibility=hidden",
     "-I", str(CSRC), "-I", str(INCLUDE),
 ]
-CXX_FLAGS = ["-O3", "-std=c++17", "-fPIC", "-fopenmp", "-march=x86-64-v3", "-I", str(CSRC),
+CXX_FLAGS = ["-O3", "-std=c++17", "-fPIC", "-fopenmp", "-march=x86-64-v3", "-mf16c", "-I", str(CSRC),
              "-I", str(INCLUDE)]
 
 GPU_LIB = LIBDIR / "libdlti_b200.so"

@@ -1,0 +1,365 @@
+"""Training engine: the loop the reference delegates to `transformers.Trainer` + `DeepSpeedEngine`
+(call stacks §3.1-3.3).
+
+    trainer = Trainer(cfg, lcfg, args, dataset, collator, weights_init=...)
+    trainer.train(resume_from_checkpoint=None)       # epochs, grad accumulation, log/save/rotate
+    trainer.train_step(list_of_host_batches) -> loss # one optimizer step (public API used by bench.py)
+    trainer.save_model(dir)                          # PEFT adapter (all ranks enter; rank 0 writes)
+
+Per optimizer step: H2D of the micro-batches (pinned, non-blocking) -> forward/backward per
+micro-batch with the loss pre-scaled by loss_scale / (target tokens in the whole global batch)
+(token-normalised, App. H) -> ZeRO gradient reduce -> global norm + overflow -> AdamW on the owned
+partition -> all-gather of updated slices -> scheduler / loss-scaler update -> loss read-back.
+Logging every `logging_steps` in the HF dict format {'loss','grad_norm','learning_rate','epoch'}
+(reference training/train.ipynb:339).
+"""
+from __future__ import annotations
+
+import json
+import math
+import os
+import time
+from pathlib import Path
+
+import torch
+
+from ..config.args import TrainingArgs
+from ..config.ds_config import DSConfig
+from ..data.sampler import DataLoader, DistributedBatchSampler
+from ..models.config import LlamaConfig
+from ..models.llama import LoraLlama, PackedBatch, ResidentWeights, pack_batch
+from ..models.lora import LoraConfig, LoraParams
+from ..models.peft_io import save_adapter
+from ..optim.loss_scaler import build_loss_scaler
+from ..optim.sched import build_scheduler
+from ..parallel import comm
+from ..parallel.zero import ZeroOptimizer
+from ..parallel.zero3 import Zero3Weights
+from . import checkpoint as ckpt
+
+_PREC = {"bf16": torch.bfloat16, "fp16": torch.float16, "fp32": torch.float32}
+
+
+class Trainer:
+    def __init__(self, cfg: LlamaConfig, lcfg: LoraConfig, args: TrainingArgs, train_dataset=None,
+                 collator=None, *, model_path: str | None = None, info: comm.DistInfo | None = None,
+                 tokenizer=None, init_seed: int = 0):
+        self.cfg, self.lcfg, self.args = cfg, lcfg, args
+        self.dataset, self.collator, self.tokenizer = train_dataset, collator, tokenizer
+        self.info = info or comm.init_distributed(args.device, args.local_rank)
+        info = self.info
+        self.is_main = info.is_main
+        # ---- config resolution (D10) ----
+        self.ds = DSConfig.load(args.deepspeed) if args.deepspeed else DSConfig.baseline()
+        if args.no_offload:
+            self.ds.override_no_offload()
+        self.loader = None
+        self.steps_per_epoch, self.max_steps = 1, max(1, args.max_steps)
+        if train_dataset is not None:
+            sampler = DistributedBatchSampler(len(train_dataset), args.per_device_train_batch_size,
+                                              info.rank, info.world_size, seed=args.seed)
+            self.loader = DataLoader(train_dataset, sampler, collator)
+            n = len(self.loader)
+            ga = args.gradient_accumulation_steps
+            self.steps_per_epoch = max(n // ga + int(n % ga > 0), 1)
+            self.max_steps = (args.max_steps if args.max_steps > 0
+                              else math.ceil(args.num_train_epochs * self.steps_per_epoch))
+        self.ds.resolve(micro_batch=args.per_device_train_batch_size,
+                        grad_accum=args.gradient_accumulation_steps, world_size=info.world_size,
+                        lr=args.learning_rate, betas=(args.adam_beta1, args.adam_beta2),
+                        eps=args.adam_epsilon, weight_decay=args.weight_decay,
+                        max_grad_norm=args.max_grad_norm, warmup_steps=args.warmup_steps,
+                        total_steps=self.max_steps, precision=args.precision)
+        self.precision = self.ds.precision
+        if info.device.type == "cpu" and self.precision != "fp32":
+            # CPU plumbing path computes in fp32 (BASELINE.json config 1); scaler logic still runs
+            self.compute_dtype = torch.float32
+        else:
+            self.compute_dtype = _PREC[self.precision]
+        self.stage = self.ds.zero_stage
+        # ---- communication backend ----
+        self.fused = None
+        if args.backend == "fused" and info.distributed and info.device.type == "cuda":
+            from ..parallel.fused import FusedComm
+            self.fused = FusedComm(info)
+        # ---- weights ----
+        if self.stage == 3:
+            self.weights = Zero3Weights(cfg, self.ds, info, self.compute_dtype,
+                                        backend=args.backend, fused=self.fused)
+            if model_path:
+                self.weights.load_from_hf(model_path)
+            else:
+                self.weights.init_random(init_seed)
+        else:
+            if model_path:
+                from ..models.hf_io import load_resident
+                _, self.weights = load_resident(model_path, info.device, self.compute_dtype)
+            else:
+                self.weights = ResidentWeights.random_init(cfg, info.device, self.compute_dtype, init_seed)
+        # ---- adapters, optimizer, schedule ----
+        self.lora = LoraParams(cfg, lcfg, info.device, self.compute_dtype, seed=args.seed,
+                               pad_to=info.world_size * 64)
+        self.model = LoraLlama(cfg, self.weights, self.lora, args.gradient_checkpointing,
+                               dropout_seed=args.seed)
+        self.scaler = build_loss_scaler(self.ds.fp16_block if self.precision == "fp16" else None)
+        op = self.ds.optimizer_params if self.ds.has_optimizer else {}
+        betas = tuple(op.get("betas", (args.adam_beta1, args.adam_beta2)))
+        self.optimizer = ZeroOptimizer(
+            self.lora, self.ds, info, lr=float(op.get("lr", args.learning_rate)), betas=betas,
+            eps=float(op.get("eps", args.adam_epsilon)),
+            weight_decay=float(op.get("weight_decay", args.weight_decay)),
+            max_grad_norm=self.ds.gradient_clipping if args.deepspeed else args.max_grad_norm,
+            scaler=self.scaler, backend=args.backend, fused=self.fused)
+        if self.ds.has_scheduler:
+            kind, sp = self.ds.scheduler
+            self.scheduler = build_scheduler(kind, **sp)
+        else:
+            self.scheduler = build_scheduler(args.lr_scheduler_type, base_lr=args.learning_rate,
+                                             total_steps=self.max_steps, warmup_steps=args.warmup_steps)
+        self.gscale = torch.zeros(1, dtype=torch.float32, device=info.device)
+        # ---- state ----
+        self.global_step = 0
+        self.epoch = 0.0
+        self.log_history: list[dict] = []
+        self.skipped_steps = 0
+        self._win_loss, self._win_n = 0.0, 0
+        self._step_events: list = []
+        self.step_ms: list[float] = []
+        self.tokens_seen = 0
+        self.timers: dict[str, float] = {}
+        self.fault_at = int(os.environ.get("DLTI_FAULT_AT_STEP", "-1"))
+        self.fault_rank = int(os.environ.get("DLTI_FAULT_RANK", "0"))
+
+    # ---- one optimizer step (public API) -----------------------------------------------------
+    def _to_packed(self, batch) -> PackedBatch:
+        if isinstance(batch, PackedBatch):
+            return batch
+        return pack_batch(batch["input_ids"], batch["labels"], batch.get("attention_mask"),
+                          pin=self.args.dataloader_pin_memory and self.info.device.type == "cuda")
+
+    def train_step(self, micro_batches: list) -> float:
+        """One optimizer step over a list of host micro-batches (dicts from the collator or
+        PackedBatch on pinned memory). Returns the token-normalised global loss (host float)."""
+        loss_t, n_total = self._step_device(micro_batches)
+        return float(loss_t.item()) / max(1.0, n_total)
+
+    def _step_device(self, micro_batches: list):
+        info, opt = self.info, self.optimizer
+        dev = info.device
+        packed = [self._to_packed(b) for b in micro_batches]
+        n_local = float(sum(b.n_valid for b in packed))
+        n_total = comm.all_reduce_host_scalar(n_local, info) if info.distributed else n_local
+        n_total = max(1.0, n_total)
+        timed = dev.type == "cuda"
+        if timed:
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record()
+        loss_sum = None
+        ga = len(packed)
+        for k, pb in enumerate(packed):
+            if self.args.loss_norm == "microbatch":
+                scale = self.scaler.cur_scale / (max(1, pb.n_valid) * ga * info.world_size)
+            else:
+                scale = self.scaler.cur_scale / n_total
+            self.gscale.fill_(scale)
+            pbd = pb.to(dev) if dev.type == "cuda" else pb
+            opt.wait_reduce()
+            ls = self.model.forward_backward(pbd, self.gscale if dev.type == "cuda" else scale)
+            loss_sum = ls if loss_sum is None else loss_sum + ls
+            opt.on_micro_batch_end(is_boundary=(k == ga - 1))
+            self.tokens_seen += pb.n_tokens
+        lr = self.scheduler.get_lr()
+        skipped, gnorm = opt.step(lr)
+        self.scaler.update(skipped)
+        if skipped:
+            self.skipped_steps += 1
+        else:
+            self.scheduler.step()
+        loss_sum = comm.all_reduce_sum_(loss_sum.reshape(1).float(), info)
+        if timed:
+            e1.record()
+            self._step_events.append((e0, e1))
+        self.last_grad_norm, self.last_skipped = gnorm, skipped
+        return loss_sum, n_total
+
+    # ---- the loop ------------------------------------------------------------------------------
+    def train(self, resume_from_checkpoint: str | bool | None = None) -> dict:
+        args, info = self.args, self.info
+        assert self.loader is not None, "Trainer.train needs a dataset"
+        start_epoch, skip_batches = 0, 0
+        if resume_from_checkpoint:
+            path = resume_from_checkpoint
+            if path is True:
+                path = ckpt.latest_checkpoint(args.output_dir) if self.is_main else None
+            path = comm.broadcast_object(str(path) if path else None, 0, info)   # App. D #4
+            if path:
+                self.load_checkpoint(path)
+                start_epoch = self.global_step // self.steps_per_epoch
+                skip_batches = (self.global_step % self.steps_per_epoch) * args.gradient_accumulation_steps
+                if self.is_main:
+                    print(f"Resuming from {path} at global step {self.global_step}")
+        ga = args.gradient_accumulation_steps
+        t_start = time.time()
+        done = self.global_step >= self.max_steps
+        epoch = start_epoch
+        while not done:
+            window = []
+            nb = len(self.loader)
+            for bi, batch in enumerate(self.loader.iter_epoch(epoch, skip_batches), start=skip_batches):
+                window.append(batch)
+                last_in_epoch = bi == nb - 1
+                if len(window) < ga and not last_in_epoch:
+                    continue
+                loss_t, n_total = self._step_device(window)
+                window = []
+                self.global_step += 1
+                self.epoch = epoch + (bi + 1) / nb
+                self._win_loss = self._win_loss + loss_t / n_total
+                self._win_n += 1
+                if self.fault_at == self.global_step and info.rank == self.fault_rank:
+                    os._exit(17)                                  # test-only fault injection (§5.3)
+                if self.global_step % args.logging_steps == 0:
+                    self._log()
+                if args.save_strategy == "steps" and self.global_step % args.save_steps == 0:
+                    self.save_checkpoint()
+                if self.global_step >= self.max_steps:
+                    done = True
+                    break
+            skip_batches = 0
+            if args.save_strategy == "epoch" and (not done or self.global_step >= self.max_steps):
+                self.save_checkpoint()
+            epoch += 1
+            if epoch >= math.ceil(args.num_train_epochs) and args.max_steps <= 0:
+                done = True
+        if self._win_n:
+            self._log()
+        if info.device.type == "cuda":
+            torch.cuda.synchronize()
+        self._drain_events()
+        wall = time.time() - t_start
+        return self._final_metrics(wall)
+
+    def _drain_events(self) -> None:
+        for e0, e1 in self._step_events:
+            self.step_ms.append(e0.elapsed_time(e1))
+        self._step_events = []
+
+    def _log(self) -> None:
+        loss = float(self._win_loss.item() if torch.is_tensor(self._win_loss) else self._win_loss) / max(1, self._win_n)
+        self._win_loss, self._win_n = 0.0, 0
+        entry = {"loss": round(loss, 4), "grad_norm": self.last_grad_norm,
+                 "learning_rate": self.scheduler.get_lr(), "epoch": round(self.epoch, 2)}
+        self.log_history.append(dict(entry, step=self.global_step))
+        if self.is_main:
+            print(entry, flush=True)
+            if self.ds.wall_clock_breakdown and self.info.device.type == "cuda":
+                torch.cuda.synchronize()
+                self._drain_events()
+                recent = self.step_ms[-self.args.logging_steps:]
+                print(f"[wall_clock_breakdown] step {self.global_step}: device step time "
+                      f"mean {sum(recent) / max(1, len(recent)):.2f} ms", flush=True)
+
+    def _final_metrics(self, wall: float) -> dict:
+        info = self.info
+        ms = sum(self.step_ms) / max(1, len(self.step_ms)) if self.step_ms else 0.0
+        peak = torch.cuda.max_memory_allocated() / 1e9 if info.device.type == "cuda" else 0.0
+        t = torch.tensor([ms, peak, float(self.tokens_seen)], dtype=torch.float64)
+        if info.distributed:
+            import torch.distributed as dist
+            mx = t.clone()
+            dist.all_reduce(mx, op=dist.ReduceOp.MAX)
+            sm = t.clone()
+            dist.all_reduce(sm, op=dist.ReduceOp.SUM)
+            ms, peak_max, tokens = float(mx[0]), float(mx[1]), float(sm[2])
+        else:
+            peak_max, tokens = peak, float(self.tokens_seen)
+        final_loss = next((e["loss"] for e in reversed(self.log_history) if "loss" in e), 0.0)
+        return {"training_time_s": wall, "max_rank_step_ms": ms, "peak_memory_gb": peak,
+                "peak_memory_gb_max_rank": peak_max, "tokens": tokens,
+                "tokens_per_second": tokens / wall if wall > 0 else 0.0, "final_loss": final_loss,
+                "global_step": self.global_step, "skipped_steps": self.skipped_steps}
+
+    # ---- saving --------------------------------------------------------------------------------
+    def save_model(self, directory: str | Path) -> None:
+        """PEFT adapter + tokenizer + training_args.bin. Under ZeRO every rank must enter
+        (consolidation is a collective, D23; reference defect App. D #3 called it on rank 0 only)."""
+        state = self.lora.state_dict()          # master is fully gathered on every rank after step()
+        comm.barrier(self.info)
+        if self.is_main:
+            d = Path(directory)
+            save_adapter(state, self.lcfg, d)
+            torch.save(self.args.to_dict(), d / "training_args.bin")
+            if self.tokenizer is not None:
+                self.tokenizer.save_pretrained(str(d))
+        comm.barrier(self.info)
+
+    def trainer_state(self) -> dict:
+        return {"global_step": self.global_step, "epoch": self.epoch, "max_steps": self.max_steps,
+                "num_train_epochs": self.args.num_train_epochs, "log_history": self.log_history,
+                "logging_steps": self.args.logging_steps, "save_steps": self.args.save_steps,
+                "train_batch_size": self.args.per_device_train_batch_size,
+                "skipped_steps": self.skipped_steps, "tokens_seen": self.tokens_seen,
+                "micro_step": self.model.micro_step, "world_size": self.info.world_size}
+
+    def save_checkpoint(self) -> Path:
+        args, info = self.args, self.info
+        path = Path(args.output_dir) / f"checkpoint-{self.global_step}"
+        if self.is_main:
+            path.mkdir(parents=True, exist_ok=True)
+        comm.barrier(info)
+        self.save_model(path)
+        if self.is_main:
+            ckpt.save_trainer_state(path, self.trainer_state())
+        torch.save(ckpt.rng_state(), ckpt.rng_file(path, info.rank, info.world_size))
+        sched_state = {"scheduler": self.scheduler.state_dict(), "scaler": self.scaler.state_dict()}
+        if self.stage == 0:
+            if self.is_main:
+                torch.save(self.optimizer.state_dict(), path / "optimizer.pt")
+                torch.save(sched_state["scheduler"], path / "scheduler.pt")
+                torch.save(sched_state["scaler"], path / "scaler.pt")
+        else:
+            tag = ckpt.ds_tag_dir(path, self.global_step)
+            if self.is_main:
+                tag.mkdir(parents=True, exist_ok=True)
+            comm.barrier(info)
+            torch.save(self.optimizer.state_dict(), ckpt.optim_file(tag, info.rank))
+            if self.is_main:
+                torch.save(dict(sched_state, global_step=self.global_step,
+                                skipped_steps=self.skipped_steps, ds_config=self.ds.cfg),
+                           tag / "mp_rank_00_model_states.pt")
+                ckpt.write_latest(path, self.global_step)
+        comm.barrier(info)
+        if self.is_main:
+            ckpt.rotate_checkpoints(args.output_dir, args.save_total_limit)
+        comm.barrier(info)
+        return path
+
+    def load_checkpoint(self, path: str | Path) -> None:
+        from ..models.peft_io import load_adapter_state
+
+        path, info = Path(path), self.info
+        st = ckpt.load_trainer_state(path)
+        if st.get("world_size", info.world_size) != info.world_size and self.stage >= 1:
+            raise ValueError("resuming with a different world size is not supported for ZeRO stages >= 1 "
+                             "(optimizer partitions are per rank)")
+        self.lora.load_state_dict(load_adapter_state(path))
+        self.global_step = int(st["global_step"])
+        self.epoch = float(st["epoch"])
+        self.log_history = list(st.get("log_history", []))
+        self.skipped_steps = int(st.get("skipped_steps", 0))
+        self.tokens_seen = int(st.get("tokens_seen", 0))
+        self.model.micro_step = int(st.get("micro_step", 0))
+        if self.stage == 0:
+            self.optimizer.load_state_dict(torch.load(path / "optimizer.pt", weights_only=False))
+            self.scheduler.load_state_dict(torch.load(path / "scheduler.pt", weights_only=False))
+            self.scaler.load_state_dict(torch.load(path / "scaler.pt", weights_only=False))
+        else:
+            tagname = ckpt.read_latest(path) or f"global_step{self.global_step}"
+            tag = path / tagname
+            self.optimizer.load_state_dict(torch.load(ckpt.optim_file(tag, info.rank), weights_only=False))
+            ms = torch.load(tag / "mp_rank_00_model_states.pt", weights_only=False)
+            self.scheduler.load_state_dict(ms["scheduler"])
+            self.scaler.load_state_dict(ms["scaler"])
+        rf = ckpt.rng_file(path, info.rank, info.world_size)
+        if rf.exists():
+            ckpt.set_rng_state(torch.load(rf, weights_only=False))

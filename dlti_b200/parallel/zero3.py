@@ -1,0 +1,259 @@
+"""ZeRO stage-3 partitioning of the FROZEN base weights (collective C4).
+
+Every matrix [R, C] is split by rows: rank r owns rows [r*Rp, (r+1)*Rp), Rp = ceil(R/N) (zero
+padded). Row-major row blocks mean the gathered matrix is simply the rank-ordered concatenation,
+so a gather lands directly in the layout the GEMM consumes — and a fused kernel can address
+"the rows of tile n" on their owner without any index table.
+
+Parameters with numel <= stage3_param_persistence_threshold stay replicated (for Llama that is
+exactly the RMSNorm weights; every LoRA tensor is also below the threshold — SURVEY D14).
+
+Gather scheduling mirrors DeepSpeed's coordinator at decoder-layer granularity: `prefetch(i)`
+starts the gather of layer i on a side stream into one of `n_slots` full-layer staging buffers
+(n_slots bounded by stage3_max_live_parameters), `layer(i)` waits for it, `release(i)` frees the
+slot. The look-ahead is one whole layer (DeepSpeed's stage3_prefetch_bucket_size counts elements;
+one 7B layer is 2e8 elements — we round the window up to a layer so forward GEMMs never wait).
+
+Backends: "nccl" = all_gather_into_tensor per matrix (baseline; gloo on CPU);
+          "fused" = peer-pull sm_100a copy kernel over symmetric memory (parallel.fused).
+offload_param = "cpu": shards live in pinned host memory and are copied H2D before each gather.
+"""
+from __future__ import annotations
+
+import torch
+
+from ..config.ds_config import DSConfig
+from ..models.config import LlamaConfig
+from ..models.llama import LayerWeights
+from . import comm
+from .comm import DistInfo
+
+_MATS = ("w_qkv", "w_o", "w_gu", "w_down")
+
+
+def _rows_per_rank(rows: int, world: int) -> int:
+    return -(-rows // world)
+
+
+class Zero3Weights:
+    def __init__(self, cfg: LlamaConfig, ds: DSConfig, info: DistInfo, dtype: torch.dtype,
+                 backend: str = "nccl", fused=None):
+        self.cfg, self.ds, self.info, self.dtype = cfg, ds, info, dtype
+        self.device = info.device
+        self.world, self.rank = info.world_size, info.rank
+        self.backend, self.fused = backend, fused
+        d, ff = cfg.hidden_size, cfg.intermediate_size
+        self.shapes = {"w_qkv": (cfg.qkv_size, d), "w_o": (d, cfg.q_size), "w_gu": (2 * ff, d),
+                       "w_down": (d, ff)}
+        self.offload = ds.offload_param == "cpu"
+        self.persist_thr = ds.stage3_param_persistence_threshold
+        sdev = "cpu" if self.offload else self.device
+        pin = self.offload and ds.pin_memory and torch.cuda.is_available()
+        L = cfg.num_hidden_layers
+
+        def shard_buf(rows, cols):
+            rp = _rows_per_rank(rows, self.world)
+            if fused is not None and not self.offload:
+                return fused.alloc_symmetric((rp, cols), dtype)
+            t = torch.zeros(rp, cols, dtype=dtype, device=sdev)
+            return t.pin_memory() if pin else t
+
+        self.layer_shards = [{m: shard_buf(*self.shapes[m]) for m in _MATS} for _ in range(L)]
+        self.norms = [(torch.ones(d, dtype=dtype, device=self.device),
+                       torch.ones(d, dtype=dtype, device=self.device)) for _ in range(L)]
+        self.final_norm = torch.ones(d, dtype=dtype, device=self.device)
+        self.embed_shard = shard_buf(cfg.vocab_size, d)
+        self.lm_head_shard = self.embed_shard if cfg.tie_word_embeddings else shard_buf(cfg.vocab_size, d)
+        # staging: full-layer slots
+        layer_elems = sum(r * c for r, c in self.shapes.values())
+        max_live = max(layer_elems, ds.stage3_max_live_parameters)
+        self.n_slots = max(1, min(3, max_live // layer_elems)) if self.world > 1 else 0
+        self.slots = []
+        for _ in range(self.n_slots):
+            self.slots.append({m: torch.empty(_rows_per_rank(r, self.world) * self.world, c, dtype=dtype,
+                                              device=self.device) for m, (r, c) in self.shapes.items()})
+        self.slot_of: dict[int, int] = {}
+        self.slot_free_event: list = [None] * self.n_slots
+        self.slot_ready_event: list = [None] * self.n_slots
+        self.free_slots = list(range(self.n_slots))
+        self.stream = torch.cuda.Stream(device=self.device) if self.device.type == "cuda" and self.world > 1 else None
+        self._big = {}          # gathered embed / lm_head staging (allocated on demand)
+        self._h2d = {}          # offload: device copies of this rank's shards while in flight
+        self.gather_bytes = 0   # bytes received from peers (for roofline reports)
+
+    # ---- initialisation ------------------------------------------------------------------------
+    def init_random(self, seed: int = 0) -> None:
+        """Random-init (std 0.02) of the LOCAL shards only; deterministic per (matrix, rank)."""
+        g = torch.Generator(device="cpu").manual_seed(seed * 1000003 + self.rank)
+
+        def fill(t, rows_total):
+            rp = t.shape[0]
+            valid = max(0, min(rp, rows_total - self.rank * rp))
+            tmp = torch.zeros(t.shape, dtype=torch.float32)
+            if valid:
+                tmp[:valid].normal_(0.0, 0.02, generator=g)
+            t.copy_(tmp.to(t.dtype))
+
+        if self.device.type == "cuda" and not self.offload:
+            gd = torch.Generator(device=self.device).manual_seed(seed * 1000003 + self.rank)
+            def fill(t, rows_total):  # noqa: F811  (device-side init: 13.5 GB on the host is too slow)
+                rp = t.shape[0]
+                valid = max(0, min(rp, rows_total - self.rank * rp))
+                t.zero_()
+                if valid:
+                    t[:valid].normal_(0.0, 0.02, generator=gd)
+        for sh in self.layer_shards:
+            for m in _MATS:
+                fill(sh[m], self.shapes[m][0])
+        fill(self.embed_shard, self.cfg.vocab_size)
+        if self.lm_head_shard is not self.embed_shard:
+            fill(self.lm_head_shard, self.cfg.vocab_size)
+
+    def load_from_resident(self, w) -> None:
+        """Shard a fully materialised ResidentWeights (tests, small models)."""
+        def take(dst, full):
+            rp = dst.shape[0]
+            lo = self.rank * rp
+            hi = min(full.shape[0], lo + rp)
+            dst.zero_()
+            if hi > lo:
+                dst[: hi - lo].copy_(full[lo:hi])
+        for i, sh in enumerate(self.layer_shards):
+            lw = w.layers[i]
+            for m in _MATS:
+                take(sh[m], getattr(lw, m))
+            self.norms[i][0].copy_(lw.ln1)
+            self.norms[i][1].copy_(lw.ln2)
+        self.final_norm.copy_(w.final_norm)
+        take(self.embed_shard, w.embed)
+        if self.lm_head_shard is not self.embed_shard:
+            take(self.lm_head_shard, w.lm_head)
+
+    def load_from_hf(self, directory) -> None:
+        """Each rank reads only the byte ranges of its own row blocks (fixes App. D #6)."""
+        from ..models.hf_io import CheckpointReader, hf_layer_names
+
+        rd = CheckpointReader(directory)
+        cfg = self.cfg
+        q, kv, ff = cfg.q_size, cfg.kv_size, cfg.intermediate_size
+
+        def take(dst, pieces):
+            """pieces: list of (name, rows) stacked along dim 0 to form the logical matrix."""
+            rp = dst.shape[0]
+            lo, hi = self.rank * rp, (self.rank + 1) * rp
+            dst.zero_()
+            base = 0
+            for name, rows in pieces:
+                a, b = max(lo, base), min(hi, base + rows)
+                if b > a:
+                    dst[a - lo:b - lo].copy_(rd.get(name, rows=(a - base, b - base)).to(self.dtype))
+                base += rows
+
+        for i, sh in enumerate(self.layer_shards):
+            n = hf_layer_names(i)
+            take(sh["w_qkv"], [(n["q"], q), (n["k"], kv), (n["v"], kv)])
+            take(sh["w_o"], [(n["o"], cfg.hidden_size)])
+            take(sh["w_gu"], [(n["gate"], ff), (n["up"], ff)])
+            take(sh["w_down"], [(n["down"], cfg.hidden_size)])
+            self.norms[i][0].copy_(rd.get(n["ln1"]).to(self.dtype))
+            self.norms[i][1].copy_(rd.get(n["ln2"]).to(self.dtype))
+        self.final_norm.copy_(rd.get("model.norm.weight").to(self.dtype))
+        take(self.embed_shard, [("model.embed_tokens.weight", cfg.vocab_size)])
+        if self.lm_head_shard is not self.embed_shard:
+            nm = "lm_head.weight" if rd.has("lm_head.weight") else "model.embed_tokens.weight"
+            take(self.lm_head_shard, [(nm, cfg.vocab_size)])
+
+    # ---- gathers -------------------------------------------------------------------------------
+    def _device_shard(self, key, shard: torch.Tensor) -> torch.Tensor:
+        if not self.offload:
+            return shard
+        t = shard.to(self.device, non_blocking=True)       # H2D of the local shard (D16)
+        self._h2d[key] = t
+        return t
+
+    def _gather(self, key, shard: torch.Tensor, out: torch.Tensor) -> None:
+        src = self._device_shard(key, shard)
+        if self.fused is not None and not self.offload:
+            self.fused.all_gather_rows(shard, out)
+        else:
+            comm.all_gather_into(out.view(-1), src.reshape(-1), self.info)
+        self.gather_bytes += out.numel() * out.element_size() * (self.world - 1) // self.world
+
+    def prefetch(self, i: int) -> None:
+        if self.world == 1 or i in self.slot_of or i < 0 or i >= self.cfg.num_hidden_layers:
+            return
+        if not self.free_slots:
+            return                                   # window full (stage3_max_live_parameters)
+        s = self.free_slots.pop(0)
+        self.slot_of[i] = s
+        st = self.stream
+        if st is not None:
+            if self.slot_free_event[s] is not None:
+                st.wait_event(self.slot_free_event[s])
+            with torch.cuda.stream(st):
+                for m in _MATS:
+                    self._gather((i, m), self.layer_shards[i][m], self.slots[s][m])
+                ev = torch.cuda.Event()
+                ev.record(st)
+            self.slot_ready_event[s] = ev
+        else:
+            for m in _MATS:
+                self._gather((i, m), self.layer_shards[i][m], self.slots[s][m])
+
+    def layer(self, i: int) -> LayerWeights:
+        if self.world == 1:
+            sh = self.layer_shards[i]
+            dev = (lambda t: t.to(self.device, non_blocking=True)) if self.offload else (lambda t: t)
+            r = {m: dev(sh[m])[: self.shapes[m][0]] for m in _MATS}
+            return LayerWeights(r["w_qkv"], r["w_o"], r["w_gu"], r["w_down"], *self.norms[i])
+        if i not in self.slot_of:
+            self.prefetch(i)
+            if i not in self.slot_of:
+                raise RuntimeError("ZeRO-3: no free gather slot (release() not called?)")
+        s = self.slot_of[i]
+        if self.slot_ready_event[s] is not None:
+            torch.cuda.current_stream().wait_event(self.slot_ready_event[s])
+        sl = self.slots[s]
+        r = {m: sl[m][: self.shapes[m][0]] for m in _MATS}
+        return LayerWeights(r["w_qkv"], r["w_o"], r["w_gu"], r["w_down"], *self.norms[i])
+
+    def release(self, i: int) -> None:
+        if self.world == 1 or i not in self.slot_of:
+            return
+        s = self.slot_of.pop(i)
+        if self.stream is not None:
+            ev = torch.cuda.Event()
+            ev.record(torch.cuda.current_stream())
+            self.slot_free_event[s] = ev
+        for m in _MATS:
+            self._h2d.pop((i, m), None)
+        self.free_slots.append(s)
+
+    def _gather_big(self, name: str, shard: torch.Tensor) -> torch.Tensor:
+        rows = self.cfg.vocab_size
+        if self.world == 1:
+            return (shard.to(self.device, non_blocking=True) if self.offload else shard)[:rows]
+        buf = self._big.get(name)
+        if buf is None:
+            buf = torch.empty(shard.shape[0] * self.world, shard.shape[1], dtype=self.dtype, device=self.device)
+            self._big[name] = buf
+        self._gather((name,), shard, buf)
+        return buf[:rows]
+
+    def get_embed(self) -> torch.Tensor:
+        return self._gather_big("embed", self.embed_shard)
+
+    def get_lm_head(self) -> torch.Tensor:
+        if self.lm_head_shard is self.embed_shard and "embed" in self._big:
+            return self._big["embed"][: self.cfg.vocab_size]
+        return self._gather_big("lm_head", self.lm_head_shard)
+
+    def get_final_norm(self) -> torch.Tensor:
+        return self.final_norm
+
+    def nbytes_local(self) -> int:
+        n = sum(t.numel() * t.element_size() for sh in self.layer_shards for t in sh.values())
+        n += self.embed_shard.numel() * self.embed_shard.element_size()
+        if self.lm_head_shard is not self.embed_shard:
+            n += self.lm_head_shard.numel() * self.lm_head_shard.element_size()
+        return n

@@ -127,6 +127,7 @@ class Trainer:
         self.step_ms: list[float] = []
         self.tokens_seen = 0
         self.timers: dict[str, float] = {}
+        self.stop_at_step = -1      # test hook: leave the loop after this step (simulated interruption)
         self.fault_at = int(os.environ.get("DLTI_FAULT_AT_STEP", "-1"))
         self.fault_rank = int(os.environ.get("DLTI_FAULT_RANK", "0"))
 
@@ -222,11 +223,11 @@ class Trainer:
                     self._log()
                 if args.save_strategy == "steps" and self.global_step % args.save_steps == 0:
                     self.save_checkpoint()
-                if self.global_step >= self.max_steps:
+                if self.global_step >= self.max_steps or self.global_step == self.stop_at_step:
                     done = True
                     break
             skip_batches = 0
-            if args.save_strategy == "epoch" and (not done or self.global_step >= self.max_steps):
+            if args.save_strategy == "epoch" and self.global_step != self.stop_at_step:
                 self.save_checkpoint()
             epoch += 1
             if epoch >= math.ceil(args.num_train_epochs) and args.max_steps <= 0:

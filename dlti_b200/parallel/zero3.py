@@ -83,31 +83,31 @@ class Zero3Weights:
 
     # ---- initialisation ------------------------------------------------------------------------
     def init_random(self, seed: int = 0) -> None:
-        """Random-init (std 0.02) of the LOCAL shards only; deterministic per (matrix, rank)."""
-        g = torch.Generator(device="cpu").manual_seed(seed * 1000003 + self.rank)
+        """Random-init (std 0.02). Every matrix is generated from a generator seeded by
+        (seed, matrix id) — independent of the world size, so N-rank and 1-rank runs see the same
+        model — on the compute device (a 7B layer matrix is a ~180 MB temporary), and only this
+        rank's row block is kept."""
+        gdev = self.device
+        gen = torch.Generator(device=gdev)
 
-        def fill(t, rows_total):
-            rp = t.shape[0]
-            valid = max(0, min(rp, rows_total - self.rank * rp))
-            tmp = torch.zeros(t.shape, dtype=torch.float32)
-            if valid:
-                tmp[:valid].normal_(0.0, 0.02, generator=g)
-            t.copy_(tmp.to(t.dtype))
+        def fill(dst, rows_total, cols, key):
+            gen.manual_seed((seed * 1000003 + key) & 0x7FFFFFFFFFFF)
+            full = torch.empty(rows_total, cols, dtype=torch.float32 if gdev.type == "cpu" else self.dtype,
+                               device=gdev)
+            full.normal_(0.0, 0.02, generator=gen)
+            rp = dst.shape[0]
+            lo = self.rank * rp
+            hi = min(rows_total, lo + rp)
+            dst.zero_()
+            if hi > lo:
+                dst[: hi - lo].copy_(full[lo:hi])
 
-        if self.device.type == "cuda" and not self.offload:
-            gd = torch.Generator(device=self.device).manual_seed(seed * 1000003 + self.rank)
-            def fill(t, rows_total):  # noqa: F811  (device-side init: 13.5 GB on the host is too slow)
-                rp = t.shape[0]
-                valid = max(0, min(rp, rows_total - self.rank * rp))
-                t.zero_()
-                if valid:
-                    t[:valid].normal_(0.0, 0.02, generator=gd)
-        for sh in self.layer_shards:
-            for m in _MATS:
-                fill(sh[m], self.shapes[m][0])
-        fill(self.embed_shard, self.cfg.vocab_size)
+        for li, sh in enumerate(self.layer_shards):
+            for mi, m in enumerate(_MATS):
+                fill(sh[m], *self.shapes[m], key=li * 8 + mi + 16)
+        fill(self.embed_shard, self.cfg.vocab_size, self.cfg.hidden_size, key=1)
         if self.lm_head_shard is not self.embed_shard:
-            fill(self.lm_head_shard, self.cfg.vocab_size)
+            fill(self.lm_head_shard, self.cfg.vocab_size, self.cfg.hidden_size, key=2)
 
     def load_from_resident(self, w) -> None:
         """Shard a fully materialised ResidentWeights (tests, small models)."""

@@ -1,0 +1,208 @@
+"""CPU unit tier: config resolution, naming/CSV, schedules, loss scaler, collator,
+sampler, IO round-trips, merge, checkpoint rotation, Philox restatement."""
+import json
+import math
+import os
+
+import pytest
+import torch
+
+from dlti_b200.config.ds_config import DSConfig, DSConfigError
+from dlti_b200.data.collate import CausalLMCollator
+from dlti_b200.data.sampler import DistributedBatchSampler
+from dlti_b200.data.synthetic import SyntheticInstructionDataset
+from dlti_b200.data.text import format_conversation_for_llama2
+from dlti_b200.engine import checkpoint as ckpt
+from dlti_b200.models.config import PRESETS, LlamaConfig, resolve_config
+from dlti_b200.models.hf_io import load_resident, resident_state_dict, save_hf_checkpoint
+from dlti_b200.models.llama import LoraLlama, ResidentWeights, pack_batch
+from dlti_b200.models.lora import LoraConfig, LoraParams
+from dlti_b200.models.merge import merge_checkpoint
+from dlti_b200.models.peft_io import load_adapter_config, load_adapter_state, save_adapter
+from dlti_b200.optim.loss_scaler import DynamicLossScaler, build_loss_scaler
+from dlti_b200.optim.sched import LinearDecaySchedule, WarmupLR
+from dlti_b200.utils import metrics as M
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+RES = dict(micro_batch=2, grad_accum=4, world_size=2, lr=2e-4, betas=(0.9, 0.999), eps=1e-8, weight_decay=0.0,
+           max_grad_norm=1.0, warmup_steps=0, total_steps=100)
+
+
+@pytest.mark.parametrize("stage", [1, 2, 3])
+def test_reference_configs_resolve(stage):
+    ds = DSConfig.load(os.path.join(ROOT, f"configs/ds_config_zero{stage}.json")).resolve(**RES)
+    assert ds.zero_stage == stage and ds.precision == "fp16" and ds.gradient_clipping == 1.0
+    assert ds.cfg["train_batch_size"] == 16 and ds.cfg["train_micro_batch_size_per_gpu"] == 2
+    kind, sp = ds.scheduler
+    assert kind == "WarmupLR" and sp["warmup_max_lr"] == 2e-4 and sp["warmup_num_steps"] == 0
+    assert ds.has_optimizer == (stage != 2)
+    if stage == 3:
+        assert ds.offload_optimizer == "cpu" and ds.offload_param == "cpu" and ds.pin_memory
+        assert ds.stage3_param_persistence_threshold == 100000 and ds.reduce_bucket_size == 50000000
+        ds.override_no_offload()
+        assert ds.offload_optimizer == "none" and ds.offload_param == "none"
+    if stage == 2:
+        assert ds.offload_optimizer == "none" and ds.allgather_bucket_size == 200000000
+
+
+def test_config_mismatch_and_precision_override():
+    raw = json.load(open(os.path.join(ROOT, "configs/ds_config_zero1.json")))
+    raw["optimizer"]["params"]["lr"] = 1e-3
+    raw["gradient_clipping"] = 0.5
+    with pytest.raises(DSConfigError) as e:
+        DSConfig(raw).resolve(**RES)
+    assert "optimizer.params.lr" in str(e.value) and "gradient_clipping" in str(e.value)
+    ds = DSConfig(json.load(open(os.path.join(ROOT, "configs/ds_config_zero3.json")))).resolve(**RES, precision="bf16")
+    assert ds.precision == "bf16"
+    with pytest.raises(DSConfigError):
+        DSConfig({"zero_optimization": {"stage": 7}})
+
+
+def test_naming_and_csv(tmp_path):
+    assert M.create_experiment_name(1, 0) == "baseline"
+    assert M.create_experiment_name(2, 2) == "zero2_2gpu" and M.create_experiment_name(8, 3) == "zero3_8gpu"
+    assert M.get_zero_stage_from_config(os.path.join(ROOT, "configs/ds_config_zero3.json")) == 3
+    p = tmp_path / "results" / "m.csv"
+    row = {c: 1 for c in M.CORE_COLUMNS}
+    row.update(experiment="baseline", strategy="pytorch_lora", tokens_per_second=5.0)
+    M.save_training_metrics(row, str(p))
+    M.save_training_metrics(dict(row, experiment="zero2_2gpu"), str(p))
+    lines = p.read_text().strip().splitlines()
+    assert lines[0].split(",")[:8] == M.CORE_COLUMNS and len(lines) == 3
+    import doctest
+    assert doctest.testmod(M).failed == 0
+
+
+def test_schedules():
+    s = WarmupLR(0.0, 2e-4, 0)
+    assert s.get_lr() == 0.0          # before the first step (DeepSpeed warning path)
+    assert s.step() == 0.0            # it 0: log(1)/log(2) = 0 (warmup clamped to 2 steps)
+    assert s.step() == pytest.approx(2e-4) and s.step() == pytest.approx(2e-4)
+    s = WarmupLR(0.0, 1.0, 100)
+    vals = [s.step() for _ in range(120)]
+    assert vals[9] == pytest.approx(math.log(10) / math.log(100)) and vals[-1] == 1.0
+    lin = LinearDecaySchedule(2e-4, 10)
+    assert lin.get_lr() == pytest.approx(2e-4)
+    got = [lin.step() for _ in range(10)]
+    assert got[0] == pytest.approx(2e-4 * 0.9) and got[-1] == 0.0
+    sd = lin.state_dict()
+    l2 = LinearDecaySchedule(2e-4, 10)
+    l2.load_state_dict(sd)
+    assert l2.get_lr() == lin.get_lr()
+
+
+def test_dynamic_loss_scaler_state_machine():
+    sc = build_loss_scaler({"enabled": True, "loss_scale": 0, "loss_scale_window": 4, "initial_scale_power": 16,
+                            "hysteresis": 2, "min_loss_scale": 1})
+    assert isinstance(sc, DynamicLossScaler) and sc.cur_scale == 65536
+    sc.update(True)                      # first overflow absorbed by hysteresis
+    assert sc.cur_scale == 65536
+    sc.update(True)                      # second halves
+    assert sc.cur_scale == 32768
+    for _ in range(3):
+        sc.update(False)
+    assert sc.cur_scale == 32768
+    sc.update(False)                     # window of 4 clean iterations since last overflow => x2
+    assert sc.cur_scale == 65536
+    floor = DynamicLossScaler(initial_scale_power=1, hysteresis=1)
+    for _ in range(5):
+        floor.update(True)
+    assert floor.cur_scale == 1.0
+    assert build_loss_scaler(None).cur_scale == 1.0 and build_loss_scaler({"enabled": True, "loss_scale": 128}).cur_scale == 128
+
+
+def test_collator_and_pack():
+    feats = [{"input_ids": [1, 5, 6, 2]}, {"input_ids": [1, 7, 2]}, {"input_ids": [1, 2, 9, 9, 2]}]
+    b = CausalLMCollator(pad_token_id=2, mask_by="pad_id")(feats)
+    assert b["input_ids"].shape == (3, 5) and b["labels"][1].tolist() == [1, 7, -100, -100, -100]
+    assert b["labels"][0].tolist() == [1, 5, 6, -100, -100]        # real EOS masked too (pad == eos)
+    b2 = CausalLMCollator(pad_token_id=2, mask_by="attention")(feats)
+    assert b2["labels"][0].tolist() == [1, 5, 6, 2, -100]
+    pk = pack_batch(b2["input_ids"], b2["labels"], b2["attention_mask"])
+    assert pk.cu_seqlens.tolist() == [0, 4, 7, 12] and pk.max_seqlen == 5
+    assert pk.input_ids.tolist() == [1, 5, 6, 2, 1, 7, 2, 1, 2, 9, 9, 2]
+    assert pk.labels.tolist() == [5, 6, 2, -100, 7, 2, -100, 2, 9, 9, 2, -100]
+    assert pk.positions.tolist() == [0, 1, 2, 3, 0, 1, 2, 0, 1, 2, 3, 4] and pk.n_valid == 9
+
+
+def test_sampler_shards_and_resume():
+    s0 = DistributedBatchSampler(10, 2, rank=0, world_size=2, seed=42)
+    s1 = DistributedBatchSampler(10, 2, rank=1, world_size=2, seed=42)
+    a, b = s0.epoch_indices(0), s1.epoch_indices(0)
+    assert len(a) == len(b) == 5 and sorted(a + b) == list(range(10))
+    assert s0.epoch_indices(0) == a and s0.epoch_indices(1) != a
+    full = list(s0.iter_epoch(0))
+    assert list(s0.iter_epoch(0, skip_batches=2)) == full[2:] and len(s0) == 3
+
+
+def test_synthetic_dataset_shapes():
+    ds = SyntheticInstructionDataset(16, 1000, max_length=64)
+    x = ds[3]
+    assert x == ds[3] and 10 <= len(x["input_ids"]) <= 64 and x["input_ids"][0] == 1
+    fx = SyntheticInstructionDataset(4, 1000, max_length=32, fixed_length=True)[0]
+    assert len(fx["input_ids"]) == 32
+    assert format_conversation_for_llama2({"question": " q ", "answer": "a"})["text"] == "<s>[INST] q [/INST] a</s>"
+
+
+def test_presets_and_param_counts():
+    c = resolve_config("meta-llama/Llama-2-7b-hf")
+    assert c.num_params() == 6738415616 and c.params_per_layer() == 202383360
+    lp_numel = 32 * (4 * 16 * 4096 + 4 * 4096 * 16)
+    assert lp_numel == 16777216
+    assert resolve_config("llama2-70b").num_params() == 68976648192
+    with pytest.raises(ValueError):
+        resolve_config("nope")
+
+
+def test_hf_and_peft_roundtrip_and_merge(tmp_path):
+    cfg = PRESETS["tiny-gqa"]
+    w = ResidentWeights.random_init(cfg, "cpu", torch.float32, seed=0)
+    files = save_hf_checkpoint(cfg, resident_state_dict(w), tmp_path / "base", max_shard_bytes=3_000_000)
+    assert len(files) > 1 and (tmp_path / "base" / "model.safetensors.index.json").exists()
+    cfg2, w2 = load_resident(tmp_path / "base", "cpu", torch.float32)
+    assert cfg2.num_key_value_heads == 2
+    for a, b in zip(w.all_matrices(), w2.all_matrices()):
+        assert torch.equal(a, b)
+    lcfg = LoraConfig(r=8, lora_alpha=16, base_model_name_or_path="tiny-gqa")
+    lora = LoraParams(cfg, lcfg, "cpu", torch.float32, seed=1)
+    for n in lora.slots:
+        if n.endswith("lora_B"):
+            lora.view(n).normal_(0, 0.1)
+    save_adapter(lora.state_dict(), lcfg, tmp_path / "ad")
+    ac = json.load(open(tmp_path / "ad" / "adapter_config.json"))
+    assert ac["peft_type"] == "LORA" and ac["r"] == 8 and ac["lora_alpha"] == 16 and ac["bias"] == "none"
+    sd = load_adapter_state(tmp_path / "ad")
+    k = "base_model.model.model.layers.1.self_attn.v_proj.lora_B.weight"
+    assert k in sd and sd[k].shape == (cfg.kv_size, 8) and sd[k].dtype == torch.float32
+    l2 = LoraParams(cfg, load_adapter_config(tmp_path / "ad"), "cpu", torch.float32, seed=5)
+    l2.load_state_dict(sd)
+    assert torch.equal(l2.master[: l2.numel], lora.master[: lora.numel])
+    # merged model == base + adapter
+    merge_checkpoint(tmp_path / "base", tmp_path / "ad", tmp_path / "merged", dtype=torch.float32)
+    _, wm = load_resident(tmp_path / "merged", "cpu", torch.float32)
+    lora.refresh_compute()
+    ids = torch.randint(3, cfg.vocab_size, (2, 12))
+    b = pack_batch(ids, ids.clone(), None)
+    m_ad = LoraLlama(cfg, w, lora); m_ad.training = False
+    m_mg = LoraLlama(cfg, wm, None); m_mg.training = False
+    torch.testing.assert_close(m_ad.forward_logits(b), m_mg.forward_logits(b), rtol=1e-4, atol=1e-4)
+
+
+def test_checkpoint_rotation(tmp_path):
+    for s in (100, 200, 300, 1000):
+        (tmp_path / f"checkpoint-{s}").mkdir()
+    (tmp_path / "final").mkdir()
+    assert ckpt.latest_checkpoint(tmp_path).name == "checkpoint-1000"
+    gone = ckpt.rotate_checkpoints(tmp_path, 2)
+    assert [p.name for p in gone] == ["checkpoint-100", "checkpoint-200"]
+    assert [p.name for p in ckpt.list_checkpoints(tmp_path)] == ["checkpoint-300", "checkpoint-1000"]
+
+
+def test_philox_known_answer():
+    from dlti_b200.ops.rng import keep_mask, philox4x32
+    import numpy as np
+    # Random123 known-answer test for philox4x32-10: counter = key = 0
+    r = philox4x32(np.array([0]), np.array([0]), np.array([0]), np.array([0]), 0, 0)
+    assert [int(x[0]) for x in r] == [0x6627E8D5, 0xE169C58D, 0xBC57AC4C, 0x9B00DBD8]
+    m = keep_mask(64, 128, 0.05, 1, 2)
+    assert 0.02 < 1 - m.float().mean().item() < 0.09

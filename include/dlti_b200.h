@@ -52,6 +52,88 @@ int dlti_gemm(const void* A, const void* B, void* C, const void* R, int M, int N
               int in_dtype, int out_dtype, float alpha, int accumulate, int split_k, int block_n,
               int max_ctas, dlti_stream_t stream);
 
+/* ---- K4: RMSNorm ---------------------------------------------------------------------------
+ * fwd: y = w * T(x * rsqrt(mean(x^2) + eps)); optional residual_inout (+= x, then normalised: the
+ * serving path's fused add+norm), optional ydrop = dropout(y) (LoRA-branch input, Philox mask
+ * keyed by (seed, stream_id, element index)), rstd (fp32 per row) for the backward.
+ * bwd: dx (norm weights are frozen: no dw); dres (optional) is added to dx.
+ * Replaces HF LlamaRMSNorm's ~5 ATen kernels / vLLM rms_norm + fused_add_rms_norm. */
+int dlti_rmsnorm_fwd(const void* x, void* residual_inout, const void* w, void* y, void* ydrop,
+                     float* rstd, long long rows, int d, float eps, float drop_p,
+                     unsigned long long seed, unsigned long long stream_id, int dtype,
+                     dlti_stream_t stream);
+int dlti_rmsnorm_bwd(const void* dy, const void* x, const void* w, const float* rstd,
+                     const void* dres, void* dx, long long rows, int d, int dtype,
+                     dlti_stream_t stream);
+
+/* ---- K5: RoPE (rotate-half), in place on the first n_rot_heads heads of each [tokens, row_stride]
+ * row (merged qkv: q heads then k heads). cos/sin: fp32 [max_pos, hd/2]. backward = inverse
+ * rotation. Replaces HF apply_rotary_pos_emb / vLLM rotary_embedding. */
+int dlti_rope(void* buf, const int* pos, const float* cos_t, const float* sin_t, long long tokens,
+              int n_rot_heads, int hd, long long row_stride, int backward, int dtype,
+              dlti_stream_t stream);
+
+/* ---- K7: SwiGLU on gu = [tokens, 2*ff] (gate | up). Replaces silu + mul / vLLM silu_and_mul
+ * (SURVEY O7, S8). */
+int dlti_swiglu_fwd(const void* gu, void* h, long long tokens, int ff, long long gu_stride,
+                    long long h_stride, int dtype, dlti_stream_t stream);
+int dlti_swiglu_bwd(const void* dh, const void* gu, void* dgu, long long tokens, int ff,
+                    long long dh_stride, long long gu_stride, int dtype, dlti_stream_t stream);
+
+/* ---- dropout / a + dropout(b): counter-based masks (mask index = row*cols + col), reproducible in
+ * layer recompute. Replaces torch.nn.Dropout inside PEFT lora.Linear (lora_dropout = 0.05). */
+int dlti_dropout(const void* x, void* y, long long rows, int cols, long long x_stride,
+                 long long y_stride, float p, unsigned long long seed, unsigned long long stream_id,
+                 int dtype, dlti_stream_t stream);
+int dlti_add_dropout(const void* a, const void* b, void* y, long long rows, int cols, float p,
+                     unsigned long long seed, unsigned long long stream_id, int dtype,
+                     dlti_stream_t stream);
+
+/* ---- K15: embedding gather; ids outside [vocab_start, vocab_start + vocab_rows) give zero rows
+ * (vocab-parallel shard contribution). Replaces ATen embedding. */
+int dlti_embedding(const long long* ids, const void* table, void* out, long long tokens, int d,
+                   long long vocab_start, long long vocab_rows, int dtype, dlti_stream_t stream);
+
+/* ---- K8 (loss): softmax cross-entropy over 16-bit logits, fp32 math. loss_rows[t] = lse - logit
+ * [label] (0 when label == ignore_index); dlogits (may alias logits) = (softmax - onehot) * *gscale.
+ * Replaces ATen log_softmax + nll_loss (+ backward). */
+int dlti_cross_entropy(const void* logits, void* dlogits, const long long* labels, float* loss_rows,
+                       const float* gscale, long long rows, int V, long long ld, long long ldd,
+                       long long ignore_index, int dtype, dlti_stream_t stream);
+
+/* ---- K9 (single-GPU part): out[0] (+)= sum(g^2) over a flat fp32 vector (gradient norm; a
+ * non-finite element makes it non-finite = fp16 overflow). `partials` is caller-provided SCRATCH of
+ * dlti_sumsq_scratch_floats() floats. Replaces clip_grad_norm_ + GradScaler's finite check
+ * (SURVEY N7, O12, C6, C7). */
+int dlti_sumsq_scratch_floats(void);
+int dlti_sumsq(const float* g, long long n, float* partials, float* out, int accumulate,
+               dlti_stream_t stream);
+
+/* Fused unscale + global-norm clip + AdamW (decoupled weight decay) on a flat fp32 partition with
+ * optional 16-bit copy-out; skipped (and *skipped_out = 1) when *gnorm_sq is not finite.
+ * Replaces torch.optim.AdamW / DeepSpeed FusedAdam multi_tensor_adam.cu. */
+int dlti_adamw(float* p, float* m, float* v, float* g, void* p16, int p16_dtype, long long n,
+               float lr, float b1, float b2, float eps, float wd, int step, const float* gnorm_sq,
+               float inv_scale, float max_norm, int* skipped_out, int zero_grad,
+               dlti_stream_t stream);
+
+/* Batched 2-D fp32 -> 16-bit casts with per-job scale; jobs_dev = device array of 48-byte records
+ * {src*, dst*, rows, cols, src_pitch, dst_pitch, scale, pad}. Refreshes the packed LoRA buffers. */
+int dlti_cast_job_bytes(void);
+int dlti_multi_cast(const void* jobs_dev, int njobs, int dst_dtype, dlti_stream_t stream);
+
+/* ---- K6: causal varlen flash attention, head_dim 128, GQA. qkv = [T, (H+2KV)*128] (q|k|v per
+ * token row, RoPE applied); out = [T, H*128]; lse = [H, T] fp32 (NULL allowed for inference).
+ * Backward writes dqkv = [T, (H+2KV)*128]; D_scratch = [H, T] fp32 workspace.
+ * Replaces PyTorch SDPA / flash-attn. */
+int dlti_attn_fwd(const void* qkv, void* out, float* lse, const int* cu_seqlens, int batch,
+                  int max_seqlen, long long T_total, int H, int KV, int hd, float scale, int dtype,
+                  dlti_stream_t stream);
+int dlti_attn_bwd(const void* dout, const void* qkv, const void* out, const float* lse,
+                  float* D_scratch, void* dqkv, const int* cu_seqlens, int batch, int max_seqlen,
+                  long long T_total, int H, int KV, int hd, float scale, int dtype,
+                  dlti_stream_t stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -8,6 +8,8 @@
 // and clip_grad_norm_ [N7, O12] (reference configs: configs/ds_config_zero1.json:6-14,44).
 #include "common.cuh"
 
+#include <cstdio>
+
 namespace {
 
 template <typename T>
@@ -281,3 +283,101 @@ DLTI_API int dlti_multi_cast(const void* jobs_dev, int njobs, int dst_dtype, cud
   return (int)cudaGetLastError();
 }
 DLTI_API int dlti_cast_job_bytes() { return (int)sizeof(CastJob); }
+
+// =============================================================================================
+// dlti_sumsq_noalloc — the same reduction as dlti_sumsq for callers that cannot supply (or create)
+// a device workspace.
+//
+// Who needs it: a process that has already handed every free byte of HBM to its own pool (the
+// serving engine's KV-cache arena does exactly that at start-up), so a later cudaMalloc of even a
+// few KB can fail; a latency-critical loop that must not call cudaMalloc/cudaFree because both
+// synchronise the whole device; and a plain C host that links this library without any tensor
+// allocator from which to carve the `partials` buffer dlti_sumsq asks for.
+//
+// How: the per-CTA partial sums go to a fixed array that is part of the library image
+// (32 KB per GPU that loads the library, held until the process exits). Each CTA reduces one fixed
+// chunk of NOALLOC_CHUNK elements, so the array bounds the input:
+//     n <= dlti_sumsq_noalloc_max_elems() = 16384 * 8192 = 134,217,728 floats (512 MB of gradients)
+// Larger inputs are rejected with DLTI_ERR_TOO_LARGE (use dlti_sumsq with your own scratch).
+//
+// Set-up: the FIRST call on each device resolves the array's device address with
+// cudaGetSymbolAddress (the array's name is only a host-side handle, not a pointer a kernel can
+// use) and caches it per device. Make that first call before starting any stream capture.
+//
+// Sharing: every call on a device uses the same array and leaves its partials behind. Nothing has
+// to be cleared between calls — a launch overwrites every slot it later reads — but two calls whose
+// kernels overlap on the GPU (different streams, no ordering between them) race on the array and
+// give wrong sums. Serialise them (same stream, or an event).
+//
+// The function itself calls no cudaMalloc / cudaFree / allocating library routine.
+// =============================================================================================
+namespace {
+
+constexpr int NOALLOC_CHUNK = 16384;       // elements reduced by one CTA
+constexpr int NOALLOC_MAX_BLOCKS = 8192;   // slots in the built-in scratch array
+
+static __device__ __align__(256) float g_sumsq_noalloc_scratch[NOALLOC_MAX_BLOCKS];
+
+__global__ void __launch_bounds__(256) sumsq_chunk_kernel(const float* __restrict__ g, long long n,
+                                                         float* __restrict__ partials, int vec_ok) {
+  __shared__ float red[8];
+  const long long lo = (long long)blockIdx.x * NOALLOC_CHUNK;
+  const long long hi = (lo + NOALLOC_CHUNK < n) ? lo + NOALLOC_CHUNK : n;
+  float acc = 0.f;
+  if (vec_ok && hi - lo == NOALLOC_CHUNK) {
+    const float4* g4 = reinterpret_cast<const float4*>(g + lo);
+    for (int i = threadIdx.x; i < NOALLOC_CHUNK / 4; i += 256) {
+      const float4 v = g4[i];
+      acc += v.x * v.x + v.y * v.y + v.z * v.z + v.w * v.w;
+    }
+  } else {
+    for (long long i = lo + threadIdx.x; i < hi; i += 256) acc += g[i] * g[i];
+  }
+  acc = warp_sum(acc);
+  if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = acc;
+  __syncthreads();
+  if (threadIdx.x < 32) {
+    float t = threadIdx.x < 8 ? red[threadIdx.x] : 0.f;
+    t = warp_sum(t);
+    if (threadIdx.x == 0) partials[blockIdx.x] = t;
+  }
+}
+
+constexpr int NOALLOC_MAX_DEVICES = 64;
+float* g_noalloc_scratch_addr[NOALLOC_MAX_DEVICES] = {nullptr};
+
+}  // namespace
+
+DLTI_API long long dlti_sumsq_noalloc_max_elems() {
+  return (long long)NOALLOC_CHUNK * NOALLOC_MAX_BLOCKS;
+}
+
+DLTI_API int dlti_sumsq_noalloc(const float* g, long long n, float* out, int accumulate,
+                                cudaStream_t st) {
+  if (n < 0 || !out || (n > 0 && !g)) return DLTI_ERR_BAD_ARG;
+  if (n > dlti_sumsq_noalloc_max_elems()) {
+    char buf[256];
+    snprintf(buf, sizeof(buf),
+             "dlti_sumsq_noalloc: n = %lld exceeds the built-in scratch capacity of %lld elements; "
+             "use dlti_sumsq with caller-provided scratch",
+             n, dlti_sumsq_noalloc_max_elems());
+    dlti_set_error(buf);
+    return DLTI_ERR_TOO_LARGE;
+  }
+  int dev = 0;
+  DLTI_CUDA_CHECK(cudaGetDevice(&dev));
+  if (dev < 0 || dev >= NOALLOC_MAX_DEVICES) return DLTI_ERR_UNSUPPORTED;
+  float* scratch = g_noalloc_scratch_addr[dev];
+  if (!scratch) {
+    // once per device, with that device current: name -> device address
+    DLTI_CUDA_CHECK(cudaGetSymbolAddress((void**)&scratch, g_sumsq_noalloc_scratch));
+    g_noalloc_scratch_addr[dev] = scratch;
+  }
+  long long nb = (n + NOALLOC_CHUNK - 1) / NOALLOC_CHUNK;
+  if (nb < 1) nb = 1;
+  const int vec_ok = (reinterpret_cast<uintptr_t>(g) & 15) == 0;
+  sumsq_chunk_kernel<<<(unsigned)nb, 256, 0, st>>>(g, n, scratch, vec_ok);
+  sumsq_final_kernel<<<1, 256, 0, st>>>(scratch, (int)nb, out, accumulate);
+  dlti_count_launch(2);
+  return (int)cudaGetLastError();
+}

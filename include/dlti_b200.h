@@ -109,6 +109,19 @@ int dlti_sumsq_scratch_floats(void);
 int dlti_sumsq(const float* g, long long n, float* partials, float* out, int accumulate,
                dlti_stream_t stream);
 
+/* Same reduction as dlti_sumsq for callers that cannot hand the library a device workspace: a
+ * process whose own pool (e.g. a KV-cache arena) already holds all free HBM, a loop that must not
+ * pay the device-wide synchronisation of cudaMalloc/cudaFree, or a plain C host with no tensor
+ * allocator. The partial sums live in a 32 KB array built into the library (one copy per GPU that
+ * loads it, until exit), so n is limited to dlti_sumsq_noalloc_max_elems() = 134,217,728 floats;
+ * larger n returns DLTI_ERR_TOO_LARGE (-4) with a message in dlti_last_error(). The first call on
+ * each device looks up the array's device address (cudaGetSymbolAddress) — make it before any
+ * stream capture. Calls share the array: calls whose kernels overlap on the GPU race; keep them
+ * ordered. No cudaMalloc/cudaFree is made. This entry point has no counterpart in the reference. */
+long long dlti_sumsq_noalloc_max_elems(void);
+int dlti_sumsq_noalloc(const float* g, long long n, float* out, int accumulate,
+                       dlti_stream_t stream);
+
 /* Fused unscale + global-norm clip + AdamW (decoupled weight decay) on a flat fp32 partition with
  * optional 16-bit copy-out; skipped (and *skipped_out = 1) when *gnorm_sq is not finite.
  * Replaces torch.optim.AdamW / DeepSpeed FusedAdam multi_tensor_adam.cu. */

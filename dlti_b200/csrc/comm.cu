@@ -1,0 +1,218 @@
+// Peer-memory communication kernels over NVLink 5 / NVSwitch (symmetric arena mapped into every
+// rank; see dlti_b200/parallel/fused.py). These replace the NCCL collectives the reference's stack
+// issues through torch.distributed on the "fused" backend:
+//
+//   peer_barrier        cross-rank barrier on signal words (st.release.sys / ld.acquire.sys)
+//   allgather_rows      pull-based all-gather of row-sharded weights (ZeRO-3 C4, stand-alone form;
+//                       the tile-by-tile fused form lives in gemm.cu, GATHER=true)
+//   rs_accumulate       reduce-scatter by peer reads: part += sum_r grad_r[lo:hi], fixed rank order
+//                       (deterministic) — C2/C5
+//   sumsq_exchange      global gradient norm / overflow flag: every rank publishes its partial sum
+//                       of squares to all peers and sums the board in rank order — C6 + C7
+//   adamw_push          unscale + clip + AdamW on the owned partition, and the updated fp32 values
+//                       are stored straight into every peer's parameter buffer (all-gather by
+//                       push) — O11/O12 + C3/C7b
+//
+// Every spin-wait has a clock-based timeout (~10 s) that raises an error word instead of hanging
+// the GPU when a peer never arrives.
+#include "common.cuh"
+
+namespace {
+
+constexpr int MAX_RANKS = 16;
+constexpr long long SPIN_TIMEOUT_CYCLES = 20000000000LL;   // ~10 s at ~2 GHz
+
+struct Peers {
+  void* p[MAX_RANKS];
+};
+
+__device__ __forceinline__ bool wait_ge_sys(const uint32_t* flag, uint32_t target, int* err) {
+  const long long t0 = clock64();
+  while ((int32_t)(ld_acquire_sys_u32(flag) - target) < 0) {
+    if (clock64() - t0 > SPIN_TIMEOUT_CYCLES) {
+      if (err) atomicExch(err, 1);
+      return false;
+    }
+    __nanosleep(64);
+  }
+  return true;
+}
+
+// One CTA, one thread per rank. pads.p[r] = rank r's signal array (uint32), slot layout:
+// [channel * MAX_RANKS + source_rank]. Monotonic epochs: a flag only ever grows.
+__global__ void peer_barrier_kernel(Peers pads, int rank, int world, int channel, uint32_t epoch,
+                                    int* err) {
+  const int t = threadIdx.x;
+  if (t < world) {
+    __threadfence_system();
+    uint32_t* remote = reinterpret_cast<uint32_t*>(pads.p[t]) + channel * MAX_RANKS + rank;
+    st_release_sys_u32(remote, epoch);
+    const uint32_t* mine = reinterpret_cast<const uint32_t*>(pads.p[rank]) + channel * MAX_RANKS + t;
+    wait_ge_sys(mine, epoch, err);
+  }
+}
+
+// out[r * shard_bytes ...] <- shard of rank r, 16-byte vectors, 4 loads in flight per thread.
+// grid = (blocks_per_peer, world). Weights are immutable during a step: non-coherent loads.
+__global__ void __launch_bounds__(256) allgather_rows_kernel(Peers shards, uint8_t* __restrict__ out,
+                                                            long long shard_bytes, int rank) {
+  const int r = blockIdx.y;
+  const int4* src = reinterpret_cast<const int4*>(shards.p[r]);
+  int4* dst = reinterpret_cast<int4*>(out + (long long)r * shard_bytes);
+  const long long n = shard_bytes >> 4;
+  const long long stride = (long long)gridDim.x * 256;
+  long long i = (long long)blockIdx.x * 256 + threadIdx.x;
+  for (; i + 3 * stride < n; i += 4 * stride) {
+    int4 a = ld_nc_v4(src + i), b = ld_nc_v4(src + i + stride), c = ld_nc_v4(src + i + 2 * stride),
+         d = ld_nc_v4(src + i + 3 * stride);
+    dst[i] = a; dst[i + stride] = b; dst[i + 2 * stride] = c; dst[i + 3 * stride] = d;
+  }
+  for (; i < n; i += stride) dst[i] = ld_nc_v4(src + i);
+}
+
+// part[i] += sum_{r=0..world-1} grads.p[r][lo + i]   (fp32; fixed order => bitwise reproducible)
+__global__ void __launch_bounds__(256) rs_accumulate_kernel(Peers grads, float* __restrict__ part,
+                                                           long long lo, long long n, int world) {
+  const long long n4 = n >> 2;
+  for (long long i = (long long)blockIdx.x * 256 + threadIdx.x; i < n4; i += (long long)gridDim.x * 256) {
+    float4 acc = reinterpret_cast<float4*>(part)[i];
+    for (int r = 0; r < world; ++r) {
+      const int4 v = ld_relaxed_sys_v4(reinterpret_cast<const float4*>(reinterpret_cast<const float*>(grads.p[r]) + lo) + i);
+      acc.x += __int_as_float(v.x); acc.y += __int_as_float(v.y);
+      acc.z += __int_as_float(v.z); acc.w += __int_as_float(v.w);
+    }
+    reinterpret_cast<float4*>(part)[i] = acc;
+  }
+}
+
+// boards.p[r] = rank r's float board [MAX_RANKS]. Publish my partial to every peer, signal, wait for
+// all, sum in rank order. One CTA.
+__global__ void sumsq_exchange_kernel(const float* __restrict__ local, Peers boards, Peers pads, int rank,
+                                      int world, int channel, uint32_t epoch, float* __restrict__ out,
+                                      int* err) {
+  const int t = threadIdx.x;
+  __shared__ int ok;
+  if (t == 0) ok = 1;
+  __syncthreads();
+  if (t < world) {
+    float* rb = reinterpret_cast<float*>(boards.p[t]) + rank;
+    asm volatile("st.relaxed.sys.global.f32 [%0], %1;" ::"l"(rb), "f"(*local) : "memory");
+    __threadfence_system();
+    st_release_sys_u32(reinterpret_cast<uint32_t*>(pads.p[t]) + channel * MAX_RANKS + rank, epoch);
+    if (!wait_ge_sys(reinterpret_cast<const uint32_t*>(pads.p[rank]) + channel * MAX_RANKS + t, epoch, err))
+      ok = 0;
+  }
+  __syncthreads();
+  if (t == 0) {
+    float s = 0.f;
+    const float* mb = reinterpret_cast<const float*>(boards.p[rank]);
+    for (int r = 0; r < world; ++r) {
+      float v;
+      asm volatile("ld.relaxed.sys.global.f32 %0, [%1];" : "=f"(v) : "l"(mb + r) : "memory");
+      s += v;
+    }
+    *out = ok ? s : __int_as_float(0x7fc00000);
+  }
+}
+
+// AdamW on the owned partition [lo, lo+n) of the flat parameter space; the new fp32 value is written
+// to masters.p[r][lo + i] for EVERY rank r (own copy included).
+__global__ void __launch_bounds__(256) adamw_push_kernel(Peers masters, float* __restrict__ m,
+                                                        float* __restrict__ v, float* __restrict__ g,
+                                                        long long lo, long long n, int rank, int world,
+                                                        float lr, float b1, float b2, float eps, float wd,
+                                                        float bc1, float bc2,
+                                                        const float* __restrict__ gnorm_sq, float inv_scale,
+                                                        float max_norm, int* __restrict__ skipped_out) {
+  float coef = inv_scale;
+  const float nsq = *gnorm_sq;
+  if (!isfinite(nsq)) {
+    if (blockIdx.x == 0 && threadIdx.x == 0 && skipped_out) *skipped_out = 1;
+    return;
+  }
+  if (max_norm > 0.f) coef *= fminf(1.f, max_norm / (sqrtf(nsq) * inv_scale + 1e-6f));
+  if (blockIdx.x == 0 && threadIdx.x == 0 && skipped_out) *skipped_out = 0;
+  const float ibc1 = 1.f / bc1, ibc2 = 1.f / bc2;
+  float* mine = reinterpret_cast<float*>(masters.p[rank]) + lo;
+  for (long long i = (long long)blockIdx.x * 256 + threadIdx.x; i < n; i += (long long)gridDim.x * 256) {
+    const float ge = g[i] * coef;
+    const float mi = b1 * m[i] + (1.f - b1) * ge;
+    const float vi = b2 * v[i] + (1.f - b2) * ge * ge;
+    float pi = mine[i];
+    pi -= lr * ((mi * ibc1) / (sqrtf(vi * ibc2) + eps) + wd * pi);
+    m[i] = mi; v[i] = vi; g[i] = 0.f;
+    for (int r = 0; r < world; ++r) (reinterpret_cast<float*>(masters.p[r]) + lo)[i] = pi;
+  }
+}
+
+int fill(Peers& P, const void* const* ptrs, int world) {
+  if (world < 1 || world > MAX_RANKS) return DLTI_ERR_BAD_ARG;
+  for (int i = 0; i < MAX_RANKS; ++i) P.p[i] = i < world ? const_cast<void*>(ptrs[i]) : nullptr;
+  return 0;
+}
+
+}  // namespace
+
+DLTI_API int dlti_comm_max_ranks() { return MAX_RANKS; }
+
+DLTI_API int dlti_peer_barrier(const void* const* signal_pads, int rank, int world, int channel,
+                               unsigned int epoch, int* err_flag, cudaStream_t st) {
+  Peers P;
+  if (int rc = fill(P, signal_pads, world)) return rc;
+  peer_barrier_kernel<<<1, 32, 0, st>>>(P, rank, world, channel, epoch, err_flag);
+  dlti_count_launch();
+  return (int)cudaGetLastError();
+}
+
+DLTI_API int dlti_allgather_rows(const void* const* shards, void* out, long long shard_bytes, int rank,
+                                 int world, int blocks_per_peer, cudaStream_t st) {
+  Peers P;
+  if (int rc = fill(P, shards, world)) return rc;
+  if (shard_bytes % 16) { dlti_set_error("allgather_rows: shard bytes must be a multiple of 16"); return DLTI_ERR_BAD_ARG; }
+  if (blocks_per_peer <= 0) blocks_per_peer = 8;
+  dim3 grid(blocks_per_peer, world);
+  allgather_rows_kernel<<<grid, 256, 0, st>>>(P, (uint8_t*)out, shard_bytes, rank);
+  dlti_count_launch();
+  return (int)cudaGetLastError();
+}
+
+DLTI_API int dlti_rs_accumulate(const void* const* grads, float* part, long long lo, long long n,
+                                int world, cudaStream_t st) {
+  Peers P;
+  if (int rc = fill(P, grads, world)) return rc;
+  if (n % 4 || lo % 4) { dlti_set_error("rs_accumulate: partition must be 16-byte aligned"); return DLTI_ERR_BAD_ARG; }
+  long long want = (n / 4 + 255) / 256;
+  const long long cap = (long long)dlti_num_sms() * 4;
+  rs_accumulate_kernel<<<(unsigned)(want > cap ? cap : (want < 1 ? 1 : want)), 256, 0, st>>>(P, part, lo, n, world);
+  dlti_count_launch();
+  return (int)cudaGetLastError();
+}
+
+DLTI_API int dlti_sumsq_exchange(const float* local, const void* const* boards,
+                                 const void* const* signal_pads, int rank, int world, int channel,
+                                 unsigned int epoch, float* out, int* err_flag, cudaStream_t st) {
+  Peers B, S;
+  if (int rc = fill(B, boards, world)) return rc;
+  if (int rc = fill(S, signal_pads, world)) return rc;
+  sumsq_exchange_kernel<<<1, 32, 0, st>>>(local, B, S, rank, world, channel, epoch, out, err_flag);
+  dlti_count_launch();
+  return (int)cudaGetLastError();
+}
+
+DLTI_API int dlti_adamw_push(const void* const* masters, float* m, float* v, float* g, long long lo,
+                             long long n, int rank, int world, float lr, float b1, float b2, float eps,
+                             float wd, int step, const float* gnorm_sq, float inv_scale, float max_norm,
+                             int* skipped_out, cudaStream_t st) {
+  Peers P;
+  if (int rc = fill(P, masters, world)) return rc;
+  if (n <= 0) return 0;
+  if (step < 1 || !gnorm_sq) return DLTI_ERR_BAD_ARG;
+  const float bc1 = 1.f - powf(b1, (float)step), bc2 = 1.f - powf(b2, (float)step);
+  long long want = (n + 255) / 256;
+  const long long cap = (long long)dlti_num_sms() * 4;
+  adamw_push_kernel<<<(unsigned)(want > cap ? cap : want), 256, 0, st>>>(
+      P, m, v, g, lo, n, rank, world, lr, b1, b2, eps, wd, bc1, bc2, gnorm_sq, inv_scale, max_norm,
+      skipped_out);
+  dlti_count_launch();
+  return (int)cudaGetLastError();
+}

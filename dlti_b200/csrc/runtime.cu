@@ -97,3 +97,36 @@ int dlti_make_tmap_2d(CUtensorMap* out, const void* base, uint64_t inner, uint64
   }
   return 0;
 }
+
+// ---- CUDA IPC helpers for the symmetric arena (fallback when torch symmetric memory is
+// unavailable): open a peer's cudaIpcMemHandle_t (64 bytes) in this process. P2P access over
+// NVLink is enabled lazily by the driver. -------------------------------------------------------
+DLTI_API int dlti_ipc_get_handle(const void* dev_ptr, void* handle_out_64) {
+  cudaIpcMemHandle_t h;
+  DLTI_CUDA_CHECK(cudaIpcGetMemHandle(&h, const_cast<void*>(dev_ptr)));
+  std::memcpy(handle_out_64, &h, sizeof(h));
+  return 0;
+}
+DLTI_API int dlti_ipc_open(const void* handle_64, void** out_ptr) {
+  cudaIpcMemHandle_t h;
+  std::memcpy(&h, handle_64, sizeof(h));
+  DLTI_CUDA_CHECK(cudaIpcOpenMemHandle(out_ptr, h, cudaIpcMemLazyEnablePeerAccess));
+  return 0;
+}
+DLTI_API int dlti_ipc_close(void* ptr) {
+  DLTI_CUDA_CHECK(cudaIpcCloseMemHandle(ptr));
+  return 0;
+}
+DLTI_API int dlti_mem_base(const void* dev_ptr, void** base_out, unsigned long long* size_out) {
+  CUdeviceptr base = 0;
+  size_t size = 0;
+  void* fn = nullptr;
+  cudaDriverEntryPointQueryResult q;
+  if (cudaGetDriverEntryPoint("cuMemGetAddressRange", &fn, cudaEnableDefault, &q) != cudaSuccess || !fn)
+    return DLTI_ERR_DRIVER;
+  typedef CUresult (*fn_t)(CUdeviceptr*, size_t*, CUdeviceptr);
+  if (reinterpret_cast<fn_t>(fn)(&base, &size, (CUdeviceptr)dev_ptr) != CUDA_SUCCESS) return DLTI_ERR_DRIVER;
+  *base_out = (void*)base;
+  *size_out = size;
+  return 0;
+}

@@ -98,7 +98,8 @@ class Trainer:
                 self.weights = ResidentWeights.random_init(cfg, info.device, self.compute_dtype, init_seed)
         # ---- adapters, optimizer, schedule ----
         self.lora = LoraParams(cfg, lcfg, info.device, self.compute_dtype, seed=args.seed,
-                               pad_to=info.world_size * 64)
+                               pad_to=info.world_size * 64,
+                               alloc=self.fused.alloc_symmetric if self.fused is not None else None)
         self.model = LoraLlama(cfg, self.weights, self.lora, args.gradient_checkpointing,
                                dropout_seed=args.seed)
         self.scaler = build_loss_scaler(self.ds.fp16_block if self.precision == "fp16" else None)

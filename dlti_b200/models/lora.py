@@ -70,7 +70,9 @@ class LoraParams:
     """Flat fp32 master/grad buffers + packed compute buffers for every layer."""
 
     def __init__(self, cfg: LlamaConfig, lcfg: LoraConfig, device, compute_dtype: torch.dtype,
-                 seed: int = 42, pad_to: int = 1):
+                 seed: int = 42, pad_to: int = 1, alloc=None):
+        """alloc: optional callable (shape, dtype) -> tensor used for the flat master / gradient
+        buffers (the fused backend passes its symmetric-arena allocator so peers can address them)."""
         self.cfg, self.lcfg = cfg, lcfg
         self.device = torch.device(device)
         self.compute_dtype = compute_dtype
@@ -92,8 +94,14 @@ class LoraParams:
                     off += self.slots[n].numel
         self.numel = off
         self.padded_numel = (off + pad_to - 1) // pad_to * pad_to
-        self.master = torch.zeros(self.padded_numel, dtype=torch.float32, device=self.device)
-        self.grad = torch.zeros(self.padded_numel, dtype=torch.float32, device=self.device)
+        if alloc is not None:
+            self.master = alloc((self.padded_numel,), torch.float32)
+            self.grad = alloc((self.padded_numel,), torch.float32)
+            self.master.zero_()
+            self.grad.zero_()
+        else:
+            self.master = torch.zeros(self.padded_numel, dtype=torch.float32, device=self.device)
+            self.grad = torch.zeros(self.padded_numel, dtype=torch.float32, device=self.device)
         self.reset_parameters(seed)
 
         # packed compute buffers

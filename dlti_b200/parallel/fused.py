@@ -1,0 +1,227 @@
+"""Peer-memory ("fused") communication backend over NVLink 5 / NVSwitch.
+
+A *symmetric arena*: every rank allocates the same sequence of chunks; each chunk is mapped into
+every peer's address space (torch symmetric memory — CUDA VMM + handle exchange — when available,
+classic CUDA IPC otherwise), so a kernel on rank i can load/store rank j's buffers directly. All
+ZeRO-3 weight shards, the flat LoRA master/gradient buffers, gather staging and the signal words
+live in the arena.
+
+On top of it (kernels in csrc/comm.cu and the GATHER variant of csrc/gemm.cu):
+  barrier()                      signal-word barrier kernel (no NCCL)
+  all_gather_rows()              pull-based all-gather of a row-sharded matrix
+  gather_spec() / fused GEMM     all-gather fused INTO the GEMM: gather warps of the persistent
+                                 GEMM pull remote 64-row units into local staging, bump per-unit
+                                 counters, and the TMA producer consumes tiles as units land (K1)
+  reduce_scatter_accumulate()    grad_part += sum over peers (peer loads, fixed order)      (K9)
+  global_sumsq()                 norm / overflow exchange over peer stores                    (K9)
+  adamw_push()                   AdamW on the owned slice + push of new values to all peers   (K9)
+
+This replaces deepspeed.comm / NCCL for the hot collectives; torch.distributed
+stays for bootstrap and as the "nccl" baseline backend.
+"""
+from __future__ import annotations
+
+import ctypes as C
+
+import torch
+import torch.distributed as dist
+
+from ..ops import _lib
+from .comm import DistInfo
+
+_V, _I, _L, _F, _U = C.c_void_p, C.c_int, C.c_longlong, C.c_float, C.c_uint
+MAX_RANKS = 16
+
+
+class _RawCuda:
+    """Minimal __cuda_array_interface__ holder so torch can view foreign device memory."""
+
+    def __init__(self, ptr: int, nbytes: int):
+        self.__cuda_array_interface__ = {"shape": (nbytes,), "typestr": "|u1", "data": (ptr, False),
+                                         "version": 2}
+
+
+class SymmetricArena:
+    def __init__(self, info: DistInfo, chunk_bytes: int = 2 << 30):
+        self.info = info
+        self.chunk_bytes = chunk_bytes
+        self.chunks: list[dict] = []       # {"local": tensor(uint8), "ptrs": [int]*world, "used": int}
+        self.mode = None
+        self._keep = []
+
+    # -- chunk creation (collective) ---------------------------------------------------------
+    def _new_chunk(self, nbytes: int) -> dict:
+        info = self.info
+        nbytes = (nbytes + (2 << 20) - 1) // (2 << 20) * (2 << 20)
+        if self.mode in (None, "symm"):
+            try:
+                import torch.distributed._symmetric_memory as symm
+
+                t = symm.empty(nbytes, dtype=torch.uint8, device=info.device)
+                hdl = symm.rendezvous(t, dist.group.WORLD)
+                ptrs = [int(p) for p in hdl.buffer_ptrs]
+                assert ptrs[info.rank] == t.data_ptr()
+                self.mode = "symm"
+                self._keep.append(hdl)
+                mc = 0
+                try:
+                    mc = int(hdl.multicast_ptr) if hdl.has_multicast_support(info.device.type, info.device.index) else 0
+                except Exception:
+                    mc = 0
+                return {"local": t, "ptrs": ptrs, "used": 0, "multicast": mc}
+            except Exception as e:  # pragma: no cover - depends on the box
+                if self.mode == "symm":
+                    raise
+                if info.is_main:
+                    print(f"[fused] torch symmetric memory unavailable ({type(e).__name__}: {e}); using CUDA IPC")
+                self.mode = "ipc"
+        # ---- CUDA IPC fallback: torch allocation + cudaIpc handle exchange ----
+        t = torch.empty(nbytes, dtype=torch.uint8, device=info.device)
+        base = C.c_void_p()
+        size = C.c_ulonglong()
+        _lib.check(_lib.fn("dlti_mem_base", [_V, C.POINTER(C.c_void_p), C.POINTER(C.c_ulonglong)])(
+            t.data_ptr(), C.byref(base), C.byref(size)), "mem_base")
+        handle = (C.c_ubyte * 64)()
+        _lib.check(_lib.fn("dlti_ipc_get_handle", [_V, _V])(base.value, handle), "ipc_get_handle")
+        mine = (bytes(handle), t.data_ptr() - base.value)
+        allh = [None] * info.world_size
+        dist.all_gather_object(allh, mine)
+        ptrs = []
+        for r, (h, off) in enumerate(allh):
+            if r == info.rank:
+                ptrs.append(t.data_ptr())
+                continue
+            out = C.c_void_p()
+            buf = (C.c_ubyte * 64).from_buffer_copy(h)
+            _lib.check(_lib.fn("dlti_ipc_open", [_V, C.POINTER(C.c_void_p)])(buf, C.byref(out)), "ipc_open")
+            ptrs.append(out.value + off)
+        return {"local": t, "ptrs": ptrs, "used": 0, "multicast": 0}
+
+    def alloc(self, nbytes: int, align: int = 1024) -> tuple[torch.Tensor, list[int]]:
+        """Collective: every rank must call with the same sizes in the same order."""
+        nbytes = max(align, (nbytes + align - 1) // align * align)
+        ch = self.chunks[-1] if self.chunks else None
+        if ch is None or ch["used"] + nbytes > ch["local"].numel():
+            ch = self._new_chunk(max(self.chunk_bytes, nbytes))
+            self.chunks.append(ch)
+        off = ch["used"]
+        ch["used"] += nbytes
+        return ch["local"][off:off + nbytes], [p + off for p in ch["ptrs"]]
+
+    def total_bytes(self) -> int:
+        return sum(c["local"].numel() for c in self.chunks)
+
+
+class GatherSpec:
+    """Arguments of the fused all-gather -> GEMM kernel for one row-sharded weight matrix."""
+
+    def __init__(self, peer_ptrs, staging: torch.Tensor, counters: torch.Tensor, rows_per_rank: int,
+                 rank: int, world: int):
+        self.peer_arr = (C.c_void_p * MAX_RANKS)(*peer_ptrs, *([None] * (MAX_RANKS - len(peer_ptrs))))
+        self.staging, self.counters = staging, counters
+        self.rows_per_rank, self.rank, self.world = rows_per_rank, rank, world
+        self.epoch = 0
+
+
+class FusedComm:
+    N_CHANNELS = 32
+
+    def __init__(self, info: DistInfo):
+        assert info.distributed and info.device.type == "cuda"
+        if info.world_size > MAX_RANKS:
+            raise ValueError(f"fused backend supports up to {MAX_RANKS} ranks per node")
+        self.info = info
+        self.rank, self.world = info.rank, info.world_size
+        self.arena = SymmetricArena(info)
+        self._ptrs: dict[int, list[int]] = {}
+        # signal words [channels, MAX_RANKS] u32 and the norm board [MAX_RANKS] f32
+        self.pads = self.alloc_symmetric((self.N_CHANNELS * MAX_RANKS,), torch.int32)
+        self.board = self.alloc_symmetric((MAX_RANKS,), torch.float32)
+        self.pads.zero_()
+        self.board.zero_()
+        self.err = torch.zeros(1, dtype=torch.int32, device=info.device)
+        self.epochs = [0] * self.N_CHANNELS
+        self._tmp = torch.zeros(1, dtype=torch.float32, device=info.device)
+        torch.cuda.synchronize()
+        dist.barrier()
+
+    # ---- allocation --------------------------------------------------------------------------
+    def alloc_symmetric(self, shape, dtype: torch.dtype) -> torch.Tensor:
+        n = 1
+        for s in shape:
+            n *= int(s)
+        esz = torch.empty(0, dtype=dtype).element_size()
+        raw, ptrs = self.arena.alloc(max(1, n) * esz)
+        t = raw[: n * esz].view(dtype).view(*shape)
+        self._ptrs[t.data_ptr()] = ptrs
+        return t
+
+    def peer_ptrs(self, t: torch.Tensor) -> list[int]:
+        base = self._ptrs.get(t.data_ptr())
+        if base is None:
+            raise ValueError("tensor was not allocated from the symmetric arena")
+        return base
+
+    def _arr(self, ptrs: list[int]):
+        return (C.c_void_p * MAX_RANKS)(*ptrs, *([None] * (MAX_RANKS - len(ptrs))))
+
+    def peer_array(self, t: torch.Tensor):
+        return self._arr(self.peer_ptrs(t))
+
+    def check_error(self) -> None:
+        if int(self.err.item()) != 0:
+            raise RuntimeError("fused backend: a peer did not arrive within the spin-wait timeout")
+
+    # ---- primitives --------------------------------------------------------------------------
+    def barrier(self, channel: int = 0) -> None:
+        self.epochs[channel] += 1
+        f = _lib.fn("dlti_peer_barrier", [_V, _I, _I, _I, _U, _V, _V])
+        _lib.check(f(self.peer_array(self.pads), self.rank, self.world, channel, self.epochs[channel],
+                     _lib.ptr(self.err), _lib.stream_ptr()), "peer_barrier")
+
+    def all_gather_rows(self, shard: torch.Tensor, out: torch.Tensor, blocks_per_peer: int = 8) -> None:
+        """out [world*rows, cols] <- row blocks of every rank (pull). shard must be symmetric."""
+        nbytes = shard.numel() * shard.element_size()
+        assert out.numel() * out.element_size() == nbytes * self.world and out.is_contiguous()
+        f = _lib.fn("dlti_allgather_rows", [_V, _V, _L, _I, _I, _I, _V])
+        _lib.check(f(self.peer_array(shard), _lib.ptr(out), nbytes, self.rank, self.world,
+                     blocks_per_peer, _lib.stream_ptr()), "allgather_rows")
+
+    def reduce_scatter_accumulate(self, g_full: torch.Tensor, grad_part: torch.Tensor) -> None:
+        """grad_part += sum over ranks of their g_full[lo:hi]. g_full must be symmetric.
+        barrier (all grads final) -> peer-read reduce -> barrier (peers may overwrite their grads)."""
+        part = grad_part.numel()
+        self.barrier(1)
+        f = _lib.fn("dlti_rs_accumulate", [_V, _V, _L, _L, _I, _V])
+        _lib.check(f(self.peer_array(g_full), _lib.ptr(grad_part), self.rank * part, part, self.world,
+                     _lib.stream_ptr()), "rs_accumulate")
+        self.barrier(2)
+
+    def global_sumsq(self, g: torch.Tensor, out: torch.Tensor) -> None:
+        from ..ops import optim as O
+
+        O.sumsq(g, out=self._tmp)
+        ch = 3
+        self.epochs[ch] += 1
+        f = _lib.fn("dlti_sumsq_exchange", [_V, _V, _V, _I, _I, _I, _U, _V, _V, _V])
+        _lib.check(f(_lib.ptr(self._tmp), self.peer_array(self.board), self.peer_array(self.pads),
+                     self.rank, self.world, ch, self.epochs[ch], _lib.ptr(out), _lib.ptr(self.err),
+                     _lib.stream_ptr()), "sumsq_exchange")
+
+    def adamw_push(self, master_full: torch.Tensor, m, v, g, lo: int, n: int, *, lr, betas, eps, wd, step,
+                   gnorm_sq, inv_scale, max_norm, skipped_out) -> None:
+        """AdamW on [lo, lo+n) and push the new fp32 values into every rank's master buffer; the
+        trailing barrier makes them visible before anyone refreshes its compute copies."""
+        f = _lib.fn("dlti_adamw_push", [_V, _V, _V, _V, _L, _L, _I, _I, _F, _F, _F, _F, _F, _I, _V, _F, _F, _V, _V])
+        _lib.check(f(self.peer_array(master_full), _lib.ptr(m), _lib.ptr(v), _lib.ptr(g), lo, n, self.rank,
+                     self.world, lr, betas[0], betas[1], eps, wd, int(step), _lib.ptr(gnorm_sq),
+                     float(inv_scale), float(max_norm), _lib.ptr(skipped_out), _lib.stream_ptr()), "adamw_push")
+        self.barrier(4)
+
+    # ---- fused all-gather -> GEMM ----------------------------------------------------------------
+    def gather_spec(self, shard: torch.Tensor, staging: torch.Tensor) -> GatherSpec:
+        rows = shard.shape[0]
+        assert rows % 64 == 0, "fused gather needs rows_per_rank % 64 == 0"
+        n_units = rows * self.world // 64
+        counters = torch.zeros(n_units, dtype=torch.int32, device=self.info.device)
+        return GatherSpec(self.peer_ptrs(shard), staging, counters, rows, self.rank, self.world)

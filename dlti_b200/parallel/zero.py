@@ -139,6 +139,7 @@ class ZeroOptimizer:
             if self.stage >= 1:
                 comm.all_reduce_sum_(self.gnorm_sq, info)
         step = self.step_count + 1
+        pushed = False
         if self.offload:
             nsq = float(self.gnorm_sq.item())
             self.grad_host.copy_(g, non_blocking=False)
@@ -150,6 +151,15 @@ class ZeroOptimizer:
                              float(self.max_grad_norm), 0))
             if not skipped:
                 self.master_part().copy_(self.master_host, non_blocking=True)
+        elif self.fused is not None and self.world > 1 and self.stage >= 1:
+            # K9: AdamW on the owned slice, new values pushed into every peer's master buffer
+            self.fused.adamw_push(self.lora.master, self.m, self.v, g, self.lo, self.part, lr=lr,
+                                  betas=self.betas, eps=self.eps, wd=self.wd, step=step,
+                                  gnorm_sq=self.gnorm_sq, inv_scale=inv_scale,
+                                  max_norm=self.max_grad_norm, skipped_out=self.skipped_flag)
+            nsq, sk = torch.cat([self.gnorm_sq, self.skipped_flag.float()]).tolist()
+            skipped = bool(sk)
+            pushed = True
         else:
             r = O.adamw_step(self.master_part() if self.stage >= 1 else self.lora.master, self.m, self.v, g,
                              lr=lr, betas=self.betas, eps=self.eps, weight_decay=self.wd, step=step,
@@ -163,11 +173,8 @@ class ZeroOptimizer:
         g.zero_()
         if not skipped:
             self.step_count = step
-            if self.stage >= 1 and self.world > 1:
-                if self.fused is not None:
-                    self.fused.all_gather_master(self.lora.master, self.lo, self.part)
-                else:
-                    self._all_gather_master()
+            if self.stage >= 1 and self.world > 1 and not pushed:
+                self._all_gather_master()
             self.lora.refresh_compute()
         self.last_grad_norm = math.sqrt(nsq) * inv_scale if math.isfinite(nsq) else float("nan")
         return skipped, self.last_grad_norm

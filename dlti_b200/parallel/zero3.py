@@ -31,8 +31,9 @@ from .comm import DistInfo
 _MATS = ("w_qkv", "w_o", "w_gu", "w_down")
 
 
-def _rows_per_rank(rows: int, world: int) -> int:
-    return -(-rows // world)
+def _rows_per_rank(rows: int, world: int, align: int = 1) -> int:
+    rp = -(-rows // world)
+    return -(-rp // align) * align
 
 
 class Zero3Weights:
@@ -46,13 +47,15 @@ class Zero3Weights:
         self.shapes = {"w_qkv": (cfg.qkv_size, d), "w_o": (d, cfg.q_size), "w_gu": (2 * ff, d),
                        "w_down": (d, ff)}
         self.offload = ds.offload_param == "cpu"
+        # the fused gather works in 64-row units (one UMMA K block / a quarter N tile)
+        self.row_align = 64 if (fused is not None and not self.offload) else 1
         self.persist_thr = ds.stage3_param_persistence_threshold
         sdev = "cpu" if self.offload else self.device
         pin = self.offload and ds.pin_memory and torch.cuda.is_available()
         L = cfg.num_hidden_layers
 
         def shard_buf(rows, cols):
-            rp = _rows_per_rank(rows, self.world)
+            rp = _rows_per_rank(rows, self.world, self.row_align)
             if fused is not None and not self.offload:
                 return fused.alloc_symmetric((rp, cols), dtype)
             t = torch.zeros(rp, cols, dtype=dtype, device=sdev)
@@ -70,7 +73,7 @@ class Zero3Weights:
         self.n_slots = max(1, min(3, max_live // layer_elems)) if self.world > 1 else 0
         self.slots = []
         for _ in range(self.n_slots):
-            self.slots.append({m: torch.empty(_rows_per_rank(r, self.world) * self.world, c, dtype=dtype,
+            self.slots.append({m: torch.empty(_rows_per_rank(r, self.world, self.row_align) * self.world, c, dtype=dtype,
                                               device=self.device) for m, (r, c) in self.shapes.items()})
         self.slot_of: dict[int, int] = {}
         self.slot_free_event: list = [None] * self.n_slots

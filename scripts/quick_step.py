@@ -18,12 +18,12 @@ model = LoraLlama(cfg, w, lora, gradient_checkpointing=ckpt)
 torch.cuda.synchronize(); print("init s", time.time() - t0, "weights GB", w.nbytes() / 1e9, flush=True)
 ids = torch.randint(3, cfg.vocab_size, (B, S)); b = pack_batch(ids, ids.clone(), None).to("cuda")
 gs = torch.tensor([1.0 / b.n_valid], device="cuda")
-for i in range(3):
+for i in range(int(os.environ.get('WARM', 3))):
     loss = model.forward_backward(b, gs)
 torch.cuda.synchronize()
 _lib.reset_launch_count()
 s, e = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-n = 5
+n = int(os.environ.get('N', 5))
 s.record()
 for i in range(n):
     loss = model.forward_backward(b, gs)

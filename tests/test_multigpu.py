@@ -1,0 +1,21 @@
+"""Multi-GPU tier (needs >= 2 B200s): peer-memory kernels vs NCCL, fused vs nccl training backends."""
+import os
+import subprocess
+import sys
+
+import pytest
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+pytestmark = [pytest.mark.gpu, pytest.mark.multigpu]
+
+
+def test_fused_backend_two_gpus():
+    import torch
+
+    n = min(2, torch.cuda.device_count())
+    r = subprocess.run([sys.executable, "-m", "dlti_b200.launch", f"--num_gpus={n}", "--master_port=29731",
+                        "--no_local_rank", os.path.join(ROOT, "tests", "mp_fused_worker.py")],
+                       capture_output=True, text=True, timeout=900, cwd=ROOT,
+                       env=dict(os.environ, PYTHONPATH=ROOT))
+    print(r.stdout[-4000:])
+    assert r.returncode == 0 and "ALL MULTI-GPU CHECKS PASSED" in r.stdout, r.stdout[-3000:] + r.stderr[-3000:]

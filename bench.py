@@ -208,7 +208,8 @@ def main() -> None:
     e2e_ms = max_over_ranks(max(e2.elapsed_time(e3), wall_ms)) / a.steps
     clocks = sampler.stop() if sampler else None
     sync_all()
-    peak = max_over_ranks(torch.cuda.max_memory_allocated() / 1e9)
+    arena_gb = tr.fused.arena.total_bytes() / 1e9 if tr.fused is not None else 0.0   # symmetric arena is
+    peak = max_over_ranks(torch.cuda.max_memory_allocated() / 1e9 + arena_gb)         # outside torch's allocator
 
     if info.rank == 0:
         value = tokens_per_step / dev_ms * 1e3

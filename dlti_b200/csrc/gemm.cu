@@ -45,6 +45,27 @@ struct Cfg {
   static constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + BAR_BYTES + 1024;
 };
 
+// K1: all-gather fused into the GEMM. The B operand (a ZeRO-3 row-sharded weight) is consumed from
+// a local staging buffer that the SAME kernel fills: two extra "gather" warps per CTA pull 64-row
+// units (in 4-row chunks) from their owner ranks over NVLink (peer loads from the symmetric arena)
+// and bump a per-unit counter with a release; the TMA producer acquires the counters of the units
+// its next B tile needs before issuing the load. Tiles (NT) / K blocks (NN) are visited starting at
+// this rank's own rows, so the math on early tiles overlaps the transfer of later ones.
+constexpr int GATHER_CH = 16;              // chunks per 64-row unit (4 rows each)
+constexpr int GATHER_THREADS = 128;
+struct GatherParams {
+  const void* peer[16];     // each rank's shard base (peer-mapped); peer[rank] is the local shard
+  uint8_t* staging;         // local full matrix [world * rows_per_rank, row_bytes]
+  uint32_t* counters;       // [n_units] completed-chunk counters (monotonic across epochs)
+  int* err;                 // set to 1 on spin-wait timeout
+  long long row_bytes;
+  uint32_t target;          // unit complete  <=>  counters[u] >= target  (= epoch * GATHER_CH)
+  int rank, world;
+  int units_per_rank;       // rows_per_rank / 64
+  int n_units;
+  int local_direct;         // this rank's own rows are read straight from its shard (no staging copy)
+};
+
 struct GemmParams {
   int M, N;
   int nmb, nnb;           // tile counts
@@ -60,14 +81,35 @@ struct GemmParams {
   int vec_ok;      // 16-byte vector stores allowed
   float alpha;
   uint32_t idesc;
+  int n_rot, k_rot;   // GATHER: first N block / K block owned by this rank
 };
 
-template <int BN, bool A_MN, bool B_MN>
-__global__ void __launch_bounds__(NUM_THREADS, 1)
+__device__ __forceinline__ uint32_t ld_relaxed_gpu_u32(const uint32_t* p) {
+  uint32_t v;
+  asm volatile("ld.relaxed.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ void fence_acq_rel_gpu() { asm volatile("fence.acq_rel.gpu;" ::: "memory"); }
+
+__device__ __forceinline__ void gather_wait_unit(const GatherParams& g, int u) {
+  if (u >= g.n_units) return;
+  const long long t0 = clock64();
+  while ((int32_t)(ld_acquire_gpu_u32(g.counters + u) - g.target) < 0) {
+    if (clock64() - t0 > 20000000000LL) {
+      if (g.err) atomicExch(g.err, 1);
+      return;
+    }
+    __nanosleep(32);
+  }
+}
+
+template <int BN, bool A_MN, bool B_MN, bool GATHER>
+__global__ void __launch_bounds__(NUM_THREADS + (GATHER ? GATHER_THREADS : 0), 1)
 gemm_tcgen05_kernel(const GemmParams p, const __grid_constant__ CUtensorMap tmA,
                     const __grid_constant__ CUtensorMap tmB,
                     const __grid_constant__ CUtensorMap tmA2,
-                    const __grid_constant__ CUtensorMap tmB2) {
+                    const __grid_constant__ CUtensorMap tmB2,
+                    const __grid_constant__ CUtensorMap tmBL, const GatherParams gp) {
   using C_ = Cfg<BN>;
   extern __shared__ uint8_t smem_raw[];
   const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;
@@ -115,17 +157,50 @@ gemm_tcgen05_kernel(const GemmParams p, const __grid_constant__ CUtensorMap tmA,
 
   if (warp == 0) {
     // ===================== TMA producer =====================
+    bool all_ready = true;      // GATHER: every unit this kernel could need has already landed
+    if (GATHER) {
+      for (int u = lane; u < gp.n_units; u += 32) {
+        const bool mine = gp.local_direct && (u / gp.units_per_rank) == gp.rank;
+        if (!mine && (int32_t)(ld_relaxed_gpu_u32(gp.counters + u) - gp.target) < 0) all_ready = false;
+      }
+      all_ready = __all_sync(0xffffffffu, all_ready);
+      fence_acq_rel_gpu();
+      asm volatile("fence.proxy.async.global;" ::: "memory");
+    }
     if (lane == 0) {
       int stage = 0;
       uint32_t phase = 0;
       for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
         const int split = tile / tiles_mn;
         const int rem = tile - split * tiles_mn;
-        const int n_blk = rem / p.nmb;
+        int n_blk = rem / p.nmb;
         const int m_blk = rem - n_blk * p.nmb;
+        if (GATHER && !B_MN) n_blk = (n_blk + p.n_rot) % p.nnb;      // start at this rank's own rows
         const int m0 = m_blk * BM, n0 = n_blk * BN;
         const int kb0 = split * p.kb_per_split;
         const int kb1 = min(nkb_total, kb0 + p.kb_per_split);
+        bool b_local = false;       // B tile comes straight from this rank's shard
+        int b_row_off = 0;
+        const int lo_unit = GATHER ? gp.rank * gp.units_per_rank : 0;
+        const int hi_unit = GATHER ? lo_unit + gp.units_per_rank : 0;
+        if (GATHER) {
+          const int lo_row = gp.rank * gp.units_per_rank * 64;
+          b_row_off = lo_row;
+          if (!B_MN) {
+            b_local = gp.local_direct && n0 >= lo_row && n0 + BN <= lo_row + gp.units_per_rank * 64;
+            if (!b_local && !all_ready) {
+              uint32_t cv[BN / 64];
+#pragma unroll
+              for (int j = 0; j < BN / 64; ++j)      // independent relaxed loads, in flight together
+                cv[j] = (n0 / 64 + j < gp.n_units) ? ld_relaxed_gpu_u32(gp.counters + n0 / 64 + j) : gp.target;
+#pragma unroll
+              for (int j = 0; j < BN / 64; ++j)
+                if ((int32_t)(cv[j] - gp.target) < 0) gather_wait_unit(gp, n0 / 64 + j);
+              fence_acq_rel_gpu();
+              asm volatile("fence.proxy.async.global;" ::: "memory");
+            }
+          }
+        }
         for (int kb = kb0; kb < kb1; ++kb) {
           mbar_wait(empty_bar(stage), phase ^ 1u);
           const uint32_t sa = smem_base + stage * C_::STAGE_BYTES;
@@ -135,14 +210,33 @@ gemm_tcgen05_kernel(const GemmParams p, const __grid_constant__ CUtensorMap tmA,
           const bool ext = kb >= p.nkb_main;
           const CUtensorMap* ma = ext ? &tmA2 : &tmA;
           const CUtensorMap* mb = ext ? &tmB2 : &tmB;
-          const int k0 = (ext ? kb - p.nkb_main : kb) * BK;
+          int kb_eff = ext ? kb - p.nkb_main : kb;
+          if (GATHER && B_MN && !ext) {
+            // contraction starts at this rank's own rows; no div/mod here: the producer thread's
+            // per-stage budget is only ~500 cycles
+            kb_eff = kb + p.k_rot;
+            if (kb_eff >= p.nkb_main) kb_eff -= p.nkb_main;
+            b_local = gp.local_direct && kb_eff >= lo_unit && kb_eff < hi_unit;
+            if (!b_local && !all_ready) {
+              gather_wait_unit(gp, kb_eff);
+              asm volatile("fence.proxy.async.global;" ::: "memory");
+            }
+          }
+          const int k0 = kb_eff * BK;
           if constexpr (!A_MN) {
             tma_load_2d(sa, ma, fb, k0, m0);
           } else {
 #pragma unroll
             for (int j = 0; j < BM / 64; ++j) tma_load_2d(sa + j * (BK * 128), ma, fb, m0 + 64 * j, k0);
           }
-          if constexpr (!B_MN) {
+          if (GATHER && b_local && !ext) {
+            if constexpr (!B_MN) {
+              tma_load_2d(sb, &tmBL, fb, k0, n0 - b_row_off);
+            } else {
+#pragma unroll
+              for (int j = 0; j < BN / 64; ++j) tma_load_2d(sb + j * (BK * 128), &tmBL, fb, n0 + 64 * j, k0 - b_row_off);
+            }
+          } else if constexpr (!B_MN) {
             tma_load_2d(sb, mb, fb, k0, n0);
           } else {
 #pragma unroll
@@ -187,6 +281,35 @@ gemm_tcgen05_kernel(const GemmParams p, const __grid_constant__ CUtensorMap tmA,
         if (++acc == 2) { acc = 0; acc_phase ^= 1u; }
       }
     }
+  } else if (GATHER && warp >= 6) {
+    // ===================== gather warps: pull weight units from their owners ==================
+    const int gt = threadIdx.x - NUM_THREADS;                  // 0..127
+    const long long chunk_bytes = 4 * gp.row_bytes;            // 4 rows
+    const long long unit_bytes = 64 * gp.row_bytes;
+    const int skip = gp.local_direct ? gp.units_per_rank : 0;  // own rows are read in place
+    const int total_chunks = (gp.n_units - skip) * GATHER_CH;
+    for (int c = blockIdx.x; c < total_chunks; c += gridDim.x) {
+      const int j = c / GATHER_CH + skip, part = c % GATHER_CH;
+      const int u = (gp.rank * gp.units_per_rank + j) % gp.n_units;   // needed-first order
+      if ((int32_t)(ld_acquire_gpu_u32(gp.counters + u) - gp.target) >= 0) continue;  // landed earlier this epoch
+      const int owner = u / gp.units_per_rank;
+      const uint8_t* src = reinterpret_cast<const uint8_t*>(gp.peer[owner]) +
+                           (long long)(u - owner * gp.units_per_rank) * unit_bytes + part * chunk_bytes;
+      uint8_t* dst = gp.staging + (long long)u * unit_bytes + part * chunk_bytes;
+      const long long nvec = chunk_bytes >> 4;
+      long long i = gt;
+      for (; i + 7 * GATHER_THREADS < nvec; i += 8 * GATHER_THREADS) {
+        int4 v[8];
+#pragma unroll
+        for (int q = 0; q < 8; ++q) v[q] = ld_nc_v4(src + ((i + q * GATHER_THREADS) << 4));
+#pragma unroll
+        for (int q = 0; q < 8; ++q) st_v4(dst + ((i + q * GATHER_THREADS) << 4), v[q]);
+      }
+      for (; i < nvec; i += GATHER_THREADS) st_v4(dst + (i << 4), ld_nc_v4(src + (i << 4)));
+      __threadfence();
+      asm volatile("bar.sync 2, 128;" ::: "memory");
+      if (gt == 0) red_release_gpu_add_u32(gp.counters + u, 1u);
+    }
   } else {
     // ===================== epilogue (4 warps; warp w owns TMEM lanes 32*(w%4)..) =============
     const int quarter = warp & 3;
@@ -195,8 +318,9 @@ gemm_tcgen05_kernel(const GemmParams p, const __grid_constant__ CUtensorMap tmA,
     for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
       const int split = tile / tiles_mn;
       const int rem = tile - split * tiles_mn;
-      const int n_blk = rem / p.nmb;
+      int n_blk = rem / p.nmb;
       const int m_blk = rem - n_blk * p.nmb;
+      if (GATHER && !B_MN) n_blk = (n_blk + p.n_rot) % p.nnb;
       const int row = m_blk * BM + quarter * 32 + lane;
       const int n0 = n_blk * BN;
       mbar_wait(tfull_bar(acc), acc_phase);
@@ -336,32 +460,34 @@ int get_tmap(CUtensorMap* out, const void* base, uint64_t inner, uint64_t outer,
   return 0;
 }
 
-template <int BN, bool A_MN, bool B_MN>
+template <int BN, bool A_MN, bool B_MN, bool GATHER>
 int launch(const GemmParams& p, const CUtensorMap& a, const CUtensorMap& b, const CUtensorMap& a2,
-           const CUtensorMap& b2, int grid, cudaStream_t stream) {
+           const CUtensorMap& b2, const CUtensorMap& bl, const GatherParams& gp, int grid,
+           cudaStream_t stream) {
   using C_ = Cfg<BN>;
   static bool configured[64] = {false};
   int dev = 0;
   cudaGetDevice(&dev);
   if (!configured[dev & 63]) {
-    DLTI_CUDA_CHECK(cudaFuncSetAttribute(gemm_tcgen05_kernel<BN, A_MN, B_MN>,
+    DLTI_CUDA_CHECK(cudaFuncSetAttribute(gemm_tcgen05_kernel<BN, A_MN, B_MN, GATHER>,
                                          cudaFuncAttributeMaxDynamicSharedMemorySize,
                                          C_::SMEM_BYTES));
     configured[dev & 63] = true;
   }
-  gemm_tcgen05_kernel<BN, A_MN, B_MN><<<grid, NUM_THREADS, C_::SMEM_BYTES, stream>>>(p, a, b, a2, b2);
+  gemm_tcgen05_kernel<BN, A_MN, B_MN, GATHER>
+      <<<grid, NUM_THREADS + (GATHER ? GATHER_THREADS : 0), C_::SMEM_BYTES, stream>>>(p, a, b, a2, b2, bl, gp);
   dlti_count_launch();
   return (int)cudaGetLastError();
 }
 
 }  // namespace
 
-// See include/dlti_b200.h for the contract.
-DLTI_API int dlti_gemm(const void* A, const void* B, void* C, const void* R, int M, int N, int K,
-                       long long lda, long long ldb, long long ldc, long long ldr, int a_mn,
-                       int b_mn, const void* A2, const void* B2, int K2, long long lda2,
-                       long long ldb2, int in_dtype, int out_dtype, float alpha, int accumulate,
-                       int split_k, int block_n, int max_ctas, cudaStream_t stream) {
+static int gemm_impl(const void* A, const void* B, void* C, const void* R, int M, int N, int K,
+                     long long lda, long long ldb, long long ldc, long long ldr, int a_mn,
+                     int b_mn, const void* A2, const void* B2, int K2, long long lda2,
+                     long long ldb2, int in_dtype, int out_dtype, float alpha, int accumulate,
+                     int split_k, int block_n, int max_ctas, cudaStream_t stream,
+                     const GatherParams* gather) {
   if (M <= 0 || N <= 0 || K < 0 || (K == 0 && K2 == 0)) return DLTI_ERR_BAD_ARG;
   if (in_dtype != DLTI_BF16 && in_dtype != DLTI_FP16) return DLTI_ERR_UNSUPPORTED;
   if (K2 % BK) { dlti_set_error("K2 must be a multiple of 64"); return DLTI_ERR_BAD_ARG; }
@@ -396,6 +522,13 @@ DLTI_API int dlti_gemm(const void* A, const void* B, void* C, const void* R, int
              (!R || (((reinterpret_cast<uintptr_t>(R) & 15) == 0) && ((ldr * 2) % 16 == 0)));
   p.alpha = alpha;
   p.idesc = umma_idesc_f16(in_dtype, BM, bn, a_mn != 0, b_mn != 0);
+  GatherParams gp{};
+  if (gather) {
+    if (a_mn || p.split_k != 1) { dlti_set_error("gather GEMM: A must be K-major and split_k = 1"); return DLTI_ERR_UNSUPPORTED; }
+    gp = *gather;
+    p.n_rot = (int)(((long long)gp.rank * gp.units_per_rank * 64) / bn) % p.nnb;
+    p.k_rot = (gp.rank * gp.units_per_rank) % (p.nkb_main > 0 ? p.nkb_main : 1);
+  }
 
   CUtensorMap ta, tb, ta2, tb2;
   int rc;
@@ -415,14 +548,31 @@ DLTI_API int dlti_gemm(const void* A, const void* B, void* C, const void* R, int
     ta2 = ta; tb2 = tb;
   }
 
+  CUtensorMap tbl = tb;
+  if (gather) {
+    const long long rpr = (long long)gp.units_per_rank * 64;
+    gp.local_direct = (b_mn || (rpr % bn) == 0) ? 1 : 0;
+    if (gp.local_direct) {
+      const void* lsh = gp.peer[gp.rank];
+      rc = b_mn ? get_tmap(&tbl, lsh, N, rpr, ldb, 64, 64) : get_tmap(&tbl, lsh, K, rpr, ldb, 64, bn);
+      if (rc) return rc;
+    }
+  }
   const int total = p.nmb * p.nnb * p.split_k;
   int grid = dlti_num_sms();
   if (max_ctas > 0 && max_ctas < grid) grid = max_ctas;
   if (total < grid) grid = total;
 
+  if (gather) {
+    if (bn == 256 && !b_mn) return launch<256, false, false, true>(p, ta, tb, ta2, tb2, tbl, gp, grid, stream);
+    if (bn == 128 && !b_mn) return launch<128, false, false, true>(p, ta, tb, ta2, tb2, tbl, gp, grid, stream);
+    if (bn == 256 && b_mn) return launch<256, false, true, true>(p, ta, tb, ta2, tb2, tbl, gp, grid, stream);
+    if (bn == 128 && b_mn) return launch<128, false, true, true>(p, ta, tb, ta2, tb2, tbl, gp, grid, stream);
+    return DLTI_ERR_UNSUPPORTED;
+  }
 #define DLTI_GEMM_CASE(BN_, AM_, BM_) \
   if (bn == BN_ && (a_mn != 0) == AM_ && (b_mn != 0) == BM_) \
-    return launch<BN_, AM_, BM_>(p, ta, tb, ta2, tb2, grid, stream);
+    return launch<BN_, AM_, BM_, false>(p, ta, tb, ta2, tb2, tbl, gp, grid, stream);
   DLTI_GEMM_CASE(256, false, false)
   DLTI_GEMM_CASE(128, false, false)
   DLTI_GEMM_CASE(64, false, false)
@@ -433,4 +583,41 @@ DLTI_API int dlti_gemm(const void* A, const void* B, void* C, const void* R, int
   DLTI_GEMM_CASE(64, true, true)
 #undef DLTI_GEMM_CASE
   return DLTI_ERR_UNSUPPORTED;
+}
+
+// See include/dlti_b200.h for the contract.
+DLTI_API int dlti_gemm(const void* A, const void* B, void* C, const void* R, int M, int N, int K,
+                       long long lda, long long ldb, long long ldc, long long ldr, int a_mn,
+                       int b_mn, const void* A2, const void* B2, int K2, long long lda2,
+                       long long ldb2, int in_dtype, int out_dtype, float alpha, int accumulate,
+                       int split_k, int block_n, int max_ctas, cudaStream_t stream) {
+  return gemm_impl(A, B, C, R, M, N, K, lda, ldb, ldc, ldr, a_mn, b_mn, A2, B2, K2, lda2, ldb2, in_dtype,
+                   out_dtype, alpha, accumulate, split_k, block_n, max_ctas, stream, nullptr);
+}
+
+// K1: same GEMM, with the B operand (a row-sharded weight [world*rows_per_rank, ldb]) gathered from
+// its owner ranks by the kernel itself while it computes. B must be the local staging buffer; peer_
+// shards[r] is rank r's shard base in the symmetric arena; counters = u32[world*rows_per_rank/64]
+// (zero-initialised once, then monotonic); epoch must increase each time the staging is to be
+// refilled (same epoch => units already landed are reused: forward recompute -> backward).
+DLTI_API int dlti_gemm_gather(const void* A, void* B_staging, void* C, const void* R, int M, int N, int K,
+                              long long lda, long long ldb, long long ldc, long long ldr, int b_mn,
+                              const void* A2, const void* B2, int K2, long long lda2, long long ldb2,
+                              int in_dtype, int out_dtype, float alpha, int block_n, int max_ctas,
+                              const void* const* peer_shards, unsigned int* counters, unsigned int epoch,
+                              int rank, int world, int rows_per_rank, int* err_flag, cudaStream_t stream) {
+  if (world < 1 || world > 16 || rows_per_rank % 64 || !counters) return DLTI_ERR_BAD_ARG;
+  GatherParams g{};
+  for (int i = 0; i < world; ++i) g.peer[i] = peer_shards[i];
+  g.staging = reinterpret_cast<uint8_t*>(B_staging);
+  g.counters = counters;
+  g.err = err_flag;
+  g.row_bytes = ldb * 2;
+  g.target = epoch * (unsigned)GATHER_CH;
+  g.rank = rank; g.world = world;
+  g.units_per_rank = rows_per_rank / 64;
+  g.n_units = g.units_per_rank * world;
+  if ((g.row_bytes * 4) % 16) return DLTI_ERR_BAD_ARG;
+  return gemm_impl(A, B_staging, C, R, M, N, K, lda, ldb, ldc, ldr, 0, b_mn, A2, B2, K2, lda2, ldb2,
+                   in_dtype, out_dtype, alpha, 0, 1, block_n, max_ctas, stream, &g);
 }

@@ -156,20 +156,26 @@ class Trainer:
         if timed:
             e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
             e0.record()
-        loss_sum = None
         ga = len(packed)
-        for k, pb in enumerate(packed):
-            if self.args.loss_norm == "microbatch":
-                scale = self.scaler.cur_scale / (max(1, pb.n_valid) * ga * info.world_size)
+        on_gpu = dev.type == "cuda"
+        if self.args.loss_norm == "microbatch":
+            scales = [self.scaler.cur_scale / (max(1, pb.n_valid) * ga * info.world_size) for pb in packed]
+        else:
+            scales = [self.scaler.cur_scale / n_total] * ga
+        if on_gpu:
+            if len(set(scales)) == 1:
+                self.gscale.fill_(scales[0])
+                gs = [self.gscale] * ga
             else:
-                scale = self.scaler.cur_scale / n_total
-            self.gscale.fill_(scale)
-            pbd = pb.to(dev) if dev.type == "cuda" else pb
-            opt.wait_reduce()
-            ls = self.model.forward_backward(pbd, self.gscale if dev.type == "cuda" else scale)
-            loss_sum = ls if loss_sum is None else loss_sum + ls
-            opt.on_micro_batch_end(is_boundary=(k == ga - 1))
-            self.tokens_seen += pb.n_tokens
+                gs = [torch.full((1,), sc, dtype=torch.float32, device=dev) for sc in scales]
+        else:
+            gs = scales
+        devb = [pb.to(dev) if on_gpu else pb for pb in packed]
+        opt.wait_reduce()
+        # the whole accumulation window in one layer-major pass (one ZeRO-3 gather per layer per pass)
+        loss_sum = self.model.forward_backward_multi(devb, gs)
+        opt.on_micro_batch_end(is_boundary=True)
+        self.tokens_seen += sum(pb.n_tokens for pb in packed)
         lr = self.scheduler.get_lr()
         skipped, gnorm = opt.step(lr)
         self.scaler.update(skipped)
@@ -265,6 +271,8 @@ class Trainer:
         info = self.info
         ms = sum(self.step_ms) / max(1, len(self.step_ms)) if self.step_ms else 0.0
         peak = torch.cuda.max_memory_allocated() / 1e9 if info.device.type == "cuda" else 0.0
+        if self.fused is not None and self.fused.arena.mode == "symm":
+            peak += self.fused.arena.total_bytes() / 1e9    # VMM arena is invisible to torch's allocator (D27)
         t = torch.tensor([ms, peak, float(self.tokens_seen)], dtype=torch.float64)
         if info.distributed:
             import torch.distributed as dist

@@ -53,7 +53,9 @@ def gemm(a: torch.Tensor, b: torch.Tensor, *, a_mn: bool = False, b_mn: bool = F
          a2: torch.Tensor | None = None, b2: torch.Tensor | None = None,
          residual: torch.Tensor | None = None, out: torch.Tensor | None = None,
          out_dtype: torch.dtype | None = None, alpha: float = 1.0, accumulate: bool = False,
-         split_k: int = 1, block_n: int = 0, max_ctas: int = 0) -> torch.Tensor:
+         split_k: int = 1, block_n: int = 0, max_ctas: int = 0, gather=None) -> torch.Tensor:
+    """gather: optional parallel.fused.GatherSpec — `b` is then the local staging buffer of a row-
+    sharded weight and the kernel pulls the shards from their owner ranks while it computes (K1)."""
     if not _lib.use_native(a, b):
         return gemm_ref(a, b, a_mn=a_mn, b_mn=b_mn, a2=a2, b2=b2, residual=residual, out=out,
                         out_dtype=out_dtype, alpha=alpha, accumulate=accumulate)
@@ -73,6 +75,24 @@ def gemm(a: torch.Tensor, b: torch.Tensor, *, a_mn: bool = False, b_mn: bool = F
     assert out.shape == (M, N) and out.stride(1) == 1 and out.dtype == out_dtype
     if residual is not None:
         assert residual.shape == (M, N) and residual.stride(1) == 1 and residual.dtype == out.dtype
+    if gather is not None:
+        assert not a_mn and not accumulate and split_k == 1
+        assert b.data_ptr() == gather.staging.data_ptr() and b.stride(0) == gather.staging.stride(0)
+        f = _lib.fn("dlti_gemm_gather", [
+            C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int,
+            C.c_longlong, C.c_longlong, C.c_longlong, C.c_longlong, C.c_int,
+            C.c_void_p, C.c_void_p, C.c_int, C.c_longlong, C.c_longlong,
+            C.c_int, C.c_int, C.c_float, C.c_int, C.c_int,
+            C.c_void_p, C.c_void_p, C.c_uint, C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_void_p])
+        rc = f(_lib.ptr(a), _lib.ptr(b), _lib.ptr(out), _lib.ptr(residual), M, N, K,
+               a.stride(0), b.stride(0), out.stride(0), residual.stride(0) if residual is not None else 0,
+               int(b_mn), _lib.ptr(a2), _lib.ptr(b2), K2,
+               a2.stride(0) if a2 is not None else 0, b2.stride(0) if b2 is not None else 0,
+               _lib.dtype_code(a.dtype), _lib.dtype_code(out_dtype), float(alpha), int(block_n), int(max_ctas),
+               gather.peer_arr, _lib.ptr(gather.counters), int(gather.epoch), gather.rank, gather.world,
+               gather.rows_per_rank, _lib.ptr(gather.err), _lib.stream_ptr())
+        _lib.check(rc, "dlti_gemm_gather")
+        return out
     rc = _gemm_fn()(
         _lib.ptr(a), _lib.ptr(b), _lib.ptr(out), _lib.ptr(residual), M, N, K,
         a.stride(0), b.stride(0), out.stride(0), residual.stride(0) if residual is not None else 0,

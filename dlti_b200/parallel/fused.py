@@ -116,9 +116,9 @@ class GatherSpec:
     """Arguments of the fused all-gather -> GEMM kernel for one row-sharded weight matrix."""
 
     def __init__(self, peer_ptrs, staging: torch.Tensor, counters: torch.Tensor, rows_per_rank: int,
-                 rank: int, world: int):
+                 rank: int, world: int, err: torch.Tensor):
         self.peer_arr = (C.c_void_p * MAX_RANKS)(*peer_ptrs, *([None] * (MAX_RANKS - len(peer_ptrs))))
-        self.staging, self.counters = staging, counters
+        self.staging, self.counters, self.err = staging, counters, err
         self.rows_per_rank, self.rank, self.world = rows_per_rank, rank, world
         self.epoch = 0
 
@@ -219,9 +219,10 @@ class FusedComm:
         self.barrier(4)
 
     # ---- fused all-gather -> GEMM ----------------------------------------------------------------
-    def gather_spec(self, shard: torch.Tensor, staging: torch.Tensor) -> GatherSpec:
+    def gather_spec(self, shard: torch.Tensor, staging: torch.Tensor, counters: torch.Tensor) -> GatherSpec:
+        """counters: int32[world*rows/64], zero-initialised once and shared by every shard that is
+        gathered into the same staging buffer (epochs keep growing)."""
         rows = shard.shape[0]
         assert rows % 64 == 0, "fused gather needs rows_per_rank % 64 == 0"
-        n_units = rows * self.world // 64
-        counters = torch.zeros(n_units, dtype=torch.int32, device=self.info.device)
-        return GatherSpec(self.peer_ptrs(shard), staging, counters, rows, self.rank, self.world)
+        assert counters.numel() == rows * self.world // 64
+        return GatherSpec(self.peer_ptrs(shard), staging, counters, rows, self.rank, self.world, self.err)

@@ -80,6 +80,18 @@ class Zero3Weights:
         self.slot_ready_event: list = [None] * self.n_slots
         self.free_slots = list(range(self.n_slots))
         self.stream = torch.cuda.Stream(device=self.device) if self.device.type == "cuda" and self.world > 1 else None
+        # K1 mode: one staging buffer per matrix kind, filled by the consuming GEMM kernel itself
+        self.in_gemm_gather = fused is not None and not self.offload and self.world > 1
+        if self.in_gemm_gather:
+            self.slots, self.n_slots, self.free_slots = [], 0, []
+            self.staging, self.counters, self.epoch, self.specs = {}, {}, {}, []
+            for m, (r, c) in self.shapes.items():
+                rp = _rows_per_rank(r, self.world, self.row_align)
+                self.staging[m] = torch.empty(rp * self.world, c, dtype=dtype, device=self.device)
+                self.counters[m] = torch.zeros(rp * self.world // 64, dtype=torch.int32, device=self.device)
+                self.epoch[m] = 0
+            for sh in self.layer_shards:
+                self.specs.append({m: fused.gather_spec(sh[m], self.staging[m], self.counters[m]) for m in _MATS})
         self._big = {}          # gathered embed / lm_head staging (allocated on demand)
         self._h2d = {}          # offload: device copies of this rank's shards while in flight
         self.gather_bytes = 0   # bytes received from peers (for roofline reports)
@@ -177,13 +189,13 @@ class Zero3Weights:
     def _gather(self, key, shard: torch.Tensor, out: torch.Tensor) -> None:
         src = self._device_shard(key, shard)
         if self.fused is not None and not self.offload:
-            self.fused.all_gather_rows(shard, out)
+            self.fused.all_gather_rows(shard, out, blocks_per_peer=max(8, 96 // self.world))
         else:
             comm.all_gather_into(out.view(-1), src.reshape(-1), self.info)
         self.gather_bytes += out.numel() * out.element_size() * (self.world - 1) // self.world
 
     def prefetch(self, i: int) -> None:
-        if self.world == 1 or i in self.slot_of or i < 0 or i >= self.cfg.num_hidden_layers:
+        if self.world == 1 or self.in_gemm_gather or i in self.slot_of or i < 0 or i >= self.cfg.num_hidden_layers:
             return
         if not self.free_slots:
             return                                   # window full (stage3_max_live_parameters)
@@ -209,6 +221,21 @@ class Zero3Weights:
             dev = (lambda t: t.to(self.device, non_blocking=True)) if self.offload else (lambda t: t)
             r = {m: dev(sh[m])[: self.shapes[m][0]] for m in _MATS}
             return LayerWeights(r["w_qkv"], r["w_o"], r["w_gu"], r["w_down"], *self.norms[i])
+        if self.in_gemm_gather:
+            # every call starts a new epoch: the first GEMM that touches a matrix pulls it from the
+            # owner ranks tile by tile; later GEMMs of the same call (recompute -> backward) reuse it
+            g = {}
+            for m in _MATS:
+                self.epoch[m] += 1
+                sp = self.specs[i][m]
+                sp.epoch = self.epoch[m]
+                g[m] = sp
+                rows = self.staging[m].shape[0]
+                self.gather_bytes += rows * self.shapes[m][1] * 2 * (self.world - 1) // self.world
+            st = self.staging
+            return LayerWeights(st["w_qkv"][: self.shapes["w_qkv"][0]], st["w_o"][: self.shapes["w_o"][0]],
+                                st["w_gu"][: self.shapes["w_gu"][0]], st["w_down"][: self.shapes["w_down"][0]],
+                                *self.norms[i], gather=g)
         if i not in self.slot_of:
             self.prefetch(i)
             if i not in self.slot_of:
@@ -221,7 +248,7 @@ class Zero3Weights:
         return LayerWeights(r["w_qkv"], r["w_o"], r["w_gu"], r["w_down"], *self.norms[i])
 
     def release(self, i: int) -> None:
-        if self.world == 1 or i not in self.slot_of:
+        if self.world == 1 or self.in_gemm_gather or i not in self.slot_of:
             return
         s = self.slot_of.pop(i)
         if self.stream is not None:

@@ -95,6 +95,38 @@ def main():
     check("adamw_push: all ranks hold the updated full master", torch.allclose(master, ref_full, rtol=1e-5, atol=1e-6))
     fc.check_error()
 
+    # K1: all-gather fused into the GEMM (NT and NN forms) vs a plain GEMM on the NCCL-gathered weight
+    from dlti_b200.ops.gemm import gemm, gemm_ref
+    rp, K, M = 256, 512, 384
+    wshard = fc.alloc_symmetric((rp, K), torch.bfloat16)
+    wshard.copy_(torch.randn(rp, K, device=dev))
+    torch.cuda.synchronize(); dist.barrier()
+    wfull = torch.empty(world * rp, K, dtype=torch.bfloat16, device=dev)
+    dist.all_gather_into_tensor(wfull, wshard.contiguous())
+    staging = torch.zeros(world * rp, K, dtype=torch.bfloat16, device=dev)
+    counters = torch.zeros(world * rp // 64, dtype=torch.int32, device=dev)
+    spec = fc.gather_spec(wshard, staging, counters)
+    x = torch.randn(M, K, device=dev, dtype=torch.bfloat16)
+    spec.epoch = 1
+    y = gemm(x, staging, gather=spec)                       # NT: pulls while computing
+    yr = gemm(x, wfull)
+    torch.cuda.synchronize()
+    remote = torch.ones(world * rp, dtype=torch.bool, device=dev)
+    remote[rank * rp:(rank + 1) * rp] = False          # own rows are read in place, never staged
+    check("gather-GEMM NT == GEMM on gathered weight", torch.equal(y, yr) and torch.equal(staging[remote], wfull[remote]))
+    dy = torch.randn(M, world * rp, device=dev, dtype=torch.bfloat16)
+    dx = gemm(dy, staging, b_mn=True, gather=spec)          # same epoch: staging reused, no pull
+    dxr = gemm_ref(dy, wfull, b_mn=True, out_dtype=torch.float32)
+    torch.cuda.synchronize()
+    check("gather-GEMM NN (reuse epoch)", ((dx.float() - dxr).abs().max() / dxr.abs().max()).item() < 2e-2)
+    staging.zero_()
+    spec.epoch = 2
+    dx2 = gemm(dy, staging, b_mn=True, gather=spec)         # NN form pulling K blocks
+    torch.cuda.synchronize()
+    check("gather-GEMM NN (fresh epoch)", torch.equal(staging[remote], wfull[remote]) and
+          ((dx2.float() - dxr).abs().max() / dxr.abs().max()).item() < 2e-2)
+    fc.check_error()
+
     # training: fused vs nccl backends give the same losses (ZeRO-3 and ZeRO-2)
     from tests.test_trainer_gpu_common import run_short
     for stage in (3, 2):

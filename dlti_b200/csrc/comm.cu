@@ -52,6 +52,23 @@ __global__ void peer_barrier_kernel(Peers pads, int rank, int world, int channel
   }
 }
 
+// Same barrier with the epoch kept in device memory (incremented by the kernel itself), so the launch
+// carries no per-call host value and can be replayed from a CUDA graph. All ranks execute the same
+// sequence of barriers on a channel, so their counters advance in lockstep.
+__global__ void peer_barrier_auto_kernel(Peers pads, int rank, int world, int channel, uint32_t* counter,
+                                         int* err) {
+  __shared__ uint32_t s_epoch;
+  if (threadIdx.x == 0) s_epoch = atomicAdd(counter, 1u) + 1u;
+  __syncthreads();
+  const uint32_t epoch = s_epoch;
+  const int t = threadIdx.x;
+  if (t < world) {
+    __threadfence_system();
+    st_release_sys_u32(reinterpret_cast<uint32_t*>(pads.p[t]) + channel * MAX_RANKS + rank, epoch);
+    wait_ge_sys(reinterpret_cast<const uint32_t*>(pads.p[rank]) + channel * MAX_RANKS + t, epoch, err);
+  }
+}
+
 // out[r * shard_bytes ...] <- shard of rank r, 16-byte vectors, 4 loads in flight per thread.
 // grid = (blocks_per_peer, world). Weights are immutable during a step: non-coherent loads.
 __global__ void __launch_bounds__(256) allgather_rows_kernel(Peers shards, uint8_t* __restrict__ out,
@@ -145,6 +162,71 @@ __global__ void __launch_bounds__(256) adamw_push_kernel(Peers masters, float* _
   }
 }
 
+// K10/K11 consumer: residual[row] += sum_{r < world} recv[r][row]  (fp32, fixed rank order => every
+// rank computes bit-identical sums), then y[row] = w * T(residual * rstd). One CTA per token row.
+template <typename T, int VPT>
+__global__ void __launch_bounds__(128) tp_reduce_add_norm_kernel(const T* __restrict__ recv, long long slot_stride,
+                                                                int world, T* __restrict__ residual,
+                                                                const T* __restrict__ w, T* __restrict__ y,
+                                                                int d, float eps) {
+  __shared__ float red[32];
+  const long long row = blockIdx.x;
+  const int nvec = d >> 3;
+  float f[VPT][8];
+  float ss = 0.f;
+#pragma unroll
+  for (int i = 0; i < VPT; ++i) {
+    const int v = threadIdx.x + i * 128;
+    if (v < nvec) {
+      {
+        const int4 rv = reinterpret_cast<const int4*>(residual + row * d)[v];
+        const uint32_t* u = reinterpret_cast<const uint32_t*>(&rv);
+#pragma unroll
+        for (int j = 0; j < 4; ++j) { float2 t = Cvt<T>::unpack2(u[j]); f[i][2 * j] = t.x; f[i][2 * j + 1] = t.y; }
+      }
+      for (int r = 0; r < world; ++r) {
+        const int4 pv = reinterpret_cast<const int4*>(recv + r * slot_stride + row * d)[v];
+        const uint32_t* u = reinterpret_cast<const uint32_t*>(&pv);
+#pragma unroll
+        for (int j = 0; j < 4; ++j) { float2 t = Cvt<T>::unpack2(u[j]); f[i][2 * j] += t.x; f[i][2 * j + 1] += t.y; }
+      }
+      int4 sv;
+      uint32_t* su = reinterpret_cast<uint32_t*>(&sv);
+#pragma unroll
+      for (int j = 0; j < 4; ++j) su[j] = Cvt<T>::pack2(f[i][2 * j], f[i][2 * j + 1]);
+      reinterpret_cast<int4*>(residual + row * d)[v] = sv;
+#pragma unroll
+      for (int j = 0; j < 4; ++j) { float2 t = Cvt<T>::unpack2(su[j]); f[i][2 * j] = t.x; f[i][2 * j + 1] = t.y; }
+#pragma unroll
+      for (int j = 0; j < 8; ++j) ss += f[i][j] * f[i][j];
+    }
+  }
+  ss = warp_sum(ss);
+  if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = ss;
+  __syncthreads();
+  float tot = (threadIdx.x & 31) < 4 ? red[threadIdx.x & 31] : 0.f;
+  tot = warp_sum(tot);
+  const float rstd = rsqrtf(tot / (float)d + eps);
+#pragma unroll
+  for (int i = 0; i < VPT; ++i) {
+    const int v = threadIdx.x + i * 128;
+    if (v < nvec) {
+      const int4 wv = reinterpret_cast<const int4*>(w)[v];
+      const uint32_t* wu = reinterpret_cast<const uint32_t*>(&wv);
+      int4 ov;
+      uint32_t* ou = reinterpret_cast<uint32_t*>(&ov);
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        float2 wf = Cvt<T>::unpack2(wu[j]);
+        const float a = wf.x * Cvt<T>::to_f(Cvt<T>::from_f(f[i][2 * j] * rstd));
+        const float b = wf.y * Cvt<T>::to_f(Cvt<T>::from_f(f[i][2 * j + 1] * rstd));
+        ou[j] = Cvt<T>::pack2(a, b);
+      }
+      reinterpret_cast<int4*>(y + row * d)[v] = ov;
+    }
+  }
+}
+
 int fill(Peers& P, const void* const* ptrs, int world) {
   if (world < 1 || world > MAX_RANKS) return DLTI_ERR_BAD_ARG;
   for (int i = 0; i < MAX_RANKS; ++i) P.p[i] = i < world ? const_cast<void*>(ptrs[i]) : nullptr;
@@ -160,6 +242,15 @@ DLTI_API int dlti_peer_barrier(const void* const* signal_pads, int rank, int wor
   Peers P;
   if (int rc = fill(P, signal_pads, world)) return rc;
   peer_barrier_kernel<<<1, 32, 0, st>>>(P, rank, world, channel, epoch, err_flag);
+  dlti_count_launch();
+  return (int)cudaGetLastError();
+}
+
+DLTI_API int dlti_peer_barrier_auto(const void* const* signal_pads, int rank, int world, int channel,
+                                    unsigned int* device_counter, int* err_flag, cudaStream_t st) {
+  Peers P;
+  if (int rc = fill(P, signal_pads, world)) return rc;
+  peer_barrier_auto_kernel<<<1, 32, 0, st>>>(P, rank, world, channel, device_counter, err_flag);
   dlti_count_launch();
   return (int)cudaGetLastError();
 }
@@ -213,6 +304,25 @@ DLTI_API int dlti_adamw_push(const void* const* masters, float* m, float* v, flo
   adamw_push_kernel<<<(unsigned)(want > cap ? cap : want), 256, 0, st>>>(
       P, m, v, g, lo, n, rank, world, lr, b1, b2, eps, wd, bc1, bc2, gnorm_sq, inv_scale, max_norm,
       skipped_out);
+  dlti_count_launch();
+  return (int)cudaGetLastError();
+}
+
+DLTI_API int dlti_tp_reduce_add_norm(const void* recv, long long slot_stride, int world, void* residual,
+                                     const void* w, void* y, long long rows, int d, float eps, int dtype,
+                                     cudaStream_t st) {
+  if (rows <= 0) return 0;
+  if (d % 8 || d > 8192 || world < 1) return DLTI_ERR_BAD_ARG;
+  const int vpt = (d / 8 + 127) / 128;
+#define TRN(T, V) tp_reduce_add_norm_kernel<T, V><<<(unsigned)rows, 128, 0, st>>>((const T*)recv, slot_stride, world, (T*)residual, (const T*)w, (T*)y, d, eps)
+  if (dtype == DLTI_BF16) {
+    if (vpt <= 1) TRN(__nv_bfloat16, 1); else if (vpt <= 2) TRN(__nv_bfloat16, 2); else if (vpt <= 4) TRN(__nv_bfloat16, 4); else TRN(__nv_bfloat16, 8);
+  } else if (dtype == DLTI_FP16) {
+    if (vpt <= 1) TRN(__half, 1); else if (vpt <= 2) TRN(__half, 2); else if (vpt <= 4) TRN(__half, 4); else TRN(__half, 8);
+  } else {
+    return DLTI_ERR_UNSUPPORTED;
+  }
+#undef TRN
   dlti_count_launch();
   return (int)cudaGetLastError();
 }

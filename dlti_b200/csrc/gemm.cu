@@ -82,6 +82,12 @@ struct GemmParams {
   float alpha;
   uint32_t idesc;
   int n_rot, k_rot;   // GATHER: first N block / K block owned by this rank
+  // K10: row-parallel GEMM -> collective in the epilogue. When push_world > 0 the 16-bit output tile
+  // is stored into EVERY rank's receive buffer (peer stores over NVLink) at slot `push_rank`:
+  //   dst_r = push_peer[r] + push_rank * push_slot_stride + row * ldc + col
+  void* push_peer[16];
+  long long push_slot_stride;
+  int push_world, push_rank;
 };
 
 __device__ __forceinline__ uint32_t ld_relaxed_gpu_u32(const uint32_t* p) {
@@ -377,15 +383,25 @@ gemm_tcgen05_kernel(const GemmParams p, const __grid_constant__ CUtensorMap tmA,
                   }
                 }
               }
+              int4 ov[4];
 #pragma unroll
               for (int i = 0; i < 4; ++i) {
-                int4 o;
-                uint32_t* ou = reinterpret_cast<uint32_t*>(&o);
+                uint32_t* ou = reinterpret_cast<uint32_t*>(&ov[i]);
 #pragma unroll
                 for (int j = 0; j < 4; ++j)
                   ou[j] = bf ? Cvt<__nv_bfloat16>::pack2(f[8 * i + 2 * j], f[8 * i + 2 * j + 1])
                              : Cvt<__half>::pack2(f[8 * i + 2 * j], f[8 * i + 2 * j + 1]);
-                *(reinterpret_cast<int4*>(crow) + i) = o;
+              }
+              if (p.push_world > 0) {
+                const long long off = (long long)p.push_rank * p.push_slot_stride + (long long)row * p.ldc + col0;
+                for (int r = 0; r < p.push_world; ++r) {
+                  int4* dst = reinterpret_cast<int4*>(reinterpret_cast<uint16_t*>(p.push_peer[r]) + off);
+#pragma unroll
+                  for (int i = 0; i < 4; ++i) dst[i] = ov[i];
+                }
+              } else {
+#pragma unroll
+                for (int i = 0; i < 4; ++i) *(reinterpret_cast<int4*>(crow) + i) = ov[i];
               }
             } else {
               for (int i = 0; i < 32; ++i) {
@@ -395,8 +411,15 @@ gemm_tcgen05_kernel(const GemmParams p, const __grid_constant__ CUtensorMap tmA,
                     x += bf ? __bfloat162float(*reinterpret_cast<const __nv_bfloat16*>(rrow + i))
                             : __half2float(*reinterpret_cast<const __half*>(rrow + i));
                   }
-                  if (bf) *reinterpret_cast<__nv_bfloat16*>(crow + i) = __float2bfloat16_rn(x);
-                  else    *reinterpret_cast<__half*>(crow + i) = __float2half_rn(x);
+                  uint16_t bits;
+                  if (bf) { __nv_bfloat16 t = __float2bfloat16_rn(x); bits = *reinterpret_cast<uint16_t*>(&t); }
+                  else    { __half t = __float2half_rn(x); bits = *reinterpret_cast<uint16_t*>(&t); }
+                  if (p.push_world > 0) {
+                    const long long off = (long long)p.push_rank * p.push_slot_stride + (long long)row * p.ldc + col0 + i;
+                    for (int r = 0; r < p.push_world; ++r) reinterpret_cast<uint16_t*>(p.push_peer[r])[off] = bits;
+                  } else {
+                    crow[i] = bits;
+                  }
                 }
               }
             }
@@ -408,6 +431,7 @@ gemm_tcgen05_kernel(const GemmParams p, const __grid_constant__ CUtensorMap tmA,
       if (lane == 0) mbar_arrive(tempty_bar(acc));
       if (++acc == 2) { acc = 0; acc_phase ^= 1u; }
     }
+    if (p.push_world > 0) __threadfence_system();
   }
 
   tc_fence_before();
@@ -487,14 +511,23 @@ static int gemm_impl(const void* A, const void* B, void* C, const void* R, int M
                      int b_mn, const void* A2, const void* B2, int K2, long long lda2,
                      long long ldb2, int in_dtype, int out_dtype, float alpha, int accumulate,
                      int split_k, int block_n, int max_ctas, cudaStream_t stream,
-                     const GatherParams* gather) {
+                     const GatherParams* gather, const void* const* push_peers = nullptr,
+                     int push_rank = 0, int push_world = 0, long long push_slot_stride = 0) {
   if (M <= 0 || N <= 0 || K < 0 || (K == 0 && K2 == 0)) return DLTI_ERR_BAD_ARG;
   if (in_dtype != DLTI_BF16 && in_dtype != DLTI_FP16) return DLTI_ERR_UNSUPPORTED;
   if (K2 % BK) { dlti_set_error("K2 must be a multiple of 64"); return DLTI_ERR_BAD_ARG; }
   if (out_dtype != DLTI_FP32 && accumulate) { dlti_set_error("accumulate needs fp32 output"); return DLTI_ERR_BAD_ARG; }
   if (a_mn && !b_mn) return DLTI_ERR_UNSUPPORTED;
   int bn = block_n;
-  if (bn == 0) bn = (N <= 64) ? 64 : (N <= 128 ? 128 : 256);
+  if (bn == 0) {
+    bn = (N <= 64) ? 64 : (N <= 128 ? 128 : 256);
+    // decode-sized M (one M tile): the GEMM is a weight stream, so spread N over as many SMs as possible
+    if (M <= BM && !gather) {
+      const int sms = dlti_num_sms();
+      if ((N + 255) / 256 < sms) bn = 128;
+      if ((N + 127) / 128 < sms) bn = 64;
+    }
+  }
   if (a_mn && bn == 256) bn = 128;
   if (bn != 64 && bn != 128 && bn != 256) return DLTI_ERR_BAD_ARG;
 
@@ -522,6 +555,12 @@ static int gemm_impl(const void* A, const void* B, void* C, const void* R, int M
              (!R || (((reinterpret_cast<uintptr_t>(R) & 15) == 0) && ((ldr * 2) % 16 == 0)));
   p.alpha = alpha;
   p.idesc = umma_idesc_f16(in_dtype, BM, bn, a_mn != 0, b_mn != 0);
+  if (push_world > 0) {
+    if (out_dtype == DLTI_FP32 || R || push_world > 16 || !p.vec_ok && false) { dlti_set_error("push GEMM: 16-bit output without residual"); return DLTI_ERR_UNSUPPORTED; }
+    for (int i = 0; i < push_world; ++i) p.push_peer[i] = const_cast<void*>(push_peers[i]);
+    p.push_world = push_world; p.push_rank = push_rank; p.push_slot_stride = push_slot_stride;
+    p.vec_ok = p.vec_ok && ((push_slot_stride * 2) % 16 == 0);
+  }
   GatherParams gp{};
   if (gather) {
     if (a_mn || p.split_k != 1) { dlti_set_error("gather GEMM: A must be K-major and split_k = 1"); return DLTI_ERR_UNSUPPORTED; }
@@ -620,4 +659,16 @@ DLTI_API int dlti_gemm_gather(const void* A, void* B_staging, void* C, const voi
   if ((g.row_bytes * 4) % 16) return DLTI_ERR_BAD_ARG;
   return gemm_impl(A, B_staging, C, R, M, N, K, lda, ldb, ldc, ldr, 0, b_mn, A2, B2, K2, lda2, ldb2,
                    in_dtype, out_dtype, alpha, 0, 1, block_n, max_ctas, stream, &g);
+}
+
+// K10: row-parallel GEMM whose epilogue stores the (partial) 16-bit output tile into every rank's
+// receive buffer at slot `rank` (peer stores over NVLink): C_r = recv_peers[r] + rank*slot_stride.
+// The consumer (dlti_tp_reduce_add_norm) sums the slots in rank order after a peer barrier.
+DLTI_API int dlti_gemm_push(const void* A, const void* B, int M, int N, int K, long long lda, long long ldb,
+                            long long ldc, int in_dtype, int block_n, const void* const* recv_peers,
+                            int rank, int world, long long slot_stride, cudaStream_t stream) {
+  if (world < 1 || world > 16) return DLTI_ERR_BAD_ARG;
+  void* local = const_cast<void*>(recv_peers[rank]);
+  return gemm_impl(A, B, local, nullptr, M, N, K, lda, ldb, ldc, 0, 0, 0, nullptr, nullptr, 0, 0, 0, in_dtype,
+                   in_dtype, 1.f, 0, 1, block_n, 0, stream, nullptr, recv_peers, rank, world, slot_stride);
 }

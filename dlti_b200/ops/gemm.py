@@ -53,7 +53,7 @@ def gemm(a: torch.Tensor, b: torch.Tensor, *, a_mn: bool = False, b_mn: bool = F
          a2: torch.Tensor | None = None, b2: torch.Tensor | None = None,
          residual: torch.Tensor | None = None, out: torch.Tensor | None = None,
          out_dtype: torch.dtype | None = None, alpha: float = 1.0, accumulate: bool = False,
-         split_k: int = 1, block_n: int = 0, max_ctas: int = 0, gather=None) -> torch.Tensor:
+         split_k: int = 1, block_n: int = 0, max_ctas: int = 0, gather=None, push=None) -> torch.Tensor:
     """gather: optional parallel.fused.GatherSpec — `b` is then the local staging buffer of a row-
     sharded weight and the kernel pulls the shards from their owner ranks while it computes (K1)."""
     if not _lib.use_native(a, b):
@@ -69,12 +69,23 @@ def gemm(a: torch.Tensor, b: torch.Tensor, *, a_mn: bool = False, b_mn: bool = F
         assert b2 is not None and a2.stride(1) == 1 and b2.stride(1) == 1 and a2.dtype == a.dtype
         K2 = a2.shape[0] if a_mn else a2.shape[1]
     out_dtype = out_dtype or (out.dtype if out is not None else a.dtype)
-    if out is None:
+    if out is None and push is None:
         assert not accumulate
         out = torch.empty((M, N), dtype=out_dtype, device=a.device)
-    assert out.shape == (M, N) and out.stride(1) == 1 and out.dtype == out_dtype
+    assert push is not None or (out.shape == (M, N) and out.stride(1) == 1 and out.dtype == out_dtype)
     if residual is not None:
         assert residual.shape == (M, N) and residual.stride(1) == 1 and residual.dtype == out.dtype
+    if push is not None:
+        # K10: the epilogue stores the partial output into every rank's receive slot (peer stores)
+        peer_arr, recv, rank, world, max_tokens = push
+        assert not a_mn and not b_mn and a2 is None and residual is None and M <= max_tokens
+        assert recv.shape[-1] == N and recv.dtype == a.dtype
+        f = _lib.fn("dlti_gemm_push", [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_longlong,
+                                       C.c_longlong, C.c_longlong, C.c_int, C.c_int, C.c_void_p, C.c_int,
+                                       C.c_int, C.c_longlong, C.c_void_p])
+        _lib.check(f(_lib.ptr(a), _lib.ptr(b), M, N, K, a.stride(0), b.stride(0), N, _lib.dtype_code(a.dtype),
+                     int(block_n), peer_arr, rank, world, max_tokens * N, _lib.stream_ptr()), "dlti_gemm_push")
+        return recv
     if gather is not None:
         assert not a_mn and not accumulate and split_k == 1
         assert b.data_ptr() == gather.staging.data_ptr() and b.stride(0) == gather.staging.stride(0)

@@ -179,6 +179,16 @@ class FusedComm:
         _lib.check(f(self.peer_array(self.pads), self.rank, self.world, channel, self.epochs[channel],
                      _lib.ptr(self.err), _lib.stream_ptr()), "peer_barrier")
 
+    def barrier_graph_safe(self, channel: int) -> None:
+        """Barrier whose epoch lives on the device: safe to capture in / replay from a CUDA graph. Use a
+        channel that is never mixed with the host-epoch `barrier()`."""
+        if not hasattr(self, "_dev_epochs"):
+            self._dev_epochs = torch.zeros(self.N_CHANNELS, dtype=torch.int32, device=self.info.device)
+        f = _lib.fn("dlti_peer_barrier_auto", [_V, _I, _I, _I, _V, _V, _V])
+        _lib.check(f(self.peer_array(self.pads), self.rank, self.world, channel,
+                     C.c_void_p(self._dev_epochs.data_ptr() + 4 * channel), _lib.ptr(self.err),
+                     _lib.stream_ptr()), "peer_barrier_auto")
+
     def all_gather_rows(self, shard: torch.Tensor, out: torch.Tensor, blocks_per_peer: int = 8) -> None:
         """out [world*rows, cols] <- row blocks of every rank (pull). shard must be symmetric."""
         nbytes = shard.numel() * shard.element_size()
@@ -226,3 +236,15 @@ class FusedComm:
         assert rows % 64 == 0, "fused gather needs rows_per_rank % 64 == 0"
         assert counters.numel() == rows * self.world // 64
         return GatherSpec(self.peer_ptrs(shard), staging, counters, rows, self.rank, self.world, self.err)
+
+
+def tp_reduce_add_norm(recv: torch.Tensor, T: int, residual: torch.Tensor, w: torch.Tensor, eps: float,
+                       world: int, max_tokens: int) -> torch.Tensor:
+    """residual[:T] += sum over ranks of recv[r, :T] (fixed order); returns RMSNorm(residual) * w.
+    recv: [world, max_tokens, d] receive slots filled by every rank's GEMM epilogue (K10)."""
+    d = residual.shape[-1]
+    y = torch.empty((T, d), dtype=residual.dtype, device=residual.device)
+    f = _lib.fn("dlti_tp_reduce_add_norm", [_V, _L, _I, _V, _V, _V, _L, _I, _F, _I, _V])
+    _lib.check(f(_lib.ptr(recv), max_tokens * d, world, _lib.ptr(residual), _lib.ptr(w), _lib.ptr(y), T, d,
+                 float(eps), _lib.dtype_code(residual.dtype), _lib.stream_ptr()), "tp_reduce_add_norm")
+    return y

@@ -1,0 +1,101 @@
+"""Closed-loop load generator for /v1/completions: N concurrent users, each sending
+the next request as soon as the previous one finishes, fixed prompt / output lengths, streaming.
+Reports request/s, output tokens/s, TTFT p50/p95/p99 (time from request send to the first streamed
+chunk — the definition used by vLLM's benchmark client, SP:vllm/benchmarks/lib/endpoint_request_func.py
+:193-238), inter-token latency and end-to-end latency. Locust (reference requirements.txt:35) is not on
+the image; aiohttp is."""
+from __future__ import annotations
+
+import asyncio
+import json
+import random
+import statistics
+import time
+
+
+def _pct(xs, p):
+    if not xs:
+        return None
+    xs = sorted(xs)
+    return xs[min(len(xs) - 1, int(round(p / 100 * (len(xs) - 1))))]
+
+
+async def _one(session, url, model, prompt_ids, max_tokens, rec):
+    body = {"model": model, "prompt": prompt_ids, "max_tokens": max_tokens, "temperature": 0.0,
+            "ignore_eos": True, "stream": True}
+    t0 = time.perf_counter()
+    first = None
+    n = 0
+    last = t0
+    itl = []
+    try:
+        async with session.post(url, json=body) as resp:
+            if resp.status != 200:
+                rec["errors"] += 1
+                return
+            async for raw in resp.content:
+                line = raw.decode().strip()
+                if not line.startswith("data:"):
+                    continue
+                data = line[5:].strip()
+                if data == "[DONE]":
+                    break
+                now = time.perf_counter()
+                if first is None:
+                    first = now - t0
+                else:
+                    itl.append(now - last)
+                last = now
+                ch = json.loads(data).get("choices") or []
+                if ch:
+                    n += 1
+    except Exception:
+        rec["errors"] += 1
+        return
+    rec["ttft"].append(first if first is not None else float("nan"))
+    rec["e2e"].append(time.perf_counter() - t0)
+    rec["itl"] += itl
+    rec["tokens"] += n
+    rec["requests"] += 1
+
+
+async def run_load(base_url: str, model: str, concurrency: int, num_requests: int, input_len: int = 512,
+                   output_len: int = 128, vocab: int = 32000, seed: int = 0) -> dict:
+    import aiohttp
+
+    rng = random.Random(seed)
+    url = base_url.rstrip("/") + "/v1/completions"
+    rec = {"ttft": [], "e2e": [], "itl": [], "tokens": 0, "requests": 0, "errors": 0}
+    pending = [[1] + [rng.randrange(3, vocab) for _ in range(input_len - 1)] for _ in range(num_requests)]
+    lock = asyncio.Lock()
+
+    async def user(session):
+        while True:
+            async with lock:
+                if not pending:
+                    return
+                p = pending.pop()
+            await _one(session, url, model, p, output_len, rec)
+
+    timeout = aiohttp.ClientTimeout(total=3600)
+    t0 = time.perf_counter()
+    async with aiohttp.ClientSession(timeout=timeout, connector=aiohttp.TCPConnector(limit=0)) as s:
+        await asyncio.gather(*[user(s) for _ in range(concurrency)])
+    wall = time.perf_counter() - t0
+    return {"concurrency": concurrency, "requests": rec["requests"], "errors": rec["errors"], "wall_s": wall,
+            "input_len": input_len, "output_len": output_len,
+            "requests_per_s": rec["requests"] / wall, "output_tokens_per_s": rec["tokens"] / wall,
+            "total_tokens_per_s": (rec["tokens"] + rec["requests"] * input_len) / wall,
+            "ttft_p50_ms": 1e3 * (_pct(rec["ttft"], 50) or 0), "ttft_p95_ms": 1e3 * (_pct(rec["ttft"], 95) or 0),
+            "ttft_p99_ms": 1e3 * (_pct(rec["ttft"], 99) or 0),
+            "itl_mean_ms": 1e3 * (statistics.mean(rec["itl"]) if rec["itl"] else 0),
+            "e2e_p50_ms": 1e3 * (_pct(rec["e2e"], 50) or 0), "e2e_p99_ms": 1e3 * (_pct(rec["e2e"], 99) or 0)}
+
+
+async def sweep(base_url, model, concurrencies, requests_per_level=None, **kw):
+    out = []
+    for c in concurrencies:
+        n = requests_per_level or max(4 * c, 16)
+        out.append(await run_load(base_url, model, c, n, **kw))
+        print(json.dumps(out[-1]), flush=True)
+    return out

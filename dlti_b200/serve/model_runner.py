@@ -1,0 +1,200 @@
+"""Inference forward pass over the paged KV cache, single GPU or Megatron-style tensor parallel
+(§2.7 S1-S12).
+
+TP layout per rank (tp = world size): q/k/v heads and gate/up columns are column-parallel, o_proj and
+down_proj are row-parallel, the LM head is vocab-parallel; the embedding table is replicated (262 MB
+at 7B: on 180 GB parts that removes collective C8 entirely). The two row-parallel GEMMs of a layer
+produce partial sums that are combined by `TPContext.reduce_add_norm`: on the "fused" backend the
+GEMM epilogue pushes its partial tile straight into every peer's receive slot over NVLink (K10) and
+one kernel sums the slots in rank order, adds the residual and applies RMSNorm (the all-gather side of
+K11 is implicit: every rank ends up with the full normalised activations); on the "nccl" backend it is
+NCCL all-reduce + the fused add+norm kernel.
+
+Prefill uses the varlen tcgen05 flash-attention kernel on the packed prompts; decode uses the paged-KV
+split-KV kernel. RoPE and the KV-cache write are one kernel.
+"""
+from __future__ import annotations
+
+import math
+
+import torch
+
+from ..models.config import LlamaConfig
+from ..ops import attention as A
+from ..ops import elementwise as E
+from ..ops import serving as S
+from ..ops.gemm import gemm
+from .kv_cache import KVCache
+
+
+class TPContext:
+    """Collectives used by the TP forward. world == 1 => no-ops."""
+
+    def __init__(self, info=None, backend: str = "nccl", fused=None, cfg: LlamaConfig | None = None,
+                 max_tokens: int = 8192, dtype=torch.bfloat16):
+        self.rank = info.rank if info else 0
+        self.world = info.world_size if info else 1
+        self.backend, self.fused = backend, fused
+        self.use_fused = fused is not None and self.world > 1
+        if self.use_fused:
+            d = cfg.hidden_size
+            # two alternating receive buffers [world, max_tokens, d] in the symmetric arena
+            self.recv = [fused.alloc_symmetric((self.world, max_tokens, d), dtype) for _ in range(2)]
+            self.flip = 0
+            self.max_tokens = max_tokens
+
+    def reduce_add_norm(self, partial_fn, T: int, residual, w, eps):
+        """partial_fn(out=None|tensor, push=None|spec) runs the row-parallel GEMM. Returns the normalised
+        activations; `residual` (fp [T, d]) is updated in place with residual += sum_r partial_r."""
+        if self.world == 1:
+            part = partial_fn(None, None)
+            y, _, _ = E.rmsnorm_fwd(part, w, eps, residual=residual)
+            return y
+        if self.use_fused:
+            from ..parallel.fused import tp_reduce_add_norm
+            buf = self.recv[self.flip]
+            self.flip ^= 1
+            partial_fn(None, (self.fused.peer_array(buf), buf, self.rank, self.world, self.max_tokens))
+            self.fused.barrier_graph_safe(5)
+            return tp_reduce_add_norm(buf, T, residual, w, eps, self.world, self.max_tokens)
+        import torch.distributed as dist
+        part = partial_fn(None, None)
+        dist.all_reduce(part)
+        y, _, _ = E.rmsnorm_fwd(part, w, eps, residual=residual)
+        return y
+
+    def all_gather_cols(self, local: torch.Tensor) -> torch.Tensor:
+        if self.world == 1:
+            return local
+        import torch.distributed as dist
+        out = torch.empty(self.world, *local.shape, dtype=local.dtype, device=local.device)
+        dist.all_gather_into_tensor(out, local.contiguous())
+        return out.permute(1, 0, 2).reshape(local.shape[0], -1)
+
+
+class TPWeights:
+    """This rank's slice of every weight, built from a ResidentWeights-like provider or random init."""
+
+    def __init__(self, cfg: LlamaConfig, rank: int, world: int, device, dtype):
+        self.cfg, self.rank, self.world = cfg, rank, world
+        assert cfg.num_attention_heads % world == 0 and cfg.num_key_value_heads % world == 0, \
+            "tp size must divide the number of q and kv heads"
+        assert cfg.intermediate_size % world == 0 and cfg.vocab_size % world == 0
+        self.H, self.KV = cfg.num_attention_heads // world, cfg.num_key_value_heads // world
+        self.ff = cfg.intermediate_size // world
+        self.V = cfg.vocab_size // world
+        d, hd = cfg.hidden_size, cfg.head_dim
+        mk = lambda *s: torch.empty(*s, dtype=dtype, device=device)
+        self.embed = mk(cfg.vocab_size, d)
+        self.final_norm = mk(d)
+        self.lm_head = mk(self.V, d)
+        self.layers = [dict(w_qkv=mk((self.H + 2 * self.KV) * hd, d), w_o=mk(d, self.H * hd),
+                            w_gu=mk(2 * self.ff, d), w_down=mk(d, self.ff), ln1=mk(d), ln2=mk(d))
+                       for _ in range(cfg.num_hidden_layers)]
+
+    def load_from_full(self, w) -> "TPWeights":
+        """Slice a full ResidentWeights (any device) into this rank's shards."""
+        c, r, hd = self.cfg, self.rank, self.cfg.head_dim
+        q, kv, ff = c.q_size, c.kv_size, c.intermediate_size
+        Hl, KVl, ffl = self.H * hd, self.KV * hd, self.ff
+        self.embed.copy_(w.embed)
+        self.final_norm.copy_(w.final_norm)
+        self.lm_head.copy_(w.lm_head[r * self.V:(r + 1) * self.V])
+        for dst, src in zip(self.layers, w.layers):
+            dst["w_qkv"][:Hl].copy_(src.w_qkv[r * Hl:(r + 1) * Hl])
+            dst["w_qkv"][Hl:Hl + KVl].copy_(src.w_qkv[q + r * KVl:q + (r + 1) * KVl])
+            dst["w_qkv"][Hl + KVl:].copy_(src.w_qkv[q + kv + r * KVl:q + kv + (r + 1) * KVl])
+            dst["w_o"].copy_(src.w_o[:, r * Hl:(r + 1) * Hl])
+            dst["w_gu"][:ffl].copy_(src.w_gu[r * ffl:(r + 1) * ffl])
+            dst["w_gu"][ffl:].copy_(src.w_gu[ff + r * ffl:ff + (r + 1) * ffl])
+            dst["w_down"].copy_(src.w_down[:, r * ffl:(r + 1) * ffl])
+            dst["ln1"].copy_(src.ln1)
+            dst["ln2"].copy_(src.ln2)
+        return self
+
+    def init_random(self, seed: int = 0) -> "TPWeights":
+        """Random init identical to slicing ResidentWeights.random_init-style full matrices: every full
+        matrix is generated from (seed, matrix id) on the device and sliced (so TP=1 and TP=N serve the
+        same model)."""
+        c, hd = self.cfg, self.cfg.head_dim
+        dev = self.embed.device
+        gen = torch.Generator(device=dev)
+
+        def full(rows, cols, key):
+            gen.manual_seed((seed * 1000003 + key) & 0x7FFFFFFFFFFF)
+            t = torch.empty(rows, cols, dtype=self.embed.dtype, device=dev)
+            t.normal_(0.0, 0.02, generator=gen)
+            return t
+
+        class _L:
+            pass
+
+        class _W:
+            pass
+
+        w = _W()
+        w.embed = full(c.vocab_size, c.hidden_size, 1)
+        w.lm_head = w.embed if c.tie_word_embeddings else full(c.vocab_size, c.hidden_size, 2)
+        w.final_norm = torch.ones(c.hidden_size, dtype=self.embed.dtype, device=dev)
+        self.embed.copy_(w.embed)
+        self.final_norm.copy_(w.final_norm)
+        self.lm_head.copy_(w.lm_head[self.rank * self.V:(self.rank + 1) * self.V])
+        del w.embed, w.lm_head
+        one = torch.ones(c.hidden_size, dtype=self.embed.dtype, device=dev)
+        r = self.rank
+        q, kv, ff = c.q_size, c.kv_size, c.intermediate_size
+        Hl, KVl, ffl = self.H * hd, self.KV * hd, self.ff
+        for li, dst in enumerate(self.layers):
+            wq = full(c.qkv_size, c.hidden_size, li * 8 + 16)
+            dst["w_qkv"][:Hl].copy_(wq[r * Hl:(r + 1) * Hl])
+            dst["w_qkv"][Hl:Hl + KVl].copy_(wq[q + r * KVl:q + (r + 1) * KVl])
+            dst["w_qkv"][Hl + KVl:].copy_(wq[q + kv + r * KVl:q + kv + (r + 1) * KVl])
+            del wq
+            dst["w_o"].copy_(full(c.hidden_size, c.q_size, li * 8 + 17)[:, r * Hl:(r + 1) * Hl])
+            wg = full(2 * ff, c.hidden_size, li * 8 + 18)
+            dst["w_gu"][:ffl].copy_(wg[r * ffl:(r + 1) * ffl])
+            dst["w_gu"][ffl:].copy_(wg[ff + r * ffl:ff + (r + 1) * ffl])
+            del wg
+            dst["w_down"].copy_(full(c.hidden_size, ff, li * 8 + 19)[:, r * ffl:(r + 1) * ffl])
+            dst["ln1"].copy_(one)
+            dst["ln2"].copy_(one)
+        return self
+
+
+class ModelRunner:
+    def __init__(self, cfg: LlamaConfig, weights: TPWeights, kv: KVCache, tp: TPContext):
+        self.cfg, self.w, self.kv, self.tp = cfg, weights, kv, tp
+        self.scale = 1.0 / math.sqrt(cfg.head_dim)
+        self.cos, self.sin = E.rope_tables(cfg.max_position_embeddings, cfg.head_dim, cfg.rope_theta,
+                                           weights.embed.device)
+        self.device = weights.embed.device
+
+    @torch.no_grad()
+    def forward(self, kind: str, input_ids, positions, slots, cu_seqlens=None, max_seqlen=0,
+                block_tables=None, ctx_lens=None, last_idx=None, max_ctx=None) -> torch.Tensor:
+        """kind = "prefill": tokens are whole prompts packed along T (cu_seqlens); "decode": one token
+        per sequence with block_tables / ctx_lens. Returns logits [num_seqs, vocab] (fp of the model)."""
+        cfg, w, tp = self.cfg, self.w, self.tp
+        H, KV, hd, eps = w.H, w.KV, cfg.head_dim, cfg.rms_norm_eps
+        T = input_ids.numel()
+        residual = E.embedding(input_ids.view(-1), w.embed)                  # [T, d] residual stream
+        xn, _, _ = E.rmsnorm_fwd(residual, w.layers[0]["ln1"], eps)
+        L = cfg.num_hidden_layers
+        for li, lw in enumerate(w.layers):
+            qkv = gemm(xn, lw["w_qkv"])
+            S.rope_cache_(qkv, positions, self.cos, self.sin, slots, self.kv.k[li], self.kv.v[li], H, KV, hd)
+            if kind == "prefill":
+                attn, _ = A.attention_fwd(qkv, cu_seqlens, max_seqlen, H, KV, hd, self.scale, want_lse=False)
+            else:
+                attn = S.paged_decode(qkv, self.kv.k[li], self.kv.v[li], block_tables, ctx_lens, H, KV, hd,
+                                      self.scale, max_ctx=max_ctx)
+            xn = tp.reduce_add_norm(lambda out, push: gemm(attn, lw["w_o"], out=out, push=push),
+                                    T, residual, lw["ln2"], eps)
+            gu = gemm(xn, lw["w_gu"])
+            h = E.swiglu_fwd(gu)
+            nxt = w.layers[li + 1]["ln1"] if li + 1 < L else w.final_norm
+            xn = tp.reduce_add_norm(lambda out, push: gemm(h, lw["w_down"], out=out, push=push),
+                                    T, residual, nxt, eps)
+        xl = xn if last_idx is None else xn.index_select(0, last_idx)
+        logits = gemm(xl, w.lm_head)                                         # [B, V/tp]
+        return tp.all_gather_cols(logits)

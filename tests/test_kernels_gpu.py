@@ -175,3 +175,87 @@ def test_attention_fwd_bwd(H, KV, seqs, dtype):
     dqkv_r = A.attention_bwd_ref(dout.cpu(), qkv.cpu(), out_r, lse_r, cu.cpu(), H, KV, hd, 1 / math.sqrt(hd))
     scale = dqkv_r.float().abs().max().item()
     close(dqkv, dqkv_r, 3e-2, 3e-2 * max(scale, 1.0))
+
+
+# ---- serving kernels ------------------------------------------------------------------------
+from dlti_b200.ops import serving as S  # noqa: E402
+
+
+@pytest.mark.parametrize("H,KV", [(4, 4), (8, 2)])
+def test_rope_cache_and_paged_decode(H, KV):
+    torch.manual_seed(8)
+    hd, bs, nblocks = 128, 16, 64
+    W = (H + 2 * KV) * hd
+    cos, sin = E.rope_tables(4096, hd, 1e4, DEV)
+    kc = torch.zeros(nblocks, bs, KV, hd, device=DEV, dtype=torch.bfloat16)
+    vc = torch.zeros_like(kc)
+    kc_r, vc_r = kc.cpu().clone(), vc.cpu().clone()
+    ctx = [37, 200, 1]
+    perm = torch.randperm(nblocks)
+    tables = torch.full((len(ctx), 16), 0, dtype=torch.int32)
+    nb = 0
+    slots, pos = [], []
+    for b, n in enumerate(ctx):
+        need = (n + bs - 1) // bs
+        tables[b, :need] = perm[nb:nb + need].to(torch.int32)
+        nb += need
+        for t in range(n):
+            slots.append(int(tables[b, t // bs]) * bs + t % bs)
+            pos.append(t)
+    T = len(slots)
+    qkv = torch.randn(T, W, device=DEV, dtype=torch.bfloat16)
+    slots_t = torch.tensor(slots, dtype=torch.int64)
+    pos_t = torch.tensor(pos, dtype=torch.int32)
+    ref = S.rope_cache_ref(qkv.cpu().clone(), pos_t, cos.cpu(), sin.cpu(), slots_t, kc_r, vc_r, H, KV, hd)
+    S.rope_cache_(qkv, pos_t.to(DEV), cos, sin, slots_t.to(DEV), kc, vc, H, KV, hd)
+    close(qkv, ref, 1e-2, 1e-2)
+    close(kc, kc_r, 1e-2, 1e-2)
+    close(vc, vc_r, 1e-2, 1e-2)
+    # decode: last token of each sequence queries its whole context
+    ends = torch.tensor(ctx).cumsum(0) - 1
+    q = qkv[ends.to(DEV)].contiguous()
+    ctx_t = torch.tensor(ctx, dtype=torch.int32)
+    out = S.paged_decode(q, kc, vc, tables.to(DEV), ctx_t.to(DEV), H, KV, hd)
+    out_r = S.paged_decode_ref(q.cpu(), kc.cpu(), vc.cpu(), tables, ctx_t, H, KV, hd, 1 / math.sqrt(hd))
+    close(out, out_r, 2e-2, 2e-2)
+
+
+def test_paged_decode_long_context_split_kv():
+    torch.manual_seed(9)
+    H = KV = 4
+    hd, bs = 128, 16
+    n = 3000
+    nblocks = (n + bs - 1) // bs + 4
+    kc = torch.randn(nblocks, bs, KV, hd, device=DEV, dtype=torch.bfloat16)
+    vc = torch.randn_like(kc)
+    tables = torch.arange(nblocks, dtype=torch.int32).flip(0)[None, :].contiguous()
+    q = torch.randn(1, H * hd, device=DEV, dtype=torch.bfloat16)
+    ctx = torch.tensor([n], dtype=torch.int32)
+    out = S.paged_decode(q, kc, vc, tables.to(DEV), ctx.to(DEV), H, KV, hd)
+    out_r = S.paged_decode_ref(q.cpu(), kc.cpu(), vc.cpu(), tables, ctx, H, KV, hd, 1 / math.sqrt(hd))
+    close(out, out_r, 2e-2, 2e-2)
+
+
+def test_sampling_kernel():
+    torch.manual_seed(10)
+    B, V = 6, 32000
+    logits = (3 * torch.randn(B, V, device=DEV)).to(torch.bfloat16)
+    temp = torch.tensor([0.0, 1.0, 0.7, 1.0, 1.0, 2.0], device=DEV)
+    top_k = torch.tensor([0, 0, 50, 1, 0, 10], dtype=torch.int32, device=DEV)
+    top_p = torch.tensor([1.0, 1.0, 1.0, 1.0, 0.5, 0.9], device=DEV)
+    seeds = torch.arange(B, dtype=torch.int64, device=DEV)
+    greedy, keep = S.sample_ref(logits.cpu(), temp.cpu(), top_k.cpu(), top_p.cpu())
+    seen = [set() for _ in range(B)]
+    for step in range(40):
+        tok, lp = S.sample(logits, temp, top_k, top_p, seeds, step=step, want_logprob=True)
+        tok = tok.cpu()
+        for b in range(B):
+            assert keep[b, tok[b]], (b, int(tok[b]))
+            seen[b].add(int(tok[b]))
+        ref_lp = torch.log_softmax(logits.float().cpu(), -1).gather(-1, tok.unsqueeze(-1)).squeeze(-1)
+        close(lp, ref_lp, 2e-2, 2e-2)
+    assert seen[0] == {int(greedy[0])} and seen[3] == {int(greedy[3])}      # greedy and top_k = 1
+    assert len(seen[1]) > 10 and 1 < len(seen[5]) <= 10 and len(seen[2]) <= 50
+    t1, _ = S.sample(logits, temp, top_k, top_p, seeds, step=5)
+    t2, _ = S.sample(logits, temp, top_k, top_p, seeds, step=5)
+    assert torch.equal(t1, t2)                                               # seeded => reproducible

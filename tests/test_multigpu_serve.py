@@ -1,0 +1,20 @@
+"""Multi-GPU serving tier (needs >= 2 B200s): TP=N greedy decoding == TP=1 on nccl / fused / fused+graphs."""
+import os
+import subprocess
+import sys
+
+import pytest
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+pytestmark = [pytest.mark.gpu, pytest.mark.multigpu]
+
+
+def test_tp_serving_two_gpus():
+    import torch
+
+    n = min(2, torch.cuda.device_count())
+    r = subprocess.run([sys.executable, "-m", "dlti_b200.launch", f"--num_gpus={n}", "--master_port=29741",
+                        "--no_local_rank", os.path.join(ROOT, "tests", "mp_serve_worker.py")],
+                       capture_output=True, text=True, timeout=900, cwd=ROOT, env=dict(os.environ, PYTHONPATH=ROOT))
+    print(r.stdout[-3000:])
+    assert r.returncode == 0 and "ALL TP SERVING CHECKS PASSED" in r.stdout, r.stdout[-3000:] + r.stderr[-3000:]

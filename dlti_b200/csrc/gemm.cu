@@ -565,7 +565,9 @@ static int gemm_impl(const void* A, const void* B, void* C, const void* R, int M
   if (gather) {
     if (a_mn || p.split_k != 1) { dlti_set_error("gather GEMM: A must be K-major and split_k = 1"); return DLTI_ERR_UNSUPPORTED; }
     gp = *gather;
-    p.n_rot = (int)(((long long)gp.rank * gp.units_per_rank * 64) / bn) % p.nnb;
+    // first N tile lying entirely inside this rank's own rows (ceil): a tile that straddles into the
+    // previous rank's rows would need the units that are gathered LAST and stall every CTA at once
+    p.n_rot = (int)((((long long)gp.rank * gp.units_per_rank * 64) + bn - 1) / bn) % p.nnb;
     p.k_rot = (gp.rank * gp.units_per_rank) % (p.nkb_main > 0 ? p.nkb_main : 1);
   }
 

@@ -327,8 +327,11 @@ attn_bwd_kernel(const AttnParams p, const __grid_constant__ CUtensorMap tmQKV128
   const int seqlen = p.cu_seqlens[b + 1] - row0;
   const int G = p.H / p.KV;
   const int n64 = (seqlen + 63) >> 6;
-  const int blk = (int)blockIdx.x;          // stationary 128-row block index
-  if (blk * 128 >= seqlen) return;
+  // stationary 128-row block index. dK/dV: block 0 has the most query blocks to visit; dQ: the LAST
+  // query block has the most key blocks -> walk it in reverse so heavy CTAs are scheduled first.
+  const int nblk128 = (seqlen + 127) >> 7;
+  const int blk = DKDV ? (int)blockIdx.x : nblk128 - 1 - (int)blockIdx.x;
+  if (blk < 0 || blk * 128 >= seqlen) return;
   const int head = blockIdx.y;              // DKDV: kv head; else: q head
   // streamed block range and iteration count
   int y0, ny, iters;
@@ -341,15 +344,18 @@ attn_bwd_kernel(const AttnParams p, const __grid_constant__ CUtensorMap tmQKV128
   extern __shared__ uint8_t smem_raw[];
   const uint32_t base = (smem_u32(smem_raw) + 1023u) & ~1023u;
   const uint32_t sX1 = base, sX2 = base + 32768;
-  const uint32_t sY1 = base + 65536;            // 2 stages x 16 KB
-  const uint32_t sY2 = base + 65536 + 32768;    // 2 stages x 16 KB
-  const uint32_t sP = base + 131072;            // 16 KB
-  const uint32_t sDS = base + 131072 + 16384;   // 16 KB
-  const uint32_t sStat = base + 163840;         // 2 stages x (64 lse + 64 D) floats = 1 KB
-  const uint32_t bars = base + 163840 + 1024;
-  const uint32_t x_full = bars, y_full = bars + 8, y_empty = bars + 24, ab_full = bars + 40,
-                 ab_free = bars + 56, pds_full = bars + 72, pds_free = bars + 80,
-                 tmem_slot = bars + 88;
+  // streamed tiles: NYS-deep ring (3: the load for iteration it+2 is issued as soon as the MMAs of
+  // iteration it-1 retire, so two tiles are in flight and the TMA latency is off the critical path)
+  constexpr int NYS = 3;
+  const uint32_t sY1 = base + 65536;                    // NYS stages x 16 KB
+  const uint32_t sY2 = base + 65536 + NYS * 16384;      // NYS stages x 16 KB
+  const uint32_t sP = base + 65536 + 2 * NYS * 16384;   // 16 KB
+  const uint32_t sDS = sP + 16384;                      // 16 KB
+  const uint32_t sStat = sDS + 16384;                   // 2 x (64 lse + 64 D) floats = 1 KB
+  const uint32_t bars = sStat + 1024;
+  const uint32_t x_full = bars, y_full = bars + 8, y_empty = bars + 32, ab_full = bars + 56,
+                 ab_free = bars + 72, pds_full = bars + 88, pds_free = bars + 96,
+                 tmem_slot = bars + 104;
   volatile uint32_t* tmem_slot_ptr =
       reinterpret_cast<volatile uint32_t*>(smem_raw + (tmem_slot - smem_u32(smem_raw)));
   float* stat = reinterpret_cast<float*>(smem_raw + (sStat - smem_u32(smem_raw)));
@@ -357,9 +363,11 @@ attn_bwd_kernel(const AttnParams p, const __grid_constant__ CUtensorMap tmQKV128
 
   if (warp == 0 && lane == 0) {
     mbar_init(x_full, 1);
-    for (int s = 0; s < 2; ++s) {
+    for (int s = 0; s < NYS; ++s) {
       mbar_init(y_full + 8 * s, 1);
       mbar_init(y_empty + 8 * s, 1);
+    }
+    for (int s = 0; s < 2; ++s) {
       mbar_init(ab_full + 8 * s, 1);
       mbar_init(ab_free + 8 * s, 4);
     }
@@ -397,8 +405,8 @@ attn_bwd_kernel(const AttnParams p, const __grid_constant__ CUtensorMap tmQKV128
         tma_load_2d(sX2 + 16384, &tmDO128, x_full, qc + 64, r);
       }
       for (int it = 0; it < iters; ++it) {
-        const int s = it & 1;
-        if (it >= 2) mbar_wait(y_empty + 8 * s, ((it >> 1) - 1) & 1);
+        const int s = it % NYS;
+        if (it >= NYS) mbar_wait(y_empty + 8 * s, ((it / NYS) - 1) & 1);
         mbar_expect_tx(y_full + 8 * s, 32768);
         if (DKDV) {
           const int g = it / ny, i = y0 + (it - g * ny);
@@ -422,38 +430,38 @@ attn_bwd_kernel(const AttnParams p, const __grid_constant__ CUtensorMap tmQKV128
       const uint32_t idesc_ab = umma_idesc_f16(p.dtype, 128, 64, false, false);
       const uint32_t idesc_acc = umma_idesc_f16(p.dtype, 128, 128, false, true);
       auto issue_ab = [&](int it) {
-        const int s = it & 1;
-        mbar_wait(y_full + 8 * s, (it >> 1) & 1);
+        const int s = it & 1, ys = it % NYS;
+        mbar_wait(y_full + 8 * ys, (it / NYS) & 1);
         if (it >= 2) mbar_wait(ab_free + 8 * s, ((it >> 1) - 1) & 1);
         tc_fence_after();
 #pragma unroll
         for (int kk = 0; kk < 8; ++kk)
           umma_f16_ss(tmem + TA + s * 64, desc_kmajor(sX1, 128, kk),
-                      desc_kmajor(sY1 + s * 16384, 64, kk), idesc_ab, kk > 0);
+                      desc_kmajor(sY1 + ys * 16384, 64, kk), idesc_ab, kk > 0);
 #pragma unroll
         for (int kk = 0; kk < 8; ++kk)
           umma_f16_ss(tmem + TB + s * 64, desc_kmajor(sX2, 128, kk),
-                      desc_kmajor(sY2 + s * 16384, 64, kk), idesc_ab, kk > 0);
+                      desc_kmajor(sY2 + ys * 16384, 64, kk), idesc_ab, kk > 0);
         umma_commit(ab_full + 8 * s);
       };
       mbar_wait(x_full, 0);
       issue_ab(0);
       for (int it = 0; it < iters; ++it) {
-        const int s = it & 1;
+        const int ys = it % NYS;
         if (it + 1 < iters) issue_ab(it + 1);
         mbar_wait(pds_full, it & 1);
         tc_fence_after();
         if (DKDV) {
 #pragma unroll
           for (int kk = 0; kk < 4; ++kk)   // dV += P^T · dO
-            umma_f16_ss(tmem + TACC1, desc_kmajor64(sP, kk), desc_mnmajor(sY2 + s * 16384, 64, kk),
+            umma_f16_ss(tmem + TACC1, desc_kmajor64(sP, kk), desc_mnmajor(sY2 + ys * 16384, 64, kk),
                         idesc_acc, (it > 0 || kk > 0));
         }
 #pragma unroll
         for (int kk = 0; kk < 4; ++kk)     // dK += dS^T · Q   /   dQ += dS · K
-          umma_f16_ss(tmem + TACC2, desc_kmajor64(sDS, kk), desc_mnmajor(sY1 + s * 16384, 64, kk),
+          umma_f16_ss(tmem + TACC2, desc_kmajor64(sDS, kk), desc_mnmajor(sY1 + ys * 16384, 64, kk),
                       idesc_acc, (it > 0 || kk > 0));
-        umma_commit(y_empty + 8 * s);
+        umma_commit(y_empty + 8 * ys);
         umma_commit(pds_free);
       }
     }
@@ -510,9 +518,12 @@ attn_bwd_kernel(const AttnParams p, const __grid_constant__ CUtensorMap tmQKV128
             lse_v = my_lse; D_v = my_D;
             valid = (sidx < seqlen) && (yi <= sidx);
           }
-          float pv = exp2f(__uint_as_float(sv[i]) * sl2 - lse_v);
-          pr[i] = valid ? pv : 0.f;
-          ds[i] = valid ? pv * (__uint_as_float(dv[i]) - D_v) * p.scale : 0.f;
+          // branch-free masking: clamp the exponent (masked / garbage scores may be huge) and
+          // multiply by a 0/1 mask, so the compiler cannot wrap exp2f in a per-element branch
+          const float msk = valid ? 1.f : 0.f;
+          const float pv = exp2f(fminf(__uint_as_float(sv[i]) * sl2 - lse_v, 16.f)) * msk;
+          pr[i] = pv;
+          ds[i] = pv * (__uint_as_float(dv[i]) - D_v) * p.scale;
         }
         if (c == 0 && it > 0) mbar_wait(pds_free, (it - 1) & 1);
         if (DKDV) store_row32<T>(sP, r, c * 4, pr);
@@ -564,7 +575,7 @@ attn_bwd_kernel(const AttnParams p, const __grid_constant__ CUtensorMap tmQKV128
 }
 
 constexpr int FWD_SMEM = 6 * 32768 + 256 + 1024;
-constexpr int BWD_SMEM = 163840 + 1024 + 256 + 1024;
+constexpr int BWD_SMEM = 65536 + 2 * 3 * 16384 + 32768 + 1024 + 256 + 1024;
 
 int make_map(CUtensorMap* m, const void* base, long long T_total, long long width, int box_rows) {
   return dlti_make_tmap_2d(m, base, (uint64_t)width, (uint64_t)T_total, (uint64_t)width, 64,

@@ -109,7 +109,7 @@ __device__ __forceinline__ void gather_wait_unit(const GatherParams& g, int u) {
   }
 }
 
-template <int BN, bool A_MN, bool B_MN, bool GATHER>
+template <int BN, bool A_MN, bool B_MN, bool GATHER, bool PUSH>
 __global__ void __launch_bounds__(NUM_THREADS + (GATHER ? GATHER_THREADS : 0), 1)
 gemm_tcgen05_kernel(const GemmParams p, const __grid_constant__ CUtensorMap tmA,
                     const __grid_constant__ CUtensorMap tmB,
@@ -129,6 +129,12 @@ gemm_tcgen05_kernel(const GemmParams p, const __grid_constant__ CUtensorMap tmA,
   volatile uint32_t* tmem_slot_ptr =
       reinterpret_cast<volatile uint32_t*>(smem_raw + (tmem_slot - smem_u32(smem_raw)));
 
+  __shared__ void* s_peers[16];   // GATHER: shard bases; PUSH: receive-buffer bases
+  if (GATHER || PUSH) {
+#pragma unroll
+    for (int i = 0; i < 16; ++i)   // static indices: keeps the parameters in the constant bank
+      if (threadIdx.x == i) s_peers[i] = GATHER ? const_cast<void*>(gp.peer[i]) : p.push_peer[i];
+  }
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
   const int tiles_mn = p.nmb * p.nnb;
@@ -299,7 +305,7 @@ gemm_tcgen05_kernel(const GemmParams p, const __grid_constant__ CUtensorMap tmA,
       const int u = (gp.rank * gp.units_per_rank + j) % gp.n_units;   // needed-first order
       if ((int32_t)(ld_acquire_gpu_u32(gp.counters + u) - gp.target) >= 0) continue;  // landed earlier this epoch
       const int owner = u / gp.units_per_rank;
-      const uint8_t* src = reinterpret_cast<const uint8_t*>(gp.peer[owner]) +
+      const uint8_t* src = reinterpret_cast<const uint8_t*>(s_peers[owner]) +
                            (long long)(u - owner * gp.units_per_rank) * unit_bytes + part * chunk_bytes;
       uint8_t* dst = gp.staging + (long long)u * unit_bytes + part * chunk_bytes;
       const long long nvec = chunk_bytes >> 4;
@@ -392,10 +398,10 @@ gemm_tcgen05_kernel(const GemmParams p, const __grid_constant__ CUtensorMap tmA,
                   ou[j] = bf ? Cvt<__nv_bfloat16>::pack2(f[8 * i + 2 * j], f[8 * i + 2 * j + 1])
                              : Cvt<__half>::pack2(f[8 * i + 2 * j], f[8 * i + 2 * j + 1]);
               }
-              if (p.push_world > 0) {
+              if (PUSH) {
                 const long long off = (long long)p.push_rank * p.push_slot_stride + (long long)row * p.ldc + col0;
                 for (int r = 0; r < p.push_world; ++r) {
-                  int4* dst = reinterpret_cast<int4*>(reinterpret_cast<uint16_t*>(p.push_peer[r]) + off);
+                  int4* dst = reinterpret_cast<int4*>(reinterpret_cast<uint16_t*>(s_peers[r]) + off);
 #pragma unroll
                   for (int i = 0; i < 4; ++i) dst[i] = ov[i];
                 }
@@ -414,9 +420,9 @@ gemm_tcgen05_kernel(const GemmParams p, const __grid_constant__ CUtensorMap tmA,
                   uint16_t bits;
                   if (bf) { __nv_bfloat16 t = __float2bfloat16_rn(x); bits = *reinterpret_cast<uint16_t*>(&t); }
                   else    { __half t = __float2half_rn(x); bits = *reinterpret_cast<uint16_t*>(&t); }
-                  if (p.push_world > 0) {
+                  if (PUSH) {
                     const long long off = (long long)p.push_rank * p.push_slot_stride + (long long)row * p.ldc + col0 + i;
-                    for (int r = 0; r < p.push_world; ++r) reinterpret_cast<uint16_t*>(p.push_peer[r])[off] = bits;
+                    for (int r = 0; r < p.push_world; ++r) reinterpret_cast<uint16_t*>(s_peers[r])[off] = bits;
                   } else {
                     crow[i] = bits;
                   }
@@ -431,7 +437,7 @@ gemm_tcgen05_kernel(const GemmParams p, const __grid_constant__ CUtensorMap tmA,
       if (lane == 0) mbar_arrive(tempty_bar(acc));
       if (++acc == 2) { acc = 0; acc_phase ^= 1u; }
     }
-    if (p.push_world > 0) __threadfence_system();
+    if (PUSH) __threadfence_system();
   }
 
   tc_fence_before();
@@ -484,7 +490,7 @@ int get_tmap(CUtensorMap* out, const void* base, uint64_t inner, uint64_t outer,
   return 0;
 }
 
-template <int BN, bool A_MN, bool B_MN, bool GATHER>
+template <int BN, bool A_MN, bool B_MN, bool GATHER, bool PUSH = false>
 int launch(const GemmParams& p, const CUtensorMap& a, const CUtensorMap& b, const CUtensorMap& a2,
            const CUtensorMap& b2, const CUtensorMap& bl, const GatherParams& gp, int grid,
            cudaStream_t stream) {
@@ -493,12 +499,12 @@ int launch(const GemmParams& p, const CUtensorMap& a, const CUtensorMap& b, cons
   int dev = 0;
   cudaGetDevice(&dev);
   if (!configured[dev & 63]) {
-    DLTI_CUDA_CHECK(cudaFuncSetAttribute(gemm_tcgen05_kernel<BN, A_MN, B_MN, GATHER>,
+    DLTI_CUDA_CHECK(cudaFuncSetAttribute(gemm_tcgen05_kernel<BN, A_MN, B_MN, GATHER, PUSH>,
                                          cudaFuncAttributeMaxDynamicSharedMemorySize,
                                          C_::SMEM_BYTES));
     configured[dev & 63] = true;
   }
-  gemm_tcgen05_kernel<BN, A_MN, B_MN, GATHER>
+  gemm_tcgen05_kernel<BN, A_MN, B_MN, GATHER, PUSH>
       <<<grid, NUM_THREADS + (GATHER ? GATHER_THREADS : 0), C_::SMEM_BYTES, stream>>>(p, a, b, a2, b2, bl, gp);
   dlti_count_launch();
   return (int)cudaGetLastError();
@@ -604,6 +610,12 @@ static int gemm_impl(const void* A, const void* B, void* C, const void* R, int M
   if (max_ctas > 0 && max_ctas < grid) grid = max_ctas;
   if (total < grid) grid = total;
 
+  if (push_world > 0) {
+    if (a_mn || b_mn) return DLTI_ERR_UNSUPPORTED;
+    if (bn == 256) return launch<256, false, false, false, true>(p, ta, tb, ta2, tb2, tbl, gp, grid, stream);
+    if (bn == 128) return launch<128, false, false, false, true>(p, ta, tb, ta2, tb2, tbl, gp, grid, stream);
+    return launch<64, false, false, false, true>(p, ta, tb, ta2, tb2, tbl, gp, grid, stream);
+  }
   if (gather) {
     if (bn == 256 && !b_mn) return launch<256, false, false, true>(p, ta, tb, ta2, tb2, tbl, gp, grid, stream);
     if (bn == 128 && !b_mn) return launch<128, false, false, true>(p, ta, tb, ta2, tb2, tbl, gp, grid, stream);

@@ -172,12 +172,20 @@ class Trainer:
             gs = scales
         devb = [pb.to(dev) if on_gpu else pb for pb in packed]
         opt.wait_reduce()
+        nvtx = on_gpu and self.args.profile            # --profile: NVTX ranges for nsys / ncu filtering (§5.1)
+        if nvtx:
+            torch.cuda.nvtx.range_push(f"step{self.global_step + 1}/fwd_bwd")
         # the whole accumulation window in one layer-major pass (one ZeRO-3 gather per layer per pass)
         loss_sum = self.model.forward_backward_multi(devb, gs)
         opt.on_micro_batch_end(is_boundary=True)
         self.tokens_seen += sum(pb.n_tokens for pb in packed)
+        if nvtx:
+            torch.cuda.nvtx.range_pop()
+            torch.cuda.nvtx.range_push(f"step{self.global_step + 1}/optimizer")
         lr = self.scheduler.get_lr()
         skipped, gnorm = opt.step(lr)
+        if nvtx:
+            torch.cuda.nvtx.range_pop()
         self.scaler.update(skipped)
         if skipped:
             self.skipped_steps += 1

@@ -25,12 +25,14 @@ _lib.reset_launch_count()
 s, e = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
 n = int(os.environ.get('N', 5))
 s.record()
+t_cpu0 = time.perf_counter()
 for i in range(n):
     loss = model.forward_backward(b, gs)
+cpu_enqueue_ms = (time.perf_counter() - t_cpu0) * 1e3 / n      # host time to enqueue one micro-step
 e.record(); torch.cuda.synchronize()
 ms = s.elapsed_time(e) / n
 toks = B * S
 flops = 6 * cfg.num_params() * toks if ckpt else 4 * cfg.num_params() * toks
 print(json.dumps({"model": name, "B": B, "S": S, "ckpt": ckpt, "ms_per_microstep": ms, "tok_per_s": toks / ms * 1e3,
                   "model_tflops": flops / ms / 1e9, "loss": loss.item() / b.n_valid, "launches_per_step": _lib.launch_count() / n,
-                  "peak_mem_gb": torch.cuda.max_memory_allocated() / 1e9}))
+                  "peak_mem_gb": torch.cuda.max_memory_allocated() / 1e9, "cpu_enqueue_ms": cpu_enqueue_ms}))

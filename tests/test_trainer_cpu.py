@@ -126,3 +126,41 @@ def test_zero_stages_match_single_process(tmp_path, stage, offload):
     for a, b in zip(got["losses"], ref["losses"]):
         assert abs(a - b) < 2e-3
     assert (out / "final" / "adapter_model.safetensors").exists()      # consolidated save, all ranks entered
+
+
+FAULT_WORKER = r'''
+import os, sys, torch
+sys.path.insert(0, {root!r})
+from tests.test_trainer_cpu import make_trainer
+out = sys.argv[1]
+cfgp = os.path.join({root!r}, "configs/ds_config_zero2.json")
+tr = make_trainer(out, deepspeed=cfgp, precision="fp32", gradient_accumulation_steps=1, save_steps=2,
+                  lora_dropout=0.0)
+tr.train(resume_from_checkpoint=True if os.environ.get("RESUME") else None)
+if tr.is_main:
+    torch.save(tr.lora.master[: tr.lora.numel].clone(), os.path.join(out, "final_master.pt"))
+'''
+
+
+def test_fault_injection_fail_fast_and_resume(tmp_path):
+    """§5.3: a rank dying (DLTI_FAULT_AT_STEP) makes the launcher tear the job down with a non-zero code;
+    restarting with resume continues from the last checkpoint and ends where an uninterrupted run ends."""
+    script = tmp_path / "fw.py"
+    script.write_text(FAULT_WORKER.format(root=ROOT))
+    env = dict(os.environ, PYTHONPATH=ROOT, OMP_NUM_THREADS="2")
+
+    def launch(out, extra_env):
+        return subprocess.run([sys.executable, "-m", "dlti_b200.launch", "--num_gpus=2", "--master_port=29655",
+                               "--no_local_rank", str(script), str(out)], env=dict(env, **extra_env),
+                              capture_output=True, text=True, timeout=600, cwd=ROOT)
+
+    ref = launch(tmp_path / "ref", {})
+    assert ref.returncode == 0, ref.stderr[-2000:]
+    bad = launch(tmp_path / "run", {"DLTI_FAULT_AT_STEP": "5", "DLTI_FAULT_RANK": "1"})
+    assert bad.returncode != 0 and "killing the other ranks" in bad.stderr
+    assert ckpt.latest_checkpoint(tmp_path / "run").name == "checkpoint-4"
+    ok = launch(tmp_path / "run", {"RESUME": "1"})
+    assert ok.returncode == 0, ok.stderr[-2000:]
+    a = torch.load(tmp_path / "ref" / "final_master.pt")
+    b = torch.load(tmp_path / "run" / "final_master.pt")
+    torch.testing.assert_close(a, b, rtol=1e-5, atol=1e-6)

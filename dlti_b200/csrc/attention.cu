@@ -32,7 +32,7 @@
 namespace {
 
 constexpr int HD = 128;           // head dim
-constexpr int AT_THREADS = 192;   // producer, mma, 4 softmax warps
+constexpr int AT_THREADS = 320;   // producer, mma, 8 softmax warps (two threads per row: column halves)
 constexpr float LOG2E = 1.4426950408889634f;
 constexpr float LN2 = 0.6931471805599453f;
 
@@ -120,9 +120,9 @@ attn_fwd_kernel(const AttnParams p, const __grid_constant__ CUtensorMap tm128) {
       mbar_init(v_full + 8 * s, 1);
       mbar_init(kv_empty + 8 * s, 1);
       mbar_init(s_full + 8 * s, 1);
-      mbar_init(s_free + 8 * s, 4);
+      mbar_init(s_free + 8 * s, 8);
     }
-    mbar_init(p_full, 4);
+    mbar_init(p_full, 8);
     mbar_init(pv_full, 1);
     mbar_fence_init();
   }
@@ -185,22 +185,29 @@ attn_fwd_kernel(const AttnParams p, const __grid_constant__ CUtensorMap tm128) {
       }
     }
   } else {
+    // Two threads per query row: warps 2-5 take S/P/O columns [0,64), warps 6-9 take [64,128). Twice
+    // the warps per scheduler hides the ALU/MUFU/TMEM latencies of the per-element softmax chain; the
+    // only cross-thread traffic is one row-max exchange per KV block and one row-sum merge at the end.
     const int quarter = warp & 3;
+    const int half = (warp - 2) >> 2;           // column half owned by this thread
     const int r = quarter * 32 + lane;          // query row inside the tile
     const uint32_t trow = tmem + ((uint32_t)(quarter * 32) << 16);
     const float sl2 = p.scale * LOG2E;
-    float o[128];
+    __shared__ float s_xmax[2][2][128];         // [iteration parity][half][row]
+    __shared__ float s_xsum[2][128];
+    float o[64];
 #pragma unroll
-    for (int i = 0; i < 128; ++i) o[i] = 0.f;
+    for (int i = 0; i < 64; ++i) o[i] = 0.f;
     float m = -INFINITY, l = 0.f;
     for (int j = 0; j < nkv; ++j) {
       const int s = j & 1;
       const bool diag = (j == qb);
       mbar_wait(s_full + 8 * s, (j >> 1) & 1);
       tc_fence_after();
-      float mx = m;
+      float mx = -INFINITY;
 #pragma unroll 1
-      for (int c = 0; c < 4; ++c) {
+      for (int cc = 0; cc < 2; ++cc) {
+        const int c = half * 2 + cc;
         uint32_t v[32];
         tmem_ld_32x32b_x32(trow + TS0 + s * 128 + c * 32, v);
         tmem_wait_ld();
@@ -211,22 +218,26 @@ attn_fwd_kernel(const AttnParams p, const __grid_constant__ CUtensorMap tm128) {
           mx = fmaxf(mx, sv);
         }
       }
+      s_xmax[s][half][r] = mx;
+      asm volatile("bar.sync 1, 256;" ::: "memory");
+      mx = fmaxf(m, fmaxf(mx, s_xmax[s][half ^ 1][r]));
       const float alpha = exp2f(m - mx);
       if (j > 0) {
         mbar_wait(pv_full, (j - 1) & 1);
         tc_fence_after();
 #pragma unroll
-        for (int c = 0; c < 4; ++c) {
+        for (int cc = 0; cc < 2; ++cc) {
           uint32_t v[32];
-          tmem_ld_32x32b_x32(trow + TPV + c * 32, v);
+          tmem_ld_32x32b_x32(trow + TPV + (half * 2 + cc) * 32, v);
           tmem_wait_ld();
 #pragma unroll
-          for (int i = 0; i < 32; ++i) o[c * 32 + i] = (o[c * 32 + i] + __uint_as_float(v[i])) * alpha;
+          for (int i = 0; i < 32; ++i) o[cc * 32 + i] = (o[cc * 32 + i] + __uint_as_float(v[i])) * alpha;
         }
       }
       l *= alpha;
 #pragma unroll 1
-      for (int c = 0; c < 4; ++c) {
+      for (int cc = 0; cc < 2; ++cc) {
+        const int c = half * 2 + cc;
         uint32_t v[32];
         tmem_ld_32x32b_x32(trow + TS0 + s * 128 + c * 32, v);
         tmem_wait_ld();
@@ -240,7 +251,7 @@ attn_fwd_kernel(const AttnParams p, const __grid_constant__ CUtensorMap tm128) {
           l += pv;
           pr[i] = pv;
         }
-        store_row32<T>(sP + (c >> 1) * 16384, r, (c & 1) * 4, pr);
+        store_row32<T>(sP + half * 16384, r, cc * 4, pr);
       }
       tc_fence_before();
       fence_proxy_async_smem();
@@ -253,13 +264,16 @@ attn_fwd_kernel(const AttnParams p, const __grid_constant__ CUtensorMap tm128) {
     }
     mbar_wait(pv_full, (nkv - 1) & 1);
     tc_fence_after();
+    s_xsum[half][r] = l;
+    asm volatile("bar.sync 1, 256;" ::: "memory");
+    l += s_xsum[half ^ 1][r];
     const float inv = 1.f / l;
     const int qi = qb * 128 + r;
-    T* orow = reinterpret_cast<T*>(p.O) + (long long)(row0 + qi) * p.ldo + h * HD;
+    T* orow = reinterpret_cast<T*>(p.O) + (long long)(row0 + qi) * p.ldo + h * HD + half * 64;
 #pragma unroll
-    for (int c = 0; c < 4; ++c) {
+    for (int cc = 0; cc < 2; ++cc) {
       uint32_t v[32];
-      tmem_ld_32x32b_x32(trow + TPV + c * 32, v);
+      tmem_ld_32x32b_x32(trow + TPV + (half * 2 + cc) * 32, v);
       tmem_wait_ld();
       if (qi < seqlen) {
 #pragma unroll
@@ -269,14 +283,14 @@ attn_fwd_kernel(const AttnParams p, const __grid_constant__ CUtensorMap tm128) {
 #pragma unroll
           for (int q = 0; q < 4; ++q) {
             const int i = 8 * k + 2 * q;
-            ou[q] = Cvt<T>::pack2((o[c * 32 + i] + __uint_as_float(v[i])) * inv,
-                                  (o[c * 32 + i + 1] + __uint_as_float(v[i + 1])) * inv);
+            ou[q] = Cvt<T>::pack2((o[cc * 32 + i] + __uint_as_float(v[i])) * inv,
+                                  (o[cc * 32 + i + 1] + __uint_as_float(v[i + 1])) * inv);
           }
-          *reinterpret_cast<int4*>(orow + c * 32 + 8 * k) = ov;
+          *reinterpret_cast<int4*>(orow + cc * 32 + 8 * k) = ov;
         }
       }
     }
-    if (qi < seqlen && p.lse) p.lse[(long long)h * p.T_total + row0 + qi] = (m + log2f(l)) * LN2;
+    if (half == 0 && qi < seqlen && p.lse) p.lse[(long long)h * p.T_total + row0 + qi] = (m + log2f(l)) * LN2;
   }
   tc_fence_before();
   __syncthreads();
@@ -369,9 +383,9 @@ attn_bwd_kernel(const AttnParams p, const __grid_constant__ CUtensorMap tmQKV128
     }
     for (int s = 0; s < 2; ++s) {
       mbar_init(ab_full + 8 * s, 1);
-      mbar_init(ab_free + 8 * s, 4);
+      mbar_init(ab_free + 8 * s, 8);
     }
-    mbar_init(pds_full, 4);
+    mbar_init(pds_full, 8);
     mbar_init(pds_free, 1);
     mbar_fence_init();
   }
@@ -466,12 +480,14 @@ attn_bwd_kernel(const AttnParams p, const __grid_constant__ CUtensorMap tmQKV128
       }
     }
   } else {
+    // two threads per row: warps 2-5 own streamed columns [0,32), warps 6-9 own [32,64)
     const int quarter = warp & 3;
+    const int half = (warp - 2) >> 2;
     const int r = quarter * 32 + lane;
     const int sidx = blk * 128 + r;            // key index (DKDV) or query index (!DKDV)
     const uint32_t trow = tmem + ((uint32_t)(quarter * 32) << 16);
     const float sl2 = p.scale * LOG2E;
-    const int tid128 = threadIdx.x - 64;
+    const int tid128 = threadIdx.x - 64;       // 0..255; the first 128 stage lse / D
     float my_lse = 0.f, my_D = 0.f;
     if (!DKDV && sidx < seqlen) {
       my_lse = p.lse[(long long)head * p.T_total + row0 + sidx] * LOG2E;
@@ -486,20 +502,22 @@ attn_bwd_kernel(const AttnParams p, const __grid_constant__ CUtensorMap tmQKV128
         // stage this q block's lse / D (64 values each) into smem
         const int qh = head * G + g;
         const int q = yb * 64 + (tid128 & 63);
-        float val = 0.f;
-        if (q < seqlen) {
-          const long long off = (long long)qh * p.T_total + row0 + q;
-          val = (tid128 < 64) ? p.lse[off] * LOG2E : p.D[off];
+        if (tid128 < 128) {
+          float val = 0.f;
+          if (q < seqlen) {
+            const long long off = (long long)qh * p.T_total + row0 + q;
+            val = (tid128 < 64) ? p.lse[off] * LOG2E : p.D[off];
+          }
+          stat[s * 128 + tid128] = val;
         }
-        stat[s * 128 + tid128] = val;
-        asm volatile("bar.sync 1, 128;" ::: "memory");
+        asm volatile("bar.sync 1, 256;" ::: "memory");
       } else {
         yb = y0 + it;
       }
       mbar_wait(ab_full + 8 * s, (it >> 1) & 1);
       tc_fence_after();
-#pragma unroll 1
-      for (int c = 0; c < 2; ++c) {
+      {
+        const int c = half;
         uint32_t sv[32], dv[32];
         tmem_ld_32x32b_x32(trow + TA + s * 64 + c * 32, sv);
         tmem_ld_32x32b_x32(trow + TB + s * 64 + c * 32, dv);
@@ -525,7 +543,7 @@ attn_bwd_kernel(const AttnParams p, const __grid_constant__ CUtensorMap tmQKV128
           pr[i] = pv;
           ds[i] = pv * (__uint_as_float(dv[i]) - D_v) * p.scale;
         }
-        if (c == 0 && it > 0) mbar_wait(pds_free, (it - 1) & 1);
+        if (it > 0) mbar_wait(pds_free, (it - 1) & 1);
         if (DKDV) store_row32<T>(sP, r, c * 4, pr);
         store_row32<T>(sDS, r, c * 4, ds);
       }
@@ -548,7 +566,8 @@ attn_bwd_kernel(const AttnParams p, const __grid_constant__ CUtensorMap tmQKV128
       if (DKDV) col = (a == 0) ? (vcol_base + head * HD) : (kcol_base + head * HD);
       else col = head * HD;
 #pragma unroll
-      for (int c = 0; c < 4; ++c) {
+      for (int cc = 0; cc < 2; ++cc) {
+        const int c = half * 2 + cc;
         uint32_t v[32];
         tmem_ld_32x32b_x32(trow + tacc + c * 32, v);
         tmem_wait_ld();

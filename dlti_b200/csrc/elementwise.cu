@@ -337,6 +337,25 @@ __global__ void embedding_kernel(const long long* __restrict__ ids, const T* __r
   }
 }
 
+// out[r, c] = T(acc[r, c]); acc[r, c] = 0   (finish step of the split-K decode GEMM)
+template <typename T>
+__global__ void skinny_finish_kernel(float* __restrict__ acc, T* __restrict__ out, long long rows, int cols,
+                                     long long out_stride) {
+  const int vpr = cols >> 3;
+  const long long total = rows * vpr;
+  for (long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x; idx < total;
+       idx += (long long)gridDim.x * blockDim.x) {
+    const long long r = idx / vpr;
+    const int v = (int)(idx - r * vpr);
+    float4* a = reinterpret_cast<float4*>(acc + r * cols + v * 8);
+    const float4 a0 = a[0], a1 = a[1];
+    const float f[8] = {a0.x, a0.y, a0.z, a0.w, a1.x, a1.y, a1.z, a1.w};
+    *reinterpret_cast<int4*>(out + r * out_stride + v * 8) = pack8<T>(f);
+    a[0] = make_float4(0.f, 0.f, 0.f, 0.f);
+    a[1] = make_float4(0.f, 0.f, 0.f, 0.f);
+  }
+}
+
 inline int grid_for(long long total, int block) {
   long long g = (total + block - 1) / block;
   const long long cap = (long long)dlti_num_sms() * 16;
@@ -480,6 +499,18 @@ DLTI_API int dlti_embedding(const long long* ids, const void* table, void* out, 
   DISPATCH_16(dtype,
               (embedding_kernel<__nv_bfloat16><<<g, 256, 0, st>>>(ids, (const __nv_bfloat16*)table, (__nv_bfloat16*)out, tokens, d, vocab_start, vocab_rows)),
               (embedding_kernel<__half><<<g, 256, 0, st>>>(ids, (const __half*)table, (__half*)out, tokens, d, vocab_start, vocab_rows)))
+  dlti_count_launch();
+  return (int)cudaGetLastError();
+}
+
+DLTI_API int dlti_skinny_finish(float* acc32, void* out, long long rows, int cols, long long out_stride,
+                                int dtype, cudaStream_t st) {
+  if (rows <= 0) return 0;
+  if (cols % 8) return DLTI_ERR_BAD_ARG;
+  const int g = grid_for(rows * (cols / 8), 256);
+  DISPATCH_16(dtype,
+              (skinny_finish_kernel<__nv_bfloat16><<<g, 256, 0, st>>>(acc32, (__nv_bfloat16*)out, rows, cols, out_stride)),
+              (skinny_finish_kernel<__half><<<g, 256, 0, st>>>(acc32, (__half*)out, rows, cols, out_stride)))
   dlti_count_launch();
   return (int)cudaGetLastError();
 }

@@ -78,6 +78,7 @@ struct GemmParams {
   int in_dtype;    // DltiDtype (16-bit)
   int accumulate;  // fp32 output only: C += result
   int atomic_out;  // fp32 output only: red.add (split-K)
+  int transpose_out;  // atomic fp32 output only: element (row, col) goes to C[col * ldc + row]
   int vec_ok;      // 16-byte vector stores allowed
   float alpha;
   uint32_t idesc;
@@ -353,8 +354,14 @@ gemm_tcgen05_kernel(const GemmParams p, const __grid_constant__ CUtensorMap tmA,
           if (p.out_dtype == DLTI_FP32) {
             float* crow = reinterpret_cast<float*>(p.C) + (long long)row * p.ldc + col0;
             if (p.atomic_out) {
-              for (int i = 0; i < 32; ++i)
-                if (col0 + i < p.N) atomicAdd(crow + i, f[i]);
+              if (p.transpose_out) {      // swap-AB decode GEMM: lanes (= rows) hit consecutive addresses
+                float* cb = reinterpret_cast<float*>(p.C) + row;
+                for (int i = 0; i < 32; ++i)
+                  if (col0 + i < p.N) atomicAdd(cb + (long long)(col0 + i) * p.ldc, f[i]);
+              } else {
+                for (int i = 0; i < 32; ++i)
+                  if (col0 + i < p.N) atomicAdd(crow + i, f[i]);
+              }
             } else if (full) {
 #pragma unroll
               for (int i = 0; i < 8; ++i) {
@@ -518,7 +525,8 @@ static int gemm_impl(const void* A, const void* B, void* C, const void* R, int M
                      long long ldb2, int in_dtype, int out_dtype, float alpha, int accumulate,
                      int split_k, int block_n, int max_ctas, cudaStream_t stream,
                      const GatherParams* gather, const void* const* push_peers = nullptr,
-                     int push_rank = 0, int push_world = 0, long long push_slot_stride = 0) {
+                     int push_rank = 0, int push_world = 0, long long push_slot_stride = 0,
+                     int transpose_out = 0) {
   if (M <= 0 || N <= 0 || K < 0 || (K == 0 && K2 == 0)) return DLTI_ERR_BAD_ARG;
   if (in_dtype != DLTI_BF16 && in_dtype != DLTI_FP16) return DLTI_ERR_UNSUPPORTED;
   if (K2 % BK) { dlti_set_error("K2 must be a multiple of 64"); return DLTI_ERR_BAD_ARG; }
@@ -555,7 +563,8 @@ static int gemm_impl(const void* A, const void* B, void* C, const void* R, int M
   p.C = C; p.R = R; p.ldc = ldc; p.ldr = ldr;
   p.out_dtype = out_dtype; p.in_dtype = in_dtype;
   p.accumulate = accumulate;
-  p.atomic_out = p.split_k > 1;
+  p.atomic_out = p.split_k > 1 || transpose_out;
+  p.transpose_out = transpose_out;
   const int ob = out_dtype == DLTI_FP32 ? 4 : 2;
   p.vec_ok = ((reinterpret_cast<uintptr_t>(C) & 15) == 0) && ((ldc * ob) % 16 == 0) &&
              (!R || (((reinterpret_cast<uintptr_t>(R) & 15) == 0) && ((ldr * 2) % 16 == 0)));
@@ -685,4 +694,23 @@ DLTI_API int dlti_gemm_push(const void* A, const void* B, int M, int N, int K, l
   void* local = const_cast<void*>(recv_peers[rank]);
   return gemm_impl(A, B, local, nullptr, M, N, K, lda, ldb, ldc, 0, 0, 0, nullptr, nullptr, 0, 0, 0, in_dtype,
                    in_dtype, 1.f, 0, 1, block_n, 0, stream, nullptr, recv_peers, rank, world, slot_stride);
+}
+
+// Decode-sized GEMM (M tokens <= 256): out32[M, N] += X[M, K] · W[N, K]^T computed as (W · X^T)^T so that
+// the WEIGHT is the 128-row tcgen05 A operand (every byte streamed from HBM is useful) and the handful
+// of token rows is the narrow B operand; K is split across CTAs to put every SM on the weight stream
+// and the fp32 partials are reduced with red.global.add into `acc32` (must be zero on entry;
+// dlti_skinny_finish converts it to 16 bits and re-zeroes it).
+DLTI_API int dlti_gemm_skinny(const void* X, const void* W, float* acc32, int M, int N, int K, long long ldx,
+                              long long ldw, int in_dtype, int split_k, cudaStream_t stream) {
+  if (M < 1 || M > 256) return DLTI_ERR_BAD_ARG;
+  const int bn = M <= 64 ? 64 : (M <= 128 ? 128 : 256);
+  if (split_k <= 0) {
+    const int tiles = (N + BM - 1) / BM;
+    const int nkb = (K + BK - 1) / BK;
+    split_k = (dlti_num_sms() + tiles - 1) / tiles;
+    while (split_k > 1 && nkb / split_k < 8) --split_k;
+  }
+  return gemm_impl(W, X, acc32, nullptr, N, M, K, ldw, ldx, /*ldc=*/N, 0, 0, 0, nullptr, nullptr, 0, 0, 0, in_dtype,
+                   DLTI_FP32, 1.f, 1, split_k, bn, 0, stream, nullptr, nullptr, 0, 0, 0, /*transpose_out=*/1);
 }

@@ -113,11 +113,13 @@ __global__ void __launch_bounds__(128) paged_decode_kernel(
 
   float qf[32];
   {
-    const T* qp = q + (long long)b * q_stride + (long long)h * HD + ch * 32;
+    // lane `ch` owns dims {i*32 + ch*8 .. +8 : i = 0..3}: for each i the 4 lanes of a token read 64
+    // CONTIGUOUS bytes, so every load instruction uses whole 32-byte sectors
+    const T* qp = q + (long long)b * q_stride + (long long)h * HD + ch * 8;
 #pragma unroll
     for (int i = 0; i < 4; ++i) {
       float f[8];
-      unpack8<T>(*reinterpret_cast<const int4*>(qp + i * 8), f);
+      unpack8<T>(*reinterpret_cast<const int4*>(qp + i * 32), f);
 #pragma unroll
       for (int j = 0; j < 8; ++j) qf[i * 8 + j] = f[j] * scale_log2;
     }
@@ -135,16 +137,16 @@ __global__ void __launch_bounds__(128) paged_decode_kernel(
     int4 vraw[4];
     if (valid) {
       const long long slot = (long long)bt[tok / block_size] * block_size + (tok % block_size);
-      const T* kp = k_cache + (slot * KV + kvh) * HD + ch * 32;
-      const T* vp = v_cache + (slot * KV + kvh) * HD + ch * 32;
+      const T* kp = k_cache + (slot * KV + kvh) * HD + ch * 8;
+      const T* vp = v_cache + (slot * KV + kvh) * HD + ch * 8;
       float acc = 0.f;
 #pragma unroll
       for (int i = 0; i < 4; ++i) {
         float f[8];
-        unpack8<T>(*reinterpret_cast<const int4*>(kp + i * 8), f);
+        unpack8<T>(*reinterpret_cast<const int4*>(kp + i * 32), f);
 #pragma unroll
         for (int j = 0; j < 8; ++j) acc += f[j] * qf[i * 8 + j];
-        vraw[i] = *reinterpret_cast<const int4*>(vp + i * 8);
+        vraw[i] = *reinterpret_cast<const int4*>(vp + i * 32);
       }
       s = acc;
     }
@@ -185,7 +187,7 @@ __global__ void __launch_bounds__(128) paged_decode_kernel(
   __shared__ float sm_m[4], sm_l[4];
   if (tg == 0) {
 #pragma unroll
-    for (int i = 0; i < 32; ++i) sm_o[warp][ch * 32 + i] = o[i];
+    for (int i = 0; i < 32; ++i) sm_o[warp][(i >> 3) * 32 + ch * 8 + (i & 7)] = o[i];
     if (ch == 0) { sm_m[warp] = m; sm_l[warp] = l; }
   }
   __syncthreads();

@@ -113,3 +113,32 @@ def gemm(a: torch.Tensor, b: torch.Tensor, *, a_mn: bool = False, b_mn: bool = F
         int(split_k), int(block_n), int(max_ctas), _lib.stream_ptr())
     _lib.check(rc, "dlti_gemm")
     return out
+
+
+_skinny_ws: dict = {}
+
+
+def gemm_skinny(x: torch.Tensor, w: torch.Tensor, out: torch.Tensor | None = None, split_k: int = 0) -> torch.Tensor:
+    """y[M, N] = x[M, K] · w[N, K]^T for decode-sized M (<= 256): the weight is the 128-row tensor-core
+    operand, K is split over CTAs so every SM streams weights, fp32 partials are reduced with atomics
+    into a persistent zeroed workspace and a finish kernel converts + re-zeroes it. Falls back to the
+    regular kernel on CPU tensors or larger M."""
+    M, K = x.shape
+    N = w.shape[0]
+    if not _lib.use_native(x, w) or M > 256 or N % 8:
+        return gemm(x, w, out=out)
+    key = str(x.device)
+    ws = _skinny_ws.get(key)
+    if ws is None or ws.numel() < M * N:
+        ws = torch.zeros(max(M * N, 256 * 32768), dtype=torch.float32, device=x.device)
+        _skinny_ws[key] = ws
+    if out is None:
+        out = torch.empty((M, N), dtype=x.dtype, device=x.device)
+    f = _lib.fn("dlti_gemm_skinny", [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_longlong,
+                                     C.c_longlong, C.c_int, C.c_int, C.c_void_p])
+    _lib.check(f(_lib.ptr(x), _lib.ptr(w), _lib.ptr(ws), M, N, K, x.stride(0), w.stride(0),
+                 _lib.dtype_code(x.dtype), int(split_k), _lib.stream_ptr()), "dlti_gemm_skinny")
+    g = _lib.fn("dlti_skinny_finish", [C.c_void_p, C.c_void_p, C.c_longlong, C.c_int, C.c_longlong, C.c_int, C.c_void_p])
+    _lib.check(g(_lib.ptr(ws), _lib.ptr(out), M, N, out.stride(0), _lib.dtype_code(out.dtype), _lib.stream_ptr()),
+               "dlti_skinny_finish")
+    return out

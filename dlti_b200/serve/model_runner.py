@@ -23,7 +23,7 @@ from ..models.config import LlamaConfig
 from ..ops import attention as A
 from ..ops import elementwise as E
 from ..ops import serving as S
-from ..ops.gemm import gemm
+from ..ops.gemm import gemm, gemm_skinny
 from .kv_cache import KVCache
 
 
@@ -180,21 +180,25 @@ class ModelRunner:
         residual = E.embedding(input_ids.view(-1), w.embed)                  # [T, d] residual stream
         xn, _, _ = E.rmsnorm_fwd(residual, w.layers[0]["ln1"], eps)
         L = cfg.num_hidden_layers
+        # decode-sized steps stream the weights through the swap-AB split-K kernel
+        mm = gemm_skinny if T <= 256 else (lambda a, b_: gemm(a, b_))
+
+        def rowpar(act, wgt):
+            return lambda out, push: (gemm(act, wgt, out=out, push=push) if push is not None else mm(act, wgt))
+
         for li, lw in enumerate(w.layers):
-            qkv = gemm(xn, lw["w_qkv"])
+            qkv = mm(xn, lw["w_qkv"])
             S.rope_cache_(qkv, positions, self.cos, self.sin, slots, self.kv.k[li], self.kv.v[li], H, KV, hd)
             if kind == "prefill":
                 attn, _ = A.attention_fwd(qkv, cu_seqlens, max_seqlen, H, KV, hd, self.scale, want_lse=False)
             else:
                 attn = S.paged_decode(qkv, self.kv.k[li], self.kv.v[li], block_tables, ctx_lens, H, KV, hd,
                                       self.scale, max_ctx=max_ctx)
-            xn = tp.reduce_add_norm(lambda out, push: gemm(attn, lw["w_o"], out=out, push=push),
-                                    T, residual, lw["ln2"], eps)
-            gu = gemm(xn, lw["w_gu"])
+            xn = tp.reduce_add_norm(rowpar(attn, lw["w_o"]), T, residual, lw["ln2"], eps)
+            gu = mm(xn, lw["w_gu"])
             h = E.swiglu_fwd(gu)
             nxt = w.layers[li + 1]["ln1"] if li + 1 < L else w.final_norm
-            xn = tp.reduce_add_norm(lambda out, push: gemm(h, lw["w_down"], out=out, push=push),
-                                    T, residual, nxt, eps)
+            xn = tp.reduce_add_norm(rowpar(h, lw["w_down"]), T, residual, nxt, eps)
         xl = xn if last_idx is None else xn.index_select(0, last_idx)
-        logits = gemm(xl, w.lm_head)                                         # [B, V/tp]
+        logits = (gemm_skinny if xl.shape[0] <= 256 else gemm)(xl, w.lm_head)  # [B, V/tp]
         return tp.all_gather_cols(logits)

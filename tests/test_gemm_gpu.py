@@ -90,3 +90,17 @@ def test_gemm_fp32_out_and_strided():
     out = gemm(a, b, out=cbuf[:, 128:768], out_dtype=torch.float32)
     _check(out, gemm_ref(a, b, out_dtype=torch.float32))
     assert cbuf[:, :128].abs().max().item() == 0 and cbuf[:, 768:].abs().max().item() == 0
+
+
+@pytest.mark.parametrize("M,N,K", [(1, 4096, 4096), (64, 12288, 4096), (17, 4096, 11008), (128, 22016, 4096),
+                                   (200, 1536, 512)])
+def test_gemm_skinny_decode(M, N, K):
+    """Swap-AB split-K decode GEMM (+ finish kernel) vs the oracle; workspace must come back zeroed."""
+    from dlti_b200.ops.gemm import _skinny_ws, gemm_skinny
+    torch.manual_seed(5)
+    x = torch.randn(M, K, device="cuda", dtype=torch.bfloat16)
+    w = torch.randn(N, K, device="cuda", dtype=torch.bfloat16)
+    for _ in range(2):
+        y = gemm_skinny(x, w)
+        _check(y, gemm_ref(x, w, out_dtype=torch.float32))
+    assert _skinny_ws["cuda:0"][: M * N].abs().max().item() == 0.0

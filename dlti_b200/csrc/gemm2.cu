@@ -1,0 +1,373 @@
+// K2 (large-M form): the same GEMM as gemm.cu computed by CTA PAIRS (tcgen05 cta_group::2).
+//
+// Why: with one CTA per 128x256 tile every k-block moves 48 KB into shared memory (TMA) and the four
+// MMAs read 48 KB back, ~96 + 96 B/clk against a 128 B/clk shared-memory port — ncu shows the tensor
+// pipe capped near 75 % (profiles/ncu_summary_r1.md). A CTA pair computes a 256x256 tile: each CTA
+// stages its own 128 rows of A and only HALF of the B tile (32 KB per k-block instead of 48), the
+// tensor cores of both SMs read B from both shared memories, and each CTA ends up with its 128x256
+// slice of the accumulator in its own TMEM.
+//
+//   C[M,N] = alpha * ( A[M,K] · op(B) + A2[M,K2] · op(B2) ) (+ R)      16-bit or fp32 output
+//   B K-major ([N,K], x·W^T) or MN-major ([K,N], dy·W); K-extension (LoRA) as in gemm.cu.
+//
+// Roles per CTA: warp 0 TMA producer (each CTA loads its own halves; completion bytes of BOTH CTAs land
+// on the leader's "full" barrier), warp 1 = TMEM allocator (both CTAs) + MMA issuer (leader only; its
+// tcgen05.commit multicasts the "slot free" / "accumulator ready" arrivals to both CTAs), warps 2-5 =
+// epilogue on the CTA's own 128 accumulator rows. Every wait is bounded: on timeout the kernel traps
+// instead of hanging the GPU.
+#include "common.cuh"
+
+namespace {
+
+constexpr int BM = 128;      // rows per CTA (256 per pair)
+constexpr int BN = 256;      // columns per pair (128 B-rows staged per CTA)
+constexpr int BK = 64;
+constexpr int UMMA_K = 16;
+constexpr int NUM_THREADS = 192;
+constexpr int A_BYTES = BM * BK * 2;          // 16 KB
+constexpr int B_BYTES = (BN / 2) * BK * 2;    // 16 KB (this CTA's half of the B tile)
+constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
+constexpr int STAGES = 6;
+constexpr int TMEM_COLS = 512;                // two accumulator stages of 256 columns
+constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + 256 + 1024;
+constexpr long long WAIT_LIMIT = 4000000000LL;   // ~2 s
+
+struct Gemm2Params {
+  int M, N;
+  int nmb2, nnb;          // 256-row / 256-col tile counts
+  int nkb_main, nkb_ext;
+  void* C;
+  const void* R;
+  long long ldc, ldr;
+  int out_dtype, in_dtype;
+  int accumulate;
+  int vec_ok;
+  float alpha;
+  uint32_t idesc;
+};
+
+__device__ __forceinline__ uint32_t cluster_ctarank() {
+  uint32_t r;
+  asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r));
+  return r;
+}
+__device__ __forceinline__ void cluster_sync_all() {
+  asm volatile("barrier.cluster.arrive.release.aligned;" ::: "memory");
+  asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory");
+}
+__device__ __forceinline__ uint32_t mapa_rank(uint32_t smem_addr, uint32_t rank) {
+  uint32_t r;
+  asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(r) : "r"(smem_addr), "r"(rank));
+  return r;
+}
+__device__ __forceinline__ void mbar_wait_bounded(uint32_t bar, uint32_t parity) {
+  const long long t0 = clock64();
+  while (!mbar_try_wait(bar, parity)) {
+    if (clock64() - t0 > WAIT_LIMIT) asm volatile("trap;");
+  }
+}
+__device__ __forceinline__ void mbar_arrive_cluster(uint32_t cluster_addr) {
+  asm volatile("mbarrier.arrive.release.cluster.shared::cluster.b64 _, [%0];" ::"r"(cluster_addr) : "memory");
+}
+// TMA load whose completion bytes are signalled on a barrier that may live in the peer CTA.
+__device__ __forceinline__ void tma_load_2d_2sm(uint32_t dst_smem, const CUtensorMap* m, uint32_t bar_cluster,
+                                                int c0, int c1) {
+  asm volatile(
+      "cp.async.bulk.tensor.2d.cta_group::2.shared::cluster.global.tile.mbarrier::complete_tx::bytes "
+      "[%0], [%1, {%3, %4}], [%2];" ::"r"(dst_smem),
+      "l"(reinterpret_cast<uint64_t>(m)), "r"(bar_cluster), "r"(c0), "r"(c1)
+      : "memory");
+}
+__device__ __forceinline__ void tmem_alloc2(uint32_t dst_smem_addr, uint32_t ncols) {
+  asm volatile("tcgen05.alloc.cta_group::2.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(dst_smem_addr), "r"(ncols) : "memory");
+}
+__device__ __forceinline__ void tmem_relinquish2() {
+  asm volatile("tcgen05.relinquish_alloc_permit.cta_group::2.sync.aligned;" ::: "memory");
+}
+__device__ __forceinline__ void tmem_dealloc2(uint32_t taddr, uint32_t ncols) {
+  asm volatile("tcgen05.dealloc.cta_group::2.sync.aligned.b32 %0, %1;" ::"r"(taddr), "r"(ncols) : "memory");
+}
+__device__ __forceinline__ void umma_f16_ss_2sm(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc, uint32_t idesc,
+                                                uint32_t accumulate) {
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "setp.ne.b32 p, %4, 0;\n\t"
+      "tcgen05.mma.cta_group::2.kind::f16 [%0], %1, %2, %3, p;\n\t}" ::"r"(tmem_d),
+      "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate)
+      : "memory");
+}
+// arrive on the barrier at this smem offset in BOTH CTAs of the pair once prior MMAs retire
+__device__ __forceinline__ void umma_commit_2sm(uint32_t bar) {
+  const uint16_t mask = 3;
+  asm volatile(
+      "tcgen05.commit.cta_group::2.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;" ::"r"(bar),
+      "h"(mask)
+      : "memory");
+}
+
+template <bool B_MN>
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(NUM_THREADS, 1)
+gemm2_kernel(const Gemm2Params p, const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
+             const __grid_constant__ CUtensorMap tmA2, const __grid_constant__ CUtensorMap tmB2) {
+  extern __shared__ uint8_t smem_raw[];
+  const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;
+  const uint32_t bar_base = smem_base + STAGES * STAGE_BYTES;
+  auto full_bar = [&](int s) { return bar_base + 8u * s; };
+  auto empty_bar = [&](int s) { return bar_base + 8u * (STAGES + s); };
+  auto tfull_bar = [&](int s) { return bar_base + 8u * (2 * STAGES + s); };
+  auto tempty_bar = [&](int s) { return bar_base + 8u * (2 * STAGES + 2 + s); };
+  const uint32_t tmem_slot = bar_base + 8u * (2 * STAGES + 4);
+  volatile uint32_t* tmem_slot_ptr =
+      reinterpret_cast<volatile uint32_t*>(smem_raw + (tmem_slot - smem_u32(smem_raw)));
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const uint32_t rank = cluster_ctarank();
+  const bool leader = rank == 0;
+  const int cid = blockIdx.x >> 1, ncl = gridDim.x >> 1;
+  const int total_tiles = p.nmb2 * p.nnb;
+  const int nkb_total = p.nkb_main + p.nkb_ext;
+
+  if (warp == 0 && lane == 0) {
+    tma_prefetch_desc(&tmA);
+    tma_prefetch_desc(&tmB);
+    for (int s = 0; s < STAGES; ++s) {
+      mbar_init(full_bar(s), 1);     // leader's copy is the one in use: 1 arrive (expect_tx) + bytes of both CTAs
+      mbar_init(empty_bar(s), 1);    // multicast tcgen05.commit
+    }
+    for (int s = 0; s < 2; ++s) {
+      mbar_init(tfull_bar(s), 1);    // multicast tcgen05.commit
+      mbar_init(tempty_bar(s), 8);   // leader's copy: 4 epilogue warps x 2 CTAs
+    }
+    mbar_fence_init();
+  }
+  cluster_sync_all();
+  if (warp == 1) {
+    tmem_alloc2(tmem_slot, TMEM_COLS);
+    tmem_relinquish2();
+  }
+  tc_fence_before();
+  cluster_sync_all();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot_ptr;
+
+  if (warp == 0) {
+    // ===================== TMA producer (both CTAs) =====================
+    if (lane == 0) {
+      int stage = 0;
+      uint32_t phase = 0;
+      for (int tile = cid; tile < total_tiles; tile += ncl) {
+        const int n_blk = tile / p.nmb2;
+        const int m_blk = tile - n_blk * p.nmb2;
+        const int m0 = m_blk * 2 * BM + (int)rank * BM;          // this CTA's A rows
+        const int n0 = n_blk * BN + (int)rank * (BN / 2);        // this CTA's half of the B tile
+        for (int kb = 0; kb < nkb_total; ++kb) {
+          mbar_wait_bounded(empty_bar(stage), phase ^ 1u);
+          const uint32_t sa = smem_base + stage * STAGE_BYTES;
+          const uint32_t sb = sa + A_BYTES;
+          const uint32_t fb = mapa_rank(full_bar(stage), 0);      // the leader's barrier
+          if (leader) mbar_expect_tx(full_bar(stage), 2 * STAGE_BYTES);
+          const bool ext = kb >= p.nkb_main;
+          const CUtensorMap* ma = ext ? &tmA2 : &tmA;
+          const CUtensorMap* mb = ext ? &tmB2 : &tmB;
+          const int k0 = (ext ? kb - p.nkb_main : kb) * BK;
+          tma_load_2d_2sm(sa, ma, fb, k0, m0);
+          if constexpr (!B_MN) {
+            tma_load_2d_2sm(sb, mb, fb, k0, n0);
+          } else {
+#pragma unroll
+            for (int j = 0; j < (BN / 2) / 64; ++j) tma_load_2d_2sm(sb + j * (BK * 128), mb, fb, n0 + 64 * j, k0);
+          }
+          if (++stage == STAGES) { stage = 0; phase ^= 1u; }
+        }
+      }
+    }
+  } else if (warp == 1) {
+    // ===================== MMA issuer (leader CTA only) =====================
+    if (leader && lane == 0) {
+      int stage = 0;
+      uint32_t phase = 0;
+      int acc = 0;
+      uint32_t acc_phase = 0;
+      for (int tile = cid; tile < total_tiles; tile += ncl) {
+        mbar_wait_bounded(tempty_bar(acc), acc_phase ^ 1u);
+        tc_fence_after();
+        const uint32_t d_tmem = tmem_base + (uint32_t)(acc * BN);
+        for (int kb = 0; kb < nkb_total; ++kb) {
+          mbar_wait_bounded(full_bar(stage), phase);
+          tc_fence_after();
+          const uint32_t sa = smem_base + stage * STAGE_BYTES;
+          const uint32_t sb = sa + A_BYTES;
+#pragma unroll
+          for (int k = 0; k < BK / UMMA_K; ++k) {
+            const uint64_t ad = umma_smem_desc(sa + k * (UMMA_K * 2), 0, 1024);
+            uint64_t bd;
+            if constexpr (!B_MN) bd = umma_smem_desc(sb + k * (UMMA_K * 2), 0, 1024);
+            else                 bd = umma_smem_desc(sb + k * (UMMA_K * 128), BK * 128, 1024);
+            umma_f16_ss_2sm(d_tmem, ad, bd, p.idesc, (kb > 0 || k > 0) ? 1u : 0u);
+          }
+          umma_commit_2sm(empty_bar(stage));
+          if (kb == nkb_total - 1) umma_commit_2sm(tfull_bar(acc));
+          if (++stage == STAGES) { stage = 0; phase ^= 1u; }
+        }
+        if (++acc == 2) { acc = 0; acc_phase ^= 1u; }
+      }
+    }
+  } else {
+    // ===================== epilogue (both CTAs; own 128 rows x 256 columns) =====================
+    const int quarter = warp & 3;
+    int acc = 0;
+    uint32_t acc_phase = 0;
+    const uint32_t leader_tempty0 = mapa_rank(tempty_bar(0), 0), leader_tempty1 = mapa_rank(tempty_bar(1), 0);
+    for (int tile = cid; tile < total_tiles; tile += ncl) {
+      const int n_blk = tile / p.nmb2;
+      const int m_blk = tile - n_blk * p.nmb2;
+      const int row = m_blk * 2 * BM + (int)rank * BM + quarter * 32 + lane;
+      const int n0 = n_blk * BN;
+      mbar_wait_bounded(tfull_bar(acc), acc_phase);
+      tc_fence_after();
+      const uint32_t t_row = tmem_base + ((uint32_t)(quarter * 32) << 16) + (uint32_t)(acc * BN);
+#pragma unroll 1
+      for (int c = 0; c < BN / 32; ++c) {
+        const int col0 = n0 + c * 32;
+        if (col0 >= p.N) break;
+        uint32_t v[32];
+        tmem_ld_32x32b_x32(t_row + c * 32, v);
+        tmem_wait_ld();
+        if (row < p.M) {
+          float f[32];
+#pragma unroll
+          for (int i = 0; i < 32; ++i) f[i] = __uint_as_float(v[i]) * p.alpha;
+          const bool full = (col0 + 32 <= p.N) && p.vec_ok;
+          if (p.out_dtype == DLTI_FP32) {
+            float* crow = reinterpret_cast<float*>(p.C) + (long long)row * p.ldc + col0;
+            if (full) {
+#pragma unroll
+              for (int i = 0; i < 8; ++i) {
+                float4 o = make_float4(f[4 * i], f[4 * i + 1], f[4 * i + 2], f[4 * i + 3]);
+                float4* dst = reinterpret_cast<float4*>(crow) + i;
+                if (p.accumulate) {
+                  float4 old = *dst;
+                  o.x += old.x; o.y += old.y; o.z += old.z; o.w += old.w;
+                }
+                *dst = o;
+              }
+            } else {
+              for (int i = 0; i < 32; ++i)
+                if (col0 + i < p.N) crow[i] = p.accumulate ? crow[i] + f[i] : f[i];
+            }
+          } else {
+            uint16_t* crow = reinterpret_cast<uint16_t*>(p.C) + (long long)row * p.ldc + col0;
+            const uint16_t* rrow =
+                p.R ? reinterpret_cast<const uint16_t*>(p.R) + (long long)row * p.ldr + col0 : nullptr;
+            const bool bf = p.out_dtype == DLTI_BF16;
+            if (full) {
+              if (rrow) {
+#pragma unroll
+                for (int i = 0; i < 4; ++i) {
+                  int4 rv = *(reinterpret_cast<const int4*>(rrow) + i);
+                  const uint32_t* ru = reinterpret_cast<const uint32_t*>(&rv);
+#pragma unroll
+                  for (int j = 0; j < 4; ++j) {
+                    float2 r2 = bf ? Cvt<__nv_bfloat16>::unpack2(ru[j]) : Cvt<__half>::unpack2(ru[j]);
+                    f[8 * i + 2 * j] += r2.x;
+                    f[8 * i + 2 * j + 1] += r2.y;
+                  }
+                }
+              }
+#pragma unroll
+              for (int i = 0; i < 4; ++i) {
+                int4 o;
+                uint32_t* ou = reinterpret_cast<uint32_t*>(&o);
+#pragma unroll
+                for (int j = 0; j < 4; ++j)
+                  ou[j] = bf ? Cvt<__nv_bfloat16>::pack2(f[8 * i + 2 * j], f[8 * i + 2 * j + 1])
+                             : Cvt<__half>::pack2(f[8 * i + 2 * j], f[8 * i + 2 * j + 1]);
+                *(reinterpret_cast<int4*>(crow) + i) = o;
+              }
+            } else {
+              for (int i = 0; i < 32; ++i) {
+                if (col0 + i < p.N) {
+                  float x = f[i];
+                  if (rrow)
+                    x += bf ? __bfloat162float(*reinterpret_cast<const __nv_bfloat16*>(rrow + i))
+                            : __half2float(*reinterpret_cast<const __half*>(rrow + i));
+                  if (bf) *reinterpret_cast<__nv_bfloat16*>(crow + i) = __float2bfloat16_rn(x);
+                  else    *reinterpret_cast<__half*>(crow + i) = __float2half_rn(x);
+                }
+              }
+            }
+          }
+        }
+      }
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive_cluster(acc == 0 ? leader_tempty0 : leader_tempty1);
+      if (++acc == 2) { acc = 0; acc_phase ^= 1u; }
+    }
+  }
+
+  tc_fence_before();
+  cluster_sync_all();      // the peer's tensor core may still be reading this CTA's shared memory until here
+  if (warp == 1) {
+    tc_fence_after();
+    tmem_dealloc2(tmem_base, TMEM_COLS);
+  }
+}
+
+template <bool B_MN>
+int launch2(const Gemm2Params& p, const CUtensorMap& a, const CUtensorMap& b, const CUtensorMap& a2,
+            const CUtensorMap& b2, int grid, cudaStream_t stream) {
+  static bool configured[64] = {false};
+  int dev = 0;
+  cudaGetDevice(&dev);
+  if (!configured[dev & 63]) {
+    DLTI_CUDA_CHECK(cudaFuncSetAttribute(gemm2_kernel<B_MN>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES));
+    configured[dev & 63] = true;
+  }
+  gemm2_kernel<B_MN><<<grid, NUM_THREADS, SMEM_BYTES, stream>>>(p, a, b, a2, b2);
+  dlti_count_launch();
+  return (int)cudaGetLastError();
+}
+
+}  // namespace
+
+// Same contract as dlti_gemm restricted to: A K-major, no split-K. Returns DLTI_ERR_UNSUPPORTED for
+// configurations it does not cover (the caller then uses the 1-CTA kernel).
+DLTI_API int dlti_gemm_2cta(const void* A, const void* B, void* C, const void* R, int M, int N, int K,
+                            long long lda, long long ldb, long long ldc, long long ldr, int b_mn,
+                            const void* A2, const void* B2, int K2, long long lda2, long long ldb2,
+                            int in_dtype, int out_dtype, float alpha, int accumulate, cudaStream_t stream) {
+  if (M <= 0 || N <= 0 || K <= 0) return DLTI_ERR_BAD_ARG;
+  if (in_dtype != DLTI_BF16 && in_dtype != DLTI_FP16) return DLTI_ERR_UNSUPPORTED;
+  if (K2 % BK) return DLTI_ERR_BAD_ARG;
+  if (out_dtype != DLTI_FP32 && accumulate) return DLTI_ERR_BAD_ARG;
+  Gemm2Params p{};
+  p.M = M; p.N = N;
+  p.nmb2 = (M + 2 * BM - 1) / (2 * BM);
+  p.nnb = (N + BN - 1) / BN;
+  p.nkb_main = (K + BK - 1) / BK;
+  p.nkb_ext = (A2 && B2) ? K2 / BK : 0;
+  p.C = C; p.R = R; p.ldc = ldc; p.ldr = ldr;
+  p.out_dtype = out_dtype; p.in_dtype = in_dtype; p.accumulate = accumulate;
+  const int ob = out_dtype == DLTI_FP32 ? 4 : 2;
+  p.vec_ok = ((reinterpret_cast<uintptr_t>(C) & 15) == 0) && ((ldc * ob) % 16 == 0) &&
+             (!R || (((reinterpret_cast<uintptr_t>(R) & 15) == 0) && ((ldr * 2) % 16 == 0)));
+  p.alpha = alpha;
+  p.idesc = umma_idesc_f16(in_dtype, 2 * BM, BN, false, b_mn != 0);
+  CUtensorMap ta, tb, ta2, tb2;
+  int rc;
+  if ((rc = dlti_make_tmap_2d(&ta, A, K, M, lda, 64, BM, 2, 128))) return rc;
+  rc = b_mn ? dlti_make_tmap_2d(&tb, B, N, K, ldb, 64, 64, 2, 128) : dlti_make_tmap_2d(&tb, B, K, N, ldb, 64, BN / 2, 2, 128);
+  if (rc) return rc;
+  ta2 = ta; tb2 = tb;
+  if (p.nkb_ext > 0) {
+    if ((rc = dlti_make_tmap_2d(&ta2, A2, K2, M, lda2, 64, BM, 2, 128))) return rc;
+    rc = b_mn ? dlti_make_tmap_2d(&tb2, B2, N, K2, ldb2, 64, 64, 2, 128)
+              : dlti_make_tmap_2d(&tb2, B2, K2, N, ldb2, 64, BN / 2, 2, 128);
+    if (rc) return rc;
+  }
+  int grid = dlti_num_sms() & ~1;
+  const int total = p.nmb2 * p.nnb;
+  if (2 * total < grid) grid = 2 * total;
+  return b_mn ? launch2<true>(p, ta, tb, ta2, tb2, grid, stream) : launch2<false>(p, ta, tb, ta2, tb2, grid, stream);
+}

@@ -53,7 +53,7 @@ SPECS = {
                            "./checkpoints/baseline_1gpu", 1, 16, None, None, False, False, "epoch", 500, 2, True),
     "zero1": ScriptSpec("zero1", "Fine-tune with ZeRO-1 (optimizer-state partitioning)",
                         "./checkpoints/deepspeed_zero1", 1, 16, "--deepspeed_config",
-                        "./configs/ds_config_zero1.json", False, True, "steps", 100, 3, False),
+                        "./configs/ds_config_zero1.json", False, True, "steps", 100, 3, True),   # metrics row added (reference zero1 wrote none)
     "zero2": ScriptSpec("zero2", "Fine-tune with ZeRO-2 (+ gradient partitioning)", None, 1, 1,
                         "--deepspeed_config", "./configs/ds_config_zero2.json", False, True, "steps", 100, 3, True),
     "zero3": ScriptSpec("zero3", "Fine-tune with ZeRO-3 (+ parameter partitioning, optional CPU offload)",

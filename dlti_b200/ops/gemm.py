@@ -12,6 +12,7 @@ Replaces torch.nn.functional.linear / cuBLAS in the reference stack (SURVEY.md N
 from __future__ import annotations
 
 import ctypes as C
+import os
 
 import torch
 
@@ -49,12 +50,18 @@ def _gemm_fn():
         C.c_int, C.c_int, C.c_float, C.c_int, C.c_int, C.c_int, C.c_int, C.c_void_p])
 
 
+_TWO_CTA_DEFAULT = os.environ.get("DLTI_GEMM_2CTA", "0") == "1"
+
+
 def gemm(a: torch.Tensor, b: torch.Tensor, *, a_mn: bool = False, b_mn: bool = False,
          a2: torch.Tensor | None = None, b2: torch.Tensor | None = None,
          residual: torch.Tensor | None = None, out: torch.Tensor | None = None,
          out_dtype: torch.dtype | None = None, alpha: float = 1.0, accumulate: bool = False,
-         split_k: int = 1, block_n: int = 0, max_ctas: int = 0, gather=None, push=None) -> torch.Tensor:
-    """gather: optional parallel.fused.GatherSpec — `b` is then the local staging buffer of a row-
+         split_k: int = 1, block_n: int = 0, max_ctas: int = 0, gather=None, push=None,
+         two_cta: bool | None = None) -> torch.Tensor:
+    """two_cta: run the CTA-pair (tcgen05 cta_group::2) kernel of csrc/gemm2.cu; None = the
+    DLTI_GEMM_2CTA environment default, applied only to shapes with M >= 512 and N >= 256.
+    gather: optional parallel.fused.GatherSpec — `b` is then the local staging buffer of a row-
     sharded weight and the kernel pulls the shards from their owner ranks while it computes (K1)."""
     if not _lib.use_native(a, b):
         return gemm_ref(a, b, a_mn=a_mn, b_mn=b_mn, a2=a2, b2=b2, residual=residual, out=out,
@@ -103,6 +110,22 @@ def gemm(a: torch.Tensor, b: torch.Tensor, *, a_mn: bool = False, b_mn: bool = F
                gather.peer_arr, _lib.ptr(gather.counters), int(gather.epoch), gather.rank, gather.world,
                gather.rows_per_rank, _lib.ptr(gather.err), _lib.stream_ptr())
         _lib.check(rc, "dlti_gemm_gather")
+        return out
+    if two_cta is None:
+        two_cta = _TWO_CTA_DEFAULT and M >= 512 and N >= 256
+    if two_cta and not a_mn and split_k == 1:
+        f = _lib.fn("dlti_gemm_2cta", [
+            C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int,
+            C.c_longlong, C.c_longlong, C.c_longlong, C.c_longlong, C.c_int,
+            C.c_void_p, C.c_void_p, C.c_int, C.c_longlong, C.c_longlong,
+            C.c_int, C.c_int, C.c_float, C.c_int, C.c_void_p])
+        rc = f(_lib.ptr(a), _lib.ptr(b), _lib.ptr(out), _lib.ptr(residual), M, N, K,
+               a.stride(0), b.stride(0), out.stride(0), residual.stride(0) if residual is not None else 0,
+               int(b_mn), _lib.ptr(a2), _lib.ptr(b2), K2,
+               a2.stride(0) if a2 is not None else 0, b2.stride(0) if b2 is not None else 0,
+               _lib.dtype_code(a.dtype), _lib.dtype_code(out_dtype), float(alpha), int(accumulate),
+               _lib.stream_ptr())
+        _lib.check(rc, "dlti_gemm_2cta")
         return out
     rc = _gemm_fn()(
         _lib.ptr(a), _lib.ptr(b), _lib.ptr(out), _lib.ptr(residual), M, N, K,

@@ -20,9 +20,11 @@ def _pct(xs, p):
     return xs[min(len(xs) - 1, int(round(p / 100 * (len(xs) - 1))))]
 
 
-async def _one(session, url, model, prompt_ids, max_tokens, rec):
+async def _one(session, url, model, prompt_ids, max_tokens, rec, extra=None):
     body = {"model": model, "prompt": prompt_ids, "max_tokens": max_tokens, "temperature": 0.0,
             "ignore_eos": True, "stream": True}
+    if extra:
+        body.update(extra)
     t0 = time.perf_counter()
     first = None
     n = 0
@@ -60,7 +62,7 @@ async def _one(session, url, model, prompt_ids, max_tokens, rec):
 
 
 async def run_load(base_url: str, model: str, concurrency: int, num_requests: int, input_len: int = 512,
-                   output_len: int = 128, vocab: int = 32000, seed: int = 0) -> dict:
+                   output_len: int = 128, vocab: int = 32000, seed: int = 0, extra: dict | None = None) -> dict:
     import aiohttp
 
     rng = random.Random(seed)
@@ -75,7 +77,7 @@ async def run_load(base_url: str, model: str, concurrency: int, num_requests: in
                 if not pending:
                     return
                 p = pending.pop()
-            await _one(session, url, model, p, output_len, rec)
+            await _one(session, url, model, p, output_len, rec, extra)
 
     timeout = aiohttp.ClientTimeout(total=3600)
     t0 = time.perf_counter()

@@ -147,6 +147,93 @@ int dlti_attn_bwd(const void* dout, const void* qkv, const void* out, const floa
                   long long T_total, int H, int KV, int hd, float scale, int dtype,
                   dlti_stream_t stream);
 
+/* ---- K2 (CTA-pair form): same contract as dlti_gemm with A K-major and no split-K, computed by
+ * tcgen05 cta_group::2 pairs (256x256 tile per pair, each CTA stages half of the B tile). */
+int dlti_gemm_2cta(const void* A, const void* B, void* C, const void* R, int M, int N, int K,
+                   long long lda, long long ldb, long long ldc, long long ldr, int b_mn, const void* A2,
+                   const void* B2, int K2, long long lda2, long long ldb2, int in_dtype, int out_dtype,
+                   float alpha, int accumulate, dlti_stream_t stream);
+
+/* ---- Decode-sized GEMM (M <= 256): swap-AB (the weight is the 128-row tensor-core operand), K split
+ * over CTAs, fp32 partials reduced with atomics into acc32[M,N] (must be zero on entry);
+ * dlti_skinny_finish converts acc32 -> out and re-zeroes it. Replaces the cuBLAS GEMV/GEMM calls of the
+ * vLLM decode path. */
+int dlti_gemm_skinny(const void* X, const void* W, float* acc32, int M, int N, int K, long long ldx,
+                     long long ldw, int in_dtype, int split_k, dlti_stream_t stream);
+int dlti_skinny_finish(float* acc32, void* out, long long rows, int cols, long long out_stride, int dtype,
+                       dlti_stream_t stream);
+
+/* ---- Peer memory plumbing (symmetric arena fallbacks): CUDA IPC handle export/open/close and the
+ * base/size of the allocation that contains a pointer. */
+int dlti_ipc_get_handle(const void* dev_ptr, void* handle_out_64);
+int dlti_ipc_open(const void* handle_64, void** out_ptr);
+int dlti_ipc_close(void* ptr);
+int dlti_mem_base(const void* dev_ptr, void** base_out, unsigned long long* size_out);
+
+/* ---- K1/K9/K10/K11: fused compute + collective kernels over NVLink peer memory. All pointer tables
+ * are DEVICE arrays of `world` peer pointers (index = rank); `err_flag` receives a non-zero code when a
+ * bounded wait expires (the kernels never spin forever). Replace NCCL all-gather / reduce-scatter /
+ * all-reduce in DeepSpeed ZeRO and vLLM TP. */
+int dlti_comm_max_ranks(void);
+/* all ranks arrive on `channel` with a host-chosen epoch (eager) or a device-side counter (graph-safe) */
+int dlti_peer_barrier(const void* const* signal_pads, int rank, int world, int channel,
+                      unsigned int epoch, int* err_flag, dlti_stream_t stream);
+int dlti_peer_barrier_auto(const void* const* signal_pads, int rank, int world, int channel,
+                           unsigned int* device_counter, int* err_flag, dlti_stream_t stream);
+/* pull-based all-gather of equally sized row shards into `out` (K1 stand-alone form) */
+int dlti_allgather_rows(const void* const* shards, void* out, long long shard_bytes, int rank, int world,
+                        int blocks_per_peer, dlti_stream_t stream);
+/* K1: C = A · op(gathered B): B is row-sharded over `world` ranks; gather warps inside the GEMM pull
+ * the shards into B_staging (own rows are read in place) and publish per-unit counters (= epoch*16)
+ * that the TMA producer waits on, so the transfer overlaps the math tile by tile. */
+int dlti_gemm_gather(const void* A, void* B_staging, void* C, const void* R, int M, int N, int K,
+                     long long lda, long long ldb, long long ldc, long long ldr, int b_mn, const void* A2,
+                     const void* B2, int K2, long long lda2, long long ldb2, int in_dtype, int out_dtype,
+                     float alpha, int block_n, int max_ctas, const void* const* peer_shards,
+                     unsigned int* counters, unsigned int epoch, int rank, int world, int rows_per_rank,
+                     int* err_flag, dlti_stream_t stream);
+/* K10: row-parallel GEMM whose epilogue stores the partial tile into slot `rank` of every peer's
+ * receive buffer [world, slot_stride] (followed by a barrier and dlti_tp_reduce_add_norm). */
+int dlti_gemm_push(const void* A, const void* B, int M, int N, int K, long long lda, long long ldb,
+                   long long ldc, int in_dtype, int block_n, const void* const* recv_peers, int rank,
+                   int world, long long slot_stride, dlti_stream_t stream);
+/* K11: residual += sum over ranks (fixed order) of the received partials; y = rmsnorm(residual) * w */
+int dlti_tp_reduce_add_norm(const void* recv, long long slot_stride, int world, void* residual,
+                            const void* w, void* y, long long rows, int d, float eps, int dtype,
+                            dlti_stream_t stream);
+/* K9: reduce-scatter by pull: part[0:n] += sum over ranks of grads[r][lo:lo+n] (fixed rank order) */
+int dlti_rs_accumulate(const void* const* grads, float* part, long long lo, long long n, int world,
+                       dlti_stream_t stream);
+/* K9: all-reduce of one fp32 scalar (the grad-norm partial) through per-rank boards + signal pads */
+int dlti_sumsq_exchange(const float* local, const void* const* boards, const void* const* signal_pads,
+                        int rank, int world, int channel, unsigned int epoch, float* out, int* err_flag,
+                        dlti_stream_t stream);
+/* K9: AdamW on this rank's fp32 partition whose updated values are pushed into every rank's fp32
+ * master copy (the all-gather of ZeRO-1/2 folded into the optimizer kernel). */
+int dlti_adamw_push(const void* const* masters, float* m, float* v, float* g, long long lo, long long n,
+                    int rank, int world, float lr, float b1, float b2, float eps, float wd, int step,
+                    const float* gnorm_sq, float inv_scale, float max_norm, int* skipped_out,
+                    dlti_stream_t stream);
+
+/* ---- Serving kernels (replace vLLM's rotary_embedding + reshape_and_cache,
+ * paged_attention_v2 and the sampler). */
+/* RoPE on q,k in place + write of the rotated k and v rows into the paged cache slots (one kernel) */
+int dlti_rope_cache(void* qkv, const int* pos, const float* cos_t, const float* sin_t,
+                    const long long* slot_mapping, void* k_cache, void* v_cache, long long tokens, int H,
+                    int KV, int hd, long long row_stride, int dtype, dlti_stream_t stream);
+/* split-KV paged decode attention; workspace holds per-split (m, l, acc) in fp32 */
+int dlti_paged_decode_workspace_floats(int batch, int H, int splits);
+int dlti_paged_decode(const void* q, long long q_stride, const void* k_cache, const void* v_cache,
+                      const int* block_tables, int max_blocks, const int* ctx_lens, int batch,
+                      int block_size, int H, int KV, int hd, float scale, int splits, float* workspace,
+                      void* out, long long out_stride, int dtype, dlti_stream_t stream);
+/* temperature / top-k / top-p / greedy sampling, one CTA per sequence, counter-based RNG keyed by
+ * (seeds[b], step); out_logprob may be NULL */
+int dlti_sample(const void* logits, long long ld, int batch, int V, const float* temperature,
+                const int* top_k, const float* top_p, const unsigned long long* seeds,
+                unsigned long long step, long long* out, float* out_logprob, int dtype,
+                dlti_stream_t stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -49,6 +49,9 @@ def main():
         for bn in (256, 128):
             t = timeit(lambda i: gemm(a[i % 2], w[i], out=out, block_n=bn), nbuf)
             res[f"dlti_nt_bn{bn}_tflops"] = fl / t / 1e9
+        if os.environ.get("BENCH_2CTA", "1") == "1":
+            t = timeit(lambda i: gemm(a[i % 2], w[i], out=out, two_cta=True), nbuf)
+            res["dlti_nt_2cta_tflops"] = fl / t / 1e9
         t = timeit(lambda i: torch.matmul(a[i % 2], w[i].t(), out=out), nbuf)
         res["cublas_nt_tflops"] = fl / t / 1e9
         # dX form: dy[m,n] @ W[n,k] -> [m,k]
@@ -56,6 +59,9 @@ def main():
         dx = torch.empty(m, k, device="cuda", dtype=torch.bfloat16)
         t = timeit(lambda i: gemm(dy[i % 2], w[i], b_mn=True, out=dx), nbuf)
         res["dlti_nn_tflops"] = fl / t / 1e9
+        if os.environ.get("BENCH_2CTA", "1") == "1":
+            t = timeit(lambda i: gemm(dy[i % 2], w[i], b_mn=True, out=dx, two_cta=True), nbuf)
+            res["dlti_nn_2cta_tflops"] = fl / t / 1e9
         t = timeit(lambda i: torch.matmul(dy[i % 2], w[i], out=dx), nbuf)
         res["cublas_nn_tflops"] = fl / t / 1e9
         res["frac_of_measured_peak"] = max(res["dlti_nt_bn256_tflops"], res["dlti_nt_bn128_tflops"]) / peak

@@ -206,3 +206,18 @@ def test_philox_known_answer():
     assert [int(x[0]) for x in r] == [0x6627E8D5, 0xE169C58D, 0xBC57AC4C, 0x9B00DBD8]
     m = keep_mask(64, 128, 0.05, 1, 2)
     assert 0.02 < 1 - m.float().mean().item() < 0.09
+
+
+def test_public_header_declares_every_entry_point():
+    """include/dlti_b200.h is the C ABI contract: every DLTI_API definition in csrc/ must be declared."""
+    import re
+    from pathlib import Path
+    root = Path(__file__).resolve().parent.parent
+    header = (root / "include" / "dlti_b200.h").read_text()
+    declared = set(re.findall(r"\b(dlti_[a-z0-9_]+)\s*\(", header))
+    defined = set()
+    for src in list((root / "dlti_b200" / "csrc").glob("*.cu")) + list((root / "dlti_b200" / "csrc").glob("*.cpp")):
+        defined |= set(re.findall(r"DLTI_API\s+[a-zA-Z_ ]+\**\s*(dlti_[a-z0-9_]+)\s*\(", src.read_text()))
+    assert defined, "no entry points found"
+    missing = sorted(defined - declared)
+    assert not missing, f"undeclared entry points: {missing}"

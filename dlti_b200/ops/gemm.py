@@ -50,7 +50,7 @@ def _gemm_fn():
         C.c_int, C.c_int, C.c_float, C.c_int, C.c_int, C.c_int, C.c_int, C.c_void_p])
 
 
-_TWO_CTA_DEFAULT = os.environ.get("DLTI_GEMM_2CTA", "0") == "1"
+_TWO_CTA_DEFAULT = os.environ.get("DLTI_GEMM_2CTA", "1") == "1"
 
 
 def gemm(a: torch.Tensor, b: torch.Tensor, *, a_mn: bool = False, b_mn: bool = False,
@@ -60,7 +60,7 @@ def gemm(a: torch.Tensor, b: torch.Tensor, *, a_mn: bool = False, b_mn: bool = F
          split_k: int = 1, block_n: int = 0, max_ctas: int = 0, gather=None, push=None,
          two_cta: bool | None = None) -> torch.Tensor:
     """two_cta: run the CTA-pair (tcgen05 cta_group::2) kernel of csrc/gemm2.cu; None = the
-    DLTI_GEMM_2CTA environment default, applied only to shapes with M >= 512 and N >= 256.
+    DLTI_GEMM_2CTA environment default (on), applied to shapes with at least 64 256x256 tiles.
     gather: optional parallel.fused.GatherSpec — `b` is then the local staging buffer of a row-
     sharded weight and the kernel pulls the shards from their owner ranks while it computes (K1)."""
     if not _lib.use_native(a, b):
@@ -112,7 +112,7 @@ def gemm(a: torch.Tensor, b: torch.Tensor, *, a_mn: bool = False, b_mn: bool = F
         _lib.check(rc, "dlti_gemm_gather")
         return out
     if two_cta is None:
-        two_cta = _TWO_CTA_DEFAULT and M >= 512 and N >= 256
+        two_cta = _TWO_CTA_DEFAULT and block_n == 0 and max_ctas == 0 and ((M + 255) // 256) * ((N + 255) // 256) >= 64
     if two_cta and not a_mn and split_k == 1:
         f = _lib.fn("dlti_gemm_2cta", [
             C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int,

@@ -104,3 +104,24 @@ def test_gemm_skinny_decode(M, N, K):
         y = gemm_skinny(x, w)
         _check(y, gemm_ref(x, w, out_dtype=torch.float32))
     assert _skinny_ws["cuda:0"][: M * N].abs().max().item() == 0.0
+
+
+@pytest.mark.parametrize("dtype", [torch.bfloat16, torch.float16])
+@pytest.mark.parametrize("b_mn", [False, True])
+@pytest.mark.parametrize("M,N,K", [(256, 256, 64), (300, 520, 200), (1000, 776, 328), (4096, 4096, 4096),
+                                   (2048, 12288, 1024)])
+def test_gemm_cta_pair(M, N, K, b_mn, dtype):
+    """csrc/gemm2.cu (tcgen05 cta_group::2): residual, alpha, LoRA K-extension, fp32 accumulate."""
+    torch.manual_seed(5)
+    a = torch.randn(M, K, device="cuda", dtype=dtype)
+    b = torch.randn((K, N) if b_mn else (N, K), device="cuda", dtype=dtype)
+    r = torch.randn(M, N, device="cuda", dtype=dtype)
+    a2 = torch.randn(M, 64, device="cuda", dtype=dtype)
+    b2 = torch.randn((64, N) if b_mn else (N, 64), device="cuda", dtype=dtype)
+    kw = dict(b_mn=b_mn, residual=r, alpha=0.5, a2=a2, b2=b2)
+    _check(gemm(a, b, two_cta=True, **kw), gemm_ref(a, b, out_dtype=torch.float32, **kw))
+    _check(gemm(a, b, two_cta=True, b_mn=b_mn), gemm_ref(a, b, b_mn=b_mn, out_dtype=torch.float32))
+    acc = torch.randn(M, N, device="cuda", dtype=torch.float32)
+    exp = acc + gemm_ref(a, b, b_mn=b_mn, out_dtype=torch.float32)
+    gemm(a, b, b_mn=b_mn, out=acc, accumulate=True, two_cta=True)
+    _check(acc, exp)

@@ -15,6 +15,8 @@
 // tcgen05.commit multicasts the "slot free" / "accumulator ready" arrivals to both CTAs), warps 2-5 =
 // epilogue on the CTA's own 128 accumulator rows. Every wait is bounded: on timeout the kernel traps
 // instead of hanging the GPU.
+#include <cstdlib>
+
 #include "common.cuh"
 
 namespace {
@@ -44,6 +46,55 @@ struct Gemm2Params {
   int vec_ok;
   float alpha;
   uint32_t idesc;
+  // stream-K: tiles [0, sk_tiles) are cut into `gridDim/2` equal ranges of (tile, k-block) iterations,
+  // tiles [sk_tiles, total) are handed out round-robin. sk_tiles == 0 => plain data-parallel schedule.
+  int sk_tiles;
+  long long sk_iters_per_range;
+  float4* sk_ws;            // [ranges][2 CTAs][8 chunks][8 quads][128 rows] float4 partial accumulators
+  unsigned int* sk_flags;   // [ranges] ready counters + [ranges] consumed counters
+};
+
+// One unit of work: k-blocks [kb0, kb1) of one 256x256 tile. kb0 > 0: the tile's head belongs to another
+// cluster -> this piece is written to the workspace; kb1 < nkb: this cluster owns the tile and adds the
+// tail piece from the workspace before the normal epilogue.
+struct Seg {
+  int tile, kb0, kb1;
+};
+struct SegIter {
+  long long it, end;      // stream-K iteration range of this cluster
+  int next_dp, total, step, nkb;
+  __device__ SegIter(const Gemm2Params& p, int cid, int ncl) {
+    nkb = p.nkb_main + p.nkb_ext;
+    total = p.nmb2 * p.nnb;
+    step = ncl;
+    next_dp = p.sk_tiles + cid;
+    if (p.sk_tiles > 0) {
+      const long long all = (long long)p.sk_tiles * nkb;
+      const int r = ncl - 1 - cid;      // range index: a tile's owner has the HIGHER cluster id than its helper
+      it = r * p.sk_iters_per_range;
+      end = it + p.sk_iters_per_range;
+      if (it > all) it = all;
+      if (end > all) end = all;
+    } else {
+      it = end = 0;
+    }
+  }
+  __device__ bool next(Seg& s) {
+    if (it < end) {
+      s.tile = (int)(it / nkb);
+      s.kb0 = (int)(it - (long long)s.tile * nkb);
+      const long long left = end - it;
+      s.kb1 = (left < nkb - s.kb0) ? s.kb0 + (int)left : nkb;
+      it += s.kb1 - s.kb0;
+      return true;
+    }
+    if (next_dp < total) {
+      s.tile = next_dp; s.kb0 = 0; s.kb1 = nkb;
+      next_dp += step;
+      return true;
+    }
+    return false;
+  }
 };
 
 __device__ __forceinline__ uint32_t cluster_ctarank() {
@@ -155,12 +206,14 @@ gemm2_kernel(const Gemm2Params p, const __grid_constant__ CUtensorMap tmA, const
     if (lane == 0) {
       int stage = 0;
       uint32_t phase = 0;
-      for (int tile = cid; tile < total_tiles; tile += ncl) {
-        const int n_blk = tile / p.nmb2;
-        const int m_blk = tile - n_blk * p.nmb2;
+      SegIter segs(p, cid, ncl);
+      Seg sg;
+      while (segs.next(sg)) {
+        const int n_blk = sg.tile / p.nmb2;
+        const int m_blk = sg.tile - n_blk * p.nmb2;
         const int m0 = m_blk * 2 * BM + (int)rank * BM;          // this CTA's A rows
         const int n0 = n_blk * BN + (int)rank * (BN / 2);        // this CTA's half of the B tile
-        for (int kb = 0; kb < nkb_total; ++kb) {
+        for (int kb = sg.kb0; kb < sg.kb1; ++kb) {
           mbar_wait_bounded(empty_bar(stage), phase ^ 1u);
           const uint32_t sa = smem_base + stage * STAGE_BYTES;
           const uint32_t sb = sa + A_BYTES;
@@ -188,11 +241,13 @@ gemm2_kernel(const Gemm2Params p, const __grid_constant__ CUtensorMap tmA, const
       uint32_t phase = 0;
       int acc = 0;
       uint32_t acc_phase = 0;
-      for (int tile = cid; tile < total_tiles; tile += ncl) {
+      SegIter segs(p, cid, ncl);
+      Seg sg;
+      while (segs.next(sg)) {
         mbar_wait_bounded(tempty_bar(acc), acc_phase ^ 1u);
         tc_fence_after();
         const uint32_t d_tmem = tmem_base + (uint32_t)(acc * BN);
-        for (int kb = 0; kb < nkb_total; ++kb) {
+        for (int kb = sg.kb0; kb < sg.kb1; ++kb) {
           mbar_wait_bounded(full_bar(stage), phase);
           tc_fence_after();
           const uint32_t sa = smem_base + stage * STAGE_BYTES;
@@ -203,10 +258,10 @@ gemm2_kernel(const Gemm2Params p, const __grid_constant__ CUtensorMap tmA, const
             uint64_t bd;
             if constexpr (!B_MN) bd = umma_smem_desc(sb + k * (UMMA_K * 2), 0, 1024);
             else                 bd = umma_smem_desc(sb + k * (UMMA_K * 128), BK * 128, 1024);
-            umma_f16_ss_2sm(d_tmem, ad, bd, p.idesc, (kb > 0 || k > 0) ? 1u : 0u);
+            umma_f16_ss_2sm(d_tmem, ad, bd, p.idesc, (kb > sg.kb0 || k > 0) ? 1u : 0u);
           }
           umma_commit_2sm(empty_bar(stage));
-          if (kb == nkb_total - 1) umma_commit_2sm(tfull_bar(acc));
+          if (kb == sg.kb1 - 1) umma_commit_2sm(tfull_bar(acc));
           if (++stage == STAGES) { stage = 0; phase ^= 1u; }
         }
         if (++acc == 2) { acc = 0; acc_phase ^= 1u; }
@@ -218,11 +273,26 @@ gemm2_kernel(const Gemm2Params p, const __grid_constant__ CUtensorMap tmA, const
     int acc = 0;
     uint32_t acc_phase = 0;
     const uint32_t leader_tempty0 = mapa_rank(tempty_bar(0), 0), leader_tempty1 = mapa_rank(tempty_bar(1), 0);
-    for (int tile = cid; tile < total_tiles; tile += ncl) {
-      const int n_blk = tile / p.nmb2;
-      const int m_blk = tile - n_blk * p.nmb2;
+    SegIter segs(p, cid, ncl);
+    Seg sg;
+    const int my_range = ncl - 1 - cid;
+    while (segs.next(sg)) {
+      const int n_blk = sg.tile / p.nmb2;
+      const int m_blk = sg.tile - n_blk * p.nmb2;
       const int row = m_blk * 2 * BM + (int)rank * BM + quarter * 32 + lane;
       const int n0 = n_blk * BN;
+      const bool helper = sg.kb0 > 0;              // write raw partial accumulators to the workspace
+      const bool fixup = sg.kb1 < nkb_total;       // add the helper's partial (range my_range + 1)
+      // float4 index of (chunk 0, quad 0, this thread's row) in the workspace slot used by this segment
+      float4* ws = p.sk_ws + ((size_t)(helper ? my_range : my_range + 1) * 2 + rank) * (size_t)(64 * BM) +
+                   (quarter * 32 + lane);
+      if (fixup) {
+        const unsigned int* flag = p.sk_flags + my_range + 1;
+        const long long t0 = clock64();
+        while (ld_acquire_gpu_u32(flag) < 8u) {
+          if (clock64() - t0 > 5 * WAIT_LIMIT) asm volatile("trap;");
+        }
+      }
       mbar_wait_bounded(tfull_bar(acc), acc_phase);
       tc_fence_after();
       const uint32_t t_row = tmem_base + ((uint32_t)(quarter * 32) << 16) + (uint32_t)(acc * BN);
@@ -233,6 +303,23 @@ gemm2_kernel(const Gemm2Params p, const __grid_constant__ CUtensorMap tmA, const
         uint32_t v[32];
         tmem_ld_32x32b_x32(t_row + c * 32, v);
         tmem_wait_ld();
+        if (helper) {
+#pragma unroll
+          for (int j = 0; j < 8; ++j)
+            ws[(c * 8 + j) * BM] = make_float4(__uint_as_float(v[4 * j]), __uint_as_float(v[4 * j + 1]),
+                                               __uint_as_float(v[4 * j + 2]), __uint_as_float(v[4 * j + 3]));
+          continue;
+        }
+        if (fixup) {
+#pragma unroll
+          for (int j = 0; j < 8; ++j) {
+            const float4 q = __ldcg(ws + (c * 8 + j) * BM);
+            v[4 * j] = __float_as_uint(__uint_as_float(v[4 * j]) + q.x);
+            v[4 * j + 1] = __float_as_uint(__uint_as_float(v[4 * j + 1]) + q.y);
+            v[4 * j + 2] = __float_as_uint(__uint_as_float(v[4 * j + 2]) + q.z);
+            v[4 * j + 3] = __float_as_uint(__uint_as_float(v[4 * j + 3]) + q.w);
+          }
+        }
         if (row < p.M) {
           float f[32];
 #pragma unroll
@@ -302,6 +389,22 @@ gemm2_kernel(const Gemm2Params p, const __grid_constant__ CUtensorMap tmA, const
       tc_fence_before();
       __syncwarp();
       if (lane == 0) mbar_arrive_cluster(acc == 0 ? leader_tempty0 : leader_tempty1);
+      if (helper) {
+        // publish this warp's part of the partial tile (8 warps per tile: 4 per CTA)
+        __threadfence();
+        __syncwarp();
+        if (lane == 0) red_release_gpu_add_u32(p.sk_flags + my_range, 1u);
+      } else if (fixup) {
+        // last of the 8 consumer warps re-arms the slot for the next launch on this stream
+        __syncwarp();
+        if (lane == 0) {
+          const unsigned int done = atomicAdd(p.sk_flags + ncl + my_range + 1, 1u);
+          if (done == 7u) {
+            p.sk_flags[ncl + my_range + 1] = 0u;
+            st_release_gpu_u32(p.sk_flags + my_range + 1, 0u);
+          }
+        }
+      }
       if (++acc == 2) { acc = 0; acc_phase ^= 1u; }
     }
   }
@@ -329,14 +432,50 @@ int launch2(const Gemm2Params& p, const CUtensorMap& a, const CUtensorMap& b, co
   return (int)cudaGetLastError();
 }
 
+// Stream-K workspace: one per (device, stream) so GEMMs on different streams never share partial slots.
+struct SkWorkspace {
+  int dev;
+  cudaStream_t stream;
+  float4* ws;
+  unsigned int* flags;
+};
+constexpr int MAX_SK_WS = 16;
+constexpr int MAX_RANGES = 128;
+SkWorkspace g_sk_ws[MAX_SK_WS];
+int g_sk_ws_count = 0;
+
+const SkWorkspace* sk_workspace(cudaStream_t stream) {
+  int dev = 0;
+  cudaGetDevice(&dev);
+  for (int i = 0; i < g_sk_ws_count; ++i)
+    if (g_sk_ws[i].dev == dev && g_sk_ws[i].stream == stream) return &g_sk_ws[i];
+  if (g_sk_ws_count == MAX_SK_WS) return nullptr;
+  cudaStreamCaptureStatus cap = cudaStreamCaptureStatusNone;
+  if (cudaStreamIsCapturing(stream, &cap) != cudaSuccess || cap != cudaStreamCaptureStatusNone) return nullptr;
+  SkWorkspace w{dev, stream, nullptr, nullptr};
+  const size_t ws_bytes = (size_t)MAX_RANGES * 2 * 64 * BM * sizeof(float4);   // 256 KB per range
+  if (cudaMalloc(&w.ws, ws_bytes) != cudaSuccess) { cudaGetLastError(); return nullptr; }
+  if (cudaMalloc(&w.flags, 2 * MAX_RANGES * sizeof(unsigned int)) != cudaSuccess) {
+    cudaGetLastError();
+    cudaFree(w.ws);
+    return nullptr;
+  }
+  cudaMemset(w.flags, 0, 2 * MAX_RANGES * sizeof(unsigned int));
+  g_sk_ws[g_sk_ws_count] = w;
+  return &g_sk_ws[g_sk_ws_count++];
+}
+
 }  // namespace
 
 // Same contract as dlti_gemm restricted to: A K-major, no split-K. Returns DLTI_ERR_UNSUPPORTED for
-// configurations it does not cover (the caller then uses the 1-CTA kernel).
+// configurations it does not cover (the caller then uses the 1-CTA kernel). stream_k: -1 = automatic
+// (ragged last wave only, and only when DLTI_GEMM_STREAMK=1), 0 = never, 1 = whenever the tile count is
+// not a multiple of the cluster count.
 DLTI_API int dlti_gemm_2cta(const void* A, const void* B, void* C, const void* R, int M, int N, int K,
                             long long lda, long long ldb, long long ldc, long long ldr, int b_mn,
                             const void* A2, const void* B2, int K2, long long lda2, long long ldb2,
-                            int in_dtype, int out_dtype, float alpha, int accumulate, cudaStream_t stream) {
+                            int in_dtype, int out_dtype, float alpha, int accumulate, int stream_k,
+                            cudaStream_t stream) {
   if (M <= 0 || N <= 0 || K <= 0) return DLTI_ERR_BAD_ARG;
   if (in_dtype != DLTI_BF16 && in_dtype != DLTI_FP16) return DLTI_ERR_UNSUPPORTED;
   if (K2 % BK) return DLTI_ERR_BAD_ARG;
@@ -369,5 +508,26 @@ DLTI_API int dlti_gemm_2cta(const void* A, const void* B, void* C, const void* R
   int grid = dlti_num_sms() & ~1;
   const int total = p.nmb2 * p.nnb;
   if (2 * total < grid) grid = 2 * total;
+  // Stream-K for the ragged last wave: when total % clusters leaves the last wave under-filled, the
+  // last (1 + remainder) waves' tiles are cut into equal (tile, k-block) ranges, one per cluster.
+  const int ncl = grid / 2;
+  const int nkb = p.nkb_main + p.nkb_ext;
+  const int rem = total % ncl;
+  // Measured (profiles/streamk_ab_r1.md): on the power-capped B200 the automatic mode LOSES end to end
+  // (774 vs 755 ms/step): the idle SMs of a ragged wave let the clocks rise, and filling them costs
+  // more in frequency than the schedule gains. So automatic stream-K is opt-in (DLTI_GEMM_STREAMK=1).
+  static const bool sk_auto = []() { const char* e = getenv("DLTI_GEMM_STREAMK"); return e && e[0] == '1'; }();
+  if ((stream_k > 0 || (stream_k < 0 && sk_auto)) && rem != 0 && total > ncl && ncl <= MAX_RANGES) {
+    const int waves = (total + ncl - 1) / ncl;
+    const double eff = (double)total / ((double)ncl * waves);
+    if (eff < 0.97 || stream_k > 0) {
+      if (const SkWorkspace* w = sk_workspace(stream)) {
+        p.sk_tiles = rem + ncl;
+        p.sk_iters_per_range = ((long long)p.sk_tiles * nkb + ncl - 1) / ncl;
+        p.sk_ws = w->ws;
+        p.sk_flags = w->flags;
+      }
+    }
+  }
   return b_mn ? launch2<true>(p, ta, tb, ta2, tb2, grid, stream) : launch2<false>(p, ta, tb, ta2, tb2, grid, stream);
 }

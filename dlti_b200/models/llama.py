@@ -177,7 +177,10 @@ class LoraLlama:
         return (self.micro_step << 20) | (li << 4) | site
 
     # ---- one decoder layer -----------------------------------------------------------------
-    def _layer_fwd(self, li: int, lw: LayerWeights, x: torch.Tensor, b: PackedBatch, save: bool):
+    def _layer_fwd(self, li: int, lw: LayerWeights, x: torch.Tensor, b: PackedBatch, save: bool,
+                   need_out: bool = True):
+        """need_out=False (recompute inside backward): stop after gate/up — SwiGLU and the down
+        projection only feed the layer output, which backward never reads."""
         cfg, lo = self.cfg, self.lora
         p = self._drop()
         H, KV, hd = cfg.num_attention_heads, cfg.num_key_value_heads, cfg.head_dim
@@ -199,8 +202,11 @@ class LoraLlama:
         x2 = gemm(attn, lw.w_o, a2=t_o, b2=lo.B_o_c[li] if use_o else None, residual=x, gather=lw.g("w_o"))
         xn2, rstd2, _ = E.rmsnorm_fwd(x2, lw.ln2, cfg.rms_norm_eps)
         gu = gemm(xn2, lw.w_gu, gather=lw.g("w_gu"))
-        h = E.swiglu_fwd(gu)
-        x3 = gemm(h, lw.w_down, residual=x2, gather=lw.g("w_down"))
+        if need_out:
+            h = E.swiglu_fwd(gu)
+            x3 = gemm(h, lw.w_down, residual=x2, gather=lw.g("w_down"))
+        else:
+            x3 = None
         if not save:
             return x3, None
         saved = dict(x=x, rstd1=rstd1, xn=xn, xn_drop=xn_drop, t_qkv=t_qkv, qkv=qkv, attn=attn,
@@ -366,7 +372,7 @@ class LoraLlama:
                 self.micro_step = base_step + k
                 sv = saves[k][li]
                 if sv is None:
-                    _, sv = self._layer_fwd(li, lw, inputs[k][li], b, save=True)
+                    _, sv = self._layer_fwd(li, lw, inputs[k][li], b, save=True, need_out=False)
                 dxs[k] = self._layer_bwd(li, lw, dxs[k], sv, b)
                 saves[k][li] = None
                 inputs[k][li] = None

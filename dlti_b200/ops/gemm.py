@@ -58,9 +58,10 @@ def gemm(a: torch.Tensor, b: torch.Tensor, *, a_mn: bool = False, b_mn: bool = F
          residual: torch.Tensor | None = None, out: torch.Tensor | None = None,
          out_dtype: torch.dtype | None = None, alpha: float = 1.0, accumulate: bool = False,
          split_k: int = 1, block_n: int = 0, max_ctas: int = 0, gather=None, push=None,
-         two_cta: bool | None = None) -> torch.Tensor:
+         two_cta: bool | None = None, stream_k: int = -1) -> torch.Tensor:
     """two_cta: run the CTA-pair (tcgen05 cta_group::2) kernel of csrc/gemm2.cu; None = the
     DLTI_GEMM_2CTA environment default (on), applied to shapes with at least 64 256x256 tiles.
+    stream_k (pair kernel only): -1 automatic (ragged last wave), 0 off, 1 forced.
     gather: optional parallel.fused.GatherSpec — `b` is then the local staging buffer of a row-
     sharded weight and the kernel pulls the shards from their owner ranks while it computes (K1)."""
     if not _lib.use_native(a, b):
@@ -118,13 +119,13 @@ def gemm(a: torch.Tensor, b: torch.Tensor, *, a_mn: bool = False, b_mn: bool = F
             C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int,
             C.c_longlong, C.c_longlong, C.c_longlong, C.c_longlong, C.c_int,
             C.c_void_p, C.c_void_p, C.c_int, C.c_longlong, C.c_longlong,
-            C.c_int, C.c_int, C.c_float, C.c_int, C.c_void_p])
+            C.c_int, C.c_int, C.c_float, C.c_int, C.c_int, C.c_void_p])
         rc = f(_lib.ptr(a), _lib.ptr(b), _lib.ptr(out), _lib.ptr(residual), M, N, K,
                a.stride(0), b.stride(0), out.stride(0), residual.stride(0) if residual is not None else 0,
                int(b_mn), _lib.ptr(a2), _lib.ptr(b2), K2,
                a2.stride(0) if a2 is not None else 0, b2.stride(0) if b2 is not None else 0,
                _lib.dtype_code(a.dtype), _lib.dtype_code(out_dtype), float(alpha), int(accumulate),
-               _lib.stream_ptr())
+               int(stream_k), _lib.stream_ptr())
         _lib.check(rc, "dlti_gemm_2cta")
         return out
     rc = _gemm_fn()(

@@ -148,11 +148,14 @@ int dlti_attn_bwd(const void* dout, const void* qkv, const void* out, const floa
                   dlti_stream_t stream);
 
 /* ---- K2 (CTA-pair form): same contract as dlti_gemm with A K-major and no split-K, computed by
- * tcgen05 cta_group::2 pairs (256x256 tile per pair, each CTA stages half of the B tile). */
+ * tcgen05 cta_group::2 pairs (256x256 tile per pair, each CTA stages half of the B tile). A ragged
+ * last wave is removed by stream-K: the last waves' tiles are cut into equal (tile, k-block) ranges and
+ * the owner of a split tile adds its helper's fp32 partial from a per-stream workspace. */
 int dlti_gemm_2cta(const void* A, const void* B, void* C, const void* R, int M, int N, int K,
                    long long lda, long long ldb, long long ldc, long long ldr, int b_mn, const void* A2,
                    const void* B2, int K2, long long lda2, long long ldb2, int in_dtype, int out_dtype,
-                   float alpha, int accumulate, dlti_stream_t stream);
+                   float alpha, int accumulate, int stream_k /* -1 auto, 0 off, 1 force */,
+                   dlti_stream_t stream);
 
 /* ---- Decode-sized GEMM (M <= 256): swap-AB (the weight is the 128-row tensor-core operand), K split
  * over CTAs, fp32 partials reduced with atomics into acc32[M,N] (must be zero on entry);

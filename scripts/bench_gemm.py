@@ -52,6 +52,8 @@ def main():
         if os.environ.get("BENCH_2CTA", "1") == "1":
             t = timeit(lambda i: gemm(a[i % 2], w[i], out=out, two_cta=True), nbuf)
             res["dlti_nt_2cta_tflops"] = fl / t / 1e9
+            t = timeit(lambda i: gemm(a[i % 2], w[i], out=out, two_cta=True, stream_k=0), nbuf)
+            res["dlti_nt_2cta_nosk_tflops"] = fl / t / 1e9
         t = timeit(lambda i: torch.matmul(a[i % 2], w[i].t(), out=out), nbuf)
         res["cublas_nt_tflops"] = fl / t / 1e9
         # dX form: dy[m,n] @ W[n,k] -> [m,k]
@@ -62,6 +64,8 @@ def main():
         if os.environ.get("BENCH_2CTA", "1") == "1":
             t = timeit(lambda i: gemm(dy[i % 2], w[i], b_mn=True, out=dx, two_cta=True), nbuf)
             res["dlti_nn_2cta_tflops"] = fl / t / 1e9
+            t = timeit(lambda i: gemm(dy[i % 2], w[i], b_mn=True, out=dx, two_cta=True, stream_k=0), nbuf)
+            res["dlti_nn_2cta_nosk_tflops"] = fl / t / 1e9
         t = timeit(lambda i: torch.matmul(dy[i % 2], w[i], out=dx), nbuf)
         res["cublas_nn_tflops"] = fl / t / 1e9
         res["frac_of_measured_peak"] = max(res["dlti_nt_bn256_tflops"], res["dlti_nt_bn128_tflops"]) / peak

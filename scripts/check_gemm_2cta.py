@@ -14,7 +14,7 @@ def main():
     dev = "cuda"
     worst = 0.0
     cases = [(256, 256, 64, False), (512, 512, 256, False), (4096, 4096, 4096, False), (300, 520, 200, False),
-             (4096, 12288, 4096, False), (512, 512, 256, True), (4096, 4096, 11008, True), (1000, 776, 328, True)]
+             (4096, 12288, 4096, False), (2560, 2560, 512, False), (2500, 2704, 136, False), (2560, 2560, 512, True), (512, 512, 256, True), (4096, 4096, 11008, True), (1000, 776, 328, True)]
     for M, N, K, b_mn in cases:
         a = torch.randn(M, K, device=dev, dtype=torch.bfloat16)
         b = torch.randn((K, N) if b_mn else (N, K), device=dev, dtype=torch.bfloat16)
@@ -27,6 +27,13 @@ def main():
                 kw.update(a2=a2, b2=b2)
             y = gemm(a, b, two_cta=True, **kw)
             torch.cuda.synchronize()
+            y0 = gemm(a, b, two_cta=True, stream_k=0, **kw)
+            y1 = gemm(a, b, two_cta=True, stream_k=1, **kw)
+            y2 = gemm(a, b, two_cta=True, stream_k=1, **kw)      # slot re-armed by the previous launch
+            torch.cuda.synchronize()
+            assert torch.equal(y1, y2), "stream-K not repeatable"
+            d = (y1.float() - y0.float()).abs().max().item()
+            assert d <= 0.02 * y0.float().abs().max().item(), f"stream-K differs from data-parallel: {d}"
             ref = gemm_ref(a, b, **kw)
             err = ((y.float() - ref.float()).abs().max() / ref.float().abs().max()).item()
             worst = max(worst, err)

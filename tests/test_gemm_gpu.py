@@ -109,7 +109,7 @@ def test_gemm_skinny_decode(M, N, K):
 @pytest.mark.parametrize("dtype", [torch.bfloat16, torch.float16])
 @pytest.mark.parametrize("b_mn", [False, True])
 @pytest.mark.parametrize("M,N,K", [(256, 256, 64), (300, 520, 200), (1000, 776, 328), (4096, 4096, 4096),
-                                   (2048, 12288, 1024)])
+                                   (2048, 12288, 1024), (2500, 2704, 136)])
 def test_gemm_cta_pair(M, N, K, b_mn, dtype):
     """csrc/gemm2.cu (tcgen05 cta_group::2): residual, alpha, LoRA K-extension, fp32 accumulate."""
     torch.manual_seed(5)
@@ -121,6 +121,9 @@ def test_gemm_cta_pair(M, N, K, b_mn, dtype):
     kw = dict(b_mn=b_mn, residual=r, alpha=0.5, a2=a2, b2=b2)
     _check(gemm(a, b, two_cta=True, **kw), gemm_ref(a, b, out_dtype=torch.float32, **kw))
     _check(gemm(a, b, two_cta=True, b_mn=b_mn), gemm_ref(a, b, b_mn=b_mn, out_dtype=torch.float32))
+    # stream-K forced / disabled (the 4096^3 and 2500x2700 shapes have a ragged last wave)
+    for sk in (0, 1, 1):
+        _check(gemm(a, b, two_cta=True, stream_k=sk, **kw), gemm_ref(a, b, out_dtype=torch.float32, **kw))
     acc = torch.randn(M, N, device="cuda", dtype=torch.float32)
     exp = acc + gemm_ref(a, b, b_mn=b_mn, out_dtype=torch.float32)
     gemm(a, b, b_mn=b_mn, out=acc, accumulate=True, two_cta=True)

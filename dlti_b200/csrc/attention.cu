@@ -26,6 +26,7 @@
 // mma.sync code elsewhere) — SURVEY.md N5, O6, S5.
 #include "common.cuh"
 
+#include <cstdlib>
 #include <mutex>
 #include <unordered_map>
 
@@ -593,6 +594,267 @@ attn_bwd_kernel(const AttnParams p, const __grid_constant__ CUtensorMap tmQKV128
   }
 }
 
+// =============================================================================================
+// Forward, ping-pong form (the default): one CTA = TWO adjacent 128-row query tiles of one head.
+//
+// The single-tile kernel above is latency-bound (ncu: tensor pipe 17.6 % active): every
+// S -> softmax -> P -> PV hand-off sits on the critical path. Here two query tiles A and B share each
+// K/V block (half the K/V traffic) and alternate on the tensor core: while the softmax warps of one
+// tile work, the MMAs of the other run.
+//   warps 0-3: softmax tile A, warps 4-7: softmax tile B — one thread per query row, the whole
+//     128-wide score row in registers (row max/sum need no cross-thread traffic);
+//   warp 8: TMA producer (Q_A, Q_B once; K and V blocks of 128 keys, 2 stages each, released separately);
+//   warp 9: MMA issuer.
+// TMEM (512 columns): S_A | S_B | O_A | O_B. P is written back as packed 16-bit pairs over the first 64
+// columns of its own S buffer (tcgen05.st) and read by the PV MMA as the TMEM A operand, so P never
+// touches shared memory. O accumulates in TMEM over all KV blocks; the reference maximum is only
+// moved (and O rescaled in TMEM) when a row maximum grows by more than 2^8 — exact after the final
+// division by the row sum, and rare in practice.
+// =============================================================================================
+constexpr int F2_THREADS = 320;
+constexpr int F2_SMEM = 6 * 32768 + 256 + 1024;
+constexpr long long F2_WAIT_LIMIT = 4000000000LL;
+
+__device__ __forceinline__ void mbar_wait_b(uint32_t bar, uint32_t parity) {
+  const long long t0 = clock64();
+  while (!mbar_try_wait(bar, parity)) {
+    if (clock64() - t0 > F2_WAIT_LIMIT) asm volatile("trap;");
+  }
+}
+__device__ __forceinline__ float ex2_approx(float x) {
+  float y;
+  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+  return y;
+}
+
+template <typename T>
+__global__ void __launch_bounds__(F2_THREADS, 1)
+attn_fwd2_kernel(const AttnParams p, const __grid_constant__ CUtensorMap tm128) {
+  const int b = blockIdx.z, h = blockIdx.y;
+  const int row0 = p.cu_seqlens[b];
+  const int seqlen = p.cu_seqlens[b + 1] - row0;
+  const int nqb = (seqlen + 127) >> 7;
+  const int npair = (nqb + 1) >> 1;
+  const int pr = npair - 1 - (int)blockIdx.x;   // heavy (late) pairs first
+  if (pr < 0) return;
+  const int qbA = 2 * pr, qbB = 2 * pr + 1;
+  const int nA = qbA + 1, nB = (qbB < nqb) ? qbB + 1 : 0;   // KV blocks each tile attends to
+  const int nblk = nB > nA ? nB : nA;
+  const bool hasB = nB > 0;
+  const int kvh = h / (p.H / p.KV);
+
+  extern __shared__ uint8_t smem_raw[];
+  const uint32_t base = (smem_u32(smem_raw) + 1023u) & ~1023u;
+  const uint32_t sQ = base, sK = base + 2 * 32768, sV = base + 4 * 32768;
+  const uint32_t bars = base + 6 * 32768;
+  const uint32_t q_full = bars, k_full = bars + 8, v_full = bars + 24, k_empty = bars + 40, v_empty = bars + 56,
+                 s_full = bars + 72, p_full = bars + 88, pv_done = bars + 104, tmem_slot = bars + 120;
+  volatile uint32_t* tmem_slot_ptr =
+      reinterpret_cast<volatile uint32_t*>(smem_raw + (tmem_slot - smem_u32(smem_raw)));
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+
+  if (warp == 8 && lane == 0) {
+    tma_prefetch_desc(&tm128);
+    mbar_init(q_full, 1);
+    for (int s = 0; s < 2; ++s) {
+      mbar_init(k_full + 8 * s, 1);
+      mbar_init(v_full + 8 * s, 1);
+      mbar_init(k_empty + 8 * s, 1);
+      mbar_init(v_empty + 8 * s, 1);
+      mbar_init(s_full + 8 * s, 1);
+      mbar_init(p_full + 8 * s, 4);
+      mbar_init(pv_done + 8 * s, 1);
+    }
+    mbar_fence_init();
+  }
+  if (warp == 9) {
+    tmem_alloc(tmem_slot, 512);
+    tmem_relinquish();
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem = *tmem_slot_ptr;
+
+  if (warp == 8) {
+    if (lane == 0) {
+      const int qcol = h * HD, kcol = p.H * HD + kvh * HD, vcol = (p.H + p.KV) * HD + kvh * HD;
+      mbar_expect_tx(q_full, hasB ? 65536 : 32768);
+      tma_load_2d(sQ, &tm128, q_full, qcol, row0 + qbA * 128);
+      tma_load_2d(sQ + 16384, &tm128, q_full, qcol + 64, row0 + qbA * 128);
+      if (hasB) {
+        tma_load_2d(sQ + 32768, &tm128, q_full, qcol, row0 + qbB * 128);
+        tma_load_2d(sQ + 32768 + 16384, &tm128, q_full, qcol + 64, row0 + qbB * 128);
+      }
+      for (int j = 0; j < nblk; ++j) {
+        const int s = j & 1;
+        const int r = row0 + j * 128;
+        if (j >= 2) mbar_wait_b(k_empty + 8 * s, ((j >> 1) - 1) & 1);
+        mbar_expect_tx(k_full + 8 * s, 32768);
+        tma_load_2d(sK + s * 32768, &tm128, k_full + 8 * s, kcol, r);
+        tma_load_2d(sK + s * 32768 + 16384, &tm128, k_full + 8 * s, kcol + 64, r);
+        if (j >= 2) mbar_wait_b(v_empty + 8 * s, ((j >> 1) - 1) & 1);
+        mbar_expect_tx(v_full + 8 * s, 32768);
+        tma_load_2d(sV + s * 32768, &tm128, v_full + 8 * s, vcol, r);
+        tma_load_2d(sV + s * 32768 + 16384, &tm128, v_full + 8 * s, vcol + 64, r);
+      }
+    }
+  } else if (warp == 9) {
+    if (lane == 0) {
+      const uint32_t idesc_s = umma_idesc_f16(p.dtype, 128, 128, false, false);
+      const uint32_t idesc_pv = umma_idesc_f16(p.dtype, 128, 128, false, true);
+      auto issue_s = [&](int X, int j) {
+#pragma unroll
+        for (int kk = 0; kk < 8; ++kk)
+          umma_f16_ss(tmem + X * 128, desc_kmajor(sQ + X * 32768, 128, kk),
+                      desc_kmajor(sK + (j & 1) * 32768, 128, kk), idesc_s, kk > 0);
+        umma_commit(s_full + 8 * X);
+      };
+      auto issue_pv = [&](int X, int j) {
+#pragma unroll
+        for (int kk = 0; kk < 8; ++kk)
+          umma_f16_ts(tmem + 256 + X * 128, tmem + X * 128 + kk * 8,
+                      desc_mnmajor(sV + (j & 1) * 32768, 128, kk), idesc_pv, (j > 0 || kk > 0) ? 1u : 0u);
+        umma_commit(pv_done + 8 * X);
+      };
+      mbar_wait_b(q_full, 0);
+      mbar_wait_b(k_full, 0);
+      tc_fence_after();
+      issue_s(0, 0);
+      if (hasB) issue_s(1, 0);
+      umma_commit(k_empty);
+      for (int j = 0; j < nblk; ++j) {
+        const int s = j & 1;
+        const bool actA = j < nA, actB = j < nB, nxtA = j + 1 < nA, nxtB = j + 1 < nB;
+        mbar_wait_b(v_full + 8 * s, (j >> 1) & 1);
+        if (nxtA || nxtB) mbar_wait_b(k_full + 8 * (s ^ 1), ((j + 1) >> 1) & 1);
+        if (actA) {
+          mbar_wait_b(p_full, j & 1);
+          tc_fence_after();
+          issue_pv(0, j);
+          if (!actB) umma_commit(v_empty + 8 * s);
+        }
+        if (nxtA) {
+          issue_s(0, j + 1);
+          if (!nxtB) umma_commit(k_empty + 8 * (s ^ 1));
+        }
+        if (actB) {
+          mbar_wait_b(p_full + 8, j & 1);
+          tc_fence_after();
+          issue_pv(1, j);
+          umma_commit(v_empty + 8 * s);
+        }
+        if (nxtB) {
+          issue_s(1, j + 1);
+          umma_commit(k_empty + 8 * (s ^ 1));
+        }
+      }
+    }
+  } else {
+    const int X = warp >> 2;                    // 0: tile A, 1: tile B
+    const int nX = X ? nB : nA;
+    const int qbX = X ? qbB : qbA;
+    if (nX > 0) {
+      const int quarter = warp & 3;
+      const int r = quarter * 32 + lane;          // query row inside the tile
+      const uint32_t tS = tmem + ((uint32_t)(quarter * 32) << 16) + X * 128;
+      const uint32_t tO = tmem + ((uint32_t)(quarter * 32) << 16) + 256 + X * 128;
+      const float sl2 = p.scale * LOG2E;
+      float m_ref = -INFINITY, l = 0.f;
+      for (int j = 0; j < nX; ++j) {
+        const bool diag = (j == qbX);
+        mbar_wait_b(s_full + 8 * X, j & 1);
+        tc_fence_after();
+        uint32_t v[128];
+#pragma unroll
+        for (int c = 0; c < 4; ++c) tmem_ld_32x32b_x32(tS + c * 32, *reinterpret_cast<uint32_t(*)[32]>(v + 32 * c));
+        tmem_wait_ld();
+        float mx = -INFINITY;
+        if (diag) {
+#pragma unroll
+          for (int i = 0; i < 128; ++i) {
+            if (i > r) v[i] = __float_as_uint(-INFINITY);
+            mx = fmaxf(mx, __uint_as_float(v[i]));
+          }
+        } else {
+#pragma unroll
+          for (int i = 0; i < 128; ++i) mx = fmaxf(mx, __uint_as_float(v[i]));
+        }
+        mx *= sl2;
+        if (j == 0) {
+          m_ref = mx;
+        } else {
+          const float mnew = fmaxf(m_ref, mx);
+          if (__any_sync(0xffffffffu, (mnew - m_ref) > 8.f)) {
+            // move the reference maximum: O (in TMEM) and l shrink by 2^(old - new)
+            const float alpha = ex2_approx(m_ref - mnew);
+            m_ref = mnew;
+            l *= alpha;
+            mbar_wait_b(pv_done + 8 * X, (j - 1) & 1);
+            tc_fence_after();
+#pragma unroll 1
+            for (int c = 0; c < 8; ++c) {
+              uint32_t o[16];
+              tmem_ld_32x32b_x16(tO + c * 16, o);
+              tmem_wait_ld();
+#pragma unroll
+              for (int i = 0; i < 16; ++i) o[i] = __float_as_uint(__uint_as_float(o[i]) * alpha);
+              tmem_st_32x32b_x16(tO + c * 16, o);
+            }
+            tmem_wait_st();
+          }
+        }
+        const float neg_m = -m_ref;
+#pragma unroll
+        for (int c = 0; c < 4; ++c) {
+          uint32_t pk[16];
+#pragma unroll
+          for (int i = 0; i < 16; ++i) {
+            const float p0 = ex2_approx(fmaf(__uint_as_float(v[32 * c + 2 * i]), sl2, neg_m));
+            const float p1 = ex2_approx(fmaf(__uint_as_float(v[32 * c + 2 * i + 1]), sl2, neg_m));
+            l += p0 + p1;
+            pk[i] = Cvt<T>::pack2(p0, p1);
+          }
+          tmem_st_32x32b_x16(tS + c * 16, pk);
+        }
+        tmem_wait_st();
+        tc_fence_before();
+        __syncwarp();
+        if (lane == 0) mbar_arrive(p_full + 8 * X);
+      }
+      mbar_wait_b(pv_done + 8 * X, (nX - 1) & 1);
+      tc_fence_after();
+      const float inv = 1.f / l;
+      const int qi = qbX * 128 + r;
+      T* orow = reinterpret_cast<T*>(p.O) + (long long)(row0 + qi) * p.ldo + h * HD;
+#pragma unroll 1
+      for (int c = 0; c < 4; ++c) {
+        uint32_t o[32];
+        tmem_ld_32x32b_x32(tO + c * 32, o);
+        tmem_wait_ld();
+        if (qi < seqlen) {
+#pragma unroll
+          for (int k = 0; k < 4; ++k) {
+            int4 ov;
+            uint32_t* ou = reinterpret_cast<uint32_t*>(&ov);
+#pragma unroll
+            for (int q = 0; q < 4; ++q)
+              ou[q] = Cvt<T>::pack2(__uint_as_float(o[8 * k + 2 * q]) * inv, __uint_as_float(o[8 * k + 2 * q + 1]) * inv);
+            *reinterpret_cast<int4*>(orow + c * 32 + 8 * k) = ov;
+          }
+        }
+      }
+      if (qi < seqlen && p.lse) p.lse[(long long)h * p.T_total + row0 + qi] = (m_ref + log2f(l)) * LN2;
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 9) {
+    tc_fence_after();
+    tmem_dealloc(tmem, 512);
+  }
+}
+
 constexpr int FWD_SMEM = 6 * 32768 + 256 + 1024;
 constexpr int BWD_SMEM = 65536 + 2 * 3 * 16384 + 32768 + 1024 + 256 + 1024;
 
@@ -616,6 +878,23 @@ DLTI_API int dlti_attn_fwd(const void* qkv, void* out, float* lse, const int* cu
   CUtensorMap tm;
   int rc = make_map(&tm, qkv, T_total, p.W, 128);
   if (rc) return rc;
+  // DLTI_ATTN_FWD=1 selects the older one-tile-per-CTA kernel (kept for A/B measurements)
+  static const bool pingpong = []() { const char* e = getenv("DLTI_ATTN_FWD"); return !e || e[0] != '1'; }();
+  if (pingpong) {
+    dim3 grid2(((max_seqlen + 127) / 128 + 1) / 2, H, batch);
+    static bool cfg2[2] = {false, false};
+    if (dtype == DLTI_BF16) {
+      if (!cfg2[0]) { DLTI_CUDA_CHECK(cudaFuncSetAttribute(attn_fwd2_kernel<__nv_bfloat16>, cudaFuncAttributeMaxDynamicSharedMemorySize, F2_SMEM)); cfg2[0] = true; }
+      attn_fwd2_kernel<__nv_bfloat16><<<grid2, F2_THREADS, F2_SMEM, st>>>(p, tm);
+    } else if (dtype == DLTI_FP16) {
+      if (!cfg2[1]) { DLTI_CUDA_CHECK(cudaFuncSetAttribute(attn_fwd2_kernel<__half>, cudaFuncAttributeMaxDynamicSharedMemorySize, F2_SMEM)); cfg2[1] = true; }
+      attn_fwd2_kernel<__half><<<grid2, F2_THREADS, F2_SMEM, st>>>(p, tm);
+    } else {
+      return DLTI_ERR_UNSUPPORTED;
+    }
+    dlti_count_launch();
+    return (int)cudaGetLastError();
+  }
   dim3 grid((max_seqlen + 127) / 128, H, batch);
   static bool cfg[2] = {false, false};
   if (dtype == DLTI_BF16) {

@@ -177,6 +177,22 @@ def test_attention_fwd_bwd(H, KV, seqs, dtype):
     close(dqkv, dqkv_r, 3e-2, 3e-2 * max(scale, 1.0))
 
 
+@pytest.mark.parametrize("seqs", [[640], [300, 1100]])
+def test_attention_fwd_peaked_scores(seqs):
+    """Large-magnitude q/k: row maxima jump by far more than 2^8 between KV blocks, which exercises the
+    forward kernel's in-TMEM rescale of the running output."""
+    torch.manual_seed(11)
+    H, KV, hd = 4, 2, 128
+    T = sum(seqs)
+    cu = torch.tensor([0] + list(torch.tensor(seqs).cumsum(0)), dtype=torch.int32, device=DEV)
+    qkv = torch.randn(T, (H + 2 * KV) * hd, device=DEV, dtype=torch.bfloat16)
+    qkv[:, :(H + KV) * hd] *= 3.0
+    out, lse = A.attention_fwd(qkv, cu, max(seqs), H, KV, hd)
+    out_r, lse_r = A.attention_fwd_ref(qkv.cpu(), cu.cpu(), H, KV, hd, 1 / math.sqrt(hd))
+    close(out, out_r, 3e-2, 3e-2)
+    close(lse, lse_r, 1e-2, 2e-2)
+
+
 # ---- serving kernels ------------------------------------------------------------------------
 from dlti_b200.ops import serving as S  # noqa: E402
 

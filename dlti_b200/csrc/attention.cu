@@ -51,6 +51,12 @@ struct AttnParams {
   int dtype;
 };
 
+__device__ __forceinline__ float ex2_approx(float x) {
+  float y;
+  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+  return y;
+}
+
 __device__ __forceinline__ uint32_t swz_off(int row, int chunk16) {
   // byte offset inside a [rows x 128 B] 128B-swizzled tile
   return (uint32_t)(row * 128 + ((chunk16 ^ (row & 7)) << 4));
@@ -329,7 +335,9 @@ __global__ void attn_bwd_prep_kernel(const T* __restrict__ dO, const T* __restri
 //   DKDV = false: stationary X1 = Q_i, X2 = dO_i (128 query rows); streamed Y1 = K_j, Y2 = V_j
 //                 (64 keys). thread = query row. acc2 (dQ) += dS·K.
 // In both, tile A = X1·Y1^T (scores) and tile B = X2·Y2^T (dP) are [128 x 64] fp32 in TMEM,
-// double-buffered; P / dS go to smem as K-major [128 x 64] 16-bit tiles.
+// double-buffered; P / dS are written back over those tiles as packed 16-bit pairs (tcgen05.st) and
+// feed the accumulate MMAs as the TMEM A operand — no shared-memory round trip, and softmax of
+// iteration it+1 never waits for the accumulate MMAs of iteration it.
 // =============================================================================================
 template <typename T, bool DKDV>
 __global__ void __launch_bounds__(AT_THREADS, 1)
@@ -364,13 +372,10 @@ attn_bwd_kernel(const AttnParams p, const __grid_constant__ CUtensorMap tmQKV128
   constexpr int NYS = 3;
   const uint32_t sY1 = base + 65536;                    // NYS stages x 16 KB
   const uint32_t sY2 = base + 65536 + NYS * 16384;      // NYS stages x 16 KB
-  const uint32_t sP = base + 65536 + 2 * NYS * 16384;   // 16 KB
-  const uint32_t sDS = sP + 16384;                      // 16 KB
-  const uint32_t sStat = sDS + 16384;                   // 2 x (64 lse + 64 D) floats = 1 KB
+  const uint32_t sStat = base + 65536 + 2 * NYS * 16384;   // 2 x (64 lse + 64 D) floats = 1 KB
   const uint32_t bars = sStat + 1024;
   const uint32_t x_full = bars, y_full = bars + 8, y_empty = bars + 32, ab_full = bars + 56,
-                 ab_free = bars + 72, pds_full = bars + 88, pds_free = bars + 96,
-                 tmem_slot = bars + 104;
+                 pds_full = bars + 72, acc_done = bars + 88, tmem_slot = bars + 96;
   volatile uint32_t* tmem_slot_ptr =
       reinterpret_cast<volatile uint32_t*>(smem_raw + (tmem_slot - smem_u32(smem_raw)));
   float* stat = reinterpret_cast<float*>(smem_raw + (sStat - smem_u32(smem_raw)));
@@ -384,10 +389,9 @@ attn_bwd_kernel(const AttnParams p, const __grid_constant__ CUtensorMap tmQKV128
     }
     for (int s = 0; s < 2; ++s) {
       mbar_init(ab_full + 8 * s, 1);
-      mbar_init(ab_free + 8 * s, 8);
+      mbar_init(pds_full + 8 * s, 8);
     }
-    mbar_init(pds_full, 8);
-    mbar_init(pds_free, 1);
+    mbar_init(acc_done, 1);
     mbar_fence_init();
   }
   if (warp == 1) {
@@ -447,7 +451,6 @@ attn_bwd_kernel(const AttnParams p, const __grid_constant__ CUtensorMap tmQKV128
       auto issue_ab = [&](int it) {
         const int s = it & 1, ys = it % NYS;
         mbar_wait(y_full + 8 * ys, (it / NYS) & 1);
-        if (it >= 2) mbar_wait(ab_free + 8 * s, ((it >> 1) - 1) & 1);
         tc_fence_after();
 #pragma unroll
         for (int kk = 0; kk < 8; ++kk)
@@ -459,26 +462,32 @@ attn_bwd_kernel(const AttnParams p, const __grid_constant__ CUtensorMap tmQKV128
                       desc_kmajor(sY2 + ys * 16384, 64, kk), idesc_ab, kk > 0);
         umma_commit(ab_full + 8 * s);
       };
+      // P / dS come back as packed 16-bit pairs written over the score tiles themselves (each softmax
+      // thread overwrites only columns it has already read): k-steps 0,1 at columns 0-15 and k-steps
+      // 2,3 at columns 32-47 of the 64-column tile. The accumulate MMAs read them as the TMEM A operand.
+      auto a_tmem = [&](uint32_t tile, int kk) { return tile + (uint32_t)((kk >> 1) * 32 + (kk & 1) * 8); };
       mbar_wait(x_full, 0);
       issue_ab(0);
+      if (iters > 1) issue_ab(1);
       for (int it = 0; it < iters; ++it) {
-        const int ys = it % NYS;
-        if (it + 1 < iters) issue_ab(it + 1);
-        mbar_wait(pds_full, it & 1);
+        const int s = it & 1, ys = it % NYS;
+        mbar_wait(pds_full + 8 * s, (it >> 1) & 1);
         tc_fence_after();
         if (DKDV) {
 #pragma unroll
           for (int kk = 0; kk < 4; ++kk)   // dV += P^T · dO
-            umma_f16_ss(tmem + TACC1, desc_kmajor64(sP, kk), desc_mnmajor(sY2 + ys * 16384, 64, kk),
+            umma_f16_ts(tmem + TACC1, a_tmem(tmem + TA + s * 64, kk), desc_mnmajor(sY2 + ys * 16384, 64, kk),
                         idesc_acc, (it > 0 || kk > 0));
         }
 #pragma unroll
         for (int kk = 0; kk < 4; ++kk)     // dK += dS^T · Q   /   dQ += dS · K
-          umma_f16_ss(tmem + TACC2, desc_kmajor64(sDS, kk), desc_mnmajor(sY1 + ys * 16384, 64, kk),
+          umma_f16_ts(tmem + TACC2, a_tmem(tmem + TB + s * 64, kk), desc_mnmajor(sY1 + ys * 16384, 64, kk),
                       idesc_acc, (it > 0 || kk > 0));
         umma_commit(y_empty + 8 * ys);
-        umma_commit(pds_free);
+        // the tensor pipe runs MMAs in issue order, so the next scores may overwrite this buffer now
+        if (it + 2 < iters) issue_ab(it + 2);
       }
+      umma_commit(acc_done);
     }
   } else {
     // two threads per row: warps 2-5 own streamed columns [0,32), warps 6-9 own [32,64)
@@ -494,27 +503,33 @@ attn_bwd_kernel(const AttnParams p, const __grid_constant__ CUtensorMap tmQKV128
       my_lse = p.lse[(long long)head * p.T_total + row0 + sidx] * LOG2E;
       my_D = p.D[(long long)head * p.T_total + row0 + sidx];
     }
+    // DKDV: per-query lse / D of the streamed block are staged through smem; the global loads run one
+    // iteration ahead of their use so their latency is off the critical path.
+    auto load_stat = [&](int it) -> float {
+      const int g = it / ny;
+      const int q = (y0 + (it - g * ny)) * 64 + (tid128 & 63);
+      float val = 0.f;
+      if (tid128 < 128 && it < iters && q < seqlen) {
+        const long long off = (long long)(head * G + g) * p.T_total + row0 + q;
+        val = (tid128 < 64) ? p.lse[off] * LOG2E : p.D[off];
+      }
+      return val;
+    };
+    float stat_next = DKDV ? load_stat(0) : 0.f;
     for (int it = 0; it < iters; ++it) {
       const int s = it & 1;
       int yb;                                   // streamed 64-block index
       if (DKDV) {
         const int g = it / ny;
         yb = y0 + (it - g * ny);
-        // stage this q block's lse / D (64 values each) into smem
-        const int qh = head * G + g;
-        const int q = yb * 64 + (tid128 & 63);
-        if (tid128 < 128) {
-          float val = 0.f;
-          if (q < seqlen) {
-            const long long off = (long long)qh * p.T_total + row0 + q;
-            val = (tid128 < 64) ? p.lse[off] * LOG2E : p.D[off];
-          }
-          stat[s * 128 + tid128] = val;
-        }
+        if (tid128 < 128) stat[s * 128 + tid128] = stat_next;
+        stat_next = load_stat(it + 1);
         asm volatile("bar.sync 1, 256;" ::: "memory");
       } else {
         yb = y0 + it;
       }
+      // Only the blocks that touch the causal diagonal (or the end of the sequence) need a mask.
+      const bool need_mask = DKDV ? (yb < 2 * blk + 2 || yb * 64 + 64 > seqlen) : (yb >= 2 * blk);
       mbar_wait(ab_full + 8 * s, (it >> 1) & 1);
       tc_fence_after();
       {
@@ -523,46 +538,63 @@ attn_bwd_kernel(const AttnParams p, const __grid_constant__ CUtensorMap tmQKV128
         tmem_ld_32x32b_x32(trow + TA + s * 64 + c * 32, sv);
         tmem_ld_32x32b_x32(trow + TB + s * 64 + c * 32, dv);
         tmem_wait_ld();
-        float pr[32], ds[32];
+        float lse_v[32], D_v[32];
+        if (DKDV) {
+          const float4* l4 = reinterpret_cast<const float4*>(stat + s * 128 + c * 32);
+          const float4* d4 = reinterpret_cast<const float4*>(stat + s * 128 + 64 + c * 32);
 #pragma unroll
-        for (int i = 0; i < 32; ++i) {
-          const int yi = yb * 64 + c * 32 + i;  // query index (DKDV) or key index (!DKDV)
-          float lse_v, D_v;
-          bool valid;
-          if (DKDV) {
-            lse_v = stat[s * 128 + c * 32 + i];
-            D_v = stat[s * 128 + 64 + c * 32 + i];
-            valid = (yi < seqlen) && (yi >= sidx);
-          } else {
-            lse_v = my_lse; D_v = my_D;
-            valid = (sidx < seqlen) && (yi <= sidx);
+          for (int i = 0; i < 8; ++i) {
+            const float4 a = l4[i], b4 = d4[i];
+            lse_v[4 * i] = a.x; lse_v[4 * i + 1] = a.y; lse_v[4 * i + 2] = a.z; lse_v[4 * i + 3] = a.w;
+            D_v[4 * i] = b4.x; D_v[4 * i + 1] = b4.y; D_v[4 * i + 2] = b4.z; D_v[4 * i + 3] = b4.w;
           }
-          // branch-free masking: clamp the exponent (masked / garbage scores may be huge) and
-          // multiply by a 0/1 mask, so the compiler cannot wrap exp2f in a per-element branch
-          const float msk = valid ? 1.f : 0.f;
-          const float pv = exp2f(fminf(__uint_as_float(sv[i]) * sl2 - lse_v, 16.f)) * msk;
-          pr[i] = pv;
-          ds[i] = pv * (__uint_as_float(dv[i]) - D_v) * p.scale;
         }
-        if (it > 0) mbar_wait(pds_free, (it - 1) & 1);
-        if (DKDV) store_row32<T>(sP, r, c * 4, pr);
-        store_row32<T>(sDS, r, c * 4, ds);
+        // p = 2^(s*scale*log2e - lse);  ds = p * (dp - D)   (the 1/sqrt(d) factor of dS is applied once,
+        // to the dK / dQ accumulators, in the epilogue)
+        float pr[32], ds[32];
+        if (!need_mask) {
+#pragma unroll
+          for (int i = 0; i < 32; ++i) {
+            const float x = fmaf(__uint_as_float(sv[i]), sl2, -(DKDV ? lse_v[i] : my_lse));
+            const float pv = ex2_approx(x);
+            pr[i] = pv;
+            ds[i] = pv * (__uint_as_float(dv[i]) - (DKDV ? D_v[i] : my_D));
+          }
+        } else {
+#pragma unroll
+          for (int i = 0; i < 32; ++i) {
+            const int yi = yb * 64 + c * 32 + i;  // query index (DKDV) or key index (!DKDV)
+            const bool valid = DKDV ? ((yi < seqlen) && (yi >= sidx)) : ((sidx < seqlen) && (yi <= sidx));
+            float x = fmaf(__uint_as_float(sv[i]), sl2, -(DKDV ? lse_v[i] : my_lse));
+            x = valid ? x : -INFINITY;            // exp2(-inf) = 0 exactly; no NaNs from garbage rows
+            const float pv = ex2_approx(x);
+            pr[i] = pv;
+            ds[i] = valid ? pv * (__uint_as_float(dv[i]) - (DKDV ? D_v[i] : my_D)) : 0.f;
+          }
+        }
+        uint32_t pk[16];
+        if (DKDV) {
+#pragma unroll
+          for (int i = 0; i < 16; ++i) pk[i] = Cvt<T>::pack2(pr[2 * i], pr[2 * i + 1]);
+          tmem_st_32x32b_x16(trow + TA + s * 64 + c * 32, pk);
+        }
+#pragma unroll
+        for (int i = 0; i < 16; ++i) pk[i] = Cvt<T>::pack2(ds[2 * i], ds[2 * i + 1]);
+        tmem_st_32x32b_x16(trow + TB + s * 64 + c * 32, pk);
       }
+      tmem_wait_st();
       tc_fence_before();
-      fence_proxy_async_smem();
       __syncwarp();
-      if (lane == 0) {
-        mbar_arrive(ab_free + 8 * s);
-        mbar_arrive(pds_full);
-      }
+      if (lane == 0) mbar_arrive(pds_full + 8 * s);
     }
-    mbar_wait(pds_free, (iters - 1) & 1);
+    mbar_wait(acc_done, 0);
     tc_fence_after();
     // write the accumulators
     T* outbase = reinterpret_cast<T*>(p.dqkv) + (long long)(row0 + sidx) * p.W;
     const int nacc = DKDV ? 2 : 1;
     for (int a = 0; a < nacc; ++a) {
       const uint32_t tacc = (DKDV && a == 0) ? TACC1 : TACC2;
+      const float osc = (tacc == TACC2) ? p.scale : 1.f;     // dK / dQ carry the softmax scale
       int col;
       if (DKDV) col = (a == 0) ? (vcol_base + head * HD) : (kcol_base + head * HD);
       else col = head * HD;
@@ -579,7 +611,7 @@ attn_bwd_kernel(const AttnParams p, const __grid_constant__ CUtensorMap tmQKV128
             uint32_t* ou = reinterpret_cast<uint32_t*>(&ov);
 #pragma unroll
             for (int q = 0; q < 4; ++q)
-              ou[q] = Cvt<T>::pack2(__uint_as_float(v[8 * k + 2 * q]), __uint_as_float(v[8 * k + 2 * q + 1]));
+              ou[q] = Cvt<T>::pack2(__uint_as_float(v[8 * k + 2 * q]) * osc, __uint_as_float(v[8 * k + 2 * q + 1]) * osc);
             *reinterpret_cast<int4*>(outbase + col + c * 32 + 8 * k) = ov;
           }
         }
@@ -620,11 +652,6 @@ __device__ __forceinline__ void mbar_wait_b(uint32_t bar, uint32_t parity) {
   while (!mbar_try_wait(bar, parity)) {
     if (clock64() - t0 > F2_WAIT_LIMIT) asm volatile("trap;");
   }
-}
-__device__ __forceinline__ float ex2_approx(float x) {
-  float y;
-  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
-  return y;
 }
 
 template <typename T>
@@ -856,7 +883,7 @@ attn_fwd2_kernel(const AttnParams p, const __grid_constant__ CUtensorMap tm128) 
 }
 
 constexpr int FWD_SMEM = 6 * 32768 + 256 + 1024;
-constexpr int BWD_SMEM = 65536 + 2 * 3 * 16384 + 32768 + 1024 + 256 + 1024;
+constexpr int BWD_SMEM = 65536 + 2 * 3 * 16384 + 1024 + 256 + 1024;
 
 int make_map(CUtensorMap* m, const void* base, long long T_total, long long width, int box_rows) {
   return dlti_make_tmap_2d(m, base, (uint64_t)width, (uint64_t)T_total, (uint64_t)width, 64,

@@ -33,6 +33,11 @@
 namespace {
 
 constexpr int HD = 128;           // head dim
+// depth of the backward kernels' streamed-tile rings (32 KB per stage). dQ runs ~1000-clk iterations and
+// needs ~1500 clk of TMA latency hidden -> 5 stages; dK/dV spends the space on its lse/D staging buffers.
+constexpr int BWD_NYS_Q = 5, BWD_NYS_KV = 4;
+constexpr int BWD_STAT_CHUNK = 8;        // dK/dV: query blocks whose lse/D are staged per bar.sync
+constexpr int BWD_STAT_BYTES = 2 * BWD_STAT_CHUNK * 64 * 2 * 4;   // double-buffered {lse, D} x 512 queries
 constexpr int AT_THREADS = 320;   // producer, mma, 8 softmax warps (two threads per row: column halves)
 constexpr float LOG2E = 1.4426950408889634f;
 constexpr float LN2 = 0.6931471805599453f;
@@ -91,6 +96,24 @@ __device__ __forceinline__ uint64_t desc_kmajor64(uint32_t base, int kk) {
 // K = krows. k-step kk covers rows 16kk..16kk+15.
 __device__ __forceinline__ uint64_t desc_mnmajor(uint32_t base, int krows, int kk) {
   return umma_smem_desc(base + kk * 2048, krows * 128, 1024);
+}
+
+// The MMAs of the attention kernels are short (32-64 clk), so the single issuing thread must not spend
+// longer than that preparing each one: descriptors are split into a precomputed (lo, hi) pair and the
+// per-MMA work is one 32-bit add of a compile-time offset (traced: ~60 clk per MMA before this).
+struct DescLoHi {
+  uint32_t lo, hi;
+  __device__ __forceinline__ uint64_t at(uint32_t byte_off) const {
+    return ((uint64_t)hi << 32) | (uint64_t)(lo + (byte_off >> 4));
+  }
+};
+__device__ __forceinline__ DescLoHi desc_split(uint32_t smem_addr, uint32_t lbo_bytes, uint32_t sbo_bytes) {
+  const uint64_t d = umma_smem_desc(smem_addr, lbo_bytes, sbo_bytes);
+  return DescLoHi{(uint32_t)d, (uint32_t)(d >> 32)};
+}
+// byte offset of k-step kk inside a K-major [rows x 128] operand (two [rows x 64] chunks)
+__device__ __forceinline__ constexpr uint32_t koff_kmajor(int rows, int kk) {
+  return (uint32_t)((kk >> 2) * (rows * 128) + (kk & 3) * 32);
 }
 
 // =============================================================================================
@@ -339,6 +362,14 @@ __global__ void attn_bwd_prep_kernel(const T* __restrict__ dO, const T* __restri
 // feed the accumulate MMAs as the TMEM A operand — no shared-memory round trip, and softmax of
 // iteration it+1 never waits for the accumulate MMAs of iteration it.
 // =============================================================================================
+#ifdef DLTI_ATTN_TRACE
+// Developer build only: clock64() timeline of one CTA (role x iteration x event) for latency hunting.
+__device__ long long g_attn_trace[2 * 3 * 64 * 4];   // [dQ | dK/dV][role][iteration][event]
+#define TRACE(role, it, ev) do { if (trace_cta && (it) < 64) g_attn_trace[(((DKDV ? 3 : 0) + (role)) * 64 + (it)) * 4 + (ev)] = clock64(); } while (0)
+#else
+#define TRACE(role, it, ev) do { } while (0)
+#endif
+
 template <typename T, bool DKDV>
 __global__ void __launch_bounds__(AT_THREADS, 1)
 attn_bwd_kernel(const AttnParams p, const __grid_constant__ CUtensorMap tmQKV128,
@@ -356,6 +387,9 @@ attn_bwd_kernel(const AttnParams p, const __grid_constant__ CUtensorMap tmQKV128
   const int blk = DKDV ? (int)blockIdx.x : nblk128 - 1 - (int)blockIdx.x;
   if (blk < 0 || blk * 128 >= seqlen) return;
   const int head = blockIdx.y;              // DKDV: kv head; else: q head
+#ifdef DLTI_ATTN_TRACE
+  const bool trace_cta = blockIdx.x == 0 && blockIdx.y == 0 && blockIdx.z == 0 && (threadIdx.x & 31) == 0;
+#endif
   // streamed block range and iteration count
   int y0, ny, iters;
   if (DKDV) {
@@ -367,19 +401,20 @@ attn_bwd_kernel(const AttnParams p, const __grid_constant__ CUtensorMap tmQKV128
   extern __shared__ uint8_t smem_raw[];
   const uint32_t base = (smem_u32(smem_raw) + 1023u) & ~1023u;
   const uint32_t sX1 = base, sX2 = base + 32768;
-  // streamed tiles: NYS-deep ring (3: the load for iteration it+2 is issued as soon as the MMAs of
-  // iteration it-1 retire, so two tiles are in flight and the TMA latency is off the critical path)
-  constexpr int NYS = 3;
+  // streamed tiles: NYS-deep ring. The load for iteration `it` is issued when the accumulate MMAs of
+  // iteration it-NYS retire and is needed when those of it-2 retire, so NYS-2 iterations of TMA latency
+  // (~1500 clk measured) are hidden.
+  constexpr int NYS = DKDV ? BWD_NYS_KV : BWD_NYS_Q;
   const uint32_t sY1 = base + 65536;                    // NYS stages x 16 KB
   const uint32_t sY2 = base + 65536 + NYS * 16384;      // NYS stages x 16 KB
-  const uint32_t sStat = base + 65536 + 2 * NYS * 16384;   // 2 x (64 lse + 64 D) floats = 1 KB
-  const uint32_t bars = sStat + 1024;
-  const uint32_t x_full = bars, y_full = bars + 8, y_empty = bars + 32, ab_full = bars + 56,
-                 pds_full = bars + 72, acc_done = bars + 88, tmem_slot = bars + 96;
+  const uint32_t sStat = base + 65536 + 2 * NYS * 16384;   // dK/dV: 2 x {512 lse, 512 D} floats
+  const uint32_t bars = sStat + (DKDV ? BWD_STAT_BYTES : 1024);
+  const uint32_t x_full = bars, y_full = bars + 8, y_empty = y_full + 8 * NYS, ab_full = y_empty + 8 * NYS,
+                 pds_full = ab_full + 16, acc_done = pds_full + 16, x_tmem = acc_done + 8, tmem_slot = x_tmem + 8;
   volatile uint32_t* tmem_slot_ptr =
       reinterpret_cast<volatile uint32_t*>(smem_raw + (tmem_slot - smem_u32(smem_raw)));
   float* stat = reinterpret_cast<float*>(smem_raw + (sStat - smem_u32(smem_raw)));
-  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int warp = __shfl_sync(0xffffffffu, threadIdx.x >> 5, 0), lane = threadIdx.x & 31;   // warp-uniform for the compiler
 
   if (warp == 0 && lane == 0) {
     mbar_init(x_full, 1);
@@ -392,6 +427,7 @@ attn_bwd_kernel(const AttnParams p, const __grid_constant__ CUtensorMap tmQKV128
       mbar_init(pds_full + 8 * s, 8);
     }
     mbar_init(acc_done, 1);
+    mbar_init(x_tmem, 8);
     mbar_fence_init();
   }
   if (warp == 1) {
@@ -401,9 +437,12 @@ attn_bwd_kernel(const AttnParams p, const __grid_constant__ CUtensorMap tmQKV128
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
-  const uint32_t tmem = *tmem_slot_ptr;
-  // TMEM columns: A tiles at 0/64, B tiles at 128/192, acc1 at 256, acc2 at 384
-  const uint32_t TA = 0, TB = 128, TACC1 = 256, TACC2 = 384;
+  const uint32_t tmem = __shfl_sync(0xffffffffu, *tmem_slot_ptr, 0);
+  // TMEM columns: A tiles at 0/64, B tiles at 128/192, acc1 at 256, acc2 at 384. The dQ kernel has no
+  // acc1: it parks its stationary Q and dO tiles there (packed 16-bit, 64 columns each) so the score
+  // MMAs take their 128-row operand from TMEM instead of re-reading 4 KB of shared memory per MMA —
+  // with N = 64 that re-read made the tensor pipe shared-memory-bound (traced: 950 clk to issue 16 MMAs).
+  const uint32_t TA = 0, TB = 128, TACC1 = 256, TACC2 = 384, TX1 = 256, TX2 = 320;
 
   const int kcol_base = p.H * HD, vcol_base = (p.H + p.KV) * HD;
 
@@ -426,6 +465,7 @@ attn_bwd_kernel(const AttnParams p, const __grid_constant__ CUtensorMap tmQKV128
       for (int it = 0; it < iters; ++it) {
         const int s = it % NYS;
         if (it >= NYS) mbar_wait(y_empty + 8 * s, ((it / NYS) - 1) & 1);
+        TRACE(2, it, 0);
         mbar_expect_tx(y_full + 8 * s, 32768);
         if (DKDV) {
           const int g = it / ny, i = y0 + (it - g * ny);
@@ -445,49 +485,78 @@ attn_bwd_kernel(const AttnParams p, const __grid_constant__ CUtensorMap tmQKV128
       }
     }
   } else if (warp == 1) {
-    if (lane == 0) {
+    {   // whole warp runs the loop (uniform operands stay in uniform registers); one elected lane issues
+      const bool leader = elect_one_sync();
       const uint32_t idesc_ab = umma_idesc_f16(p.dtype, 128, 64, false, false);
       const uint32_t idesc_acc = umma_idesc_f16(p.dtype, 128, 128, false, true);
+      // descriptor bases (stage 0); a Y stage is 16 KB = 1024 descriptor units further
+      const DescLoHi dX1 = desc_split(sX1, 0, 1024), dX2 = desc_split(sX2, 0, 1024);
+      const DescLoHi dY1k = desc_split(sY1, 0, 1024), dY2k = desc_split(sY2, 0, 1024);          // K-major view
+      const DescLoHi dY1m = desc_split(sY1, 64 * 128, 1024), dY2m = desc_split(sY2, 64 * 128, 1024);  // MN-major view
       auto issue_ab = [&](int it) {
         const int s = it & 1, ys = it % NYS;
         mbar_wait(y_full + 8 * ys, (it / NYS) & 1);
+        TRACE(1, it, 0);          // Y tile present
         tc_fence_after();
+        const uint32_t tA = tmem + TA + s * 64, tB = tmem + TB + s * 64;
+        DescLoHi y1 = dY1k, y2 = dY2k;
+        y1.lo += ys * 1024; y2.lo += ys * 1024;
+        if (!leader) return;
+        if (DKDV) {
 #pragma unroll
-        for (int kk = 0; kk < 8; ++kk)
-          umma_f16_ss(tmem + TA + s * 64, desc_kmajor(sX1, 128, kk),
-                      desc_kmajor(sY1 + ys * 16384, 64, kk), idesc_ab, kk > 0);
+          for (int kk = 0; kk < 8; ++kk)
+            umma_f16_ss(tA, dX1.at(koff_kmajor(128, kk)), y1.at(koff_kmajor(64, kk)), idesc_ab, kk > 0);
 #pragma unroll
-        for (int kk = 0; kk < 8; ++kk)
-          umma_f16_ss(tmem + TB + s * 64, desc_kmajor(sX2, 128, kk),
-                      desc_kmajor(sY2 + ys * 16384, 64, kk), idesc_ab, kk > 0);
+          for (int kk = 0; kk < 8; ++kk)
+            umma_f16_ss(tB, dX2.at(koff_kmajor(128, kk)), y2.at(koff_kmajor(64, kk)), idesc_ab, kk > 0);
+        } else {
+#pragma unroll
+          for (int kk = 0; kk < 8; ++kk)
+            umma_f16_ts(tA, tmem + TX1 + kk * 8, y1.at(koff_kmajor(64, kk)), idesc_ab, kk > 0);
+#pragma unroll
+          for (int kk = 0; kk < 8; ++kk)
+            umma_f16_ts(tB, tmem + TX2 + kk * 8, y2.at(koff_kmajor(64, kk)), idesc_ab, kk > 0);
+        }
         umma_commit(ab_full + 8 * s);
+        TRACE(1, it, 1);          // score MMAs issued
       };
       // P / dS come back as packed 16-bit pairs written over the score tiles themselves (each softmax
       // thread overwrites only columns it has already read): k-steps 0,1 at columns 0-15 and k-steps
       // 2,3 at columns 32-47 of the 64-column tile. The accumulate MMAs read them as the TMEM A operand.
-      auto a_tmem = [&](uint32_t tile, int kk) { return tile + (uint32_t)((kk >> 1) * 32 + (kk & 1) * 8); };
       mbar_wait(x_full, 0);
+      if (!DKDV) {
+        mbar_wait(x_tmem, 0);
+        tc_fence_after();
+      }
       issue_ab(0);
       if (iters > 1) issue_ab(1);
       for (int it = 0; it < iters; ++it) {
         const int s = it & 1, ys = it % NYS;
         mbar_wait(pds_full + 8 * s, (it >> 1) & 1);
+        TRACE(1, it, 2);          // P / dS present
         tc_fence_after();
+        const uint32_t tA = tmem + TA + s * 64, tB = tmem + TB + s * 64;
+        DescLoHi y1 = dY1m, y2 = dY2m;
+        y1.lo += ys * 1024; y2.lo += ys * 1024;
+        const uint32_t acc_on = it > 0 ? 1u : 0u;
+        if (leader) {
         if (DKDV) {
 #pragma unroll
           for (int kk = 0; kk < 4; ++kk)   // dV += P^T · dO
-            umma_f16_ts(tmem + TACC1, a_tmem(tmem + TA + s * 64, kk), desc_mnmajor(sY2 + ys * 16384, 64, kk),
-                        idesc_acc, (it > 0 || kk > 0));
+            umma_f16_ts(tmem + TACC1, tA + (kk >> 1) * 32 + (kk & 1) * 8, y2.at(kk * 2048), idesc_acc,
+                        kk > 0 ? 1u : acc_on);
         }
 #pragma unroll
         for (int kk = 0; kk < 4; ++kk)     // dK += dS^T · Q   /   dQ += dS · K
-          umma_f16_ts(tmem + TACC2, a_tmem(tmem + TB + s * 64, kk), desc_mnmajor(sY1 + ys * 16384, 64, kk),
-                      idesc_acc, (it > 0 || kk > 0));
+          umma_f16_ts(tmem + TACC2, tB + (kk >> 1) * 32 + (kk & 1) * 8, y1.at(kk * 2048), idesc_acc,
+                      kk > 0 ? 1u : acc_on);
         umma_commit(y_empty + 8 * ys);
+        }
+        TRACE(1, it, 3);          // accumulate MMAs issued
         // the tensor pipe runs MMAs in issue order, so the next scores may overwrite this buffer now
         if (it + 2 < iters) issue_ab(it + 2);
       }
-      umma_commit(acc_done);
+      if (leader) umma_commit(acc_done);
     }
   } else {
     // two threads per row: warps 2-5 own streamed columns [0,32), warps 6-9 own [32,64)
@@ -503,34 +572,81 @@ attn_bwd_kernel(const AttnParams p, const __grid_constant__ CUtensorMap tmQKV128
       my_lse = p.lse[(long long)head * p.T_total + row0 + sidx] * LOG2E;
       my_D = p.D[(long long)head * p.T_total + row0 + sidx];
     }
-    // DKDV: per-query lse / D of the streamed block are staged through smem; the global loads run one
-    // iteration ahead of their use so their latency is off the critical path.
-    auto load_stat = [&](int it) -> float {
-      const int g = it / ny;
-      const int q = (y0 + (it - g * ny)) * 64 + (tid128 & 63);
-      float val = 0.f;
-      if (tid128 < 128 && it < iters && q < seqlen) {
-        const long long off = (long long)(head * G + g) * p.T_total + row0 + q;
-        val = (tid128 < 64) ? p.lse[off] * LOG2E : p.D[off];
+    // DKDV: per-query lse / D are staged through smem in chunks of 8 query blocks (one bar.sync per
+    // chunk instead of per iteration); the global loads of the NEXT chunk are issued right after a chunk
+    // is published, so they have eight iterations to land.
+    constexpr int CH = BWD_STAT_CHUNK;
+    float pre[4] = {0.f, 0.f, 0.f, 0.f};
+    auto load_chunk = [&](int it0) {           // it0: iteration at which the chunk starts (may be >= iters)
+      if (it0 >= iters) return;
+      const int g = it0 / ny;
+      const int q0 = (y0 + (it0 - g * ny)) * 64;
+      const long long hb = (long long)(head * G + g) * p.T_total + row0;
+#pragma unroll
+      for (int k = 0; k < 2; ++k) {
+        const int q = q0 + k * 256 + tid128;
+        const bool ok = q < seqlen;
+        pre[k] = ok ? p.lse[hb + q] : 0.f;
+        pre[2 + k] = ok ? p.D[hb + q] : 0.f;
       }
-      return val;
     };
-    float stat_next = DKDV ? load_stat(0) : 0.f;
+    int ch_it0 = 0, ch_buf = 0;                // start iteration and smem buffer of the current chunk
+    int ch_next = 0;                           // iteration at which the next chunk starts
+    if (DKDV) load_chunk(0);
+    if (!DKDV) {
+      // this thread's row of Q and dO (its 64-element half of head_dim) -> TMEM, packed pairs in K order
+      mbar_wait(x_full, 0);
+#pragma unroll
+      for (int x = 0; x < 2; ++x) {
+        const uint32_t src = (x ? sX2 : sX1) + half * 16384;
+        const uint32_t dst = trow + (x ? TX2 : TX1) + half * 32;
+#pragma unroll
+        for (int hh = 0; hh < 2; ++hh) {
+          uint32_t w[16];
+#pragma unroll
+          for (int c4 = 0; c4 < 4; ++c4) {
+            const uint32_t addr = src + swz_off(r, hh * 4 + c4);
+            asm volatile("ld.shared.v4.b32 {%0, %1, %2, %3}, [%4];"
+                         : "=r"(w[4 * c4]), "=r"(w[4 * c4 + 1]), "=r"(w[4 * c4 + 2]), "=r"(w[4 * c4 + 3])
+                         : "r"(addr));
+          }
+          tmem_st_32x32b_x16(dst + hh * 16, w);
+        }
+      }
+      tmem_wait_st();
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(x_tmem);
+    }
     for (int it = 0; it < iters; ++it) {
       const int s = it & 1;
       int yb;                                   // streamed 64-block index
       if (DKDV) {
         const int g = it / ny;
-        yb = y0 + (it - g * ny);
-        if (tid128 < 128) stat[s * 128 + tid128] = stat_next;
-        stat_next = load_stat(it + 1);
-        asm volatile("bar.sync 1, 256;" ::: "memory");
+        const int li = it - g * ny;
+        yb = y0 + li;
+        if (it == ch_next) {
+          ch_it0 = it;
+          ch_buf ^= 1;
+          const int left = ny - li;             // a chunk never crosses into the next q head
+          ch_next = it + (left < CH ? left : CH);
+          float* dst = stat + ch_buf * (CH * 128);
+#pragma unroll
+          for (int k = 0; k < 2; ++k) {
+            dst[k * 256 + tid128] = pre[k] * LOG2E;
+            dst[CH * 64 + k * 256 + tid128] = pre[2 + k];
+          }
+          load_chunk(ch_next);
+          asm volatile("bar.sync 1, 256;" ::: "memory");
+        }
       } else {
         yb = y0 + it;
       }
       // Only the blocks that touch the causal diagonal (or the end of the sequence) need a mask.
       const bool need_mask = DKDV ? (yb < 2 * blk + 2 || yb * 64 + 64 > seqlen) : (yb >= 2 * blk);
+      if (warp == 2) TRACE(0, it, 0);      // iteration entered
       mbar_wait(ab_full + 8 * s, (it >> 1) & 1);
+      if (warp == 2) TRACE(0, it, 1);      // scores present
       tc_fence_after();
       {
         const int c = half;
@@ -538,10 +654,12 @@ attn_bwd_kernel(const AttnParams p, const __grid_constant__ CUtensorMap tmQKV128
         tmem_ld_32x32b_x32(trow + TA + s * 64 + c * 32, sv);
         tmem_ld_32x32b_x32(trow + TB + s * 64 + c * 32, dv);
         tmem_wait_ld();
+        if (warp == 2) TRACE(0, it, 2);    // scores in registers
         float lse_v[32], D_v[32];
         if (DKDV) {
-          const float4* l4 = reinterpret_cast<const float4*>(stat + s * 128 + c * 32);
-          const float4* d4 = reinterpret_cast<const float4*>(stat + s * 128 + 64 + c * 32);
+          const float* cb = stat + ch_buf * (CH * 128) + (it - ch_it0) * 64 + c * 32;
+          const float4* l4 = reinterpret_cast<const float4*>(cb);
+          const float4* d4 = reinterpret_cast<const float4*>(cb + CH * 64);
 #pragma unroll
           for (int i = 0; i < 8; ++i) {
             const float4 a = l4[i], b4 = d4[i];
@@ -586,6 +704,7 @@ attn_bwd_kernel(const AttnParams p, const __grid_constant__ CUtensorMap tmQKV128
       tc_fence_before();
       __syncwarp();
       if (lane == 0) mbar_arrive(pds_full + 8 * s);
+      if (warp == 2) TRACE(0, it, 3);      // P / dS published
     }
     mbar_wait(acc_done, 0);
     tc_fence_after();
@@ -678,7 +797,7 @@ attn_fwd2_kernel(const AttnParams p, const __grid_constant__ CUtensorMap tm128) 
                  s_full = bars + 72, p_full = bars + 88, pv_done = bars + 104, tmem_slot = bars + 120;
   volatile uint32_t* tmem_slot_ptr =
       reinterpret_cast<volatile uint32_t*>(smem_raw + (tmem_slot - smem_u32(smem_raw)));
-  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int warp = __shfl_sync(0xffffffffu, threadIdx.x >> 5, 0), lane = threadIdx.x & 31;   // warp-uniform for the compiler
 
   if (warp == 8 && lane == 0) {
     tma_prefetch_desc(&tm128);
@@ -701,7 +820,7 @@ attn_fwd2_kernel(const AttnParams p, const __grid_constant__ CUtensorMap tm128) 
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
-  const uint32_t tmem = *tmem_slot_ptr;
+  const uint32_t tmem = __shfl_sync(0xffffffffu, *tmem_slot_ptr, 0);
 
   if (warp == 8) {
     if (lane == 0) {
@@ -727,21 +846,31 @@ attn_fwd2_kernel(const AttnParams p, const __grid_constant__ CUtensorMap tm128) 
       }
     }
   } else if (warp == 9) {
-    if (lane == 0) {
+    {   // whole warp runs the loop (uniform operands stay in uniform registers); one elected lane issues
+      const bool leader = elect_one_sync();
       const uint32_t idesc_s = umma_idesc_f16(p.dtype, 128, 128, false, false);
       const uint32_t idesc_pv = umma_idesc_f16(p.dtype, 128, 128, false, true);
+      const DescLoHi dQ0 = desc_split(sQ, 0, 1024), dK0 = desc_split(sK, 0, 1024);
+      const DescLoHi dV0 = desc_split(sV, 128 * 128, 1024);     // MN-major view of a [128 keys x 128] tile
       auto issue_s = [&](int X, int j) {
+        DescLoHi q = dQ0, k = dK0;
+        q.lo += X * 2048; k.lo += (j & 1) * 2048;                // 32 KB = 2048 descriptor units
+        const uint32_t tS = tmem + X * 128;
+        if (!leader) return;
 #pragma unroll
         for (int kk = 0; kk < 8; ++kk)
-          umma_f16_ss(tmem + X * 128, desc_kmajor(sQ + X * 32768, 128, kk),
-                      desc_kmajor(sK + (j & 1) * 32768, 128, kk), idesc_s, kk > 0);
+          umma_f16_ss(tS, q.at(koff_kmajor(128, kk)), k.at(koff_kmajor(128, kk)), idesc_s, kk > 0);
         umma_commit(s_full + 8 * X);
       };
       auto issue_pv = [&](int X, int j) {
+        DescLoHi v = dV0;
+        v.lo += (j & 1) * 2048;
+        const uint32_t tO = tmem + 256 + X * 128, tP = tmem + X * 128;
+        const uint32_t acc_on = j > 0 ? 1u : 0u;
+        if (!leader) return;
 #pragma unroll
         for (int kk = 0; kk < 8; ++kk)
-          umma_f16_ts(tmem + 256 + X * 128, tmem + X * 128 + kk * 8,
-                      desc_mnmajor(sV + (j & 1) * 32768, 128, kk), idesc_pv, (j > 0 || kk > 0) ? 1u : 0u);
+          umma_f16_ts(tO, tP + kk * 8, v.at(kk * 2048), idesc_pv, kk > 0 ? 1u : acc_on);
         umma_commit(pv_done + 8 * X);
       };
       mbar_wait_b(q_full, 0);
@@ -749,7 +878,7 @@ attn_fwd2_kernel(const AttnParams p, const __grid_constant__ CUtensorMap tm128) 
       tc_fence_after();
       issue_s(0, 0);
       if (hasB) issue_s(1, 0);
-      umma_commit(k_empty);
+      if (leader) umma_commit(k_empty);
       for (int j = 0; j < nblk; ++j) {
         const int s = j & 1;
         const bool actA = j < nA, actB = j < nB, nxtA = j + 1 < nA, nxtB = j + 1 < nB;
@@ -759,21 +888,21 @@ attn_fwd2_kernel(const AttnParams p, const __grid_constant__ CUtensorMap tm128) 
           mbar_wait_b(p_full, j & 1);
           tc_fence_after();
           issue_pv(0, j);
-          if (!actB) umma_commit(v_empty + 8 * s);
+          if (!actB && leader) umma_commit(v_empty + 8 * s);
         }
         if (nxtA) {
           issue_s(0, j + 1);
-          if (!nxtB) umma_commit(k_empty + 8 * (s ^ 1));
+          if (!nxtB && leader) umma_commit(k_empty + 8 * (s ^ 1));
         }
         if (actB) {
           mbar_wait_b(p_full + 8, j & 1);
           tc_fence_after();
           issue_pv(1, j);
-          umma_commit(v_empty + 8 * s);
+          if (leader) umma_commit(v_empty + 8 * s);
         }
         if (nxtB) {
           issue_s(1, j + 1);
-          umma_commit(k_empty + 8 * (s ^ 1));
+          if (leader) umma_commit(k_empty + 8 * (s ^ 1));
         }
       }
     }
@@ -883,7 +1012,8 @@ attn_fwd2_kernel(const AttnParams p, const __grid_constant__ CUtensorMap tm128) 
 }
 
 constexpr int FWD_SMEM = 6 * 32768 + 256 + 1024;
-constexpr int BWD_SMEM = 65536 + 2 * 3 * 16384 + 1024 + 256 + 1024;
+constexpr int BWD_SMEM_Q = 65536 + 2 * BWD_NYS_Q * 16384 + 1024 + 256 + 1024;
+constexpr int BWD_SMEM_KV = 65536 + 2 * BWD_NYS_KV * 16384 + BWD_STAT_BYTES + 256 + 1024;
 
 int make_map(CUtensorMap* m, const void* base, long long T_total, long long width, int box_rows) {
   return dlti_make_tmap_2d(m, base, (uint64_t)width, (uint64_t)T_total, (uint64_t)width, 64,
@@ -891,6 +1021,12 @@ int make_map(CUtensorMap* m, const void* base, long long T_total, long long widt
 }
 
 }  // namespace
+
+#ifdef DLTI_ATTN_TRACE
+DLTI_API int dlti_attn_trace_read(long long* host_out /* [2*3*64*4] */) {
+  return (int)cudaMemcpyFromSymbol(host_out, g_attn_trace, sizeof(long long) * 2 * 3 * 64 * 4);
+}
+#endif
 
 // qkv [T, (H+2KV)*128]; out [T, H*128]; lse [H, T] fp32 (may be NULL for inference).
 DLTI_API int dlti_attn_fwd(const void* qkv, void* out, float* lse, const int* cu_seqlens, int batch,
@@ -962,23 +1098,23 @@ DLTI_API int dlti_attn_bwd(const void* dout, const void* qkv, const void* out, c
   if (dtype == DLTI_BF16) {
     using T = __nv_bfloat16;
     if (!cfg[0]) {
-      DLTI_CUDA_CHECK(cudaFuncSetAttribute(attn_bwd_kernel<T, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, BWD_SMEM));
-      DLTI_CUDA_CHECK(cudaFuncSetAttribute(attn_bwd_kernel<T, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, BWD_SMEM));
+      DLTI_CUDA_CHECK(cudaFuncSetAttribute(attn_bwd_kernel<T, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, BWD_SMEM_KV));
+      DLTI_CUDA_CHECK(cudaFuncSetAttribute(attn_bwd_kernel<T, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, BWD_SMEM_Q));
       cfg[0] = true;
     }
     attn_bwd_prep_kernel<T><<<prep_blocks, 256, 0, st>>>((const T*)dout, (const T*)out, D_scratch, T_total, H, p.ldo);
-    attn_bwd_kernel<T, true><<<g_kv, AT_THREADS, BWD_SMEM, st>>>(p, q128, q64, d128, d64);
-    attn_bwd_kernel<T, false><<<g_q, AT_THREADS, BWD_SMEM, st>>>(p, q128, q64, d128, d64);
+    attn_bwd_kernel<T, true><<<g_kv, AT_THREADS, BWD_SMEM_KV, st>>>(p, q128, q64, d128, d64);
+    attn_bwd_kernel<T, false><<<g_q, AT_THREADS, BWD_SMEM_Q, st>>>(p, q128, q64, d128, d64);
   } else if (dtype == DLTI_FP16) {
     using T = __half;
     if (!cfg[1]) {
-      DLTI_CUDA_CHECK(cudaFuncSetAttribute(attn_bwd_kernel<T, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, BWD_SMEM));
-      DLTI_CUDA_CHECK(cudaFuncSetAttribute(attn_bwd_kernel<T, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, BWD_SMEM));
+      DLTI_CUDA_CHECK(cudaFuncSetAttribute(attn_bwd_kernel<T, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, BWD_SMEM_KV));
+      DLTI_CUDA_CHECK(cudaFuncSetAttribute(attn_bwd_kernel<T, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, BWD_SMEM_Q));
       cfg[1] = true;
     }
     attn_bwd_prep_kernel<T><<<prep_blocks, 256, 0, st>>>((const T*)dout, (const T*)out, D_scratch, T_total, H, p.ldo);
-    attn_bwd_kernel<T, true><<<g_kv, AT_THREADS, BWD_SMEM, st>>>(p, q128, q64, d128, d64);
-    attn_bwd_kernel<T, false><<<g_q, AT_THREADS, BWD_SMEM, st>>>(p, q128, q64, d128, d64);
+    attn_bwd_kernel<T, true><<<g_kv, AT_THREADS, BWD_SMEM_KV, st>>>(p, q128, q64, d128, d64);
+    attn_bwd_kernel<T, false><<<g_q, AT_THREADS, BWD_SMEM_Q, st>>>(p, q128, q64, d128, d64);
   } else {
     return DLTI_ERR_UNSUPPORTED;
   }

@@ -51,7 +51,8 @@ def gpu_lib() -> C.CDLL:
             _try_build("gpu")
         if not _GPU_LIB_PATH.exists():
             raise DltiError(f"native GPU library missing: {_GPU_LIB_PATH} (run python -m dlti_b200.build)")
-        lib = C.CDLL(str(_GPU_LIB_PATH))
+        # DLTI_GPU_LIB: load an alternative build of the library (A/B experiments with compile-time knobs)
+        lib = C.CDLL(os.environ.get("DLTI_GPU_LIB") or str(_GPU_LIB_PATH))
         lib.dlti_last_error.restype = C.c_char_p
         lib.dlti_error_string.restype = C.c_char_p
         lib.dlti_error_string.argtypes = [C.c_int]

@@ -237,6 +237,12 @@ int dlti_sample(const void* logits, long long ld, int batch, int V, const float*
                 unsigned long long step, long long* out, float* out_logprob, int dtype,
                 dlti_stream_t stream);
 
+#ifdef DLTI_ATTN_TRACE
+/* Developer builds only (-DDLTI_ATTN_TRACE): clock64() timeline of CTA (0,0,0) of the last backward
+ * kernels, [dQ | dK/dV][role: softmax, mma, producer][iteration < 64][event < 4]. */
+int dlti_attn_trace_read(long long* host_out);
+#endif
+
 #ifdef __cplusplus
 }
 #endif

@@ -43,7 +43,16 @@ class LayerWeights:
                                  # GEMM itself fills from the owner ranks, K1)
 
     def g(self, name: str):
-        return self.gather[name] if self.gather else None
+        """GatherSpec for the FIRST GEMM that touches `name` after the layer was fetched (that launch pulls
+        the shards while it computes); None afterwards — the staging buffer is then complete in stream
+        order, so the remaining micro-batches / backward GEMMs run the plain (CTA-pair) kernel on it."""
+        if not self.gather:
+            return None
+        sp = self.gather[name]
+        if sp.used_epoch == sp.epoch:
+            return None
+        sp.used_epoch = sp.epoch
+        return sp
 
 
 class ResidentWeights:

@@ -121,6 +121,7 @@ class GatherSpec:
         self.staging, self.counters, self.err = staging, counters, err
         self.rows_per_rank, self.rank, self.world = rows_per_rank, rank, world
         self.epoch = 0
+        self.used_epoch = -1      # epoch whose gather has already been launched (see LayerWeights.g)
 
 
 class FusedComm:

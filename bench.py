@@ -211,6 +211,10 @@ def main() -> None:
     arena_gb = tr.fused.arena.total_bytes() / 1e9 if tr.fused is not None else 0.0   # symmetric arena is
     peak = max_over_ranks(torch.cuda.max_memory_allocated() / 1e9 + arena_gb)         # outside torch's allocator
 
+    # a step that produced a non-finite loss did not train anything: refuse to report a number for it
+    import math
+    if not (math.isfinite(loss_dev) and math.isfinite(float(loss))):
+        raise SystemExit(f"bench: non-finite loss (device region {loss_dev}, e2e {loss}); no result reported")
     if info.rank == 0:
         value = tokens_per_step / dev_ms * 1e3
         e2e = tokens_per_step / e2e_ms * 1e3

@@ -232,6 +232,11 @@ class Zero3Weights:
                 g[m] = sp
                 rows = self.staging[m].shape[0]
                 self.gather_bytes += rows * self.shapes[m][1] * 2 * (self.world - 1) // self.world
+                # The gather kernel reads this rank's own rows in place (never copies them), but the
+                # later plain GEMMs of this fetch read the staging buffer only: place the own rows now
+                # (1/world of the matrix, device-local copy in stream order).
+                rp = rows // self.world
+                self.staging[m][self.rank * rp:(self.rank + 1) * rp].copy_(self.layer_shards[i][m], non_blocking=True)
             st = self.staging
             return LayerWeights(st["w_qkv"][: self.shapes["w_qkv"][0]], st["w_o"][: self.shapes["w_o"][0]],
                                 st["w_gu"][: self.shapes["w_gu"][0]], st["w_down"][: self.shapes["w_down"][0]],

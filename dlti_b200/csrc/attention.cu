@@ -98,19 +98,6 @@ __device__ __forceinline__ uint64_t desc_mnmajor(uint32_t base, int krows, int k
   return umma_smem_desc(base + kk * 2048, krows * 128, 1024);
 }
 
-// The MMAs of the attention kernels are short (32-64 clk), so the single issuing thread must not spend
-// longer than that preparing each one: descriptors are split into a precomputed (lo, hi) pair and the
-// per-MMA work is one 32-bit add of a compile-time offset (traced: ~60 clk per MMA before this).
-struct DescLoHi {
-  uint32_t lo, hi;
-  __device__ __forceinline__ uint64_t at(uint32_t byte_off) const {
-    return ((uint64_t)hi << 32) | (uint64_t)(lo + (byte_off >> 4));
-  }
-};
-__device__ __forceinline__ DescLoHi desc_split(uint32_t smem_addr, uint32_t lbo_bytes, uint32_t sbo_bytes) {
-  const uint64_t d = umma_smem_desc(smem_addr, lbo_bytes, sbo_bytes);
-  return DescLoHi{(uint32_t)d, (uint32_t)(d >> 32)};
-}
 // byte offset of k-step kk inside a K-major [rows x 128] operand (two [rows x 64] chunks)
 __device__ __forceinline__ constexpr uint32_t koff_kmajor(int rows, int kk) {
   return (uint32_t)((kk >> 2) * (rows * 128) + (kk & 3) * 32);

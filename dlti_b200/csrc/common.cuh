@@ -270,6 +270,22 @@ __device__ __forceinline__ uint64_t umma_smem_desc(uint32_t smem_addr, uint32_t 
   d |= (uint64_t)2 << 61;                               // layout type: SWIZZLE_128B
   return d;
 }
+// MMA issue must be cheap: an MMA lasts 32-128 clk, so the issuing thread cannot spend longer than that
+// preparing each one. Descriptors are split into a precomputed (lo, hi) pair and the per-MMA work is one
+// 32-bit add of a compile-time offset. Equally important: run the issue loop WARP-UNIFORMLY (whole warp,
+// uniform operands, warp index / TMEM base made uniform with __shfl_sync) and predicate only the
+// tcgen05 instructions on elect_one_sync(): issuing from inside `if (lane == 0)` makes the compiler wrap
+// every UTCHMMA in an ELECT / R2UR / BRA.U.ANY waterfall (traced: ~60 clk per MMA).
+struct DescLoHi {
+  uint32_t lo, hi;
+  __device__ __forceinline__ uint64_t at(uint32_t byte_off) const {
+    return ((uint64_t)hi << 32) | (uint64_t)(lo + (byte_off >> 4));
+  }
+};
+__device__ __forceinline__ DescLoHi desc_split(uint32_t smem_addr, uint32_t lbo_bytes, uint32_t sbo_bytes) {
+  const uint64_t d = umma_smem_desc(smem_addr, lbo_bytes, sbo_bytes);
+  return DescLoHi{(uint32_t)d, (uint32_t)(d >> 32)};
+}
 // Instruction descriptor for kind::f16 with fp32 accumulation.
 __device__ __host__ __forceinline__ uint32_t umma_idesc_f16(int in_dtype /*DltiDtype*/, int M, int N,
                                                             bool a_mn_major, bool b_mn_major) {

@@ -136,7 +136,7 @@ gemm_tcgen05_kernel(const GemmParams p, const __grid_constant__ CUtensorMap tmA,
     for (int i = 0; i < 16; ++i)   // static indices: keeps the parameters in the constant bank
       if (threadIdx.x == i) s_peers[i] = GATHER ? const_cast<void*>(gp.peer[i]) : p.push_peer[i];
   }
-  const int warp = threadIdx.x >> 5;
+  const int warp = __shfl_sync(0xffffffffu, threadIdx.x >> 5, 0);   // uniform for the compiler
   const int lane = threadIdx.x & 31;
   const int tiles_mn = p.nmb * p.nnb;
   const int total_tiles = tiles_mn * p.split_k;
@@ -166,7 +166,7 @@ gemm_tcgen05_kernel(const GemmParams p, const __grid_constant__ CUtensorMap tmA,
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
-  const uint32_t tmem_base = *tmem_slot_ptr;
+  const uint32_t tmem_base = __shfl_sync(0xffffffffu, *tmem_slot_ptr, 0);
 
   if (warp == 0) {
     // ===================== TMA producer =====================
@@ -260,8 +260,13 @@ gemm_tcgen05_kernel(const GemmParams p, const __grid_constant__ CUtensorMap tmA,
       }
     }
   } else if (warp == 1) {
-    // ===================== MMA issuer (single thread) =====================
-    if (lane == 0) {
+    // ===================== MMA issuer =====================
+    // The whole warp runs the loop (uniform control flow and operands); one elected lane issues.
+    {
+      const bool el = elect_one_sync();
+      const DescLoHi dA = A_MN ? desc_split(smem_base, BK * 128, 1024) : desc_split(smem_base, 0, 1024);
+      const DescLoHi dB = B_MN ? desc_split(smem_base + C_::A_BYTES, BK * 128, 1024)
+                               : desc_split(smem_base + C_::A_BYTES, 0, 1024);
       int stage = 0;
       uint32_t phase = 0;
       int acc = 0;
@@ -276,19 +281,18 @@ gemm_tcgen05_kernel(const GemmParams p, const __grid_constant__ CUtensorMap tmA,
         for (int kb = kb0; kb < kb1; ++kb) {
           mbar_wait(full_bar(stage), phase);
           tc_fence_after();
-          const uint32_t sa = smem_base + stage * C_::STAGE_BYTES;
-          const uint32_t sb = sa + C_::A_BYTES;
+          DescLoHi a = dA, b = dB;
+          a.lo += stage * (C_::STAGE_BYTES >> 4);
+          b.lo += stage * (C_::STAGE_BYTES >> 4);
+          if (el) {
 #pragma unroll
-          for (int k = 0; k < BK / UMMA_K; ++k) {
-            uint64_t ad, bd;
-            if constexpr (!A_MN) ad = umma_smem_desc(sa + k * (UMMA_K * 2), 0, 1024);
-            else                 ad = umma_smem_desc(sa + k * (UMMA_K * 128), BK * 128, 1024);
-            if constexpr (!B_MN) bd = umma_smem_desc(sb + k * (UMMA_K * 2), 0, 1024);
-            else                 bd = umma_smem_desc(sb + k * (UMMA_K * 128), BK * 128, 1024);
-            umma_f16_ss(d_tmem, ad, bd, p.idesc, (kb > kb0 || k > 0) ? 1u : 0u);
+            for (int k = 0; k < BK / UMMA_K; ++k)
+              umma_f16_ss(d_tmem, a.at(A_MN ? k * (UMMA_K * 128) : k * (UMMA_K * 2)),
+                          b.at(B_MN ? k * (UMMA_K * 128) : k * (UMMA_K * 2)), p.idesc,
+                          (kb > kb0 || k > 0) ? 1u : 0u);
+            umma_commit(empty_bar(stage));  // frees the smem slot once these MMAs retire
+            if (kb == kb1 - 1) umma_commit(tfull_bar(acc));
           }
-          umma_commit(empty_bar(stage));  // frees the smem slot once these MMAs retire
-          if (kb == kb1 - 1) umma_commit(tfull_bar(acc));
           if (++stage == C_::STAGES) { stage = 0; phase ^= 1u; }
         }
         if (++acc == 2) { acc = 0; acc_phase ^= 1u; }

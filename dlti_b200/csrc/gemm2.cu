@@ -171,8 +171,8 @@ gemm2_kernel(const Gemm2Params p, const __grid_constant__ CUtensorMap tmA, const
   volatile uint32_t* tmem_slot_ptr =
       reinterpret_cast<volatile uint32_t*>(smem_raw + (tmem_slot - smem_u32(smem_raw)));
 
-  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const uint32_t rank = cluster_ctarank();
+  const int warp = __shfl_sync(0xffffffffu, threadIdx.x >> 5, 0), lane = threadIdx.x & 31;   // uniform for the compiler
+  const uint32_t rank = __shfl_sync(0xffffffffu, cluster_ctarank(), 0);
   const bool leader = rank == 0;
   const int cid = blockIdx.x >> 1, ncl = gridDim.x >> 1;
   const int total_tiles = p.nmb2 * p.nnb;
@@ -199,7 +199,7 @@ gemm2_kernel(const Gemm2Params p, const __grid_constant__ CUtensorMap tmA, const
   tc_fence_before();
   cluster_sync_all();
   tc_fence_after();
-  const uint32_t tmem_base = *tmem_slot_ptr;
+  const uint32_t tmem_base = __shfl_sync(0xffffffffu, *tmem_slot_ptr, 0);
 
   if (warp == 0) {
     // ===================== TMA producer (both CTAs) =====================
@@ -236,7 +236,11 @@ gemm2_kernel(const Gemm2Params p, const __grid_constant__ CUtensorMap tmA, const
     }
   } else if (warp == 1) {
     // ===================== MMA issuer (leader CTA only) =====================
-    if (leader && lane == 0) {
+    // The whole warp runs the loop (uniform control flow and operands); one elected lane issues.
+    if (leader) {
+      const bool el = elect_one_sync();
+      const DescLoHi dA = desc_split(smem_base, 0, 1024);
+      const DescLoHi dB = B_MN ? desc_split(smem_base + A_BYTES, BK * 128, 1024) : desc_split(smem_base + A_BYTES, 0, 1024);
       int stage = 0;
       uint32_t phase = 0;
       int acc = 0;
@@ -250,18 +254,17 @@ gemm2_kernel(const Gemm2Params p, const __grid_constant__ CUtensorMap tmA, const
         for (int kb = sg.kb0; kb < sg.kb1; ++kb) {
           mbar_wait_bounded(full_bar(stage), phase);
           tc_fence_after();
-          const uint32_t sa = smem_base + stage * STAGE_BYTES;
-          const uint32_t sb = sa + A_BYTES;
+          DescLoHi a = dA, b = dB;
+          a.lo += stage * (STAGE_BYTES >> 4);
+          b.lo += stage * (STAGE_BYTES >> 4);
+          if (el) {
 #pragma unroll
-          for (int k = 0; k < BK / UMMA_K; ++k) {
-            const uint64_t ad = umma_smem_desc(sa + k * (UMMA_K * 2), 0, 1024);
-            uint64_t bd;
-            if constexpr (!B_MN) bd = umma_smem_desc(sb + k * (UMMA_K * 2), 0, 1024);
-            else                 bd = umma_smem_desc(sb + k * (UMMA_K * 128), BK * 128, 1024);
-            umma_f16_ss_2sm(d_tmem, ad, bd, p.idesc, (kb > sg.kb0 || k > 0) ? 1u : 0u);
+            for (int k = 0; k < BK / UMMA_K; ++k)
+              umma_f16_ss_2sm(d_tmem, a.at(k * (UMMA_K * 2)), b.at(B_MN ? k * (UMMA_K * 128) : k * (UMMA_K * 2)),
+                              p.idesc, (kb > sg.kb0 || k > 0) ? 1u : 0u);
+            umma_commit_2sm(empty_bar(stage));
+            if (kb == sg.kb1 - 1) umma_commit_2sm(tfull_bar(acc));
           }
-          umma_commit_2sm(empty_bar(stage));
-          if (kb == sg.kb1 - 1) umma_commit_2sm(tfull_bar(acc));
           if (++stage == STAGES) { stage = 0; phase ^= 1u; }
         }
         if (++acc == 2) { acc = 0; acc_phase ^= 1u; }

@@ -38,7 +38,8 @@ constexpr int HD = 128;           // head dim
 constexpr int BWD_NYS_Q = 5, BWD_NYS_KV = 4;
 constexpr int BWD_STAT_CHUNK = 8;        // dK/dV: query blocks whose lse/D are staged per bar.sync
 constexpr int BWD_STAT_BYTES = 2 * BWD_STAT_CHUNK * 64 * 2 * 4;   // double-buffered {lse, D} x 512 queries
-constexpr int AT_THREADS = 320;   // producer, mma, 8 softmax warps (two threads per row: column halves)
+constexpr int AT_THREADS = 320;   // one-tile forward: producer, mma, 8 softmax warps (two threads per row)
+constexpr int BWD_THREADS = 576;  // backward: producer, mma, 16 softmax warps (four threads per row)
 constexpr float LOG2E = 1.4426950408889634f;
 constexpr float LN2 = 0.6931471805599453f;
 
@@ -358,7 +359,7 @@ __device__ long long g_attn_trace[2 * 3 * 64 * 4];   // [dQ | dK/dV][role][itera
 #endif
 
 template <typename T, bool DKDV>
-__global__ void __launch_bounds__(AT_THREADS, 1)
+__global__ void __launch_bounds__(BWD_THREADS, 1)
 attn_bwd_kernel(const AttnParams p, const __grid_constant__ CUtensorMap tmQKV128,
                 const __grid_constant__ CUtensorMap tmQKV64,
                 const __grid_constant__ CUtensorMap tmDO128,
@@ -411,10 +412,10 @@ attn_bwd_kernel(const AttnParams p, const __grid_constant__ CUtensorMap tmQKV128
     }
     for (int s = 0; s < 2; ++s) {
       mbar_init(ab_full + 8 * s, 1);
-      mbar_init(pds_full + 8 * s, 8);
+      mbar_init(pds_full + 8 * s, 16);
     }
     mbar_init(acc_done, 1);
-    mbar_init(x_tmem, 8);
+    mbar_init(x_tmem, 16);
     mbar_fence_init();
   }
   if (warp == 1) {
@@ -508,8 +509,8 @@ attn_bwd_kernel(const AttnParams p, const __grid_constant__ CUtensorMap tmQKV128
         TRACE(1, it, 1);          // score MMAs issued
       };
       // P / dS come back as packed 16-bit pairs written over the score tiles themselves (each softmax
-      // thread overwrites only columns it has already read): k-steps 0,1 at columns 0-15 and k-steps
-      // 2,3 at columns 32-47 of the 64-column tile. The accumulate MMAs read them as the TMEM A operand.
+      // thread overwrites only columns it has already read): k-step kk (16 elements) sits at columns
+      // 16*kk .. 16*kk+7 of the 64-column tile. The accumulate MMAs read them as the TMEM A operand.
       mbar_wait(x_full, 0);
       if (!DKDV) {
         mbar_wait(x_tmem, 0);
@@ -530,12 +531,12 @@ attn_bwd_kernel(const AttnParams p, const __grid_constant__ CUtensorMap tmQKV128
         if (DKDV) {
 #pragma unroll
           for (int kk = 0; kk < 4; ++kk)   // dV += P^T · dO
-            umma_f16_ts(tmem + TACC1, tA + (kk >> 1) * 32 + (kk & 1) * 8, y2.at(kk * 2048), idesc_acc,
+            umma_f16_ts(tmem + TACC1, tA + kk * 16, y2.at(kk * 2048), idesc_acc,
                         kk > 0 ? 1u : acc_on);
         }
 #pragma unroll
         for (int kk = 0; kk < 4; ++kk)     // dK += dS^T · Q   /   dQ += dS · K
-          umma_f16_ts(tmem + TACC2, tB + (kk >> 1) * 32 + (kk & 1) * 8, y1.at(kk * 2048), idesc_acc,
+          umma_f16_ts(tmem + TACC2, tB + kk * 16, y1.at(kk * 2048), idesc_acc,
                       kk > 0 ? 1u : acc_on);
         umma_commit(y_empty + 8 * ys);
         }
@@ -546,14 +547,16 @@ attn_bwd_kernel(const AttnParams p, const __grid_constant__ CUtensorMap tmQKV128
       if (leader) umma_commit(acc_done);
     }
   } else {
-    // two threads per row: warps 2-5 own streamed columns [0,32), warps 6-9 own [32,64)
+    // FOUR threads per row (16 softmax warps): warp w owns rows 32*(w&3).. and streamed columns
+    // [16*part, 16*part+16), part = (w-2)>>2. Four warps per scheduler keep the MUFU/FMA pipes fed where two
+    // left the per-iteration softmax (1160 clk traced) longer than the MMA work it overlaps with.
     const int quarter = warp & 3;
-    const int half = (warp - 2) >> 2;
+    const int part = (warp - 2) >> 2;          // 0..3
     const int r = quarter * 32 + lane;
     const int sidx = blk * 128 + r;            // key index (DKDV) or query index (!DKDV)
     const uint32_t trow = tmem + ((uint32_t)(quarter * 32) << 16);
     const float sl2 = p.scale * LOG2E;
-    const int tid128 = threadIdx.x - 64;       // 0..255; the first 128 stage lse / D
+    const int tid = threadIdx.x - 64;          // 0..511
     float my_lse = 0.f, my_D = 0.f;
     if (!DKDV && sidx < seqlen) {
       my_lse = p.lse[(long long)head * p.T_total + row0 + sidx] * LOG2E;
@@ -563,42 +566,34 @@ attn_bwd_kernel(const AttnParams p, const __grid_constant__ CUtensorMap tmQKV128
     // chunk instead of per iteration); the global loads of the NEXT chunk are issued right after a chunk
     // is published, so they have eight iterations to land.
     constexpr int CH = BWD_STAT_CHUNK;
-    float pre[4] = {0.f, 0.f, 0.f, 0.f};
+    float pre_l = 0.f, pre_d = 0.f;
     auto load_chunk = [&](int it0) {           // it0: iteration at which the chunk starts (may be >= iters)
       if (it0 >= iters) return;
       const int g = it0 / ny;
-      const int q0 = (y0 + (it0 - g * ny)) * 64;
+      const int q = (y0 + (it0 - g * ny)) * 64 + tid;
       const long long hb = (long long)(head * G + g) * p.T_total + row0;
-#pragma unroll
-      for (int k = 0; k < 2; ++k) {
-        const int q = q0 + k * 256 + tid128;
-        const bool ok = q < seqlen;
-        pre[k] = ok ? p.lse[hb + q] : 0.f;
-        pre[2 + k] = ok ? p.D[hb + q] : 0.f;
-      }
+      const bool ok = q < seqlen;
+      pre_l = ok ? p.lse[hb + q] : 0.f;
+      pre_d = ok ? p.D[hb + q] : 0.f;
     };
     int ch_it0 = 0, ch_buf = 0;                // start iteration and smem buffer of the current chunk
     int ch_next = 0;                           // iteration at which the next chunk starts
     if (DKDV) load_chunk(0);
     if (!DKDV) {
-      // this thread's row of Q and dO (its 64-element half of head_dim) -> TMEM, packed pairs in K order
+      // this thread's row of Q and dO (its 32-element quarter of head_dim) -> TMEM, packed pairs in K order
       mbar_wait(x_full, 0);
 #pragma unroll
       for (int x = 0; x < 2; ++x) {
-        const uint32_t src = (x ? sX2 : sX1) + half * 16384;
-        const uint32_t dst = trow + (x ? TX2 : TX1) + half * 32;
+        const uint32_t src = (x ? sX2 : sX1) + (part >> 1) * 16384;
+        uint32_t w[16];
 #pragma unroll
-        for (int hh = 0; hh < 2; ++hh) {
-          uint32_t w[16];
-#pragma unroll
-          for (int c4 = 0; c4 < 4; ++c4) {
-            const uint32_t addr = src + swz_off(r, hh * 4 + c4);
-            asm volatile("ld.shared.v4.b32 {%0, %1, %2, %3}, [%4];"
-                         : "=r"(w[4 * c4]), "=r"(w[4 * c4 + 1]), "=r"(w[4 * c4 + 2]), "=r"(w[4 * c4 + 3])
-                         : "r"(addr));
-          }
-          tmem_st_32x32b_x16(dst + hh * 16, w);
+        for (int c4 = 0; c4 < 4; ++c4) {
+          const uint32_t addr = src + swz_off(r, (part & 1) * 4 + c4);
+          asm volatile("ld.shared.v4.b32 {%0, %1, %2, %3}, [%4];"
+                       : "=r"(w[4 * c4]), "=r"(w[4 * c4 + 1]), "=r"(w[4 * c4 + 2]), "=r"(w[4 * c4 + 3])
+                       : "r"(addr));
         }
+        tmem_st_32x32b_x16(trow + (x ? TX2 : TX1) + part * 16, w);
       }
       tmem_wait_st();
       tc_fence_before();
@@ -618,13 +613,10 @@ attn_bwd_kernel(const AttnParams p, const __grid_constant__ CUtensorMap tmQKV128
           const int left = ny - li;             // a chunk never crosses into the next q head
           ch_next = it + (left < CH ? left : CH);
           float* dst = stat + ch_buf * (CH * 128);
-#pragma unroll
-          for (int k = 0; k < 2; ++k) {
-            dst[k * 256 + tid128] = pre[k] * LOG2E;
-            dst[CH * 64 + k * 256 + tid128] = pre[2 + k];
-          }
+          dst[tid] = pre_l * LOG2E;
+          dst[CH * 64 + tid] = pre_d;
           load_chunk(ch_next);
-          asm volatile("bar.sync 1, 256;" ::: "memory");
+          asm volatile("bar.sync 1, 512;" ::: "memory");
         }
       } else {
         yb = y0 + it;
@@ -636,19 +628,18 @@ attn_bwd_kernel(const AttnParams p, const __grid_constant__ CUtensorMap tmQKV128
       if (warp == 2) TRACE(0, it, 1);      // scores present
       tc_fence_after();
       {
-        const int c = half;
-        uint32_t sv[32], dv[32];
-        tmem_ld_32x32b_x32(trow + TA + s * 64 + c * 32, sv);
-        tmem_ld_32x32b_x32(trow + TB + s * 64 + c * 32, dv);
+        uint32_t sv[16], dv[16];
+        tmem_ld_32x32b_x16(trow + TA + s * 64 + part * 16, sv);
+        tmem_ld_32x32b_x16(trow + TB + s * 64 + part * 16, dv);
         tmem_wait_ld();
         if (warp == 2) TRACE(0, it, 2);    // scores in registers
-        float lse_v[32], D_v[32];
+        float lse_v[16], D_v[16];
         if (DKDV) {
-          const float* cb = stat + ch_buf * (CH * 128) + (it - ch_it0) * 64 + c * 32;
+          const float* cb = stat + ch_buf * (CH * 128) + (it - ch_it0) * 64 + part * 16;
           const float4* l4 = reinterpret_cast<const float4*>(cb);
           const float4* d4 = reinterpret_cast<const float4*>(cb + CH * 64);
 #pragma unroll
-          for (int i = 0; i < 8; ++i) {
+          for (int i = 0; i < 4; ++i) {
             const float4 a = l4[i], b4 = d4[i];
             lse_v[4 * i] = a.x; lse_v[4 * i + 1] = a.y; lse_v[4 * i + 2] = a.z; lse_v[4 * i + 3] = a.w;
             D_v[4 * i] = b4.x; D_v[4 * i + 1] = b4.y; D_v[4 * i + 2] = b4.z; D_v[4 * i + 3] = b4.w;
@@ -656,10 +647,10 @@ attn_bwd_kernel(const AttnParams p, const __grid_constant__ CUtensorMap tmQKV128
         }
         // p = 2^(s*scale*log2e - lse);  ds = p * (dp - D)   (the 1/sqrt(d) factor of dS is applied once,
         // to the dK / dQ accumulators, in the epilogue)
-        float pr[32], ds[32];
+        float pr[16], ds[16];
         if (!need_mask) {
 #pragma unroll
-          for (int i = 0; i < 32; ++i) {
+          for (int i = 0; i < 16; ++i) {
             const float x = fmaf(__uint_as_float(sv[i]), sl2, -(DKDV ? lse_v[i] : my_lse));
             const float pv = ex2_approx(x);
             pr[i] = pv;
@@ -667,8 +658,8 @@ attn_bwd_kernel(const AttnParams p, const __grid_constant__ CUtensorMap tmQKV128
           }
         } else {
 #pragma unroll
-          for (int i = 0; i < 32; ++i) {
-            const int yi = yb * 64 + c * 32 + i;  // query index (DKDV) or key index (!DKDV)
+          for (int i = 0; i < 16; ++i) {
+            const int yi = yb * 64 + part * 16 + i;  // query index (DKDV) or key index (!DKDV)
             const bool valid = DKDV ? ((yi < seqlen) && (yi >= sidx)) : ((sidx < seqlen) && (yi <= sidx));
             float x = fmaf(__uint_as_float(sv[i]), sl2, -(DKDV ? lse_v[i] : my_lse));
             x = valid ? x : -INFINITY;            // exp2(-inf) = 0 exactly; no NaNs from garbage rows
@@ -677,15 +668,17 @@ attn_bwd_kernel(const AttnParams p, const __grid_constant__ CUtensorMap tmQKV128
             ds[i] = valid ? pv * (__uint_as_float(dv[i]) - (DKDV ? D_v[i] : my_D)) : 0.f;
           }
         }
-        uint32_t pk[16];
+        // packed pairs go back over this thread's own (already read) score columns: k-step `part`
+        // (16 elements) occupies columns 16*part .. 16*part+7 of the tile
+        uint32_t pk[8];
         if (DKDV) {
 #pragma unroll
-          for (int i = 0; i < 16; ++i) pk[i] = Cvt<T>::pack2(pr[2 * i], pr[2 * i + 1]);
-          tmem_st_32x32b_x16(trow + TA + s * 64 + c * 32, pk);
+          for (int i = 0; i < 8; ++i) pk[i] = Cvt<T>::pack2(pr[2 * i], pr[2 * i + 1]);
+          tmem_st_32x32b_x8(trow + TA + s * 64 + part * 16, pk);
         }
 #pragma unroll
-        for (int i = 0; i < 16; ++i) pk[i] = Cvt<T>::pack2(ds[2 * i], ds[2 * i + 1]);
-        tmem_st_32x32b_x16(trow + TB + s * 64 + c * 32, pk);
+        for (int i = 0; i < 8; ++i) pk[i] = Cvt<T>::pack2(ds[2 * i], ds[2 * i + 1]);
+        tmem_st_32x32b_x8(trow + TB + s * 64 + part * 16, pk);
       }
       tmem_wait_st();
       tc_fence_before();
@@ -695,7 +688,7 @@ attn_bwd_kernel(const AttnParams p, const __grid_constant__ CUtensorMap tmQKV128
     }
     mbar_wait(acc_done, 0);
     tc_fence_after();
-    // write the accumulators
+    // write the accumulators: this thread's row, columns [32*part, 32*part+32)
     T* outbase = reinterpret_cast<T*>(p.dqkv) + (long long)(row0 + sidx) * p.W;
     const int nacc = DKDV ? 2 : 1;
     for (int a = 0; a < nacc; ++a) {
@@ -704,22 +697,18 @@ attn_bwd_kernel(const AttnParams p, const __grid_constant__ CUtensorMap tmQKV128
       int col;
       if (DKDV) col = (a == 0) ? (vcol_base + head * HD) : (kcol_base + head * HD);
       else col = head * HD;
+      uint32_t v[32];
+      tmem_ld_32x32b_x32(trow + tacc + part * 32, v);
+      tmem_wait_ld();
+      if (sidx < seqlen) {
 #pragma unroll
-      for (int cc = 0; cc < 2; ++cc) {
-        const int c = half * 2 + cc;
-        uint32_t v[32];
-        tmem_ld_32x32b_x32(trow + tacc + c * 32, v);
-        tmem_wait_ld();
-        if (sidx < seqlen) {
+        for (int k = 0; k < 4; ++k) {
+          int4 ov;
+          uint32_t* ou = reinterpret_cast<uint32_t*>(&ov);
 #pragma unroll
-          for (int k = 0; k < 4; ++k) {
-            int4 ov;
-            uint32_t* ou = reinterpret_cast<uint32_t*>(&ov);
-#pragma unroll
-            for (int q = 0; q < 4; ++q)
-              ou[q] = Cvt<T>::pack2(__uint_as_float(v[8 * k + 2 * q]) * osc, __uint_as_float(v[8 * k + 2 * q + 1]) * osc);
-            *reinterpret_cast<int4*>(outbase + col + c * 32 + 8 * k) = ov;
-          }
+          for (int q = 0; q < 4; ++q)
+            ou[q] = Cvt<T>::pack2(__uint_as_float(v[8 * k + 2 * q]) * osc, __uint_as_float(v[8 * k + 2 * q + 1]) * osc);
+          *reinterpret_cast<int4*>(outbase + col + part * 32 + 8 * k) = ov;
         }
       }
     }
@@ -1090,8 +1079,8 @@ DLTI_API int dlti_attn_bwd(const void* dout, const void* qkv, const void* out, c
       cfg[0] = true;
     }
     attn_bwd_prep_kernel<T><<<prep_blocks, 256, 0, st>>>((const T*)dout, (const T*)out, D_scratch, T_total, H, p.ldo);
-    attn_bwd_kernel<T, true><<<g_kv, AT_THREADS, BWD_SMEM_KV, st>>>(p, q128, q64, d128, d64);
-    attn_bwd_kernel<T, false><<<g_q, AT_THREADS, BWD_SMEM_Q, st>>>(p, q128, q64, d128, d64);
+    attn_bwd_kernel<T, true><<<g_kv, BWD_THREADS, BWD_SMEM_KV, st>>>(p, q128, q64, d128, d64);
+    attn_bwd_kernel<T, false><<<g_q, BWD_THREADS, BWD_SMEM_Q, st>>>(p, q128, q64, d128, d64);
   } else if (dtype == DLTI_FP16) {
     using T = __half;
     if (!cfg[1]) {
@@ -1100,8 +1089,8 @@ DLTI_API int dlti_attn_bwd(const void* dout, const void* qkv, const void* out, c
       cfg[1] = true;
     }
     attn_bwd_prep_kernel<T><<<prep_blocks, 256, 0, st>>>((const T*)dout, (const T*)out, D_scratch, T_total, H, p.ldo);
-    attn_bwd_kernel<T, true><<<g_kv, AT_THREADS, BWD_SMEM_KV, st>>>(p, q128, q64, d128, d64);
-    attn_bwd_kernel<T, false><<<g_q, AT_THREADS, BWD_SMEM_Q, st>>>(p, q128, q64, d128, d64);
+    attn_bwd_kernel<T, true><<<g_kv, BWD_THREADS, BWD_SMEM_KV, st>>>(p, q128, q64, d128, d64);
+    attn_bwd_kernel<T, false><<<g_q, BWD_THREADS, BWD_SMEM_Q, st>>>(p, q128, q64, d128, d64);
   } else {
     return DLTI_ERR_UNSUPPORTED;
   }

@@ -48,6 +48,15 @@ struct Gemm2Params {
   uint32_t idesc;
   // stream-K: tiles [0, sk_tiles) are cut into `gridDim/2` equal ranges of (tile, k-block) iterations,
   // tiles [sk_tiles, total) are handed out round-robin. sk_tiles == 0 => plain data-parallel schedule.
+  // SwiGLU mode (swiglu_ff > 0): B is the [2*ff, K] gate|up weight; CTA rank 0 stages 128 gate rows and
+  // rank 1 the matching 128 up rows, so accumulator columns 0-127 are gate and 128-255 are up of the
+  // same 128 output columns, and the epilogue writes h = silu(gate) * up  ([M, ff]).
+  int swiglu_ff;
+  // SwiGLU-backward mode (swiglu_bwd_ff > 0): the accumulator is dh = dy · W_down ([M, ff]); the epilogue
+  // reads gate|up from `gu` ([M, 2*ff]) and writes d(gate|up) into C ([M, 2*ff]); dh is never stored.
+  int swiglu_bwd_ff;
+  const void* gu;
+  long long ldgu;
   int sk_tiles;
   long long sk_iters_per_range;
   float4* sk_ws;            // [ranges][2 CTAs][8 chunks][8 quads][128 rows] float4 partial accumulators
@@ -212,7 +221,8 @@ gemm2_kernel(const Gemm2Params p, const __grid_constant__ CUtensorMap tmA, const
         const int n_blk = sg.tile / p.nmb2;
         const int m_blk = sg.tile - n_blk * p.nmb2;
         const int m0 = m_blk * 2 * BM + (int)rank * BM;          // this CTA's A rows
-        const int n0 = n_blk * BN + (int)rank * (BN / 2);        // this CTA's half of the B tile
+        // this CTA's half of the B tile (SwiGLU mode: gate rows for rank 0, the matching up rows for rank 1)
+        const int n0 = p.swiglu_ff > 0 ? n_blk * (BN / 2) + (int)rank * p.swiglu_ff : n_blk * BN + (int)rank * (BN / 2);
         for (int kb = sg.kb0; kb < sg.kb1; ++kb) {
           mbar_wait_bounded(empty_bar(stage), phase ^ 1u);
           const uint32_t sa = smem_base + stage * STAGE_BYTES;
@@ -299,6 +309,100 @@ gemm2_kernel(const Gemm2Params p, const __grid_constant__ CUtensorMap tmA, const
       mbar_wait_bounded(tfull_bar(acc), acc_phase);
       tc_fence_after();
       const uint32_t t_row = tmem_base + ((uint32_t)(quarter * 32) << 16) + (uint32_t)(acc * BN);
+      if (p.swiglu_ff > 0) {
+        // 16-bit module-boundary semantics of the unfused path: gate, up and silu(gate) are rounded to the
+        // storage type before the product (bit-identical to dlti_swiglu_fwd on the stored gate|up tensor).
+        const bool bf = p.out_dtype == DLTI_BF16;
+        uint16_t* crow = reinterpret_cast<uint16_t*>(p.C) + (long long)row * p.ldc + n_blk * (BN / 2);
+#pragma unroll 1
+        for (int c = 0; c < 4; ++c) {
+          uint32_t vg[32], vu[32];
+          tmem_ld_32x32b_x32(t_row + c * 32, vg);
+          tmem_ld_32x32b_x32(t_row + 128 + c * 32, vu);
+          tmem_wait_ld();
+          if (row < p.M) {
+            float o[32];
+#pragma unroll
+            for (int i = 0; i < 32; ++i) {
+              float g = __uint_as_float(vg[i]), u = __uint_as_float(vu[i]);
+              g = bf ? __bfloat162float(__float2bfloat16_rn(g)) : __half2float(__float2half_rn(g));
+              u = bf ? __bfloat162float(__float2bfloat16_rn(u)) : __half2float(__float2half_rn(u));
+              float sg = g / (1.f + __expf(-g));
+              sg = bf ? __bfloat162float(__float2bfloat16_rn(sg)) : __half2float(__float2half_rn(sg));
+              o[i] = sg * u;
+            }
+#pragma unroll
+            for (int i = 0; i < 4; ++i) {
+              int4 ov;
+              uint32_t* ou = reinterpret_cast<uint32_t*>(&ov);
+#pragma unroll
+              for (int j = 0; j < 4; ++j)
+                ou[j] = bf ? Cvt<__nv_bfloat16>::pack2(o[8 * i + 2 * j], o[8 * i + 2 * j + 1])
+                           : Cvt<__half>::pack2(o[8 * i + 2 * j], o[8 * i + 2 * j + 1]);
+              *(reinterpret_cast<int4*>(crow + c * 32) + i) = ov;
+            }
+          }
+        }
+      } else if (p.swiglu_bwd_ff > 0) {
+        // dgate = dh * up * sig * (1 + gate * (1 - sig)),  dup = dh * gate * sig, with dh rounded to the
+        // storage type first (bit-identical to dlti_swiglu_bwd on a stored dh). gate|up of chunk c+1 are
+        // requested before chunk c is processed so the global-load latency stays off the epilogue's path.
+        const bool bf = p.out_dtype == DLTI_BF16;
+        const int ff = p.swiglu_bwd_ff;
+        const bool rok = row < p.M;
+        const uint16_t* grow = reinterpret_cast<const uint16_t*>(p.gu) + (long long)(rok ? row : 0) * p.ldgu;
+        uint16_t* orow = reinterpret_cast<uint16_t*>(p.C) + (long long)row * p.ldc;
+        int4 gq[4], uq[4];
+        auto fetch = [&](int c) {
+          const int col0 = n0 + c * 32;
+          if (rok && col0 < ff) {
+#pragma unroll
+            for (int i = 0; i < 4; ++i) {
+              gq[i] = *(reinterpret_cast<const int4*>(grow + col0) + i);
+              uq[i] = *(reinterpret_cast<const int4*>(grow + ff + col0) + i);
+            }
+          }
+        };
+        fetch(0);
+#pragma unroll 1
+        for (int c = 0; c < BN / 32; ++c) {
+          const int col0 = n0 + c * 32;
+          if (col0 >= ff) break;
+          uint32_t v[32];
+          tmem_ld_32x32b_x32(t_row + c * 32, v);
+          int4 gc[4], uc[4];
+#pragma unroll
+          for (int i = 0; i < 4; ++i) { gc[i] = gq[i]; uc[i] = uq[i]; }
+          if (c + 1 < BN / 32) fetch(c + 1);
+          tmem_wait_ld();
+          if (rok) {
+#pragma unroll
+            for (int i = 0; i < 4; ++i) {
+              const uint32_t* gw = reinterpret_cast<const uint32_t*>(&gc[i]);
+              const uint32_t* uw = reinterpret_cast<const uint32_t*>(&uc[i]);
+              int4 og, ou4;
+              uint32_t* ogw = reinterpret_cast<uint32_t*>(&og);
+              uint32_t* ouw = reinterpret_cast<uint32_t*>(&ou4);
+#pragma unroll
+              for (int j = 0; j < 4; ++j) {
+                const float2 g2 = bf ? Cvt<__nv_bfloat16>::unpack2(gw[j]) : Cvt<__half>::unpack2(gw[j]);
+                const float2 u2 = bf ? Cvt<__nv_bfloat16>::unpack2(uw[j]) : Cvt<__half>::unpack2(uw[j]);
+                float d0 = __uint_as_float(v[8 * i + 2 * j]), d1 = __uint_as_float(v[8 * i + 2 * j + 1]);
+                d0 = bf ? __bfloat162float(__float2bfloat16_rn(d0)) : __half2float(__float2half_rn(d0));
+                d1 = bf ? __bfloat162float(__float2bfloat16_rn(d1)) : __half2float(__float2half_rn(d1));
+                const float s0 = 1.f / (1.f + __expf(-g2.x)), s1 = 1.f / (1.f + __expf(-g2.y));
+                const float dg0 = d0 * u2.x * s0 * (1.f + g2.x * (1.f - s0));
+                const float dg1 = d1 * u2.y * s1 * (1.f + g2.y * (1.f - s1));
+                const float du0 = d0 * (g2.x * s0), du1 = d1 * (g2.y * s1);
+                ogw[j] = bf ? Cvt<__nv_bfloat16>::pack2(dg0, dg1) : Cvt<__half>::pack2(dg0, dg1);
+                ouw[j] = bf ? Cvt<__nv_bfloat16>::pack2(du0, du1) : Cvt<__half>::pack2(du0, du1);
+              }
+              *(reinterpret_cast<int4*>(orow + col0) + i) = og;
+              *(reinterpret_cast<int4*>(orow + ff + col0) + i) = ou4;
+            }
+          }
+        }
+      } else
 #pragma unroll 1
       for (int c = 0; c < BN / 32; ++c) {
         const int col0 = n0 + c * 32;
@@ -533,4 +637,65 @@ DLTI_API int dlti_gemm_2cta(const void* A, const void* B, void* C, const void* R
     }
   }
   return b_mn ? launch2<true>(p, ta, tb, ta2, tb2, grid, stream) : launch2<false>(p, ta, tb, ta2, tb2, grid, stream);
+}
+
+// h[M, ff] = silu(A · Wg^T) * (A · Wu^T) with W = [gate rows (ff) ; up rows (ff)] stored [2*ff, K]
+// (the Llama gate_up projection + SwiGLU in one kernel; the [M, 2*ff] intermediate is never written).
+// Requires ff % 128 == 0 and 16-byte aligned output rows; otherwise DLTI_ERR_UNSUPPORTED.
+DLTI_API int dlti_gemm_swiglu_2cta(const void* A, const void* W, void* Hout, int M, int ff, int K, long long lda,
+                                   long long ldw, long long ldh, int dtype, cudaStream_t stream) {
+  if (M <= 0 || ff <= 0 || K <= 0) return DLTI_ERR_BAD_ARG;
+  if (dtype != DLTI_BF16 && dtype != DLTI_FP16) return DLTI_ERR_UNSUPPORTED;
+  if (ff % (BN / 2) || (reinterpret_cast<uintptr_t>(Hout) & 15) || (ldh * 2) % 16) return DLTI_ERR_UNSUPPORTED;
+  Gemm2Params p{};
+  p.M = M; p.N = 2 * ff;
+  p.nmb2 = (M + 2 * BM - 1) / (2 * BM);
+  p.nnb = ff / (BN / 2);
+  p.nkb_main = (K + BK - 1) / BK;
+  p.nkb_ext = 0;
+  p.C = Hout; p.R = nullptr; p.ldc = ldh; p.ldr = 0;
+  p.out_dtype = dtype; p.in_dtype = dtype; p.accumulate = 0; p.vec_ok = 1;
+  p.alpha = 1.f;
+  p.idesc = umma_idesc_f16(dtype, 2 * BM, BN, false, false);
+  p.swiglu_ff = ff;
+  CUtensorMap ta, tb;
+  int rc;
+  if ((rc = dlti_make_tmap_2d(&ta, A, K, M, lda, 64, BM, 2, 128))) return rc;
+  if ((rc = dlti_make_tmap_2d(&tb, W, K, 2 * (long long)ff, ldw, 64, BN / 2, 2, 128))) return rc;
+  int grid = dlti_num_sms() & ~1;
+  const int total = p.nmb2 * p.nnb;
+  if (2 * total < grid) grid = 2 * total;
+  return launch2<false>(p, ta, tb, ta, tb, grid, stream);
+}
+
+// d(gate|up)[M, 2*ff] = swiglu_backward(dh, gate|up) with dh = dY[M, K] · W_down ([K, ff], i.e. the
+// down projection weight [d_model, ff] used as the MN-major B operand): the input-gradient GEMM of the
+// down projection with the SwiGLU backward applied in its epilogue; dh is never written.
+// Requires ff % 32 == 0 and 16-byte aligned rows; otherwise DLTI_ERR_UNSUPPORTED.
+DLTI_API int dlti_gemm_swiglu_bwd_2cta(const void* dY, const void* Wdown, const void* GU, void* dGU, int M, int ff,
+                                       int K, long long ldy, long long ldw, long long ldgu, long long lddgu,
+                                       int dtype, cudaStream_t stream) {
+  if (M <= 0 || ff <= 0 || K <= 0) return DLTI_ERR_BAD_ARG;
+  if (dtype != DLTI_BF16 && dtype != DLTI_FP16) return DLTI_ERR_UNSUPPORTED;
+  if (ff % 32 || (reinterpret_cast<uintptr_t>(dGU) & 15) || (reinterpret_cast<uintptr_t>(GU) & 15) ||
+      (ldgu * 2) % 16 || (lddgu * 2) % 16 || (ff * 2) % 16)
+    return DLTI_ERR_UNSUPPORTED;
+  Gemm2Params p{};
+  p.M = M; p.N = ff;
+  p.nmb2 = (M + 2 * BM - 1) / (2 * BM);
+  p.nnb = (ff + BN - 1) / BN;
+  p.nkb_main = (K + BK - 1) / BK;
+  p.C = dGU; p.ldc = lddgu;
+  p.out_dtype = dtype; p.in_dtype = dtype; p.vec_ok = 1;
+  p.alpha = 1.f;
+  p.idesc = umma_idesc_f16(dtype, 2 * BM, BN, false, true);
+  p.swiglu_bwd_ff = ff; p.gu = GU; p.ldgu = ldgu;
+  CUtensorMap ta, tb;
+  int rc;
+  if ((rc = dlti_make_tmap_2d(&ta, dY, K, M, ldy, 64, BM, 2, 128))) return rc;
+  if ((rc = dlti_make_tmap_2d(&tb, Wdown, ff, K, ldw, 64, 64, 2, 128))) return rc;
+  int grid = dlti_num_sms() & ~1;
+  const int total = p.nmb2 * p.nnb;
+  if (2 * total < grid) grid = 2 * total;
+  return launch2<true>(p, ta, tb, ta, tb, grid, stream);
 }

@@ -25,7 +25,7 @@ import torch
 
 from ..ops import attention as A
 from ..ops import elementwise as E
-from ..ops.gemm import gemm
+from ..ops.gemm import gemm, gemm_swiglu, gemm_swiglu_bwd
 from ..ops.loss import cross_entropy
 from .config import LlamaConfig
 from .lora import LoraConfig, LoraParams
@@ -210,9 +210,16 @@ class LoraLlama:
         t_o = gemm(attn_drop, lo.A_o_c[li]) if use_o else None                 # [T, Ro]
         x2 = gemm(attn, lw.w_o, a2=t_o, b2=lo.B_o_c[li] if use_o else None, residual=x, gather=lw.g("w_o"))
         xn2, rstd2, _ = E.rmsnorm_fwd(x2, lw.ln2, cfg.rms_norm_eps)
-        gu = gemm(xn2, lw.w_gu, gather=lw.g("w_gu"))
+        g_gu = lw.g("w_gu")
+        if need_out and not save and g_gu is None:
+            # forward of a checkpointed layer: nothing downstream needs gate|up itself, so SwiGLU runs in
+            # the GEMM epilogue and the [T, 2*ff] tensor is never written
+            gu = None
+            h = gemm_swiglu(xn2, lw.w_gu)
+        else:
+            gu = gemm(xn2, lw.w_gu, gather=g_gu)
+            h = E.swiglu_fwd(gu) if need_out else None
         if need_out:
-            h = E.swiglu_fwd(gu)
             x3 = gemm(h, lw.w_down, residual=x2, gather=lw.g("w_down"))
         else:
             x3 = None
@@ -235,9 +242,13 @@ class LoraLlama:
         splitk = max(1, min(16, T // 512))
 
         # ---- MLP ----
-        dh = gemm(dx3, lw.w_down, b_mn=True, gather=lw.g("w_down"))                               # [T, ff]
-        dgu = E.swiglu_bwd(dh, s["gu"])
-        del dh
+        g_down = lw.g("w_down")
+        if g_down is None:
+            dgu = gemm_swiglu_bwd(dx3, lw.w_down, s["gu"])      # SwiGLU backward in the GEMM epilogue
+        else:
+            dh = gemm(dx3, lw.w_down, b_mn=True, gather=g_down)                                   # [T, ff]
+            dgu = E.swiglu_bwd(dh, s["gu"])
+            del dh
         dxn2 = gemm(dgu, lw.w_gu, b_mn=True, gather=lw.g("w_gu"))                               # [T, d]
         del dgu
         dx2 = E.rmsnorm_bwd(dxn2, s["x2"], lw.ln2, s["rstd2"], dres=dx3)

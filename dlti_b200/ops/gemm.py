@@ -139,6 +139,44 @@ def gemm(a: torch.Tensor, b: torch.Tensor, *, a_mn: bool = False, b_mn: bool = F
     return out
 
 
+def gemm_swiglu(x: torch.Tensor, w_gu: torch.Tensor) -> torch.Tensor:
+    """h = silu(x · Wg^T) * (x · Wu^T) for w_gu = [gate rows ; up rows] ([2*ff, K]): the gate_up projection
+    with SwiGLU applied in the GEMM epilogue (csrc/gemm2.cu). Falls back to GEMM + swiglu_fwd when the
+    shape is not covered (CPU tensors, ff % 128 != 0, fewer than 64 tiles)."""
+    from .elementwise import swiglu_fwd
+    M, K = x.shape
+    ff = w_gu.shape[0] // 2
+    if (not _lib.use_native(x, w_gu) or not _TWO_CTA_DEFAULT or ff % 128 or x.stride(1) != 1 or w_gu.stride(1) != 1
+            or ((M + 255) // 256) * (ff // 128) < 64):
+        return swiglu_fwd(gemm(x, w_gu))
+    h = torch.empty((M, ff), dtype=x.dtype, device=x.device)
+    f = _lib.fn("dlti_gemm_swiglu_2cta", [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int,
+                                          C.c_longlong, C.c_longlong, C.c_longlong, C.c_int, C.c_void_p])
+    _lib.check(f(_lib.ptr(x), _lib.ptr(w_gu), _lib.ptr(h), M, ff, K, x.stride(0), w_gu.stride(0), h.stride(0),
+                 _lib.dtype_code(x.dtype), _lib.stream_ptr()), "dlti_gemm_swiglu_2cta")
+    return h
+
+
+def gemm_swiglu_bwd(dy: torch.Tensor, w_down: torch.Tensor, gu: torch.Tensor) -> torch.Tensor:
+    """d(gate|up) = swiglu_bwd(dy · W_down, gate|up) for w_down = [d_model, ff] (dy is [T, d_model]): the
+    down projection's input-gradient GEMM with the SwiGLU backward in its epilogue."""
+    from .elementwise import swiglu_bwd
+    M, K = dy.shape
+    ff = w_down.shape[1]
+    if (not _lib.use_native(dy, w_down) or not _TWO_CTA_DEFAULT or ff % 32 or dy.stride(1) != 1
+            or w_down.stride(1) != 1 or gu.stride(1) != 1 or ((M + 255) // 256) * ((ff + 255) // 256) < 64):
+        return swiglu_bwd(gemm(dy, w_down, b_mn=True), gu)
+    assert w_down.shape[0] == K and gu.shape == (M, 2 * ff) and gu.dtype == dy.dtype
+    dgu = torch.empty_like(gu)
+    f = _lib.fn("dlti_gemm_swiglu_bwd_2cta", [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int,
+                                              C.c_longlong, C.c_longlong, C.c_longlong, C.c_longlong, C.c_int,
+                                              C.c_void_p])
+    _lib.check(f(_lib.ptr(dy), _lib.ptr(w_down), _lib.ptr(gu), _lib.ptr(dgu), M, ff, K, dy.stride(0),
+                 w_down.stride(0), gu.stride(0), dgu.stride(0), _lib.dtype_code(dy.dtype), _lib.stream_ptr()),
+               "dlti_gemm_swiglu_bwd_2cta")
+    return dgu
+
+
 _skinny_ws: dict = {}
 
 

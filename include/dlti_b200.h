@@ -157,6 +157,18 @@ int dlti_gemm_2cta(const void* A, const void* B, void* C, const void* R, int M, 
                    float alpha, int accumulate, int stream_k /* -1 auto, 0 off, 1 force */,
                    dlti_stream_t stream);
 
+/* Llama gate_up projection + SwiGLU in one kernel: h[M, ff] = silu(A·Wg^T) * (A·Wu^T), W = [gate; up]
+ * stored [2*ff, K]. CTA rank 0 of a pair stages gate rows, rank 1 the matching up rows; the [M, 2*ff]
+ * intermediate is never written. Rounding points match dlti_swiglu_fwd on a stored gate|up tensor. */
+int dlti_gemm_swiglu_2cta(const void* A, const void* W, void* Hout, int M, int ff, int K, long long lda,
+                          long long ldw, long long ldh, int dtype, dlti_stream_t stream);
+
+/* Input-gradient GEMM of the down projection with the SwiGLU backward in its epilogue:
+ * dGU[M, 2*ff] = swiglu_bwd(dY[M, K] · Wdown[K, ff], GU[M, 2*ff]); dh is never written. */
+int dlti_gemm_swiglu_bwd_2cta(const void* dY, const void* Wdown, const void* GU, void* dGU, int M, int ff, int K,
+                              long long ldy, long long ldw, long long ldgu, long long lddgu, int dtype,
+                              dlti_stream_t stream);
+
 /* ---- Decode-sized GEMM (M <= 256): swap-AB (the weight is the 128-row tensor-core operand), K split
  * over CTAs, fp32 partials reduced with atomics into acc32[M,N] (must be zero on entry);
  * dlti_skinny_finish converts acc32 -> out and re-zeroes it. Replaces the cuBLAS GEMV/GEMM calls of the

@@ -128,3 +128,35 @@ def test_gemm_cta_pair(M, N, K, b_mn, dtype):
     exp = acc + gemm_ref(a, b, b_mn=b_mn, out_dtype=torch.float32)
     gemm(a, b, b_mn=b_mn, out=acc, accumulate=True, two_cta=True)
     _check(acc, exp)
+
+
+@pytest.mark.parametrize("dtype", [torch.bfloat16, torch.float16])
+@pytest.mark.parametrize("M,ff,K", [(4096, 2048, 512), (2050, 11008, 256)])
+def test_gemm_swiglu_fused_epilogue(M, ff, K, dtype):
+    """gate_up GEMM with SwiGLU in the epilogue == GEMM followed by the stand-alone SwiGLU kernel."""
+    from dlti_b200.ops.elementwise import swiglu_fwd, swiglu_fwd_ref
+    from dlti_b200.ops.gemm import gemm_swiglu
+    torch.manual_seed(9)
+    x = torch.randn(M, K, device="cuda", dtype=dtype)
+    w = torch.randn(2 * ff, K, device="cuda", dtype=dtype) * 0.05
+    h = gemm_swiglu(x, w)
+    gu = gemm(x, w)
+    h2 = swiglu_fwd(gu)
+    assert h.shape == (M, ff)
+    _check(h, h2.float(), scale_tol=4e-3)
+    _check(h, swiglu_fwd_ref(gemm_ref(x, w, out_dtype=torch.float32).to(dtype)).float(), scale_tol=2e-2)
+
+
+@pytest.mark.parametrize("M,ff,d", [(4096, 2048, 512), (2050, 11008, 256), (4096, 4128, 128)])
+def test_gemm_swiglu_bwd_fused_epilogue(M, ff, d):
+    """down-projection input-gradient GEMM with the SwiGLU backward in the epilogue == GEMM + stand-alone kernel."""
+    from dlti_b200.ops.elementwise import swiglu_bwd
+    from dlti_b200.ops.gemm import gemm_swiglu_bwd
+    torch.manual_seed(10)
+    dy = torch.randn(M, d, device="cuda", dtype=torch.bfloat16)
+    w_down = torch.randn(d, ff, device="cuda", dtype=torch.bfloat16) * 0.05
+    gu = torch.randn(M, 2 * ff, device="cuda", dtype=torch.bfloat16)
+    out = gemm_swiglu_bwd(dy, w_down, gu)
+    ref = swiglu_bwd(gemm(dy, w_down, b_mn=True), gu)
+    assert out.shape == (M, 2 * ff)
+    _check(out, ref.float(), scale_tol=4e-3)

@@ -57,6 +57,13 @@ struct Gemm2Params {
   int swiglu_bwd_ff;
   const void* gu;
   long long ldgu;
+  // RoPE mode (rope_pos != nullptr): output columns [0, rope_cols) are attention heads of 128 that get the
+  // rotate-half rotary embedding of their row's position applied in the epilogue (q and k heads of the
+  // fused QKV projection); columns >= rope_cols (v heads) are stored unchanged.
+  const int* rope_pos;
+  const float* rope_cos;    // [max_pos, 64] fp32
+  const float* rope_sin;
+  int rope_cols;
   int sk_tiles;
   long long sk_iters_per_range;
   float4* sk_ws;            // [ranges][2 CTAs][8 chunks][8 quads][128 rows] float4 partial accumulators
@@ -340,6 +347,76 @@ gemm2_kernel(const Gemm2Params p, const __grid_constant__ CUtensorMap tmA, const
                 ou[j] = bf ? Cvt<__nv_bfloat16>::pack2(o[8 * i + 2 * j], o[8 * i + 2 * j + 1])
                            : Cvt<__half>::pack2(o[8 * i + 2 * j], o[8 * i + 2 * j + 1]);
               *(reinterpret_cast<int4*>(crow + c * 32) + i) = ov;
+            }
+          }
+        }
+      } else if (p.rope_pos != nullptr) {
+        // Same rounding points as the stand-alone kernel: the projection is rounded to the storage type,
+        // cos/sin are rounded to it too (HF casts them), the rotation runs in fp32 and is rounded once.
+        const bool bf = p.out_dtype == DLTI_BF16;
+        const bool rok = row < p.M;
+        const int pos = rok ? p.rope_pos[row] : 0;
+        const float4* cosr = reinterpret_cast<const float4*>(p.rope_cos + (long long)pos * 64);
+        const float4* sinr = reinterpret_cast<const float4*>(p.rope_sin + (long long)pos * 64);
+        uint16_t* crow = reinterpret_cast<uint16_t*>(p.C) + (long long)row * p.ldc;
+        auto rnd = [&](float x) { return bf ? __bfloat162float(__float2bfloat16_rn(x)) : __half2float(__float2half_rn(x)); };
+        auto store32 = [&](uint16_t* dst, const float (&f)[32]) {
+#pragma unroll
+          for (int i = 0; i < 4; ++i) {
+            int4 o;
+            uint32_t* ou = reinterpret_cast<uint32_t*>(&o);
+#pragma unroll
+            for (int j = 0; j < 4; ++j)
+              ou[j] = bf ? Cvt<__nv_bfloat16>::pack2(f[8 * i + 2 * j], f[8 * i + 2 * j + 1])
+                         : Cvt<__half>::pack2(f[8 * i + 2 * j], f[8 * i + 2 * j + 1]);
+            *(reinterpret_cast<int4*>(dst) + i) = o;
+          }
+        };
+#pragma unroll 1
+        for (int hb = 0; hb < BN / 128; ++hb) {
+          const int hcol = n0 + hb * 128;
+          if (hcol >= p.N) break;
+          if (hcol < p.rope_cols) {
+#pragma unroll 1
+            for (int pr = 0; pr < 2; ++pr) {            // element i pairs with i + 64: chunks pr and pr + 2
+              uint32_t v1[32], v2[32];
+              tmem_ld_32x32b_x32(t_row + hb * 128 + pr * 32, v1);
+              tmem_ld_32x32b_x32(t_row + hb * 128 + 64 + pr * 32, v2);
+              float cs[32], sn[32];
+              if (rok) {
+#pragma unroll
+                for (int i = 0; i < 8; ++i) {
+                  const float4 c4 = cosr[pr * 8 + i], s4 = sinr[pr * 8 + i];
+                  cs[4 * i] = c4.x; cs[4 * i + 1] = c4.y; cs[4 * i + 2] = c4.z; cs[4 * i + 3] = c4.w;
+                  sn[4 * i] = s4.x; sn[4 * i + 1] = s4.y; sn[4 * i + 2] = s4.z; sn[4 * i + 3] = s4.w;
+                }
+              }
+              tmem_wait_ld();
+              if (rok) {
+                float o1[32], o2[32];
+#pragma unroll
+                for (int i = 0; i < 32; ++i) {
+                  const float a = rnd(__uint_as_float(v1[i]) * p.alpha), b = rnd(__uint_as_float(v2[i]) * p.alpha);
+                  const float cj = rnd(cs[i]), sj = rnd(sn[i]);
+                  o1[i] = a * cj - b * sj;
+                  o2[i] = b * cj + a * sj;
+                }
+                store32(crow + hcol + pr * 32, o1);
+                store32(crow + hcol + 64 + pr * 32, o2);
+              }
+            }
+          } else {
+#pragma unroll 1
+            for (int c = 0; c < 4; ++c) {
+              uint32_t v[32];
+              tmem_ld_32x32b_x32(t_row + hb * 128 + c * 32, v);
+              tmem_wait_ld();
+              if (rok) {
+                float f[32];
+#pragma unroll
+                for (int i = 0; i < 32; ++i) f[i] = __uint_as_float(v[i]) * p.alpha;
+                store32(crow + hcol + c * 32, f);
+              }
             }
           }
         }
@@ -698,4 +775,42 @@ DLTI_API int dlti_gemm_swiglu_bwd_2cta(const void* dY, const void* Wdown, const 
   const int total = p.nmb2 * p.nnb;
   if (2 * total < grid) grid = 2 * total;
   return launch2<true>(p, ta, tb, ta, tb, grid, stream);
+}
+
+// C[M, N] = rope(alpha * (A · B^T + A2 · B2^T)): the fused QKV projection (B = [N, K], optional LoRA
+// K-extension) with the rotary embedding of each row's position applied in the epilogue to the first
+// rope_cols output columns (heads of 128, rotate-half convention); cos/sin are fp32 tables [max_pos, 64].
+// Requires N and rope_cols to be multiples of 128 and 16-byte aligned output rows.
+DLTI_API int dlti_gemm_rope_2cta(const void* A, const void* B, void* C, int M, int N, int K, long long lda,
+                                 long long ldb, long long ldc, const void* A2, const void* B2, int K2,
+                                 long long lda2, long long ldb2, int dtype, float alpha, const int* pos,
+                                 const float* cos_t, const float* sin_t, int rope_cols, cudaStream_t stream) {
+  if (M <= 0 || N <= 0 || K <= 0 || !pos || !cos_t || !sin_t) return DLTI_ERR_BAD_ARG;
+  if (dtype != DLTI_BF16 && dtype != DLTI_FP16) return DLTI_ERR_UNSUPPORTED;
+  if (N % 128 || rope_cols % 128 || K2 % BK || (reinterpret_cast<uintptr_t>(C) & 15) || (ldc * 2) % 16)
+    return DLTI_ERR_UNSUPPORTED;
+  Gemm2Params p{};
+  p.M = M; p.N = N;
+  p.nmb2 = (M + 2 * BM - 1) / (2 * BM);
+  p.nnb = (N + BN - 1) / BN;
+  p.nkb_main = (K + BK - 1) / BK;
+  p.nkb_ext = (A2 && B2) ? K2 / BK : 0;
+  p.C = C; p.ldc = ldc;
+  p.out_dtype = dtype; p.in_dtype = dtype; p.vec_ok = 1;
+  p.alpha = alpha;
+  p.idesc = umma_idesc_f16(dtype, 2 * BM, BN, false, false);
+  p.rope_pos = pos; p.rope_cos = cos_t; p.rope_sin = sin_t; p.rope_cols = rope_cols;
+  CUtensorMap ta, tb, ta2, tb2;
+  int rc;
+  if ((rc = dlti_make_tmap_2d(&ta, A, K, M, lda, 64, BM, 2, 128))) return rc;
+  if ((rc = dlti_make_tmap_2d(&tb, B, K, N, ldb, 64, BN / 2, 2, 128))) return rc;
+  ta2 = ta; tb2 = tb;
+  if (p.nkb_ext > 0) {
+    if ((rc = dlti_make_tmap_2d(&ta2, A2, K2, M, lda2, 64, BM, 2, 128))) return rc;
+    if ((rc = dlti_make_tmap_2d(&tb2, B2, K2, N, ldb2, 64, BN / 2, 2, 128))) return rc;
+  }
+  int grid = dlti_num_sms() & ~1;
+  const int total = p.nmb2 * p.nnb;
+  if (2 * total < grid) grid = 2 * total;
+  return launch2<false>(p, ta, tb, ta2, tb2, grid, stream);
 }

@@ -25,7 +25,7 @@ import torch
 
 from ..ops import attention as A
 from ..ops import elementwise as E
-from ..ops.gemm import gemm, gemm_swiglu, gemm_swiglu_bwd
+from ..ops.gemm import gemm, gemm_rope, gemm_swiglu, gemm_swiglu_bwd
 from ..ops.loss import cross_entropy
 from .config import LlamaConfig
 from .lora import LoraConfig, LoraParams
@@ -203,8 +203,14 @@ class LoraLlama:
         if xn_drop is None:
             xn_drop = xn
         t_qkv = gemm(xn_drop, lo.A_qkv_c[li]) if use_qkv else None            # [T, Rq]
-        qkv = gemm(xn, lw.w_qkv, a2=t_qkv, b2=lo.B_qkv_c[li] if use_qkv else None, gather=lw.g("w_qkv"))
-        E.rope_(qkv, b.positions, cos, sin, H + KV, hd)
+        g_qkv = lw.g("w_qkv")
+        if g_qkv is None:
+            # RoPE applied in the projection's epilogue
+            qkv = gemm_rope(xn, lw.w_qkv, b.positions, cos, sin, H + KV, hd, a2=t_qkv,
+                            b2=lo.B_qkv_c[li] if use_qkv else None)
+        else:
+            qkv = gemm(xn, lw.w_qkv, a2=t_qkv, b2=lo.B_qkv_c[li] if use_qkv else None, gather=g_qkv)
+            E.rope_(qkv, b.positions, cos, sin, H + KV, hd)
         attn, lse = A.attention_fwd(qkv, b.cu_seqlens, b.max_seqlen, H, KV, hd, self.scale)
         attn_drop = E.dropout(attn, p, self.dropout_seed, self._stream(li, 1)) if use_o else attn
         t_o = gemm(attn_drop, lo.A_o_c[li]) if use_o else None                 # [T, Ro]

@@ -51,6 +51,8 @@ def _gemm_fn():
 
 
 _TWO_CTA_DEFAULT = os.environ.get("DLTI_GEMM_2CTA", "1") == "1"
+_FUSE_ROPE = os.environ.get("DLTI_FUSE_ROPE", "1") == "1"      # A/B switches for the fused epilogues
+_FUSE_SWIGLU = os.environ.get("DLTI_FUSE_SWIGLU", "1") == "1"
 
 
 def gemm(a: torch.Tensor, b: torch.Tensor, *, a_mn: bool = False, b_mn: bool = False,
@@ -146,7 +148,7 @@ def gemm_swiglu(x: torch.Tensor, w_gu: torch.Tensor) -> torch.Tensor:
     from .elementwise import swiglu_fwd
     M, K = x.shape
     ff = w_gu.shape[0] // 2
-    if (not _lib.use_native(x, w_gu) or not _TWO_CTA_DEFAULT or ff % 128 or x.stride(1) != 1 or w_gu.stride(1) != 1
+    if (not _lib.use_native(x, w_gu) or not _TWO_CTA_DEFAULT or not _FUSE_SWIGLU or ff % 128 or x.stride(1) != 1 or w_gu.stride(1) != 1
             or ((M + 255) // 256) * (ff // 128) < 64):
         return swiglu_fwd(gemm(x, w_gu))
     h = torch.empty((M, ff), dtype=x.dtype, device=x.device)
@@ -157,13 +159,41 @@ def gemm_swiglu(x: torch.Tensor, w_gu: torch.Tensor) -> torch.Tensor:
     return h
 
 
+def gemm_rope(x: torch.Tensor, w: torch.Tensor, pos: torch.Tensor, cos_t: torch.Tensor, sin_t: torch.Tensor,
+              n_rot_heads: int, hd: int, a2: torch.Tensor | None = None, b2: torch.Tensor | None = None) -> torch.Tensor:
+    """qkv = rope(x · W^T + a2 · b2^T): the QKV projection (with the LoRA K-extension) whose epilogue applies
+    the rotary embedding to the first n_rot_heads heads. Falls back to GEMM + rope_ when not covered."""
+    from .elementwise import rope_
+    M, K = x.shape
+    N = w.shape[0]
+    if (not _lib.use_native(x, w) or not _TWO_CTA_DEFAULT or not _FUSE_ROPE or hd != 128 or N % 128 or x.stride(1) != 1
+            or w.stride(1) != 1 or ((M + 255) // 256) * ((N + 255) // 256) < 64 or pos.dtype != torch.int32):
+        y = gemm(x, w, a2=a2, b2=b2)
+        rope_(y, pos, cos_t, sin_t, n_rot_heads, hd)
+        return y
+    K2 = 0
+    if a2 is not None:
+        assert b2 is not None and a2.stride(1) == 1 and b2.stride(1) == 1
+        K2 = a2.shape[1]
+    y = torch.empty((M, N), dtype=x.dtype, device=x.device)
+    f = _lib.fn("dlti_gemm_rope_2cta", [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_longlong,
+                                        C.c_longlong, C.c_longlong, C.c_void_p, C.c_void_p, C.c_int, C.c_longlong,
+                                        C.c_longlong, C.c_int, C.c_float, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int,
+                                        C.c_void_p])
+    _lib.check(f(_lib.ptr(x), _lib.ptr(w), _lib.ptr(y), M, N, K, x.stride(0), w.stride(0), y.stride(0),
+                 _lib.ptr(a2), _lib.ptr(b2), K2, a2.stride(0) if a2 is not None else 0,
+                 b2.stride(0) if b2 is not None else 0, _lib.dtype_code(x.dtype), 1.0, _lib.ptr(pos),
+                 _lib.ptr(cos_t), _lib.ptr(sin_t), n_rot_heads * hd, _lib.stream_ptr()), "dlti_gemm_rope_2cta")
+    return y
+
+
 def gemm_swiglu_bwd(dy: torch.Tensor, w_down: torch.Tensor, gu: torch.Tensor) -> torch.Tensor:
     """d(gate|up) = swiglu_bwd(dy · W_down, gate|up) for w_down = [d_model, ff] (dy is [T, d_model]): the
     down projection's input-gradient GEMM with the SwiGLU backward in its epilogue."""
     from .elementwise import swiglu_bwd
     M, K = dy.shape
     ff = w_down.shape[1]
-    if (not _lib.use_native(dy, w_down) or not _TWO_CTA_DEFAULT or ff % 32 or dy.stride(1) != 1
+    if (not _lib.use_native(dy, w_down) or not _TWO_CTA_DEFAULT or not _FUSE_SWIGLU or ff % 32 or dy.stride(1) != 1
             or w_down.stride(1) != 1 or gu.stride(1) != 1 or ((M + 255) // 256) * ((ff + 255) // 256) < 64):
         return swiglu_bwd(gemm(dy, w_down, b_mn=True), gu)
     assert w_down.shape[0] == K and gu.shape == (M, 2 * ff) and gu.dtype == dy.dtype

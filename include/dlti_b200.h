@@ -163,6 +163,13 @@ int dlti_gemm_2cta(const void* A, const void* B, void* C, const void* R, int M, 
 int dlti_gemm_swiglu_2cta(const void* A, const void* W, void* Hout, int M, int ff, int K, long long lda,
                           long long ldw, long long ldh, int dtype, dlti_stream_t stream);
 
+/* Fused QKV projection (+ LoRA K-extension) with the rotary embedding applied in the epilogue to the first
+ * rope_cols output columns (heads of 128, rotate-half; cos/sin fp32 [max_pos, 64]; pos[M] int32). */
+int dlti_gemm_rope_2cta(const void* A, const void* B, void* C, int M, int N, int K, long long lda,
+                        long long ldb, long long ldc, const void* A2, const void* B2, int K2, long long lda2,
+                        long long ldb2, int dtype, float alpha, const int* pos, const float* cos_t,
+                        const float* sin_t, int rope_cols, dlti_stream_t stream);
+
 /* Input-gradient GEMM of the down projection with the SwiGLU backward in its epilogue:
  * dGU[M, 2*ff] = swiglu_bwd(dY[M, K] · Wdown[K, ff], GU[M, 2*ff]); dh is never written. */
 int dlti_gemm_swiglu_bwd_2cta(const void* dY, const void* Wdown, const void* GU, void* dGU, int M, int ff, int K,

@@ -160,3 +160,25 @@ def test_gemm_swiglu_bwd_fused_epilogue(M, ff, d):
     ref = swiglu_bwd(gemm(dy, w_down, b_mn=True), gu)
     assert out.shape == (M, 2 * ff)
     _check(out, ref.float(), scale_tol=4e-3)
+
+
+@pytest.mark.parametrize("H,KV", [(32, 32), (16, 4)])
+def test_gemm_rope_fused_epilogue(H, KV):
+    """QKV projection (+ LoRA K-extension) with RoPE in the epilogue == GEMM followed by the RoPE kernel."""
+    from dlti_b200.ops.elementwise import rope_, rope_tables
+    from dlti_b200.ops.gemm import gemm_rope
+    torch.manual_seed(12)
+    M, K, hd = 4096, 512, 128
+    N = (H + 2 * KV) * hd
+    x = torch.randn(M, K, device="cuda", dtype=torch.bfloat16)
+    w = torch.randn(N, K, device="cuda", dtype=torch.bfloat16) * 0.05
+    a2 = torch.randn(M, 64, device="cuda", dtype=torch.bfloat16)
+    b2 = torch.randn(N, 64, device="cuda", dtype=torch.bfloat16) * 0.05
+    pos = (torch.arange(M, device="cuda", dtype=torch.int32) * 7) % 2048
+    cos, sin = rope_tables(2048, hd, 1e4, "cuda")
+    y = gemm_rope(x, w, pos, cos, sin, H + KV, hd, a2=a2, b2=b2)
+    ref = gemm(x, w, a2=a2, b2=b2)
+    rope_(ref, pos, cos, sin, H + KV, hd)
+    _check(y, ref.float(), scale_tol=4e-3)
+    # v heads untouched by the rotation
+    assert torch.equal(y[:, (H + KV) * hd:], gemm(x, w, a2=a2, b2=b2)[:, (H + KV) * hd:])

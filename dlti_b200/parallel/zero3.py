@@ -20,6 +20,8 @@ offload_param = "cpu": shards live in pinned host memory and are copied H2D befo
 """
 from __future__ import annotations
 
+import os
+
 import torch
 
 from ..config.ds_config import DSConfig
@@ -81,7 +83,10 @@ class Zero3Weights:
         self.free_slots = list(range(self.n_slots))
         self.stream = torch.cuda.Stream(device=self.device) if self.device.type == "cuda" and self.world > 1 else None
         # K1 mode: one staging buffer per matrix kind, filled by the consuming GEMM kernel itself
-        self.in_gemm_gather = fused is not None and not self.offload and self.world > 1
+        # DLTI_Z3_GATHER=prefetch: pull the next layer with the stand-alone peer-memory all-gather kernel on a side
+        # stream (every GEMM then runs the plain kernels); default: gather inside the first GEMM that needs it (K1)
+        self.in_gemm_gather = (fused is not None and not self.offload and self.world > 1
+                               and os.environ.get("DLTI_Z3_GATHER", "gemm") != "prefetch")
         if self.in_gemm_gather:
             self.slots, self.n_slots, self.free_slots = [], 0, []
             self.staging, self.counters, self.epoch, self.specs = {}, {}, {}, []
@@ -189,7 +194,7 @@ class Zero3Weights:
     def _gather(self, key, shard: torch.Tensor, out: torch.Tensor) -> None:
         src = self._device_shard(key, shard)
         if self.fused is not None and not self.offload:
-            self.fused.all_gather_rows(shard, out, blocks_per_peer=max(8, 96 // self.world))
+            self.fused.all_gather_rows(shard, out, blocks_per_peer=int(os.environ.get("DLTI_AG_BLOCKS", max(8, 96 // self.world))))
         else:
             comm.all_gather_into(out.view(-1), src.reshape(-1), self.info)
         self.gather_bytes += out.numel() * out.element_size() * (self.world - 1) // self.world

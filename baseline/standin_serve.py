@@ -23,7 +23,7 @@ d = tempfile.mkdtemp(prefix="llama7b_cfg_")
 cfg.save(d)
 cmd = [sys.executable, "-m", "vllm.entrypoints.openai.api_server", "--model", d, "--served-model-name", "llama2-7b",
        "--load-format", "dummy", "--skip-tokenizer-init", "--tensor-parallel-size", str(a.tp), "--dtype", "bfloat16",
-       "--max-model-len", "4096", "--port", str(a.port), "--host", "127.0.0.1", "--disable-log-requests"]
+       "--max-model-len", "4096", "--port", str(a.port), "--host", "127.0.0.1", "--no-enable-log-requests"]
 env = dict(os.environ, VLLM_NO_USAGE_STATS="1", HF_HUB_OFFLINE="1", TRANSFORMERS_OFFLINE="1")
 log = open("gpurun_out/vllm_server.log", "w") if os.path.isdir("gpurun_out") else subprocess.DEVNULL
 srv = subprocess.Popen(cmd, env=env, stdout=log, stderr=subprocess.STDOUT, start_new_session=True)
@@ -44,7 +44,7 @@ try:
         levels = [int(x) for x in a.concurrency.split(",")]
         extra = {"detokenize": False}
         asyncio.run(sweep(url, "llama2-7b", [max(levels)], requests_per_level=max(levels), input_len=512, output_len=8,
-                          vocab=cfg.vocab_size, extra=extra))
+                          vocab=cfg.vocab_size, extra=extra, seed=12345))
         res = asyncio.run(sweep(url, "llama2-7b", levels, input_len=512, output_len=128, vocab=cfg.vocab_size, extra=extra))
         out = {"impl": "standin-vllm", "tp": a.tp, "levels": res}
         print(json.dumps(out))

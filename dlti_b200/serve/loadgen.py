@@ -65,7 +65,9 @@ async def run_load(base_url: str, model: str, concurrency: int, num_requests: in
                    output_len: int = 128, vocab: int = 32000, seed: int = 0, extra: dict | None = None) -> dict:
     import aiohttp
 
-    rng = random.Random(seed)
+    # every (seed, concurrency level) gets its own prompts: no prompt is ever sent twice, so a server-side prefix
+    # cache cannot turn prefill into a lookup
+    rng = random.Random(seed * 1000003 + concurrency * 7919 + num_requests)
     url = base_url.rstrip("/") + "/v1/completions"
     rec = {"ttft": [], "e2e": [], "itl": [], "tokens": 0, "requests": 0, "errors": 0}
     pending = [[1] + [rng.randrange(3, vocab) for _ in range(input_len - 1)] for _ in range(num_requests)]

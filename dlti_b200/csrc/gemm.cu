@@ -89,6 +89,7 @@ struct GemmParams {
   void* push_peer[16];
   long long push_slot_stride;
   int push_world, push_rank;
+  int early_a;     // SK: request the first A (weight) tiles before griddep_wait() (weights must be static)
 };
 
 __device__ __forceinline__ uint32_t ld_relaxed_gpu_u32(const uint32_t* p) {
@@ -110,7 +111,46 @@ __device__ __forceinline__ void gather_wait_unit(const GatherParams& g, int u) {
   }
 }
 
-template <int BN, bool A_MN, bool B_MN, bool GATHER, bool PUSH>
+// Work decomposition shared by the producer, MMA and epilogue roles: a sequence of segments
+// (rem = output tile index, K blocks [kb0, kb1)).
+//   SK = false: tile-major; one segment per (split, tile), CTAs stride through them.
+//   SK = true ("stream-K", atomic fp32 output only): the (tile, K block) pairs are linearised and cut
+//   into gridDim.x equal contiguous ranges, so every CTA streams the same number of K blocks whatever
+//   the tile count; a range that crosses a tile boundary yields one segment per tile and each segment's
+//   partial sum is flushed with red.add.
+template <bool SK>
+struct SegIter {
+  int rem, kb0, kb1;
+  int tile;
+  int pos, end;
+  __device__ __forceinline__ SegIter(const GemmParams& p, int tiles_mn, int nkb_total) {
+    tile = blockIdx.x;
+    if (SK) {
+      const long long total = (long long)tiles_mn * nkb_total;
+      pos = (int)(total * blockIdx.x / gridDim.x);
+      end = (int)(total * (blockIdx.x + 1) / gridDim.x);
+    }
+  }
+  __device__ __forceinline__ bool next(const GemmParams& p, int tiles_mn, int nkb_total) {
+    if (SK) {
+      if (pos >= end) return false;
+      rem = pos / nkb_total;
+      kb0 = pos - rem * nkb_total;
+      kb1 = min(nkb_total, kb0 + (end - pos));
+      pos += kb1 - kb0;
+      return true;
+    }
+    if (tile >= tiles_mn * p.split_k) return false;
+    const int split = tile / tiles_mn;
+    rem = tile - split * tiles_mn;
+    kb0 = split * p.kb_per_split;
+    kb1 = min(nkb_total, kb0 + p.kb_per_split);
+    tile += gridDim.x;
+    return true;
+  }
+};
+
+template <int BN, bool A_MN, bool B_MN, bool GATHER, bool PUSH, bool SK = false>
 __global__ void __launch_bounds__(NUM_THREADS + (GATHER ? GATHER_THREADS : 0), 1)
 gemm_tcgen05_kernel(const GemmParams p, const __grid_constant__ CUtensorMap tmA,
                     const __grid_constant__ CUtensorMap tmB,
@@ -139,7 +179,6 @@ gemm_tcgen05_kernel(const GemmParams p, const __grid_constant__ CUtensorMap tmA,
   const int warp = __shfl_sync(0xffffffffu, threadIdx.x >> 5, 0);   // uniform for the compiler
   const int lane = threadIdx.x & 31;
   const int tiles_mn = p.nmb * p.nnb;
-  const int total_tiles = tiles_mn * p.split_k;
   const int nkb_total = p.nkb_main + p.nkb_ext;
 
   if (warp == 0 && lane == 0) {
@@ -167,6 +206,7 @@ gemm_tcgen05_kernel(const GemmParams p, const __grid_constant__ CUtensorMap tmA,
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = __shfl_sync(0xffffffffu, *tmem_slot_ptr, 0);
+  if constexpr (SK) griddep_launch();       // the consumer of C may be scheduled; it waits for this grid itself
 
   if (warp == 0) {
     // ===================== TMA producer =====================
@@ -183,15 +223,29 @@ gemm_tcgen05_kernel(const GemmParams p, const __grid_constant__ CUtensorMap tmA,
     if (lane == 0) {
       int stage = 0;
       uint32_t phase = 0;
-      for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
-        const int split = tile / tiles_mn;
-        const int rem = tile - split * tiles_mn;
+      int pre = 0;              // SK: pipeline stages whose A (weight) tile was requested before griddep_wait()
+      if constexpr (SK) {
+        // Decode path, launched as a programmatic dependent of the kernel that produces B (the activations):
+        // the weights do not depend on it, so the first STAGES weight tiles are already in flight while the
+        // predecessor drains; only the activation tiles wait for it.
+        for (SegIter<SK> it(p, tiles_mn, nkb_total); p.early_a && pre < C_::STAGES && it.next(p, tiles_mn, nkb_total);) {
+          const int m0 = (it.rem % p.nmb) * BM;
+          for (int kb = it.kb0; kb < it.kb1 && pre < C_::STAGES; ++kb, ++pre) {
+            mbar_expect_tx(full_bar(pre), C_::STAGE_BYTES);
+            tma_load_2d(smem_base + pre * C_::STAGE_BYTES, &tmA, full_bar(pre), kb * BK, m0);
+          }
+        }
+        griddep_wait();
+      }
+      int issued = 0;
+      for (SegIter<SK> it(p, tiles_mn, nkb_total); it.next(p, tiles_mn, nkb_total);) {
+        const int rem = it.rem;
         int n_blk = rem / p.nmb;
         const int m_blk = rem - n_blk * p.nmb;
         if (GATHER && !B_MN) n_blk = (n_blk + p.n_rot) % p.nnb;      // start at this rank's own rows
         const int m0 = m_blk * BM, n0 = n_blk * BN;
-        const int kb0 = split * p.kb_per_split;
-        const int kb1 = min(nkb_total, kb0 + p.kb_per_split);
+        const int kb0 = it.kb0;
+        const int kb1 = it.kb1;
         bool b_local = false;       // B tile comes straight from this rank's shard
         int b_row_off = 0;
         const int lo_unit = GATHER ? gp.rank * gp.units_per_rank : 0;
@@ -219,6 +273,14 @@ gemm_tcgen05_kernel(const GemmParams p, const __grid_constant__ CUtensorMap tmA,
           const uint32_t sa = smem_base + stage * C_::STAGE_BYTES;
           const uint32_t sb = sa + C_::A_BYTES;
           const uint32_t fb = full_bar(stage);
+          if constexpr (SK) {
+            if (issued < pre) {               // weight tile and expect_tx already issued: add the activations
+              ++issued;
+              tma_load_2d(sb, &tmB, fb, kb * BK, n0);
+              if (++stage == C_::STAGES) { stage = 0; phase ^= 1u; }
+              continue;
+            }
+          }
           mbar_expect_tx(fb, C_::STAGE_BYTES);
           const bool ext = kb >= p.nkb_main;
           const CUtensorMap* ma = ext ? &tmA2 : &tmA;
@@ -271,10 +333,9 @@ gemm_tcgen05_kernel(const GemmParams p, const __grid_constant__ CUtensorMap tmA,
       uint32_t phase = 0;
       int acc = 0;
       uint32_t acc_phase = 0;
-      for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
-        const int split = tile / tiles_mn;
-        const int kb0 = split * p.kb_per_split;
-        const int kb1 = min(nkb_total, kb0 + p.kb_per_split);
+      for (SegIter<SK> it(p, tiles_mn, nkb_total); it.next(p, tiles_mn, nkb_total);) {
+        const int kb0 = it.kb0;
+        const int kb1 = it.kb1;
         mbar_wait(tempty_bar(acc), acc_phase ^ 1u);
         tc_fence_after();
         const uint32_t d_tmem = tmem_base + (uint32_t)(acc * BN);
@@ -332,9 +393,9 @@ gemm_tcgen05_kernel(const GemmParams p, const __grid_constant__ CUtensorMap tmA,
     const int quarter = warp & 3;
     int acc = 0;
     uint32_t acc_phase = 0;
-    for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
-      const int split = tile / tiles_mn;
-      const int rem = tile - split * tiles_mn;
+    if constexpr (SK) griddep_wait();       // C is re-zeroed by the predecessor: no red.add before it is done
+    for (SegIter<SK> it(p, tiles_mn, nkb_total); it.next(p, tiles_mn, nkb_total);) {
+      const int rem = it.rem;
       int n_blk = rem / p.nmb;
       const int m_blk = rem - n_blk * p.nmb;
       if (GATHER && !B_MN) n_blk = (n_blk + p.n_rot) % p.nnb;
@@ -501,7 +562,7 @@ int get_tmap(CUtensorMap* out, const void* base, uint64_t inner, uint64_t outer,
   return 0;
 }
 
-template <int BN, bool A_MN, bool B_MN, bool GATHER, bool PUSH = false>
+template <int BN, bool A_MN, bool B_MN, bool GATHER, bool PUSH = false, bool SK = false>
 int launch(const GemmParams& p, const CUtensorMap& a, const CUtensorMap& b, const CUtensorMap& a2,
            const CUtensorMap& b2, const CUtensorMap& bl, const GatherParams& gp, int grid,
            cudaStream_t stream) {
@@ -510,12 +571,18 @@ int launch(const GemmParams& p, const CUtensorMap& a, const CUtensorMap& b, cons
   int dev = 0;
   cudaGetDevice(&dev);
   if (!configured[dev & 63]) {
-    DLTI_CUDA_CHECK(cudaFuncSetAttribute(gemm_tcgen05_kernel<BN, A_MN, B_MN, GATHER, PUSH>,
+    DLTI_CUDA_CHECK(cudaFuncSetAttribute(gemm_tcgen05_kernel<BN, A_MN, B_MN, GATHER, PUSH, SK>,
                                          cudaFuncAttributeMaxDynamicSharedMemorySize,
                                          C_::SMEM_BYTES));
     configured[dev & 63] = true;
   }
-  gemm_tcgen05_kernel<BN, A_MN, B_MN, GATHER, PUSH>
+  if constexpr (SK) {
+    DLTI_CUDA_CHECK(dlti_launch_pdl(p.N, gemm_tcgen05_kernel<BN, A_MN, B_MN, GATHER, PUSH, SK>, dim3(grid),
+                                    dim3(NUM_THREADS), C_::SMEM_BYTES, stream, p, a, b, a2, b2, bl, gp));
+    dlti_count_launch();
+    return 0;
+  }
+  gemm_tcgen05_kernel<BN, A_MN, B_MN, GATHER, PUSH, SK>
       <<<grid, NUM_THREADS + (GATHER ? GATHER_THREADS : 0), C_::SMEM_BYTES, stream>>>(p, a, b, a2, b2, bl, gp);
   dlti_count_launch();
   return (int)cudaGetLastError();
@@ -530,7 +597,7 @@ static int gemm_impl(const void* A, const void* B, void* C, const void* R, int M
                      int split_k, int block_n, int max_ctas, cudaStream_t stream,
                      const GatherParams* gather, const void* const* push_peers = nullptr,
                      int push_rank = 0, int push_world = 0, long long push_slot_stride = 0,
-                     int transpose_out = 0) {
+                     int transpose_out = 0, int stream_k = 0) {
   if (M <= 0 || N <= 0 || K < 0 || (K == 0 && K2 == 0)) return DLTI_ERR_BAD_ARG;
   if (in_dtype != DLTI_BF16 && in_dtype != DLTI_FP16) return DLTI_ERR_UNSUPPORTED;
   if (K2 % BK) { dlti_set_error("K2 must be a multiple of 64"); return DLTI_ERR_BAD_ARG; }
@@ -544,6 +611,22 @@ static int gemm_impl(const void* A, const void* B, void* C, const void* R, int M
       const int sms = dlti_num_sms();
       if ((N + 255) / 256 < sms) bn = 128;
       if ((N + 127) / 128 < sms) bn = 64;
+    } else if (!gather && bn == 256) {
+      // prefill-sized problems (fewer than two waves of 128x256 tiles): narrower tiles fill the SMs better.
+      // cost = waves x tile width / relative efficiency of that width (narrow tiles are smem-bandwidth bound)
+      const int sms = dlti_num_sms();
+      const long long nmb = (M + BM - 1) / BM;
+      if (nmb * ((N + 255) / 256) < 2 * sms) {
+        const int widths[3] = {256, 128, 64};
+        const double eff[3] = {1.0, 0.92, 0.66};
+        double best = 1e30;
+        for (int i = 0; i < 3; ++i) {
+          if (a_mn && widths[i] == 256) continue;
+          const long long tiles = nmb * ((N + widths[i] - 1) / widths[i]);
+          const double cost = (double)((tiles + sms - 1) / sms) * widths[i] / eff[i];
+          if (cost < best - 1e-9) { best = cost; bn = widths[i]; }
+        }
+      }
     }
   }
   if (a_mn && bn == 256) bn = 128;
@@ -623,6 +706,18 @@ static int gemm_impl(const void* A, const void* B, void* C, const void* R, int M
   if (max_ctas > 0 && max_ctas < grid) grid = max_ctas;
   if (total < grid) grid = total;
 
+  if (stream_k) {
+    // equal K-block ranges per CTA over the linearised (tile, K block) space; needs the atomic epilogue
+    if (a_mn || b_mn || gather || push_world > 0 || !p.atomic_out || p.split_k != 1) return DLTI_ERR_UNSUPPORTED;
+    const long long items = (long long)p.nmb * p.nnb * nkb_total;
+    p.early_a = dlti_pdl_enabled() >= 2 && p.N <= DLTI_PDL_MAX_ROWS;   // p.N = token rows (swap-AB)
+    grid = dlti_num_sms();
+    if (max_ctas > 0 && max_ctas < grid) grid = max_ctas;
+    if (items < grid) grid = (int)items;
+    if (bn == 256) return launch<256, false, false, false, false, true>(p, ta, tb, ta2, tb2, tbl, gp, grid, stream);
+    if (bn == 128) return launch<128, false, false, false, false, true>(p, ta, tb, ta2, tb2, tbl, gp, grid, stream);
+    return launch<64, false, false, false, false, true>(p, ta, tb, ta2, tb2, tbl, gp, grid, stream);
+  }
   if (push_world > 0) {
     if (a_mn || b_mn) return DLTI_ERR_UNSUPPORTED;
     if (bn == 256) return launch<256, false, false, false, true>(p, ta, tb, ta2, tb2, tbl, gp, grid, stream);
@@ -704,17 +799,24 @@ DLTI_API int dlti_gemm_push(const void* A, const void* B, int M, int N, int K, l
 // the WEIGHT is the 128-row tcgen05 A operand (every byte streamed from HBM is useful) and the handful
 // of token rows is the narrow B operand; K is split across CTAs to put every SM on the weight stream
 // and the fp32 partials are reduced with red.global.add into `acc32` (must be zero on entry;
-// dlti_skinny_finish converts it to 16 bits and re-zeroes it).
+// dlti_skinny_finish or one of the dlti_acc_* consumers converts it to 16 bits and re-zeroes it).
+// split_k: 0 = stream-K (equal K-block ranges per CTA, the default), > 0 = that many tile-major splits,
+// < 0 = tile-major splits sized automatically.
 DLTI_API int dlti_gemm_skinny(const void* X, const void* W, float* acc32, int M, int N, int K, long long ldx,
                               long long ldw, int in_dtype, int split_k, cudaStream_t stream) {
   if (M < 1 || M > 256) return DLTI_ERR_BAD_ARG;
   const int bn = M <= 64 ? 64 : (M <= 128 ? 128 : 256);
-  if (split_k <= 0) {
+  int stream_k = 0;
+  if (split_k == 0) {
+    stream_k = 1;                 // default: every CTA streams the same number of K blocks
+    split_k = 1;
+  } else if (split_k < 0) {       // tile-major split-K sized to fill the SMs (ragged last wave)
     const int tiles = (N + BM - 1) / BM;
     const int nkb = (K + BK - 1) / BK;
     split_k = (dlti_num_sms() + tiles - 1) / tiles;
     while (split_k > 1 && nkb / split_k < 8) --split_k;
   }
   return gemm_impl(W, X, acc32, nullptr, N, M, K, ldw, ldx, /*ldc=*/N, 0, 0, 0, nullptr, nullptr, 0, 0, 0, in_dtype,
-                   DLTI_FP32, 1.f, 1, split_k, bn, 0, stream, nullptr, nullptr, 0, 0, 0, /*transpose_out=*/1);
+                   DLTI_FP32, 1.f, 1, split_k, bn, 0, stream, nullptr, nullptr, 0, 0, 0, /*transpose_out=*/1,
+                   stream_k);
 }

@@ -6,6 +6,7 @@
 
 #include <atomic>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <mutex>
 
@@ -48,6 +49,19 @@ int dlti_num_sms() {
   return sms[dev];
 }
 DLTI_API int dlti_sm_count() { return dlti_num_sms(); }
+
+static std::atomic<int> g_pdl{-1};
+int dlti_pdl_enabled() {
+  int v = g_pdl.load(std::memory_order_relaxed);
+  if (v < 0) {
+    const char* e = std::getenv("DLTI_PDL");
+    v = (e && e[0] >= '0' && e[0] <= '2') ? e[0] - '0' : 1;
+    g_pdl.store(v, std::memory_order_relaxed);
+  }
+  return v;
+}
+DLTI_API void dlti_set_pdl(int level) { g_pdl.store(level < 0 ? 0 : (level > 2 ? 2 : level), std::memory_order_relaxed); }
+DLTI_API int dlti_get_pdl() { return dlti_pdl_enabled(); }
 
 static PFN_cuTensorMapEncodeTiled_v12000 g_encode = nullptr;
 static std::once_flag g_encode_once;

@@ -100,7 +100,10 @@ __global__ void __launch_bounds__(128) paged_decode_kernel(
     const T* __restrict__ q, long long q_stride, const T* __restrict__ k_cache,
     const T* __restrict__ v_cache, const int* __restrict__ block_tables, int max_blocks,
     const int* __restrict__ ctx_lens, int block_size, int H, int KV, float scale_log2,
-    float* __restrict__ part_o, float* __restrict__ part_ml, int splits) {
+    float* __restrict__ part_o, float* __restrict__ part_ml, int splits, T* __restrict__ out,
+    long long out_stride) {
+  griddep_wait();            // q and this step's K/V rows come from the kernel before (see dlti_launch_pdl)
+  griddep_launch();
   const int split = blockIdx.x, h = blockIdx.y, b = blockIdx.z;
   const int ctx = ctx_lens[b];
   const int kvh = h / (H / KV);
@@ -128,7 +131,19 @@ __global__ void __launch_bounds__(128) paged_decode_kernel(
   float o[32];
 #pragma unroll
   for (int i = 0; i < 32; ++i) o[i] = 0.f;
-  const int* bt = block_tables + (long long)b * max_blocks;
+  // This split's slice of the block table goes to shared memory first: the loop's K/V addresses then depend
+  // on a shared-memory read instead of a second global round trip per iteration.
+  constexpr int BT_SMEM = 512;
+  __shared__ int s_bt[BT_SMEM];
+  const int* btg = block_tables + (long long)b * max_blocks;
+  const int blk0 = (it0 * 32) / block_size;
+  const int blk1 = min((min(it1 * 32, ctx) + block_size - 1) / block_size, max_blocks);
+  const bool bt_staged = blk1 - blk0 <= BT_SMEM;
+  if (bt_staged) {
+    for (int i = threadIdx.x; i < blk1 - blk0; i += 128) s_bt[i] = btg[blk0 + i];
+    __syncthreads();
+  }
+  const int* bt = bt_staged ? s_bt - blk0 : btg;
 
   // Software pipeline: the K/V rows of iteration it+1 are requested before iteration it is reduced, so
   // every thread always has 128 bytes in flight (the loop was latency-bound at 38 % of HBM bandwidth).
@@ -218,9 +233,13 @@ __global__ void __launch_bounds__(128) paged_decode_kernel(
       acc += sm_o[w][d] * a;
       gl += sm_l[w] * a;
     }
-    const long long pidx = ((long long)b * H + h) * splits + split;
-    part_o[pidx * HD + d] = acc;
-    if (d == 0) { part_ml[pidx * 2] = gm; part_ml[pidx * 2 + 1] = gl; }
+    if (splits == 1) {                                // nothing to combine: write the normalised row
+      out[(long long)b * out_stride + (long long)h * HD + d] = Cvt<T>::from_f(gl > 0.f ? acc / gl : 0.f);
+    } else {
+      const long long pidx = ((long long)b * H + h) * splits + split;
+      part_o[pidx * HD + d] = acc;
+      if (d == 0) { part_ml[pidx * 2] = gm; part_ml[pidx * 2 + 1] = gl; }
+    }
   }
 }
 
@@ -228,6 +247,8 @@ template <typename T>
 __global__ void __launch_bounds__(128) paged_combine_kernel(const float* __restrict__ part_o,
                                                            const float* __restrict__ part_ml, int splits,
                                                            T* __restrict__ out, long long out_stride, int H) {
+  griddep_wait();
+  griddep_launch();
   const int h = blockIdx.x, b = blockIdx.y, d = threadIdx.x;
   const long long base = ((long long)b * H + h) * splits;
   float gm = -INFINITY;
@@ -436,16 +457,25 @@ DLTI_API int dlti_paged_decode(const void* q, long long q_stride, const void* k_
   dim3 grid(splits, H, batch), g2(H, batch);
   const float sl2 = scale * 1.4426950408889634f;
   if (dtype == DLTI_BF16) {
-    paged_decode_kernel<__nv_bfloat16><<<grid, 128, 0, st>>>((const __nv_bfloat16*)q, q_stride, (const __nv_bfloat16*)k_cache, (const __nv_bfloat16*)v_cache, block_tables, max_blocks, ctx_lens, block_size, H, KV, sl2, part_o, part_ml, splits);
-    paged_combine_kernel<__nv_bfloat16><<<g2, 128, 0, st>>>(part_o, part_ml, splits, (__nv_bfloat16*)out, out_stride, H);
+    DLTI_CUDA_CHECK(dlti_launch_pdl(batch, paged_decode_kernel<__nv_bfloat16>, grid, dim3(128), 0, st, (const __nv_bfloat16*)q,
+                                    q_stride, (const __nv_bfloat16*)k_cache, (const __nv_bfloat16*)v_cache, block_tables,
+                                    max_blocks, ctx_lens, block_size, H, KV, sl2, part_o, part_ml, splits,
+                                    (__nv_bfloat16*)out, out_stride));
+    if (splits > 1)
+      DLTI_CUDA_CHECK(dlti_launch_pdl(batch, paged_combine_kernel<__nv_bfloat16>, g2, dim3(128), 0, st, (const float*)part_o,
+                                      (const float*)part_ml, splits, (__nv_bfloat16*)out, out_stride, H));
   } else if (dtype == DLTI_FP16) {
-    paged_decode_kernel<__half><<<grid, 128, 0, st>>>((const __half*)q, q_stride, (const __half*)k_cache, (const __half*)v_cache, block_tables, max_blocks, ctx_lens, block_size, H, KV, sl2, part_o, part_ml, splits);
-    paged_combine_kernel<__half><<<g2, 128, 0, st>>>(part_o, part_ml, splits, (__half*)out, out_stride, H);
+    DLTI_CUDA_CHECK(dlti_launch_pdl(batch, paged_decode_kernel<__half>, grid, dim3(128), 0, st, (const __half*)q, q_stride,
+                                    (const __half*)k_cache, (const __half*)v_cache, block_tables, max_blocks, ctx_lens,
+                                    block_size, H, KV, sl2, part_o, part_ml, splits, (__half*)out, out_stride));
+    if (splits > 1)
+      DLTI_CUDA_CHECK(dlti_launch_pdl(batch, paged_combine_kernel<__half>, g2, dim3(128), 0, st, (const float*)part_o,
+                                      (const float*)part_ml, splits, (__half*)out, out_stride, H));
   } else {
     return DLTI_ERR_UNSUPPORTED;
   }
-  dlti_count_launch(2);
-  return (int)cudaGetLastError();
+  dlti_count_launch(splits > 1 ? 2 : 1);
+  return 0;
 }
 
 // logits [B, V] (dtype 0/1/2), per-row temperature / top_k / top_p / seed device arrays (NULL =>

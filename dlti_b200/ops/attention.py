@@ -79,14 +79,21 @@ def attention_bwd_ref(dout, qkv, out, lse, cu_seqlens, H, KV, hd, scale):
     return torch.cat([dq.reshape(T, -1), dk.reshape(T, -1), dv.reshape(T, -1)], dim=1).to(qkv.dtype)
 
 
-def attention_fwd(qkv, cu_seqlens, max_seqlen, H, KV, hd, scale=None, want_lse=True):
-    """Returns (out [T, H*hd], lse [H, T] fp32 or None)."""
+def attention_fwd(qkv, cu_seqlens, max_seqlen, H, KV, hd, scale=None, want_lse=True, out=None):
+    """Returns (out [T, H*hd], lse [H, T] fp32 or None). `out`: optional contiguous [T, H*hd] destination
+    (e.g. a row slice of a larger buffer)."""
     scale = scale if scale is not None else 1.0 / math.sqrt(hd)
     if not _lib.use_native(qkv):
-        return attention_fwd_ref(qkv, cu_seqlens, H, KV, hd, scale)
+        o, lse = attention_fwd_ref(qkv, cu_seqlens, H, KV, hd, scale)
+        if out is not None:
+            out.copy_(o)
+            o = out
+        return o, lse
     assert qkv.is_contiguous() and cu_seqlens.dtype == torch.int32 and cu_seqlens.is_cuda
     T = qkv.shape[0]
-    out = torch.empty((T, H * hd), dtype=qkv.dtype, device=qkv.device)
+    if out is None:
+        out = torch.empty((T, H * hd), dtype=qkv.dtype, device=qkv.device)
+    assert out.is_contiguous() and out.shape == (T, H * hd) and out.dtype == qkv.dtype
     lse = torch.empty((H, T), dtype=torch.float32, device=qkv.device) if want_lse else None
     f = _lib.fn("dlti_attn_fwd", [_V, _V, _V, _V, _I, _I, _L, _I, _I, _I, _F, _I, _V])
     _lib.check(f(_lib.ptr(qkv), _lib.ptr(out), _lib.ptr(lse), _lib.ptr(cu_seqlens),

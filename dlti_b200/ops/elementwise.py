@@ -52,6 +52,30 @@ def rmsnorm_fwd(x, w, eps, residual=None, drop_p=0.0, seed=0, stream=0, want_dro
     return y, rstd, ydrop
 
 
+def acc_add_rmsnorm(acc, residual, w, eps):
+    """Decode path: consume the fp32 accumulator `acc` [rows, d] of gemm_skinny_acc (re-zeroing it):
+    residual += T(acc) in place, returns y = RMSNorm(residual) * w. Bit-identical to skinny_finish followed
+    by rmsnorm_fwd(x, w, eps, residual=residual)."""
+    rows, d = acc.shape
+    assert acc.is_cuda and acc.dtype == torch.float32 and acc.is_contiguous() and residual.is_contiguous()
+    y = torch.empty_like(residual)
+    f = _lib.fn("dlti_acc_add_rmsnorm", [_V, _V, _V, _V, _L, _I, _F, _I, _V])
+    _lib.check(f(_lib.ptr(acc), _lib.ptr(residual), _lib.ptr(w), _lib.ptr(y), rows, d, eps,
+                 _lib.dtype_code(residual.dtype), _lib.stream_ptr()), "acc_add_rmsnorm")
+    return y
+
+
+def acc_swiglu(acc, dtype):
+    """Decode path: h = silu(gate) * up from the fp32 gate_up accumulator [rows, 2*ff] (re-zeroed)."""
+    rows, ff2 = acc.shape
+    assert acc.is_cuda and acc.dtype == torch.float32 and acc.is_contiguous()
+    h = torch.empty((rows, ff2 // 2), dtype=dtype, device=acc.device)
+    f = _lib.fn("dlti_acc_swiglu", [_V, _V, _L, _I, _L, _I, _V])
+    _lib.check(f(_lib.ptr(acc), _lib.ptr(h), rows, ff2 // 2, h.stride(0), _lib.dtype_code(dtype), _lib.stream_ptr()),
+               "acc_swiglu")
+    return h
+
+
 def rmsnorm_bwd_ref(dy, x, w, rstd, dres=None):
     g = dy.float() * w.float()
     xh = x.float() * rstd.unsqueeze(-1).view(*x.shape[:-1], 1)

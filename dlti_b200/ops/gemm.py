@@ -208,29 +208,47 @@ def gemm_swiglu_bwd(dy: torch.Tensor, w_down: torch.Tensor, gu: torch.Tensor) ->
 
 
 _skinny_ws: dict = {}
+_SKINNY_SPLIT = int(os.environ.get("DLTI_SKINNY_SPLIT", "0"))   # 0 = stream-K, -1 = tile-major auto split, n = n splits
 
 
-def gemm_skinny(x: torch.Tensor, w: torch.Tensor, out: torch.Tensor | None = None, split_k: int = 0) -> torch.Tensor:
-    """y[M, N] = x[M, K] · w[N, K]^T for decode-sized M (<= 256): the weight is the 128-row tensor-core
-    operand, K is split over CTAs so every SM streams weights, fp32 partials are reduced with atomics
-    into a persistent zeroed workspace and a finish kernel converts + re-zeroes it. Falls back to the
-    regular kernel on CPU tensors or larger M."""
+def _skinny_workspace(device, numel: int) -> torch.Tensor:
+    key = str(device)
+    ws = _skinny_ws.get(key)
+    if ws is None or ws.numel() < numel:
+        ws = torch.zeros(max(numel, 256 * 32768), dtype=torch.float32, device=device)
+        _skinny_ws[key] = ws
+    return ws
+
+
+def gemm_skinny_acc(x: torch.Tensor, w: torch.Tensor, split_k: int | None = None) -> torch.Tensor:
+    """fp32 accumulator [M, N] of x[M, K] · w[N, K]^T for decode-sized M (<= 256), left in the shared
+    zero-on-entry workspace: the swap-AB kernel makes the weight the 128-row tensor-core operand and cuts the
+    (tile, K block) space into equal ranges per CTA (stream-K), reducing fp32 partials with atomics. The
+    caller must consume the view at once with an op that re-zeroes it (skinny_finish / ops.*.acc_*) — the
+    next gemm_skinny* call reuses the same memory."""
+    M, K = x.shape
+    N = w.shape[0]
+    assert _lib.use_native(x, w) and M <= 256 and N % 8 == 0 and x.stride(1) == 1 and w.stride(1) == 1
+    ws = _skinny_workspace(x.device, M * N)
+    f = _lib.fn("dlti_gemm_skinny", [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_longlong,
+                                     C.c_longlong, C.c_int, C.c_int, C.c_void_p])
+    _lib.check(f(_lib.ptr(x), _lib.ptr(w), _lib.ptr(ws), M, N, K, x.stride(0), w.stride(0),
+                 _lib.dtype_code(x.dtype), int(_SKINNY_SPLIT if split_k is None else split_k), _lib.stream_ptr()),
+               "dlti_gemm_skinny")
+    return ws[:M * N].view(M, N)
+
+
+def gemm_skinny(x: torch.Tensor, w: torch.Tensor, out: torch.Tensor | None = None, split_k: int | None = None) -> torch.Tensor:
+    """y[M, N] = x[M, K] · w[N, K]^T for decode-sized M (<= 256): gemm_skinny_acc + a finish kernel that
+    converts the fp32 accumulator and re-zeroes it. Falls back to the regular kernel on CPU tensors or larger M."""
     M, K = x.shape
     N = w.shape[0]
     if not _lib.use_native(x, w) or M > 256 or N % 8:
         return gemm(x, w, out=out)
-    key = str(x.device)
-    ws = _skinny_ws.get(key)
-    if ws is None or ws.numel() < M * N:
-        ws = torch.zeros(max(M * N, 256 * 32768), dtype=torch.float32, device=x.device)
-        _skinny_ws[key] = ws
+    acc = gemm_skinny_acc(x, w, split_k)
     if out is None:
         out = torch.empty((M, N), dtype=x.dtype, device=x.device)
-    f = _lib.fn("dlti_gemm_skinny", [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_longlong,
-                                     C.c_longlong, C.c_int, C.c_int, C.c_void_p])
-    _lib.check(f(_lib.ptr(x), _lib.ptr(w), _lib.ptr(ws), M, N, K, x.stride(0), w.stride(0),
-                 _lib.dtype_code(x.dtype), int(split_k), _lib.stream_ptr()), "dlti_gemm_skinny")
     g = _lib.fn("dlti_skinny_finish", [C.c_void_p, C.c_void_p, C.c_longlong, C.c_int, C.c_longlong, C.c_int, C.c_void_p])
-    _lib.check(g(_lib.ptr(ws), _lib.ptr(out), M, N, out.stride(0), _lib.dtype_code(out.dtype), _lib.stream_ptr()),
+    _lib.check(g(_lib.ptr(acc), _lib.ptr(out), M, N, out.stride(0), _lib.dtype_code(out.dtype), _lib.stream_ptr()),
                "dlti_skinny_finish")
     return out

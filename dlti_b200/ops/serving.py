@@ -39,6 +39,21 @@ def rope_cache_(qkv, pos, cos_t, sin_t, slots, k_cache, v_cache, H, KV, hd):
     return qkv
 
 
+def acc_rope_cache(acc, dtype, pos, cos_t, sin_t, slots, k_cache, v_cache, H, KV, hd):
+    """Decode path: consume the fp32 qkv accumulator [T, (H+2KV)*hd] of gemm_skinny_acc (re-zeroing it) and
+    return the 16-bit qkv with q,k rotated; rotated k and v also go to the paged cache at `slots`. Bit-identical
+    to skinny_finish + rope_cache_."""
+    T, W = acc.shape
+    assert acc.is_cuda and acc.dtype == torch.float32 and acc.is_contiguous() and W == (H + 2 * KV) * hd
+    assert pos.dtype == torch.int32 and slots.dtype == torch.int64
+    qkv = torch.empty((T, W), dtype=dtype, device=acc.device)
+    f = _lib.fn("dlti_acc_rope_cache", [_V, _V, _V, _V, _V, _V, _V, _V, _L, _I, _I, _I, _L, _I, _V])
+    _lib.check(f(_lib.ptr(acc), _lib.ptr(qkv), _lib.ptr(pos), _lib.ptr(cos_t), _lib.ptr(sin_t), _lib.ptr(slots),
+                 _lib.ptr(k_cache), _lib.ptr(v_cache), T, H, KV, hd, qkv.stride(0), _lib.dtype_code(dtype),
+                 _lib.stream_ptr()), "acc_rope_cache")
+    return qkv
+
+
 def paged_decode_ref(q, k_cache, v_cache, block_tables, ctx_lens, H, KV, hd, scale):
     B = q.shape[0]
     bs = k_cache.shape[1]
@@ -68,14 +83,20 @@ def paged_decode(q, k_cache, v_cache, block_tables, ctx_lens, H, KV, hd, scale=N
     Returns out [B, H*hd]."""
     scale = scale if scale is not None else 1.0 / math.sqrt(hd)
     if not _lib.use_native(q):
-        return paged_decode_ref(q, k_cache, v_cache, block_tables, ctx_lens, H, KV, hd, scale)
+        o = paged_decode_ref(q, k_cache, v_cache, block_tables, ctx_lens, H, KV, hd, scale)
+        if out is not None:
+            out.copy_(o)
+            o = out
+        return o
     B = q.shape[0]
     if out is None:
         out = torch.empty((B, H * hd), dtype=q.dtype, device=q.device)
     bs = k_cache.shape[1]
     mc = max_ctx if max_ctx is not None else block_tables.shape[1] * bs
+    # enough CTAs (128 threads each, ~4 resident per SM) to fill the machine: short contexts are latency-bound,
+    # so small batches are cut into more KV splits
     sms = 148
-    splits = max(1, min(16, (2 * sms) // max(1, B * H), (mc + 255) // 256))
+    splits = max(1, min(16, -(-(4 * sms) // max(1, B * H)), (mc + 255) // 256))
     need = _lib.fn("dlti_paged_decode_workspace_floats", [_I, _I, _I], C.c_int)(B, H, splits)
     key = str(q.device)
     ws = _ws.get(key)

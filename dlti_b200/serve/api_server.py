@@ -4,8 +4,11 @@ stream), GET /v1/models, GET /health, GET /metrics (Prometheus text). Schema fol
 `data: {json}\\n\\n` ... `data: [DONE]\\n\\n`. The reference only declares this capability
 (reference README.md:10,16; requirements.txt:18).
 
-The engine loop runs in its own thread; the asyncio side hands requests over a thread-safe queue and
-receives tokens through per-request asyncio queues.
+Two deployments of the same app: AsyncEngine runs the engine loop in a thread of the HTTP process (requests
+over a thread-safe queue, tokens through per-request asyncio queues); EngineProxy + engine_process_loop put the
+HTTP server in a process of its own, connected to the engine process by a pipe (one message per engine step) —
+the layout vLLM uses for its API server / engine core (SP:vllm/v1/engine/core_client.py), so the engine never
+competes with request handling for the interpreter lock.
 """
 from __future__ import annotations
 
@@ -26,67 +29,72 @@ from .engine import LLMEngine
 from .params import SamplingParams
 
 
-class AsyncEngine:
-    def __init__(self, engine: LLMEngine):
-        self.engine = engine
-        self.inbox: queue.Queue = queue.Queue()
+def _engine_stats(eng: LLMEngine, metrics: dict) -> dict:
+    return dict(metrics, running=len(eng.sched.running), waiting=len(eng.sched.waiting),
+                kv_usage=eng.blocks.usage(), preemptions=eng.sched.num_preemptions,
+                max_model_len=eng.max_model_len)
+
+
+def _handle_command(eng: LLMEngine, kind, payload, emit_error) -> None:
+    if kind == "add":
+        rid, prompt, params = payload
+        try:
+            eng.add_request(prompt, params, rid)
+        except Exception as e:  # bad request (too long, ...)
+            emit_error(rid, str(e))
+    elif kind == "abort":
+        eng.abort(payload)
+
+
+def _step_items(eng: LLMEngine, metrics: dict) -> list:
+    """One engine step -> [(request id, stream item)] for every request that produced a token."""
+    batch = []
+    for out in eng.step():
+        rid = out.request_id
+        r = eng.requests.get(rid)
+        if r is None:
+            continue
+        if len(r.output_ids) == 1:
+            metrics["ttft_sum"] += time.time() - r.arrival
+            metrics["ttft_count"] += 1
+        metrics["tokens_total"] += len(out.new_token_ids)
+        delta = eng.text_delta(rid, final=out.finished)
+        batch.append((rid, {"text": delta, "token_ids": out.new_token_ids, "finished": out.finished,
+                            "finish_reason": out.finish_reason, "logprobs": out.logprobs,
+                            "prompt_tokens": len(r.prompt_ids), "completion_tokens": len(r.output_ids)}))
+        if out.finished:
+            eng.release(rid)
+    return batch
+
+
+class _Streams:
+    """asyncio side shared by the in-process and the two-process front-ends: per-request queues fed from
+    another thread, one hand-over to the event loop per engine step."""
+
+    def __init__(self):
         self.streams: dict[str, tuple[asyncio.AbstractEventLoop, asyncio.Queue]] = {}
-        self.stop = False
-        self.thread = threading.Thread(target=self._loop, daemon=True)
-        self.metrics = {"requests_total": 0, "tokens_total": 0, "ttft_sum": 0.0, "ttft_count": 0}
 
-    def start(self):
-        self.thread.start()
+    def _emit_many(self, items):
+        by_loop: dict = {}
+        for rid, item in items:
+            s = self.streams.get(rid)
+            if s:
+                by_loop.setdefault(s[0], []).append((s[1], item))
+        for loop, pairs in by_loop.items():
+            loop.call_soon_threadsafe(self._deliver, pairs)
 
-    def _loop(self):
-        import torch
-        if self.engine.device.type == "cuda":
-            torch.cuda.set_device(self.engine.device)
-        eng = self.engine
-        while not self.stop:
-            try:
-                while True:
-                    kind, payload = self.inbox.get_nowait() if eng.has_unfinished() else self.inbox.get(timeout=0.05)
-                    if kind == "add":
-                        rid, prompt, params = payload
-                        try:
-                            eng.add_request(prompt, params, rid)
-                        except Exception as e:  # bad request (too long, ...)
-                            self._emit(rid, {"error": str(e)})
-                    elif kind == "abort":
-                        eng.abort(payload)
-            except queue.Empty:
-                pass
-            if not eng.has_unfinished():
-                continue
-            for out in eng.step():
-                rid = out.request_id
-                r = eng.requests.get(rid)
-                if r is None:
-                    continue
-                if len(r.output_ids) == 1:
-                    self.metrics["ttft_sum"] += time.time() - r.arrival
-                    self.metrics["ttft_count"] += 1
-                self.metrics["tokens_total"] += len(out.new_token_ids)
-                delta = eng.text_delta(rid, final=out.finished)
-                self._emit(rid, {"text": delta, "token_ids": out.new_token_ids, "finished": out.finished,
-                                 "finish_reason": out.finish_reason, "logprobs": out.logprobs,
-                                 "prompt_tokens": len(r.prompt_ids), "completion_tokens": len(r.output_ids)})
-                if out.finished:
-                    eng.release(rid)
-        eng.shutdown_workers()
+    @staticmethod
+    def _deliver(pairs):
+        for q, item in pairs:
+            q.put_nowait(item)
 
-    def _emit(self, rid, item):
-        s = self.streams.get(rid)
-        if s:
-            loop, q = s
-            loop.call_soon_threadsafe(q.put_nowait, item)
+    def _submit(self, kind, payload):
+        raise NotImplementedError
 
     async def generate(self, prompt, params: SamplingParams, rid: str):
         q: asyncio.Queue = asyncio.Queue()
         self.streams[rid] = (asyncio.get_running_loop(), q)
-        self.metrics["requests_total"] += 1
-        self.inbox.put(("add", (rid, prompt, params)))
+        self._submit("add", (rid, prompt, params))
         try:
             while True:
                 item = await q.get()
@@ -97,7 +105,142 @@ class AsyncEngine:
             self.streams.pop(rid, None)
 
     def abort(self, rid: str):
-        self.inbox.put(("abort", rid))
+        self._submit("abort", rid)
+
+
+class AsyncEngine(_Streams):
+    """Engine loop in a thread of the HTTP server's process (tests, notebooks, small deployments)."""
+
+    def __init__(self, engine: LLMEngine):
+        super().__init__()
+        self.engine = engine
+        self.inbox: queue.Queue = queue.Queue()
+        self.stop = False
+        self.thread = threading.Thread(target=self._loop, daemon=True)
+        self.metrics = {"requests_total": 0, "tokens_total": 0, "ttft_sum": 0.0, "ttft_count": 0}
+
+    def start(self):
+        # the engine thread re-acquires the GIL after every device sync; with the default 5 ms switch interval a
+        # busy HTTP thread can hold it that long, which is most of a decode step
+        import sys
+        sys.setswitchinterval(min(sys.getswitchinterval(), 2e-4))
+        self.thread.start()
+
+    def stats(self) -> dict:
+        return _engine_stats(self.engine, self.metrics)
+
+    def _submit(self, kind, payload):
+        if kind == "add":
+            self.metrics["requests_total"] += 1
+        self.inbox.put((kind, payload))
+
+    def _loop(self):
+        import torch
+        if self.engine.device.type == "cuda":
+            torch.cuda.set_device(self.engine.device)
+        eng = self.engine
+        while not self.stop:
+            try:
+                while True:
+                    kind, payload = self.inbox.get_nowait() if eng.has_unfinished() else self.inbox.get(timeout=0.05)
+                    _handle_command(eng, kind, payload, lambda rid, msg: self._emit_many([(rid, {"error": msg})]))
+            except queue.Empty:
+                pass
+            if not eng.has_unfinished():
+                continue
+            self._emit_many(_step_items(eng, self.metrics))
+        eng.shutdown_workers()
+
+
+class EngineProxy(_Streams):
+    """Front-end half of the two-process server: lives in the HTTP process, talks to the engine process over a
+    pipe. The engine's per-step host work then never waits on the HTTP threads for the interpreter lock, and the
+    SSE encoding of step N runs while the GPU computes step N+1."""
+
+    def __init__(self, conn, max_model_len: int):
+        super().__init__()
+        self.conn = conn
+        self._stats = {"requests_total": 0, "tokens_total": 0, "ttft_sum": 0.0, "ttft_count": 0, "running": 0,
+                       "waiting": 0, "kv_usage": 0.0, "preemptions": 0, "max_model_len": max_model_len}
+        self._lock = threading.Lock()
+        self.thread = threading.Thread(target=self._reader, daemon=True)
+
+    def start(self):
+        self.thread.start()
+
+    def stats(self) -> dict:
+        return dict(self._stats)
+
+    def _submit(self, kind, payload):
+        if kind == "add":
+            rid, prompt, params = payload
+            payload = (rid, prompt, vars(params))
+        with self._lock:
+            self.conn.send((kind, payload))
+
+    def _reader(self):
+        while True:
+            try:
+                items, stats = self.conn.recv()
+            except (EOFError, OSError):
+                return
+            self._stats.update(stats)
+            self._emit_many(items)
+
+
+def engine_process_loop(eng: LLMEngine, conn, should_stop=lambda: False) -> None:
+    """Engine half of the two-process server (runs in the process that owns the GPU): commands come in and
+    per-step outputs go out over `conn`, one message per engine step."""
+    metrics = {"requests_total": 0, "tokens_total": 0, "ttft_sum": 0.0, "ttft_count": 0}
+    errors: list = []
+    try:
+        while not should_stop():
+            ready = conn.poll(0 if eng.has_unfinished() else 0.05)
+            while ready:
+                kind, payload = conn.recv()
+                if kind == "add":
+                    metrics["requests_total"] += 1
+                    payload = (payload[0], payload[1], SamplingParams(**payload[2]))
+                _handle_command(eng, kind, payload, lambda rid, msg: errors.append((rid, {"error": msg})))
+                ready = conn.poll(0)
+            items = errors[:]
+            errors.clear()
+            if eng.has_unfinished():
+                items += _step_items(eng, metrics)
+            if items:
+                conn.send((items, _engine_stats(eng, metrics)))
+    except (EOFError, OSError, BrokenPipeError):
+        pass
+    eng.shutdown_workers()
+
+
+def frontend_main(conn, host: str, port: int, model_name: str, max_model_len: int) -> None:
+    """Entry point of the HTTP process (spawned by serve_two_process)."""
+    import uvicorn
+    proxy = EngineProxy(conn, max_model_len)
+    proxy.start()
+    uvicorn.run(build_app(proxy, model_name), host=host, port=port, log_level="warning")
+
+
+def start_frontend_process(eng: LLMEngine, host: str, port: int, model_name: str):
+    """Spawn the HTTP front-end as its own process; returns (process, engine-side connection). The caller then
+    runs engine_process_loop(eng, conn) in the thread that owns the CUDA context."""
+    import multiprocessing as mp
+    import os
+    ctx = mp.get_context("spawn")
+    parent, child = ctx.Pipe(duplex=True)
+    saved = os.environ.get("CUDA_VISIBLE_DEVICES")
+    os.environ["CUDA_VISIBLE_DEVICES"] = ""              # the front-end never touches a GPU
+    try:
+        proc = ctx.Process(target=frontend_main, args=(child, host, port, model_name, eng.max_model_len), daemon=True)
+        proc.start()
+    finally:
+        if saved is None:
+            os.environ.pop("CUDA_VISIBLE_DEVICES", None)
+        else:
+            os.environ["CUDA_VISIBLE_DEVICES"] = saved
+    child.close()
+    return proc, parent
 
 
 def _params_from_body(b: dict) -> SamplingParams:
@@ -127,15 +270,15 @@ def build_app(aeng: AsyncEngine, model_name: str):
     @app.get("/v1/models")
     async def models():
         return {"object": "list", "data": [{"id": model_name, "object": "model", "created": created,
-                                             "owned_by": "dlti_b200", "max_model_len": aeng.engine.max_model_len}]}
+                                             "owned_by": "dlti_b200", "max_model_len": aeng.stats()["max_model_len"]}]}
 
     @app.get("/metrics")
     async def metrics():
-        m, e = aeng.metrics, aeng.engine
+        m = aeng.stats()
         lines = [f"dlti_requests_total {m['requests_total']}", f"dlti_generation_tokens_total {m['tokens_total']}",
                  f"dlti_time_to_first_token_seconds_sum {m['ttft_sum']}", f"dlti_time_to_first_token_seconds_count {m['ttft_count']}",
-                 f"dlti_num_requests_running {len(e.sched.running)}", f"dlti_num_requests_waiting {len(e.sched.waiting)}",
-                 f"dlti_kv_cache_usage {e.blocks.usage():.4f}", f"dlti_num_preemptions_total {e.sched.num_preemptions}"]
+                 f"dlti_num_requests_running {m['running']}", f"dlti_num_requests_waiting {m['waiting']}",
+                 f"dlti_kv_cache_usage {m['kv_usage']:.4f}", f"dlti_num_preemptions_total {m['preemptions']}"]
         return PlainTextResponse("\n".join(lines) + "\n")
 
     @app.post("/v1/completions")
@@ -167,7 +310,6 @@ def build_app(aeng: AsyncEngine, model_name: str):
         stream = bool(body.get("stream", False))
         include_usage = bool((body.get("stream_options") or {}).get("include_usage", False))
         jobs = [(i * sp.n + j, p) for i, p in enumerate(prompts) for j in range(sp.n)]
-        tok = aeng.engine.tokenizer
 
         def chunk(idx, text, finish, lp=None):
             return {"id": base_id, "object": "text_completion", "created": int(time.time()), "model": model_name,

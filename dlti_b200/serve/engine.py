@@ -12,6 +12,7 @@ from __future__ import annotations
 import time
 import uuid
 
+import numpy as np
 import torch
 
 from ..models.config import LlamaConfig
@@ -25,11 +26,56 @@ from .tokenizer import IncrementalDetokenizer
 _BUCKETS = [1, 2, 4, 8, 16, 32, 64, 128, 256, 512]
 
 
+class StepLayout:
+    """Where each per-step array lives inside ONE int64 staging buffer, so a step's metadata reaches the
+    device (and the TP workers) as a single copy. T token rows = nd decode rows followed by the rows of npf
+    packed prompts; B = nd + npf rows are sampled; block tables are [nd, mb]. 64-bit sections first, then
+    the 32-bit ones (each padded to a whole word); the tables come last so that a prefix copy carries
+    everything but unused table rows."""
+    _I64 = ("ids", "slots", "last", "seeds")
+    _I32 = ("pos", "ctx", "cu", "topk", "temp", "topp", "tables")
+
+    def __init__(self, T: int, nd: int, npf: int, mb: int):
+        self.T, self.nd, self.npf, self.mb = T, nd, npf, mb
+        B = nd + npf
+        self.n = dict(ids=T, slots=T, last=B, seeds=B, pos=T, ctx=nd, cu=npf + 1 if npf else 0, topk=B, temp=B,
+                      topp=B, tables=nd * mb)
+        o = 0
+        self.off = {}
+        for k in self._I64:
+            self.off[k] = o
+            o += self.n[k]
+        for k in self._I32:
+            self.off[k] = o
+            o += (self.n[k] + 1) // 2
+        self.words = o
+        self.tables = self.off["tables"]
+
+    def views(self, buf, xp) -> dict:
+        """Typed views into `buf` (1-D int64 numpy array or torch tensor; xp = numpy or torch module)."""
+        i32, f32 = (np.int32, np.float32) if xp is np else (torch.int32, torch.float32)
+        out = {}
+        for k in self._I64:
+            out[k] = buf[self.off[k]:self.off[k] + self.n[k]]
+        for k in self._I32:
+            n = self.n[k]
+            out[k] = buf[self.off[k]:self.off[k] + (n + 1) // 2].view(f32 if k in ("temp", "topp") else i32)[:n]
+        out["tables"] = out["tables"].reshape(self.nd, self.mb) if self.nd * self.mb else out["tables"]
+        return out
+
+
+class PackedStep:
+    __slots__ = ("layout", "slot", "max_seqlen")
+
+    def __init__(self, layout: StepLayout, slot, max_seqlen: int):
+        self.layout, self.slot, self.max_seqlen = layout, slot, max_seqlen
+
+
 class LLMEngine:
     def __init__(self, cfg: LlamaConfig, weights: TPWeights, tp: TPContext, tokenizer, *, info=None,
                  block_size: int = 16, num_blocks: int | None = None, gpu_memory_utilization: float = 0.85,
                  max_num_seqs: int = 256, max_num_batched_tokens: int = 8192, max_model_len: int | None = None,
-                 use_cuda_graphs: bool = True):
+                 use_cuda_graphs: bool = True, mixed_batches: bool = True):
         self.cfg, self.w, self.tp, self.tokenizer, self.info = cfg, weights, tp, tokenizer, info
         self.device = weights.embed.device
         self.dtype = weights.embed.dtype
@@ -51,7 +97,8 @@ class LLMEngine:
                 num_blocks = 256
         self.kv = KVCache(cfg.num_hidden_layers, num_blocks, block_size, weights.KV, cfg.head_dim, self.dtype, self.device)
         self.blocks = BlockManager(num_blocks, block_size)
-        self.sched = Scheduler(self.blocks, max_num_seqs, max_num_batched_tokens, self.max_model_len)
+        self.sched = Scheduler(self.blocks, max_num_seqs, max_num_batched_tokens, self.max_model_len,
+                               mixed=mixed_batches)
         self.runner = ModelRunner(cfg, weights, self.kv, tp)
         self.max_blocks_per_seq = -(-self.max_model_len // block_size)
         self.requests: dict[str, Request] = {}
@@ -59,8 +106,11 @@ class LLMEngine:
         self.step_count = 0
         self.use_graphs = use_cuda_graphs and self.device.type == "cuda"
         self.graphs: dict[int, tuple] = {}
-        self.stats = {"prefill_steps": 0, "decode_steps": 0, "prompt_tokens": 0, "generated_tokens": 0,
-                      "prefill_time": 0.0, "decode_time": 0.0}
+        self.stats = {"prefill_steps": 0, "decode_steps": 0, "mixed_steps": 0, "prompt_tokens": 0,
+                      "generated_tokens": 0, "prefill_time": 0.0, "decode_time": 0.0, "mixed_time": 0.0}
+        self._rings: dict = {}
+        self._ring_pos: dict = {}
+        self._arange = np.arange(max(self.max_model_len, block_size) + 1, dtype=np.int64)
 
     # ---- request API (driver) ------------------------------------------------------------------
     def add_request(self, prompt: str | list[int], params: SamplingParams | None = None,
@@ -87,100 +137,147 @@ class LLMEngine:
         return self.sched.has_work()
 
     # ---- step ------------------------------------------------------------------------------------
-    def _meta_from_batch(self, batch: Batch) -> dict:
+    def _host_buffer(self, key, words: int):
+        """Next pinned host staging buffer (int64 words) of ring `key`; waits for the H2D copy that last read it."""
+        ring = self._rings.get(key)
+        if ring is None or ring[0][0].numel() < words:
+            cap = max(words, 1 << 12) if ring is None else max(words, 2 * ring[0][0].numel())
+            pin = self.device.type == "cuda"
+            ring = [[torch.zeros(cap, dtype=torch.int64, pin_memory=pin), None] for _ in range(4)]
+            self._rings[key] = ring
+            self._ring_pos[key] = 0
+        i = self._ring_pos[key]
+        self._ring_pos[key] = (i + 1) % len(ring)
+        slot = ring[i]
+        if slot[1] is not None:
+            slot[1].synchronize()
+        return slot
+
+    def _to_device(self, slot, words: int, dst: torch.Tensor | None = None) -> torch.Tensor:
+        host = slot[0][:words]
+        if self.device.type != "cuda":
+            return host.clone() if dst is None else dst[:words].copy_(host)
+        if dst is None:
+            dst = torch.empty(words, dtype=torch.int64, device=self.device)
+        dst[:words].copy_(host, non_blocking=True)
+        if slot[1] is None:
+            slot[1] = torch.cuda.Event()
+        slot[1].record()
+        return dst
+
+    def pack_step(self, nd: int, ids, pos, slots, ctx, tables, cu, max_seqlen: int, sampling=None) -> "PackedStep":
+        """Lay one step's metadata out in a pinned host buffer (see StepLayout). ids/pos/slots cover all T
+        rows (decode rows first); ctx/tables the nd decode rows; cu the packed prompts (relative to row nd);
+        sampling = (temperature, top_k, top_p, seeds) per sampled row or None."""
+        T, npf = len(ids), max(0, len(cu) - 1)
+        mb = max((len(t) for t in tables), default=0)
+        mb = (mb + 7) & ~7
+        lay = StepLayout(T, nd, npf, mb)
+        slot = self._host_buffer("step", lay.words)
+        v = lay.views(slot[0].numpy(), np)
+        v["ids"][:] = ids
+        v["pos"][:] = pos
+        v["slots"][:] = slots
+        if nd:
+            v["ctx"][:] = ctx
+            tab = v["tables"]
+            for i, t in enumerate(tables):
+                tab[i, :len(t)] = t
+        if npf:
+            v["cu"][:] = cu
+            v["last"][nd:] = np.asarray(cu[1:], dtype=np.int64) + (nd - 1)
+        if nd:
+            v["last"][:nd] = np.arange(nd)
+        if sampling is not None:
+            v["temp"][:], v["topk"][:], v["topp"][:], v["seeds"][:] = sampling
+        return PackedStep(lay, slot, int(max_seqlen))
+
+    def _pack_batch(self, batch: Batch) -> "PackedStep":
         bs = self.blocks.block_size
+        nd = batch.num_decode
         reqs = batch.requests
-        if batch.kind == "prefill":
-            ids, pos, slots, cu = [], [], [], [0]
-            for r in reqs:
-                toks = r.prompt_ids + r.output_ids
-                n = len(toks)
-                ids += toks
-                pos += list(range(n))
-                slots += [r.blocks[t // bs] * bs + t % bs for t in range(n)]
-                cu.append(cu[-1] + n)
-            last = [c - 1 for c in cu[1:]]
-            return dict(kind=0, ids=ids, pos=pos, slots=slots, cu=cu, last=last,
-                        max_seqlen=max(b - a for a, b in zip(cu, cu[1:])), B=len(reqs))
-        ids, pos, slots, ctx, tables = [], [], [], [], []
-        for r in reqs:
+        ids, pos, slots, ctx, tables, cu = [], [], [], [], [], []
+        for r in reqs[:nd]:
             t = r.num_tokens - 1
             ids.append((r.output_ids or r.prompt_ids)[-1])
             pos.append(t)
             slots.append(r.blocks[t // bs] * bs + t % bs)
             ctx.append(t + 1)
-            tables.append(list(r.blocks))
-        return dict(kind=1, ids=ids, pos=pos, slots=slots, ctx=ctx, tables=tables, B=len(reqs))
+            tables.append(r.blocks)
+        max_seqlen = 0
+        if len(reqs) > nd:
+            cu = [0]
+            ar = self._arange
+            sl = [np.asarray(slots, dtype=np.int64)]
+            ps = [np.asarray(pos, dtype=np.int64)]
+            for r in reqs[nd:]:
+                toks = r.prompt_ids + r.output_ids
+                n = len(toks)
+                ids += toks
+                ps.append(ar[:n])
+                blk = np.asarray(r.blocks[:-(-n // bs)], dtype=np.int64)
+                sl.append((blk[:, None] * bs + ar[None, :bs]).reshape(-1)[:n])
+                cu.append(cu[-1] + n)
+                max_seqlen = max(max_seqlen, n)
+            pos, slots = np.concatenate(ps), np.concatenate(sl)
+        sampling = ([r.params.temperature for r in reqs], [r.params.top_k for r in reqs],
+                    [r.params.top_p for r in reqs],
+                    # random stream keyed by (request seed, index of the token being generated): same seed =>
+                    # same text, whatever else the engine is doing
+                    [(r.seed * 1000003 + len(r.output_ids)) & 0x7FFFFFFFFFFFFFFF for r in reqs])
+        return self.pack_step(nd, ids, pos, slots, ctx, tables, cu, max_seqlen, sampling)
 
-    def _broadcast(self, meta: dict | None) -> dict | None:
-        """Driver -> workers. Layout: header[8] then payload."""
+    def _broadcast(self, step: "PackedStep | None") -> "PackedStep | None":
+        """Driver -> workers: header[8], then the packed step buffer exactly as the driver staged it."""
         if self.world == 1:
-            return meta
+            return step
         import torch.distributed as dist
         if self.rank == 0:
-            if meta is None:
-                hdr = torch.tensor([-1, 0, 0, 0, 0, 0, 0, 0], dtype=torch.int64)
-                dist.broadcast(hdr, 0)
+            if step is None:
+                dist.broadcast(torch.tensor([-1, 0, 0, 0, 0, 0, 0, 0], dtype=torch.int64), 0)
                 return None
-            if meta["kind"] == 0:
-                payload = meta["ids"] + meta["pos"] + meta["slots"] + meta["cu"] + meta["last"]
-                hdr = torch.tensor([0, len(meta["ids"]), meta["B"], meta["max_seqlen"], len(payload), 0, 0, 0], dtype=torch.int64)
-            else:
-                mb = max(len(t) for t in meta["tables"])
-                flat = [b for t in meta["tables"] for b in (t + [0] * (mb - len(t)))]
-                payload = meta["ids"] + meta["pos"] + meta["slots"] + meta["ctx"] + flat
-                hdr = torch.tensor([1, len(meta["ids"]), meta["B"], mb, len(payload), 0, 0, 0], dtype=torch.int64)
-            dist.broadcast(hdr, 0)
-            dist.broadcast(torch.tensor(payload, dtype=torch.int64), 0)
-            return meta
+            lay = step.layout
+            dist.broadcast(torch.tensor([0, lay.T, lay.nd, lay.npf, lay.mb, step.max_seqlen, lay.words, 0],
+                                        dtype=torch.int64), 0)
+            dist.broadcast(step.slot[0][:lay.words], 0)
+            return step
         hdr = torch.zeros(8, dtype=torch.int64)
         dist.broadcast(hdr, 0)
-        kind, T, B, x, n = (int(v) for v in hdr[:5])
+        kind, T, nd, npf, mb, max_seqlen, words = (int(x) for x in hdr[:7])
         if kind < 0:
             return None
-        pl = torch.zeros(n, dtype=torch.int64)
-        dist.broadcast(pl, 0)
-        pl = pl.tolist()
-        if kind == 0:
-            return dict(kind=0, ids=pl[:T], pos=pl[T:2 * T], slots=pl[2 * T:3 * T], cu=pl[3 * T:3 * T + B + 1],
-                        last=pl[3 * T + B + 1:], max_seqlen=x, B=B)
-        tables = [pl[4 * B + i * x:4 * B + (i + 1) * x] for i in range(B)]
-        return dict(kind=1, ids=pl[:B], pos=pl[B:2 * B], slots=pl[2 * B:3 * B], ctx=pl[3 * B:4 * B], tables=tables, B=B)
+        lay = StepLayout(T, nd, npf, mb)
+        slot = self._host_buffer("step", words)
+        dist.broadcast(slot[0][:words], 0)
+        return PackedStep(lay, slot, max_seqlen)
 
-    def _run_meta(self, meta: dict) -> torch.Tensor:
-        dev = self.device
-        t64 = lambda x: torch.tensor(x, dtype=torch.int64, device=dev)
-        t32 = lambda x: torch.tensor(x, dtype=torch.int32, device=dev)
-        if meta["kind"] == 0:
-            return self.runner.forward("prefill", t64(meta["ids"]), t32(meta["pos"]), t64(meta["slots"]),
-                                       cu_seqlens=t32(meta["cu"]), max_seqlen=meta["max_seqlen"],
-                                       last_idx=t64(meta["last"]))
-        B = meta["B"]
-        if self.use_graphs:
-            return self._decode_graph(meta)[:B]
-        mb = max(len(t) for t in meta["tables"])
-        tables = torch.zeros(B, mb, dtype=torch.int32)
-        for i, t in enumerate(meta["tables"]):
-            tables[i, :len(t)] = torch.tensor(t, dtype=torch.int32)
-        return self.runner.forward("decode", t64(meta["ids"]), t32(meta["pos"]), t64(meta["slots"]),
-                                   block_tables=tables.to(dev), ctx_lens=t32(meta["ctx"]),
-                                   max_ctx=self.max_model_len)
+    def _run_step(self, step: "PackedStep"):
+        """Run the forward pass of a packed step. Returns (logits [sampled rows, vocab], device views)."""
+        lay = step.layout
+        if lay.npf == 0 and self.use_graphs:
+            return self._decode_graph(step)
+        v = lay.views(self._to_device(step.slot, lay.words), torch)
+        logits = self.runner.forward(v["ids"], v["pos"], v["slots"], num_decode=lay.nd,
+                                     block_tables=v["tables"] if lay.nd else None, ctx_lens=v["ctx"] if lay.nd else None,
+                                     cu_seqlens=v["cu"] if lay.npf else None, max_seqlen=step.max_seqlen,
+                                     last_idx=v["last"] if lay.npf else None, max_ctx=self.max_model_len)
+        return logits, v
 
-    def _decode_graph(self, meta: dict) -> torch.Tensor:
-        B = meta["B"]
+    def _decode_graph(self, step: "PackedStep"):
+        lay = step.layout
+        B = lay.nd
         bucket = next((b for b in _BUCKETS if b >= B), None)
         if bucket is None:
             raise RuntimeError(f"decode batch {B} exceeds the largest CUDA-graph bucket")
         dev, mbs = self.device, self.max_blocks_per_seq
         g = self.graphs.get(bucket)
         if g is None:
-            st = dict(ids=torch.zeros(bucket, dtype=torch.int64, device=dev),
-                      pos=torch.zeros(bucket, dtype=torch.int32, device=dev),
-                      slots=torch.full((bucket,), -1, dtype=torch.int64, device=dev),
-                      ctx=torch.zeros(bucket, dtype=torch.int32, device=dev),
-                      tables=torch.zeros(bucket, mbs, dtype=torch.int32, device=dev))
-            run = lambda: self.runner.forward("decode", st["ids"], st["pos"], st["slots"], block_tables=st["tables"],
-                                              ctx_lens=st["ctx"], max_ctx=self.max_model_len)
+            glay = StepLayout(bucket, bucket, 0, mbs)
+            buf = torch.zeros(glay.words, dtype=torch.int64, device=dev)
+            st = glay.views(buf, torch)
+            st["slots"].fill_(-1)
+            run = lambda: self.runner.forward(st["ids"], st["pos"], st["slots"], num_decode=bucket,
+                                              block_tables=st["tables"], ctx_lens=st["ctx"], max_ctx=self.max_model_len)
             side = torch.cuda.Stream(device=dev)
             side.wait_stream(torch.cuda.current_stream())
             with torch.cuda.stream(side):                 # warm-up outside capture (workspaces, TMA maps)
@@ -191,22 +288,24 @@ class LLMEngine:
             graph = torch.cuda.CUDAGraph()
             with torch.cuda.graph(graph):
                 out = run()
-            g = (graph, st, out)
+            g = (graph, glay, buf, st, out)
             self.graphs[bucket] = g
-        graph, st, out = g
-        # stage the step's inputs (pinned host -> device copies of a few KB)
-        ids = torch.zeros(bucket, dtype=torch.int64); ids[:B] = torch.tensor(meta["ids"], dtype=torch.int64)
-        pos = torch.zeros(bucket, dtype=torch.int32); pos[:B] = torch.tensor(meta["pos"], dtype=torch.int32)
-        slots = torch.full((bucket,), -1, dtype=torch.int64); slots[:B] = torch.tensor(meta["slots"], dtype=torch.int64)
-        ctx = torch.zeros(bucket, dtype=torch.int32); ctx[:B] = torch.tensor(meta["ctx"], dtype=torch.int32)
-        tables = torch.zeros(bucket, mbs, dtype=torch.int32)
-        for i, t in enumerate(meta["tables"]):
-            tables[i, :len(t)] = torch.tensor(t, dtype=torch.int32)
-        st["ids"].copy_(ids, non_blocking=True); st["pos"].copy_(pos, non_blocking=True)
-        st["slots"].copy_(slots, non_blocking=True); st["ctx"].copy_(ctx, non_blocking=True)
-        st["tables"].copy_(tables, non_blocking=True)
+        graph, glay, buf, st, out = g
+        # re-lay the compact step into the graph's fixed layout (pinned), one H2D copy, replay
+        slot = self._host_buffer(("graph", bucket), glay.words)
+        src = lay.views(step.slot[0].numpy(), np)
+        dst = glay.views(slot[0].numpy(), np)
+        for k in ("ids", "pos", "seeds", "topk", "temp", "topp"):
+            dst[k][:B] = src[k]
+        dst["slots"][:B] = src["slots"]
+        dst["slots"][B:] = -1
+        dst["ctx"][:B] = src["ctx"]
+        dst["ctx"][B:] = 0
+        w = min(lay.mb, mbs)
+        dst["tables"][:B, :w] = src["tables"][:, :w]
+        self._to_device(slot, glay.tables + (B * mbs + 1) // 2, buf)
         graph.replay()
-        return out
+        return out[:B], {k: t[:B] for k, t in st.items() if k in ("temp", "topk", "topp", "seeds")}
 
     def step(self) -> list[StepOutput]:
         """Driver: schedule, run one model step on all ranks, sample, update requests."""
@@ -214,20 +313,12 @@ class LLMEngine:
         if batch is None:
             return []
         t0 = time.perf_counter()
-        meta = self._meta_from_batch(batch)
-        self._broadcast(meta)
-        logits = self._run_meta(meta)
+        packed = self._pack_batch(batch)
+        self._broadcast(packed)
+        logits, v = self._run_step(packed)
         reqs = batch.requests
-        dev = self.device
-        temp = torch.tensor([r.params.temperature for r in reqs], dtype=torch.float32, device=dev)
-        topk = torch.tensor([r.params.top_k for r in reqs], dtype=torch.int32, device=dev)
-        topp = torch.tensor([r.params.top_p for r in reqs], dtype=torch.float32, device=dev)
-        # random stream keyed by (request seed, index of the token being generated): same seed => same text,
-        # whatever else the engine is doing
-        seeds = torch.tensor([(r.seed * 1000003 + len(r.output_ids)) & 0x7FFFFFFFFFFFFFFF for r in reqs],
-                             dtype=torch.int64, device=dev)
         want_lp = any(r.params.logprobs is not None for r in reqs)
-        toks, lps = S.sample(logits, temp, topk, topp, seeds, step=0, want_logprob=want_lp)
+        toks, lps = S.sample(logits, v["temp"], v["topk"], v["topp"], v["seeds"], step=0, want_logprob=want_lp)
         toks = toks.tolist()
         lps = lps.tolist() if lps is not None else None
         self.step_count += 1
@@ -255,14 +346,11 @@ class LLMEngine:
                 self.sched.finish(r, reason)
             outs.append(StepOutput(r.request_id, [tok], reason is not None, reason, [lps[i]] if lps else None))
         dt = time.perf_counter() - t0
-        if batch.kind == "prefill":
-            self.stats["prefill_steps"] += 1
-            self.stats["prompt_tokens"] += len(meta["ids"])
-            self.stats["prefill_time"] += dt
-        else:
-            self.stats["decode_steps"] += 1
-            self.stats["decode_time"] += dt
-        self.stats["generated_tokens"] += len(reqs)
+        st = self.stats
+        st[batch.kind + "_steps"] += 1
+        st[batch.kind + "_time"] += dt
+        st["prompt_tokens"] += packed.layout.T - batch.num_decode
+        st["generated_tokens"] += len(reqs)
         return outs
 
     def shutdown_workers(self) -> None:
@@ -273,10 +361,10 @@ class LLMEngine:
         """TP ranks > 0: execute the steps the driver broadcasts until it sends the stop header."""
         assert self.rank != 0
         while True:
-            meta = self._broadcast(None)
-            if meta is None:
+            step = self._broadcast(None)
+            if step is None:
                 return
-            self._run_meta(meta)
+            self._run_step(step)
 
     # ---- text helpers / offline API ---------------------------------------------------------------
     def text_delta(self, request_id: str, final: bool = False) -> str:

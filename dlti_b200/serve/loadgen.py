@@ -103,3 +103,33 @@ async def sweep(base_url, model, concurrencies, requests_per_level=None, **kw):
         out.append(await run_load(base_url, model, c, n, **kw))
         print(json.dumps(out[-1]), flush=True)
     return out
+
+
+def main(argv=None) -> int:
+    """`python -m dlti_b200.serve.loadgen --url http://127.0.0.1:8000 --model llama2-7b --concurrency 1,16,64`:
+    the load generator as its own process (a client that shares the server's interpreter would compete with the
+    engine thread for the GIL and distort the latencies it measures)."""
+    import argparse
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--url", required=True)
+    ap.add_argument("--model", required=True)
+    ap.add_argument("--concurrency", default="1,8,32,64")
+    ap.add_argument("--requests_per_level", type=int, default=None)
+    ap.add_argument("--input_len", type=int, default=512)
+    ap.add_argument("--output_len", type=int, default=128)
+    ap.add_argument("--vocab", type=int, default=32000)
+    ap.add_argument("--seed", type=int, default=0)
+    ap.add_argument("--extra", type=str, default=None, help="JSON object merged into every request body")
+    ap.add_argument("--out", type=str, default=None)
+    a = ap.parse_args(argv)
+    res = asyncio.run(sweep(a.url, a.model, [int(x) for x in a.concurrency.split(",")], a.requests_per_level,
+                            input_len=a.input_len, output_len=a.output_len, vocab=a.vocab, seed=a.seed,
+                            extra=json.loads(a.extra) if a.extra else None))
+    if a.out:
+        with open(a.out, "w") as f:
+            json.dump(res, f, indent=1)
+    return 0
+
+
+if __name__ == "__main__":
+    raise SystemExit(main())

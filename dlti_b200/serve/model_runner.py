@@ -10,12 +10,14 @@ one kernel sums the slots in rank order, adds the residual and applies RMSNorm (
 K11 is implicit: every rank ends up with the full normalised activations); on the "nccl" backend it is
 NCCL all-reduce + the fused add+norm kernel.
 
-Prefill uses the varlen tcgen05 flash-attention kernel on the packed prompts; decode uses the paged-KV
-split-KV kernel. RoPE and the KV-cache write are one kernel.
+A step's token rows are [decode rows | prompt rows] (either part may be empty): the GEMMs, norms and the
+RoPE + KV-cache-write kernel run over all rows at once, the decode rows go through the paged-KV split-KV
+attention kernel and the packed prompts through the varlen tcgen05 flash-attention kernel.
 """
 from __future__ import annotations
 
 import math
+import os
 
 import torch
 
@@ -23,8 +25,11 @@ from ..models.config import LlamaConfig
 from ..ops import attention as A
 from ..ops import elementwise as E
 from ..ops import serving as S
-from ..ops.gemm import gemm, gemm_skinny
+from ..ops.gemm import gemm, gemm_skinny, gemm_skinny_acc
 from .kv_cache import KVCache
+
+
+_FUSE_ACC = os.environ.get("DLTI_DECODE_FUSE_ACC", "1") == "1"    # A/B switch: consume the fp32 accumulators directly
 
 
 class TPContext:
@@ -168,37 +173,62 @@ class ModelRunner:
         self.cos, self.sin = E.rope_tables(cfg.max_position_embeddings, cfg.head_dim, cfg.rope_theta,
                                            weights.embed.device)
         self.device = weights.embed.device
+        if self.device.type == "cuda" and "DLTI_PDL" not in os.environ:
+            # serving weights are static: the decode GEMMs may fetch weight tiles while the previous kernel drains
+            from ..ops import _lib
+            _lib.gpu_lib().dlti_set_pdl(2)
 
     @torch.no_grad()
-    def forward(self, kind: str, input_ids, positions, slots, cu_seqlens=None, max_seqlen=0,
-                block_tables=None, ctx_lens=None, last_idx=None, max_ctx=None) -> torch.Tensor:
-        """kind = "prefill": tokens are whole prompts packed along T (cu_seqlens); "decode": one token
-        per sequence with block_tables / ctx_lens. Returns logits [num_seqs, vocab] (fp of the model)."""
+    def forward(self, input_ids, positions, slots, *, num_decode: int = 0, block_tables=None, ctx_lens=None,
+                cu_seqlens=None, max_seqlen: int = 0, last_idx=None, max_ctx=None) -> torch.Tensor:
+        """One pass over T token rows: the first `num_decode` rows are single new tokens of running
+        sequences (attention over the paged cache via block_tables / ctx_lens), the remaining rows are whole
+        prompts packed back to back (cu_seqlens, relative to the first prompt row; causal attention inside
+        each prompt). Either part may be empty. Every row's rotated K and V are written to the cache at
+        `slots`. Returns logits [rows selected by last_idx (all rows if None), vocab]."""
         cfg, w, tp = self.cfg, self.w, self.tp
         H, KV, hd, eps = w.H, w.KV, cfg.head_dim, cfg.rms_norm_eps
         T = input_ids.numel()
+        nd = int(num_decode)
         residual = E.embedding(input_ids.view(-1), w.embed)                  # [T, d] residual stream
         xn, _, _ = E.rmsnorm_fwd(residual, w.layers[0]["ln1"], eps)
         L = cfg.num_hidden_layers
-        # decode-sized steps stream the weights through the swap-AB split-K kernel
-        mm = gemm_skinny if T <= 256 else (lambda a, b_: gemm(a, b_))
+        # decode-sized steps stream the weights through the swap-AB stream-K kernel; its fp32 accumulator is
+        # consumed directly by the next elementwise op (no stand-alone convert pass)
+        skinny = T <= 256
+        acc_path = skinny and _FUSE_ACC and residual.is_cuda and hd == 128 and residual.dtype != torch.float32
+        mm = gemm_skinny if skinny else (lambda a, b_: gemm(a, b_))
 
         def rowpar(act, wgt):
             return lambda out, push: (gemm(act, wgt, out=out, push=push) if push is not None else mm(act, wgt))
 
+        def row_reduce(act, wgt, norm_w):          # row-parallel GEMM -> (all-reduce) -> residual add -> norm
+            if acc_path and tp.world == 1:
+                return E.acc_add_rmsnorm(gemm_skinny_acc(act, wgt), residual, norm_w, eps)
+            return tp.reduce_add_norm(rowpar(act, wgt), T, residual, norm_w, eps)
+
         for li, lw in enumerate(w.layers):
-            qkv = mm(xn, lw["w_qkv"])
-            S.rope_cache_(qkv, positions, self.cos, self.sin, slots, self.kv.k[li], self.kv.v[li], H, KV, hd)
-            if kind == "prefill":
-                attn, _ = A.attention_fwd(qkv, cu_seqlens, max_seqlen, H, KV, hd, self.scale, want_lse=False)
+            if acc_path:
+                qkv = S.acc_rope_cache(gemm_skinny_acc(xn, lw["w_qkv"]), xn.dtype, positions, self.cos, self.sin,
+                                       slots, self.kv.k[li], self.kv.v[li], H, KV, hd)
             else:
+                qkv = mm(xn, lw["w_qkv"])
+                S.rope_cache_(qkv, positions, self.cos, self.sin, slots, self.kv.k[li], self.kv.v[li], H, KV, hd)
+            if nd == 0:
+                attn, _ = A.attention_fwd(qkv, cu_seqlens, max_seqlen, H, KV, hd, self.scale, want_lse=False)
+            elif nd == T:
                 attn = S.paged_decode(qkv, self.kv.k[li], self.kv.v[li], block_tables, ctx_lens, H, KV, hd,
                                       self.scale, max_ctx=max_ctx)
-            xn = tp.reduce_add_norm(rowpar(attn, lw["w_o"]), T, residual, lw["ln2"], eps)
-            gu = mm(xn, lw["w_gu"])
-            h = E.swiglu_fwd(gu)
+            else:
+                attn = torch.empty((T, H * hd), dtype=qkv.dtype, device=qkv.device)
+                S.paged_decode(qkv[:nd], self.kv.k[li], self.kv.v[li], block_tables, ctx_lens, H, KV, hd,
+                               self.scale, out=attn[:nd], max_ctx=max_ctx)
+                A.attention_fwd(qkv[nd:], cu_seqlens, max_seqlen, H, KV, hd, self.scale, want_lse=False,
+                                out=attn[nd:])
+            xn = row_reduce(attn, lw["w_o"], lw["ln2"])
+            h = E.acc_swiglu(gemm_skinny_acc(xn, lw["w_gu"]), xn.dtype) if acc_path else E.swiglu_fwd(mm(xn, lw["w_gu"]))
             nxt = w.layers[li + 1]["ln1"] if li + 1 < L else w.final_norm
-            xn = tp.reduce_add_norm(rowpar(h, lw["w_down"]), T, residual, nxt, eps)
+            xn = row_reduce(h, lw["w_down"], nxt)
         xl = xn if last_idx is None else xn.index_select(0, last_idx)
         logits = (gemm_skinny if xl.shape[0] <= 256 else gemm)(xl, w.lm_head)  # [B, V/tp]
         return tp.all_gather_cols(logits)

@@ -1,10 +1,10 @@
 """Continuous-batching scheduler (call stack §3.4).
 
-Policy (vLLM v0 style, prefill-first): each engine step is either a PREFILL step — admit waiting
-requests FCFS while KV blocks and the token budget allow, whole prompts in one pass — or a DECODE
-step over every running sequence (one new token each). When a decode step cannot get a block for a
-growing sequence, the most recently admitted running request is preempted (blocks freed, re-queued
-at the front; its tokens are recomputed on re-admission).
+Policy: every engine step advances all running sequences by one token (decode rows) and, in the same
+forward pass, admits waiting requests FCFS while KV blocks and the token budget allow (prefill rows,
+whole prompts). `mixed=False` restores the prefill-first policy (a step is either prompts or decode
+rows). When a running sequence cannot get a block to grow, the most recently admitted running request
+is preempted (blocks freed, re-queued at the front; its tokens are recomputed on re-admission).
 """
 from __future__ import annotations
 
@@ -17,14 +17,16 @@ from .params import Request
 
 @dataclass
 class Batch:
-    kind: str                    # "prefill" | "decode"
-    requests: list[Request]
+    kind: str                    # "prefill" | "decode" | "mixed"
+    requests: list[Request]      # decode rows first, then prefill rows
+    num_decode: int = 0
 
 
 class Scheduler:
     def __init__(self, blocks: BlockManager, max_num_seqs: int = 256, max_num_batched_tokens: int = 8192,
-                 max_model_len: int = 4096):
+                 max_model_len: int = 4096, mixed: bool = True):
         self.blocks = blocks
+        self.mixed = mixed           # False = prefill-first steps (no decode rows in a prefill pass)
         self.max_num_seqs = max_num_seqs
         self.max_num_batched_tokens = max_num_batched_tokens
         self.max_model_len = max_model_len
@@ -51,29 +53,13 @@ class Scheduler:
         return bool(self.waiting or self.running)
 
     def schedule(self) -> Batch | None:
-        # ---- prefill step: admit as many waiting prompts as fit ----
-        admitted: list[Request] = []
-        budget = self.max_num_batched_tokens
-        while self.waiting and len(self.running) + len(admitted) < self.max_num_seqs:
-            r = self.waiting[0]
-            n = r.num_tokens                      # prompt (+ already generated tokens if it was preempted)
-            if n > budget and admitted:
-                break
-            if not self.blocks.ensure(r.blocks, n + 1):
-                break
-            self.waiting.popleft()
-            r.status = "running"
-            admitted.append(r)
-            budget -= n
-            if budget <= 0:
-                break
-        if admitted:
-            self.running.extend(admitted)
-            return Batch("prefill", admitted)
-        if not self.running:
-            return None
-        # ---- decode step: every running sequence grows by one token ----
-        while True:
+        """One engine step. The running sequences each grow by one token (decode rows); waiting prompts that
+        fit the remaining token budget and the free KV blocks ride along in the same forward pass (prefill
+        rows), so a new prompt never stalls the sequences that are already generating and the decode rows
+        share the prefill's weight traffic. Batch.requests = decode rows first, then prefill rows."""
+        # ---- decode rows: every running sequence needs room for one more token ----
+        preempted = False
+        while self.running:
             ok = True
             for r in self.running:
                 if not self.blocks.ensure(r.blocks, r.num_tokens + 1):
@@ -86,9 +72,33 @@ class Scheduler:
             victim.status = "waiting"
             self.waiting.appendleft(victim)
             self.num_preemptions += 1
-            if not self.running:
-                return None
-        return Batch("decode", list(self.running))
+            preempted = True
+        decode = list(self.running)
+        # ---- prefill rows: admit waiting prompts FCFS (not in a step that had to preempt) ----
+        admitted: list[Request] = []
+        budget = self.max_num_batched_tokens - len(decode)
+        while self.waiting and not preempted and len(self.running) + len(admitted) < self.max_num_seqs:
+            r = self.waiting[0]
+            n = r.num_tokens                      # prompt (+ already generated tokens if it was preempted)
+            if n > budget and (admitted or decode):
+                break
+            if not self.blocks.ensure(r.blocks, n + 1):
+                break
+            self.waiting.popleft()
+            r.status = "running"
+            admitted.append(r)
+            budget -= n
+            if budget <= 0:
+                break
+        if admitted and decode and not self.mixed:
+            # prefill-first policy (vLLM v0 style): a step is either all prompts or all decode rows
+            self.running.extend(admitted)
+            return Batch("prefill", admitted, 0)
+        self.running.extend(admitted)
+        if not decode and not admitted:
+            return None
+        kind = "mixed" if decode and admitted else ("prefill" if admitted else "decode")
+        return Batch(kind, decode + admitted, len(decode))
 
     def finish(self, req: Request, reason: str) -> None:
         req.status, req.finish_reason = "finished", reason

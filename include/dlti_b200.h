@@ -30,6 +30,13 @@ typedef struct CUstream_st* dlti_stream_t;
 /* ---- runtime ---------------------------------------------------------------------------- */
 int dlti_version(void);
 int dlti_sm_count(void);
+/* Programmatic dependent launch on the decode path (skinny GEMM, dlti_acc_*, paged decode). Level 1 (default):
+ * those kernels start while their predecessor in the stream drains and order all global accesses behind a
+ * dependency wait. Level 2: dlti_gemm_skinny additionally requests its first weight tiles before that wait —
+ * only for weights that no kernel still in flight writes (the serving engine sets this). Level 0 = plain stream
+ * ordering. Environment: DLTI_PDL=0|1|2. */
+void dlti_set_pdl(int level);
+int dlti_get_pdl(void);
 long long dlti_launch_count(void);      /* kernels launched by this library since reset */
 void dlti_reset_launch_count(void);
 const char* dlti_last_error(void);
@@ -178,12 +185,26 @@ int dlti_gemm_swiglu_bwd_2cta(const void* dY, const void* Wdown, const void* GU,
 
 /* ---- Decode-sized GEMM (M <= 256): swap-AB (the weight is the 128-row tensor-core operand), K split
  * over CTAs, fp32 partials reduced with atomics into acc32[M,N] (must be zero on entry);
- * dlti_skinny_finish converts acc32 -> out and re-zeroes it. Replaces the cuBLAS GEMV/GEMM calls of the
- * vLLM decode path. */
+ * dlti_skinny_finish converts acc32 -> out and re-zeroes it. split_k: 0 = stream-K (the (tile, K block)
+ * space cut into equal ranges per CTA; default), n > 0 = n tile-major splits, < 0 = automatic tile-major
+ * split. Replaces the cuBLAS GEMV/GEMM calls of the vLLM decode path. */
 int dlti_gemm_skinny(const void* X, const void* W, float* acc32, int M, int N, int K, long long ldx,
                      long long ldw, int in_dtype, int split_k, dlti_stream_t stream);
 int dlti_skinny_finish(float* acc32, void* out, long long rows, int cols, long long out_stride, int dtype,
                        dlti_stream_t stream);
+
+/* Consumers of acc32 that replace dlti_skinny_finish + the next elementwise op of a decode step (each value
+ * is rounded to `dtype` first, so results equal finish -> op bit for bit; acc32 is zero on return):
+ *   residual += acc ; y = RMSNorm(residual) * w          (o_proj / down_proj; vLLM fused_add_rms_norm, S7/S9)
+ *   h = silu(acc[:, :ff]) * acc[:, ff:]                  (gate_up; vLLM silu_and_mul, S8)
+ *   qkv = rope(acc) + k/v rows into the paged cache      (qkv_proj; vLLM rotary_embedding + reshape_and_cache, S4) */
+int dlti_acc_add_rmsnorm(float* acc32, void* residual_inout, const void* w, void* y, long long rows, int d,
+                         float eps, int dtype, dlti_stream_t stream);
+int dlti_acc_swiglu(float* acc32, void* h, long long rows, int ff, long long h_stride, int dtype,
+                    dlti_stream_t stream);
+int dlti_acc_rope_cache(float* acc32, void* qkv, const int* pos, const float* cos_t, const float* sin_t,
+                        const long long* slot_mapping, void* k_cache, void* v_cache, long long tokens, int H,
+                        int KV, int hd, long long row_stride, int dtype, dlti_stream_t stream);
 
 /* ---- Peer memory plumbing (symmetric arena fallbacks): CUDA IPC handle export/open/close and the
  * base/size of the allocation that contains a pointer. */

@@ -21,20 +21,19 @@ wbytes = sum(t.numel() * t.element_size() for l in eng.w.layers for t in l.value
 rows = []
 for B in [int(x) for x in a.batches.split(",")]:
     nblk = -(-(a.ctx + 1) // bs)
-    meta = dict(kind=1, B=B, ids=[5] * B, pos=[a.ctx] * B, ctx=[a.ctx + 1] * B,
-                slots=[(i * nblk + a.ctx // bs) * bs + a.ctx % bs for i in range(B)],
-                tables=[list(range(i * nblk, (i + 1) * nblk)) for i in range(B)])
-    if info.rank == 0: eng._broadcast(meta)
+    mk = lambda: eng.pack_step(B, [5] * B, [a.ctx] * B, [(i * nblk + a.ctx // bs) * bs + a.ctx % bs for i in range(B)],
+                               [a.ctx + 1] * B, [list(range(i * nblk, (i + 1) * nblk)) for i in range(B)], [], 0,
+                               ([0.0] * B, [0] * B, [1.0] * B, [0] * B))
+    if info.rank == 0: meta = eng._broadcast(mk())
     else: meta = eng._broadcast(None)
-    for _ in range(3): eng._run_meta(meta)
+    for _ in range(3): eng._run_step(meta)
     torch.cuda.synchronize()
     s, e = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     s.record()
     for _ in range(a.iters):
-        if info.world_size > 1:
-            if info.rank == 0: eng._broadcast(meta)
-            else: eng._broadcast(None)
-        eng._run_meta(meta)
+        if info.rank == 0: meta = eng._broadcast(mk())
+        else: meta = eng._broadcast(None)
+        eng._run_step(meta)
     e.record(); torch.cuda.synchronize()
     ms = s.elapsed_time(e) / a.iters
     kvb = 2 * cfg.num_hidden_layers * (a.ctx + 1) * eng.w.KV * cfg.head_dim * 2 * B

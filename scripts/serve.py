@@ -48,7 +48,7 @@ def build_engine(a):
     eng = LLMEngine(cfg, w, tp, tok, info=info, block_size=a.block_size, num_blocks=a.num_blocks,
                     gpu_memory_utilization=a.gpu_memory_utilization, max_num_seqs=a.max_num_seqs,
                     max_num_batched_tokens=a.max_num_batched_tokens, max_model_len=a.max_model_len,
-                    use_cuda_graphs=not a.enforce_eager)
+                    use_cuda_graphs=not a.enforce_eager, mixed_batches=not a.no_mixed_batches)
     return info, cfg, eng
 
 
@@ -69,6 +69,10 @@ def add_args(ap):
     ap.add_argument("--max_num_batched_tokens", type=int, default=8192)
     ap.add_argument("--max_model_len", type=int, default=None)
     ap.add_argument("--enforce_eager", action="store_true", help="disable CUDA-graph decode")
+    ap.add_argument("--no_mixed_batches", action="store_true",
+                    help="prefill-first steps: never put decode rows and prompt rows in one forward pass")
+    ap.add_argument("--inprocess_frontend", action="store_true",
+                    help="run the HTTP server as a thread of the engine process instead of a process of its own")
     ap.add_argument("--seed", type=int, default=0)
     ap.add_argument("--served_model_name", type=str, default=None)
 
@@ -81,13 +85,24 @@ def main():
     if info.rank != 0:
         eng.worker_loop()
         return
+    name = a.served_model_name or a.model or a.model_config or cfg.name
+    print(f"serving {name} (tp={info.world_size}) on http://{a.host}:{a.port}", flush=True)
+    if not a.inprocess_frontend:
+        # HTTP server in its own process; this process (which owns the GPU) only runs the engine loop
+        from dlti_b200.serve.api_server import engine_process_loop, start_frontend_process
+        proc, conn = start_frontend_process(eng, a.host, a.port, name)
+        try:
+            engine_process_loop(eng, conn, should_stop=lambda: not proc.is_alive())
+        except KeyboardInterrupt:
+            eng.shutdown_workers()
+        finally:
+            proc.terminate()
+        return
     import uvicorn
 
     from dlti_b200.serve.api_server import AsyncEngine, build_app
     aeng = AsyncEngine(eng)
     aeng.start()
-    name = a.served_model_name or a.model or a.model_config or cfg.name
-    print(f"serving {name} (tp={info.world_size}) on http://{a.host}:{a.port}", flush=True)
     try:
         uvicorn.run(build_app(aeng, name), host=a.host, port=a.port, log_level="warning")
     finally:

@@ -92,18 +92,66 @@ def test_gemm_fp32_out_and_strided():
     assert cbuf[:, :128].abs().max().item() == 0 and cbuf[:, 768:].abs().max().item() == 0
 
 
+@pytest.mark.parametrize("split", [0, -1, 3])          # stream-K (default) / automatic tile-major split / fixed split
 @pytest.mark.parametrize("M,N,K", [(1, 4096, 4096), (64, 12288, 4096), (17, 4096, 11008), (128, 22016, 4096),
-                                   (200, 1536, 512)])
-def test_gemm_skinny_decode(M, N, K):
-    """Swap-AB split-K decode GEMM (+ finish kernel) vs the oracle; workspace must come back zeroed."""
+                                   (200, 1536, 512), (3, 1000, 320), (33, 32000, 4096), (256, 128, 64)])
+def test_gemm_skinny_decode(M, N, K, split):
+    """Swap-AB decode GEMM (+ finish kernel) vs the oracle in every work decomposition; the workspace must
+    come back zeroed."""
     from dlti_b200.ops.gemm import _skinny_ws, gemm_skinny
     torch.manual_seed(5)
     x = torch.randn(M, K, device="cuda", dtype=torch.bfloat16)
     w = torch.randn(N, K, device="cuda", dtype=torch.bfloat16)
     for _ in range(2):
-        y = gemm_skinny(x, w)
+        y = gemm_skinny(x, w, split_k=split)
         _check(y, gemm_ref(x, w, out_dtype=torch.float32))
     assert _skinny_ws["cuda:0"][: M * N].abs().max().item() == 0.0
+
+
+def test_skinny_accumulator_consumers_match_finish_then_op():
+    """dlti_acc_add_rmsnorm / dlti_acc_swiglu / dlti_acc_rope_cache read the fp32 accumulator of the decode
+    GEMM directly. They must equal (bit for bit) finish -> rmsnorm(residual) / swiglu / rope+cache-write, agree
+    with the fp32 oracles, and leave the accumulator zeroed. (One K split per tile: the default stream-K
+    decomposition adds partial sums with atomics, so two runs of the same GEMM may differ in the last bit.)"""
+    from dlti_b200.ops import elementwise as E
+    from dlti_b200.ops import serving as S
+    from dlti_b200.ops.gemm import _skinny_ws, gemm_skinny, gemm_skinny_acc
+    torch.manual_seed(11)
+    dt = torch.bfloat16
+    M, d, ff, H, KV, hd = 19, 512, 1408, 4, 2, 128
+    x = torch.randn(M, d, device="cuda", dtype=dt)
+    # o_proj/down_proj -> add + norm
+    w_o = torch.randn(d, d, device="cuda", dtype=dt) * 0.05
+    nw = (1 + 0.1 * torch.randn(d, device="cuda")).to(dt)
+    res0 = torch.randn(M, d, device="cuda", dtype=dt)
+    res_a, res_b = res0.clone(), res0.clone()
+    y_ref, _, _ = E.rmsnorm_fwd(gemm_skinny(x, w_o, split_k=1), nw, 1e-5, residual=res_a)
+    y = E.acc_add_rmsnorm(gemm_skinny_acc(x, w_o, split_k=1), res_b, nw, 1e-5)
+    assert torch.equal(y, y_ref) and torch.equal(res_a, res_b)
+    part = gemm_ref(x, w_o, out_dtype=torch.float32)
+    yo, _, _ = E.rmsnorm_fwd_ref(part.to(dt).cpu(), nw.cpu(), 1e-5, residual=res0.cpu().clone())
+    _check(y, yo.float().cuda(), 3e-2)
+    # gate_up -> swiglu
+    w_gu = torch.randn(2 * ff, d, device="cuda", dtype=dt) * 0.05
+    h_ref = E.swiglu_fwd(gemm_skinny(x, w_gu, split_k=1))
+    h = E.acc_swiglu(gemm_skinny_acc(x, w_gu, split_k=1), dt)
+    assert torch.equal(h, h_ref)
+    _check(h, E.swiglu_fwd_ref(gemm_ref(x, w_gu, out_dtype=torch.float32).to(dt)).float(), 3e-2)
+    # qkv -> rope + paged cache write
+    W = (H + 2 * KV) * hd
+    w_qkv = torch.randn(W, d, device="cuda", dtype=dt) * 0.05
+    cos, sin = E.rope_tables(512, hd, 1e4, "cuda")
+    pos = torch.randint(0, 512, (M,), device="cuda", dtype=torch.int32)
+    slots = torch.randperm(64 * 16, device="cuda")[:M].to(torch.int64)
+    slots[3] = -1
+    kc_a = torch.zeros(64, 16, KV, hd, device="cuda", dtype=dt)
+    vc_a, kc_b, vc_b = torch.zeros_like(kc_a), torch.zeros_like(kc_a), torch.zeros_like(kc_a)
+    q_ref = gemm_skinny(x, w_qkv, split_k=1)
+    S.rope_cache_(q_ref, pos, cos, sin, slots, kc_a, vc_a, H, KV, hd)
+    q = S.acc_rope_cache(gemm_skinny_acc(x, w_qkv, split_k=1), dt, pos, cos, sin, slots, kc_b, vc_b, H, KV, hd)
+    assert torch.equal(q, q_ref) and torch.equal(kc_a, kc_b) and torch.equal(vc_a, vc_b)
+    assert kc_b.abs().sum().item() > 0 and vc_b.abs().sum().item() > 0
+    assert _skinny_ws["cuda:0"][: M * max(W, 2 * ff)].abs().max().item() == 0.0
 
 
 @pytest.mark.parametrize("dtype", [torch.bfloat16, torch.float16])

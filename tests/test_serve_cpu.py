@@ -81,6 +81,47 @@ def test_engine_preemption_is_transparent():
         assert o["token_ids"] == naive_greedy(cfg, full, p, 12)
 
 
+@pytest.mark.parametrize("mixed", [True, False])
+def test_staggered_arrivals_mixed_batches(mixed):
+    """Prompts that arrive while other sequences are generating join the running step (mixed=True: decode rows
+    and prompt rows in one forward pass; False: prefill-first steps). Tokens match the naive oracle either way."""
+    cfg, full, eng = make_engine(mixed_batches=mixed)
+    sp = SamplingParams(max_tokens=10, temperature=0.0, ignore_eos=True)
+    prompts = [[1, 40, 41, 42, 43, 44], [1] + list(range(100, 130)), [1, 7, 8], [1] + list(range(60, 81)), [1, 9]]
+    arrive = {0: [0], 2: [1, 2], 3: [3], 7: [4]}                 # engine step -> prompts that arrive before it
+    rids, kinds, step = {}, [], 0
+    while step < 4 or eng.has_unfinished():
+        for i in arrive.get(step, []):
+            rids[i] = eng.add_request(prompts[i], SamplingParams(**vars(sp)))
+        before = dict(eng.stats)
+        eng.step()
+        kinds += [k for k in ("prefill", "decode", "mixed") if eng.stats[k + "_steps"] > before[k + "_steps"]]
+        step += 1
+    assert ("mixed" in kinds) == mixed and kinds[0] == "prefill"
+    if mixed:
+        assert kinds.count("mixed") == 3 and "prefill" not in kinds[1:]
+    for i, p in enumerate(prompts):
+        assert eng.requests[rids[i]].output_ids == naive_greedy(cfg, full, p, 10), i
+    assert eng.blocks.num_free == eng.blocks.num_blocks
+
+
+def test_step_layout_roundtrip():
+    import numpy as np
+    from dlti_b200.serve.engine import StepLayout
+    lay = StepLayout(T=11, nd=3, npf=2, mb=8)
+    buf = np.zeros(lay.words, dtype=np.int64)
+    v = lay.views(buf, np)
+    assert {k: len(a) for k, a in v.items() if k != "tables"} == dict(ids=11, slots=11, last=5, seeds=5, pos=11, ctx=3,
+                                                                       cu=3, topk=5, temp=5, topp=5)
+    assert v["tables"].shape == (3, 8) and v["temp"].dtype == np.float32 and v["pos"].dtype == np.int32
+    for i, (k, a) in enumerate(v.items()):                       # sections do not overlap
+        a[...] = i + 1
+    for i, (k, a) in enumerate(v.items()):
+        assert (a == i + 1).all(), k
+    t = lay.views(torch.from_numpy(buf), torch)
+    assert t["tables"].shape == (3, 8) and int(t["cu"][0]) == v["cu"][0] and t["topp"].dtype == torch.float32
+
+
 def test_sampling_params_and_stop():
     cfg, full, eng = make_engine()
     o = eng.generate([[1, 50, 51]], SamplingParams(max_tokens=8, temperature=0.9, top_k=5, seed=7, ignore_eos=True))[0]
@@ -137,3 +178,62 @@ def test_openai_http_surface():
     finally:
         aeng.stop = True
         aeng.thread.join(timeout=5)
+
+
+def test_two_process_frontend():
+    """HTTP front-end in its own process, engine loop here, one pipe message per engine step: same answers as the
+    in-process server, streaming included; the front-end's /metrics reflects the engine's counters."""
+    pytest.importorskip("fastapi")
+    import socket
+    import threading
+    import time
+    import urllib.request
+
+    from dlti_b200.serve.api_server import engine_process_loop, start_frontend_process
+
+    cfg, full, eng = make_engine()
+    with socket.socket() as so:
+        so.bind(("127.0.0.1", 0))
+        port = so.getsockname()[1]
+    proc, conn = start_frontend_process(eng, "127.0.0.1", port, "tiny")
+    stop = threading.Event()
+    th = threading.Thread(target=engine_process_loop, args=(eng, conn, stop.is_set), daemon=True)
+    th.start()
+    url = f"http://127.0.0.1:{port}"
+    try:
+        for _ in range(600):
+            try:
+                urllib.request.urlopen(url + "/health", timeout=1)
+                break
+            except Exception:
+                assert proc.is_alive()
+                time.sleep(0.1)
+
+        def post(body):
+            req = urllib.request.Request(url + "/v1/completions", data=json.dumps(body).encode(),
+                                         headers={"Content-Type": "application/json"})
+            return urllib.request.urlopen(req, timeout=60)
+
+        prompt = [1, 40, 41, 42, 43, 44]
+        j = json.loads(post({"prompt": prompt, "max_tokens": 6, "temperature": 0, "ignore_eos": True}).read())
+        assert j["usage"] == {"prompt_tokens": 6, "completion_tokens": 6, "total_tokens": 12}
+        want = ByteTokenizer(cfg.vocab_size).decode(naive_greedy(cfg, full, prompt, 6))
+        assert j["choices"][0]["text"] == want and j["choices"][0]["finish_reason"] == "length"
+        lines = [l.decode().strip() for l in post({"prompt": prompt, "max_tokens": 6, "temperature": 0, "ignore_eos": True,
+                                                   "stream": True}) if l.strip()]
+        assert lines[-1] == "data: [DONE]"
+        chunks = [json.loads(l[6:]) for l in lines[:-1]]
+        assert len(chunks) == 6 and "".join(c["choices"][0]["text"] for c in chunks) == want
+        try:
+            post({"prompt": list(range(3, 400)), "max_tokens": 4})              # longer than max_model_len
+            raise AssertionError("expected HTTP 400")
+        except urllib.error.HTTPError as e:
+            assert e.code == 400
+        m = urllib.request.urlopen(url + "/metrics", timeout=5).read().decode()
+        assert "dlti_generation_tokens_total 12" in m and "dlti_num_requests_running 0" in m
+    finally:
+        stop.set()
+        th.join(timeout=5)
+        proc.terminate()
+        proc.join(timeout=5)
+    assert eng.blocks.num_free == eng.blocks.num_blocks

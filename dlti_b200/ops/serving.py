@@ -139,13 +139,15 @@ def sample_ref(logits, temperature, top_k, top_p, generator=None):
     return greedy, keep
 
 
-def sample(logits, temperature=None, top_k=None, top_p=None, seeds=None, step: int = 0, want_logprob=False):
+def sample(logits, temperature=None, top_k=None, top_p=None, seeds=None, step: int = 0, want_logprob=False,
+           out=None):
     """logits [B, V] -> token ids int64 [B] (+ log-prob at temperature 1). Per-row device tensors:
-    temperature fp32 (<= 0 = greedy), top_k int32 (0 = off), top_p fp32 (1 = off), seeds uint64."""
+    temperature fp32 (<= 0 = greedy), top_k int32 (0 = off), top_p fp32 (1 = off), seeds uint64.
+    out: optional int64 [B] destination for the token ids."""
     if not _lib.use_native(logits):
         lf = logits.float()
         B = lf.shape[0]
-        out = lf.argmax(-1)
+        dst, out = out, lf.argmax(-1)
         if temperature is not None:
             for b in range(B):
                 t = float(temperature[b])
@@ -156,10 +158,15 @@ def sample(logits, temperature=None, top_k=None, top_p=None, seeds=None, step: i
                     g = torch.Generator().manual_seed(int(seeds[b]) * 1000003 + step if seeds is not None else step)
                     out[b] = torch.multinomial(p / p.sum(), 1, generator=g)[0]
         lp = torch.log_softmax(lf, -1).gather(-1, out.unsqueeze(-1)).squeeze(-1) if want_logprob else None
+        if dst is not None:
+            dst.copy_(out)
+            out = dst
         return out, lp
     assert logits.dim() == 2 and logits.stride(1) == 1
     B, V = logits.shape
-    out = torch.empty(B, dtype=torch.int64, device=logits.device)
+    if out is None:
+        out = torch.empty(B, dtype=torch.int64, device=logits.device)
+    assert out.dtype == torch.int64 and out.is_contiguous() and out.numel() == B
     lp = torch.empty(B, dtype=torch.float32, device=logits.device) if want_logprob else None
     f = _lib.fn("dlti_sample", [_V, _L, _I, _I, _V, _V, _V, _V, _U, _V, _V, _I, _V])
     _lib.check(f(_lib.ptr(logits), logits.stride(0), B, V, _lib.ptr(temperature), _lib.ptr(top_k),

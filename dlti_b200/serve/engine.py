@@ -29,16 +29,17 @@ _BUCKETS = [1, 2, 4, 8, 16, 32, 64, 128, 256, 512]
 class StepLayout:
     """Where each per-step array lives inside ONE int64 staging buffer, so a step's metadata reaches the
     device (and the TP workers) as a single copy. T token rows = nd decode rows followed by the rows of npf
-    packed prompts; B = nd + npf rows are sampled; block tables are [nd, mb]. 64-bit sections first, then
+    packed prompts; B = nd + npf rows are sampled; block tables are [nd, mb]; src[t] >= 0 means "the input token
+    of row t is the token sampled at row src[t] of the previous step" (it is still on the device). 64-bit sections first, then
     the 32-bit ones (each padded to a whole word); the tables come last so that a prefix copy carries
     everything but unused table rows."""
     _I64 = ("ids", "slots", "last", "seeds")
-    _I32 = ("pos", "ctx", "cu", "topk", "temp", "topp", "tables")
+    _I32 = ("pos", "src", "ctx", "cu", "topk", "temp", "topp", "tables")
 
     def __init__(self, T: int, nd: int, npf: int, mb: int):
         self.T, self.nd, self.npf, self.mb = T, nd, npf, mb
         B = nd + npf
-        self.n = dict(ids=T, slots=T, last=B, seeds=B, pos=T, ctx=nd, cu=npf + 1 if npf else 0, topk=B, temp=B,
+        self.n = dict(ids=T, slots=T, last=B, seeds=B, pos=T, src=T, ctx=nd, cu=npf + 1 if npf else 0, topk=B, temp=B,
                       topp=B, tables=nd * mb)
         o = 0
         self.off = {}
@@ -65,17 +66,17 @@ class StepLayout:
 
 
 class PackedStep:
-    __slots__ = ("layout", "slot", "max_seqlen")
+    __slots__ = ("layout", "slot", "max_seqlen", "want_lp")
 
     def __init__(self, layout: StepLayout, slot, max_seqlen: int):
-        self.layout, self.slot, self.max_seqlen = layout, slot, max_seqlen
+        self.layout, self.slot, self.max_seqlen, self.want_lp = layout, slot, max_seqlen, False
 
 
 class LLMEngine:
     def __init__(self, cfg: LlamaConfig, weights: TPWeights, tp: TPContext, tokenizer, *, info=None,
                  block_size: int = 16, num_blocks: int | None = None, gpu_memory_utilization: float = 0.85,
                  max_num_seqs: int = 256, max_num_batched_tokens: int = 8192, max_model_len: int | None = None,
-                 use_cuda_graphs: bool = True, mixed_batches: bool = True):
+                 use_cuda_graphs: bool = True, mixed_batches: bool = True, async_scheduling: bool = True):
         self.cfg, self.w, self.tp, self.tokenizer, self.info = cfg, weights, tp, tokenizer, info
         self.device = weights.embed.device
         self.dtype = weights.embed.dtype
@@ -110,6 +111,15 @@ class LLMEngine:
                       "generated_tokens": 0, "prefill_time": 0.0, "decode_time": 0.0, "mixed_time": 0.0}
         self._rings: dict = {}
         self._ring_pos: dict = {}
+        self.async_scheduling = async_scheduling
+        self._inflight: dict | None = None
+        cap = max(1024, max_num_seqs)
+        self._tok_dev = torch.zeros(cap, dtype=torch.int64, device=self.device)      # last step's samples
+        pin = self.device.type == "cuda"
+        self._tok_host = [(torch.zeros(cap, dtype=torch.int64, pin_memory=pin),
+                           torch.zeros(cap, dtype=torch.float32, pin_memory=pin),
+                           torch.cuda.Event() if pin else None) for _ in range(2)]
+        self._parity = 0
         self._arange = np.arange(max(self.max_model_len, block_size) + 1, dtype=np.int64)
 
     # ---- request API (driver) ------------------------------------------------------------------
@@ -134,7 +144,7 @@ class LLMEngine:
             self.detok.pop(request_id, None)
 
     def has_unfinished(self) -> bool:
-        return self.sched.has_work()
+        return self.sched.has_work() or self._inflight is not None
 
     # ---- step ------------------------------------------------------------------------------------
     def _host_buffer(self, key, words: int):
@@ -165,7 +175,8 @@ class LLMEngine:
         slot[1].record()
         return dst
 
-    def pack_step(self, nd: int, ids, pos, slots, ctx, tables, cu, max_seqlen: int, sampling=None) -> "PackedStep":
+    def pack_step(self, nd: int, ids, pos, slots, ctx, tables, cu, max_seqlen: int, sampling=None,
+                  src=None) -> "PackedStep":
         """Lay one step's metadata out in a pinned host buffer (see StepLayout). ids/pos/slots cover all T
         rows (decode rows first); ctx/tables the nd decode rows; cu the packed prompts (relative to row nd);
         sampling = (temperature, top_k, top_p, seeds) per sampled row or None."""
@@ -178,6 +189,9 @@ class LLMEngine:
         v["ids"][:] = ids
         v["pos"][:] = pos
         v["slots"][:] = slots
+        v["src"][:] = -1
+        if src is not None and nd:
+            v["src"][:nd] = src
         if nd:
             v["ctx"][:] = ctx
             tab = v["tables"]
@@ -196,10 +210,15 @@ class LLMEngine:
         bs = self.blocks.block_size
         nd = batch.num_decode
         reqs = batch.requests
-        ids, pos, slots, ctx, tables, cu = [], [], [], [], [], []
+        ids, pos, slots, ctx, tables, cu, src = [], [], [], [], [], [], []
         for r in reqs[:nd]:
-            t = r.num_tokens - 1
-            ids.append((r.output_ids or r.prompt_ids)[-1])
+            t = r.sched_tokens - 1                 # position of the row's input token
+            if r.pending:                          # sampled by the step in flight: fed on the device
+                ids.append(0)
+                src.append(r.row)
+            else:
+                ids.append((r.output_ids or r.prompt_ids)[-1])
+                src.append(-1)
             pos.append(t)
             slots.append(r.blocks[t // bs] * bs + t % bs)
             ctx.append(t + 1)
@@ -224,8 +243,8 @@ class LLMEngine:
                     [r.params.top_p for r in reqs],
                     # random stream keyed by (request seed, index of the token being generated): same seed =>
                     # same text, whatever else the engine is doing
-                    [(r.seed * 1000003 + len(r.output_ids)) & 0x7FFFFFFFFFFFFFFF for r in reqs])
-        return self.pack_step(nd, ids, pos, slots, ctx, tables, cu, max_seqlen, sampling)
+                    [(r.seed * 1000003 + len(r.output_ids) + r.pending) & 0x7FFFFFFFFFFFFFFF for r in reqs])
+        return self.pack_step(nd, ids, pos, slots, ctx, tables, cu, max_seqlen, sampling, src)
 
     def _broadcast(self, step: "PackedStep | None") -> "PackedStep | None":
         """Driver -> workers: header[8], then the packed step buffer exactly as the driver staged it."""
@@ -237,31 +256,50 @@ class LLMEngine:
                 dist.broadcast(torch.tensor([-1, 0, 0, 0, 0, 0, 0, 0], dtype=torch.int64), 0)
                 return None
             lay = step.layout
-            dist.broadcast(torch.tensor([0, lay.T, lay.nd, lay.npf, lay.mb, step.max_seqlen, lay.words, 0],
-                                        dtype=torch.int64), 0)
+            dist.broadcast(torch.tensor([0, lay.T, lay.nd, lay.npf, lay.mb, step.max_seqlen, lay.words,
+                                         int(step.want_lp)], dtype=torch.int64), 0)
             dist.broadcast(step.slot[0][:lay.words], 0)
             return step
         hdr = torch.zeros(8, dtype=torch.int64)
         dist.broadcast(hdr, 0)
-        kind, T, nd, npf, mb, max_seqlen, words = (int(x) for x in hdr[:7])
+        kind, T, nd, npf, mb, max_seqlen, words, want_lp = (int(x) for x in hdr[:8])
         if kind < 0:
             return None
         lay = StepLayout(T, nd, npf, mb)
         slot = self._host_buffer("step", words)
         dist.broadcast(slot[0][:words], 0)
-        return PackedStep(lay, slot, max_seqlen)
+        step = PackedStep(lay, slot, max_seqlen)
+        step.want_lp = bool(want_lp)
+        return step
 
-    def _run_step(self, step: "PackedStep"):
+    def _feed(self, ids: torch.Tensor, src: torch.Tensor) -> torch.Tensor:
+        """Input ids with the rows that continue a sequence of the step in flight taken from its device-side
+        samples (no host round trip between two steps)."""
+        return torch.where(src >= 0, self._tok_dev[src.clamp_min(0).long()], ids)
+
+    def _forward_step(self, step: "PackedStep"):
         """Run the forward pass of a packed step. Returns (logits [sampled rows, vocab], device views)."""
         lay = step.layout
         if lay.npf == 0 and self.use_graphs:
             return self._decode_graph(step)
         v = lay.views(self._to_device(step.slot, lay.words), torch)
-        logits = self.runner.forward(v["ids"], v["pos"], v["slots"], num_decode=lay.nd,
+        logits = self.runner.forward(self._feed(v["ids"], v["src"]), v["pos"], v["slots"], num_decode=lay.nd,
                                      block_tables=v["tables"] if lay.nd else None, ctx_lens=v["ctx"] if lay.nd else None,
                                      cu_seqlens=v["cu"] if lay.npf else None, max_seqlen=step.max_seqlen,
                                      last_idx=v["last"] if lay.npf else None, max_ctx=self.max_model_len)
         return logits, v
+
+    def _run_step(self, step: "PackedStep", want_lp: bool = False):
+        """Forward + sampling on this rank (every TP rank samples the same tokens from the same gathered
+        logits, so each keeps its own device-side copy to feed the next step). Returns (tokens, logprobs) on
+        the device; tokens is a view of the persistent sample buffer."""
+        logits, v = self._forward_step(step)
+        B = logits.shape[0]
+        if B > self._tok_dev.numel():
+            raise RuntimeError(f"{B} sampled rows exceed the sample buffer ({self._tok_dev.numel()})")
+        toks, lps = S.sample(logits, v["temp"], v["topk"], v["topp"], v["seeds"], step=0, want_logprob=want_lp,
+                             out=self._tok_dev[:B])
+        return toks, lps
 
     def _decode_graph(self, step: "PackedStep"):
         lay = step.layout
@@ -276,7 +314,8 @@ class LLMEngine:
             buf = torch.zeros(glay.words, dtype=torch.int64, device=dev)
             st = glay.views(buf, torch)
             st["slots"].fill_(-1)
-            run = lambda: self.runner.forward(st["ids"], st["pos"], st["slots"], num_decode=bucket,
+            st["src"].fill_(-1)
+            run = lambda: self.runner.forward(self._feed(st["ids"], st["src"]), st["pos"], st["slots"], num_decode=bucket,
                                               block_tables=st["tables"], ctx_lens=st["ctx"], max_ctx=self.max_model_len)
             side = torch.cuda.Stream(device=dev)
             side.wait_stream(torch.cuda.current_stream())
@@ -297,6 +336,8 @@ class LLMEngine:
         dst = glay.views(slot[0].numpy(), np)
         for k in ("ids", "pos", "seeds", "topk", "temp", "topp"):
             dst[k][:B] = src[k]
+        dst["src"][:B] = src["src"]
+        dst["src"][B:] = -1
         dst["slots"][:B] = src["slots"]
         dst["slots"][B:] = -1
         dst["ctx"][:B] = src["ctx"]
@@ -308,27 +349,64 @@ class LLMEngine:
         return out[:B], {k: t[:B] for k, t in st.items() if k in ("temp", "topk", "topp", "seeds")}
 
     def step(self) -> list[StepOutput]:
-        """Driver: schedule, run one model step on all ranks, sample, update requests."""
-        batch = self.sched.schedule()
-        if batch is None:
-            return []
+        """Driver: schedule and launch one model step on all ranks, then hand back the results of the step
+        launched by the PREVIOUS call (async_scheduling, the default): while the host reads those tokens,
+        updates the requests and streams text, the GPU is already running the next step, whose decode rows
+        take their input tokens from the device-side samples. The price is one wasted row when a sequence
+        ends on EOS / a stop token (known one step late); ends by length are predicted and cost nothing.
+        With async_scheduling=False the step's own results are returned."""
         t0 = time.perf_counter()
-        packed = self._pack_batch(batch)
-        self._broadcast(packed)
-        logits, v = self._run_step(packed)
+        batch = self.sched.schedule()
+        cur = self._launch(batch) if batch is not None else None
+        if not self.async_scheduling:
+            return self._finalize(cur, t0) if cur is not None else []
+        prev, self._inflight = self._inflight, cur
+        return self._finalize(prev, t0) if prev is not None else []
+
+    def _launch(self, batch: Batch) -> dict:
         reqs = batch.requests
+        packed = self._pack_batch(batch)
         want_lp = any(r.params.logprobs is not None for r in reqs)
-        toks, lps = S.sample(logits, v["temp"], v["topk"], v["topp"], v["seeds"], step=0, want_logprob=want_lp)
-        toks = toks.tolist()
-        lps = lps.tolist() if lps is not None else None
+        packed.want_lp = want_lp
+        self._broadcast(packed)
+        toks, lps = self._run_step(packed, want_lp)
+        B = len(reqs)
+        self._parity ^= 1
+        host = self._tok_host[self._parity]
+        host[0][:B].copy_(toks, non_blocking=True)
+        if lps is not None:
+            host[1][:B].copy_(lps, non_blocking=True)
+        ev = None
+        if self.device.type == "cuda":
+            ev = host[2]
+            ev.record()
+        for i, r in enumerate(reqs):
+            r.pending += 1
+            r.row = i
+        st = self.stats
+        st[batch.kind + "_steps"] += 1
+        st["prompt_tokens"] += packed.layout.T - batch.num_decode
+        return dict(batch=batch, host=host, event=ev, want_lp=lps is not None)
+
+    def _finalize(self, fl: dict, t0: float) -> list[StepOutput]:
+        batch, host = fl["batch"], fl["host"]
+        reqs = batch.requests
+        if fl["event"] is not None:
+            fl["event"].synchronize()
+        toks = host[0][:len(reqs)].tolist()
+        lps = host[1][:len(reqs)].tolist() if fl["want_lp"] else None
         self.step_count += 1
         now = time.time()
         outs = []
         eos = self.tokenizer.eos_token_id
         for i, r in enumerate(reqs):
+            r.pending -= 1
+            if r.status == "finished":           # ended (EOS / stop / abort) after this row had been launched
+                continue
             tok = toks[i]
             r.output_ids.append(tok)
-            if lps is not None:
+            want = lps is not None and r.params.logprobs is not None
+            if want:
                 r.logprobs.append(lps[i])
             if r.first_token_time is None:
                 r.first_token_time = now
@@ -344,13 +422,9 @@ class LLMEngine:
             if reason:
                 r.finish_time = now
                 self.sched.finish(r, reason)
-            outs.append(StepOutput(r.request_id, [tok], reason is not None, reason, [lps[i]] if lps else None))
-        dt = time.perf_counter() - t0
-        st = self.stats
-        st[batch.kind + "_steps"] += 1
-        st[batch.kind + "_time"] += dt
-        st["prompt_tokens"] += packed.layout.T - batch.num_decode
-        st["generated_tokens"] += len(reqs)
+            outs.append(StepOutput(r.request_id, [tok], reason is not None, reason, [lps[i]] if want else None))
+        self.stats[batch.kind + "_time"] += time.perf_counter() - t0
+        self.stats["generated_tokens"] += len(outs)
         return outs
 
     def shutdown_workers(self) -> None:
@@ -364,7 +438,7 @@ class LLMEngine:
             step = self._broadcast(None)
             if step is None:
                 return
-            self._run_step(step)
+            self._run_step(step, step.want_lp)
 
     # ---- text helpers / offline API ---------------------------------------------------------------
     def text_delta(self, request_id: str, final: bool = False) -> str:

@@ -49,10 +49,17 @@ class Request:
     finish_time: float | None = None
     text_emitted: int = 0            # characters already streamed
     seed: int = 0
+    pending: int = 0                 # tokens sampled on the device that the host has not read yet (0..2)
+    row: int = -1                    # row of this request's sample in the most recently launched step
 
     @property
     def num_tokens(self) -> int:
         return len(self.prompt_ids) + len(self.output_ids)
+
+    @property
+    def sched_tokens(self) -> int:
+        """Sequence length as the scheduler must see it: tokens in flight occupy positions and KV slots."""
+        return len(self.prompt_ids) + len(self.output_ids) + self.pending
 
 
 @dataclass

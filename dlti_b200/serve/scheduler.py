@@ -49,6 +49,9 @@ class Scheduler:
                     return True
         return False
 
+    def _at_limit(self, r: Request) -> bool:
+        return (len(r.output_ids) + r.pending >= r.params.max_tokens) or r.sched_tokens >= self.max_model_len
+
     def has_work(self) -> bool:
         return bool(self.waiting or self.running)
 
@@ -58,11 +61,13 @@ class Scheduler:
         rows), so a new prompt never stalls the sequences that are already generating and the decode rows
         share the prefill's weight traffic. Batch.requests = decode rows first, then prefill rows."""
         # ---- decode rows: every running sequence needs room for one more token ----
+        # (a sequence whose tokens in flight already reach its length limit gets no row: it ends as soon as
+        # the host has read them)
         preempted = False
         while self.running:
             ok = True
             for r in self.running:
-                if not self.blocks.ensure(r.blocks, r.num_tokens + 1):
+                if not self._at_limit(r) and not self.blocks.ensure(r.blocks, r.sched_tokens + 1):
                     ok = False
                     break
             if ok:
@@ -73,12 +78,14 @@ class Scheduler:
             self.waiting.appendleft(victim)
             self.num_preemptions += 1
             preempted = True
-        decode = list(self.running)
+        decode = [r for r in self.running if not self._at_limit(r)]
         # ---- prefill rows: admit waiting prompts FCFS (not in a step that had to preempt) ----
         admitted: list[Request] = []
         budget = self.max_num_batched_tokens - len(decode)
         while self.waiting and not preempted and len(self.running) + len(admitted) < self.max_num_seqs:
             r = self.waiting[0]
+            if r.pending:                         # preempted with a sampled token still unread: next step
+                break
             n = r.num_tokens                      # prompt (+ already generated tokens if it was preempted)
             if n > budget and (admitted or decode):
                 break

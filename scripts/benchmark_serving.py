@@ -103,7 +103,7 @@ def main():
         raise SystemExit("load generation failed")
     out = {"model": name, "tp": info.world_size, "backend": a.backend if info.world_size > 1 else "n/a",
            "dtype": a.dtype, "num_kv_blocks": eng.blocks.num_blocks, "cuda_graphs": eng.use_graphs,
-           "frontend": "thread" if a.inprocess_frontend else "process", "mixed_batches": not a.no_mixed_batches,
+           "frontend": "thread" if a.inprocess_frontend else "process", "mixed_batches": not a.no_mixed_batches, "async_scheduling": not a.no_async_scheduling,
            "native_kernel_launches": result["launches"], "engine_stats": result["stats"],
            "preemptions": eng.sched.num_preemptions, "levels": result["levels"]}
     print(json.dumps(out))

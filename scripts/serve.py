@@ -48,7 +48,8 @@ def build_engine(a):
     eng = LLMEngine(cfg, w, tp, tok, info=info, block_size=a.block_size, num_blocks=a.num_blocks,
                     gpu_memory_utilization=a.gpu_memory_utilization, max_num_seqs=a.max_num_seqs,
                     max_num_batched_tokens=a.max_num_batched_tokens, max_model_len=a.max_model_len,
-                    use_cuda_graphs=not a.enforce_eager, mixed_batches=not a.no_mixed_batches)
+                    use_cuda_graphs=not a.enforce_eager, mixed_batches=not a.no_mixed_batches,
+                    async_scheduling=not a.no_async_scheduling)
     return info, cfg, eng
 
 
@@ -71,6 +72,8 @@ def add_args(ap):
     ap.add_argument("--enforce_eager", action="store_true", help="disable CUDA-graph decode")
     ap.add_argument("--no_mixed_batches", action="store_true",
                     help="prefill-first steps: never put decode rows and prompt rows in one forward pass")
+    ap.add_argument("--no_async_scheduling", action="store_true",
+                    help="read each step's tokens on the host before launching the next step")
     ap.add_argument("--inprocess_frontend", action="store_true",
                     help="run the HTTP server as a thread of the engine process instead of a process of its own")
     ap.add_argument("--seed", type=int, default=0)

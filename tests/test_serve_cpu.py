@@ -105,13 +105,48 @@ def test_staggered_arrivals_mixed_batches(mixed):
     assert eng.blocks.num_free == eng.blocks.num_blocks
 
 
+@pytest.mark.parametrize("num_blocks", [64, 4])
+def test_async_scheduling_matches_synchronous(num_blocks):
+    """async_scheduling launches step N+1 before the host has read step N (decode rows are fed from the
+    device-side samples). Text, finish reasons and log-probs must not depend on it: greedy and seeded sampling,
+    ends by stop token (discovered one step late: the extra row is discarded), by length, under preemption
+    (4 blocks) and with requests arriving mid-flight."""
+    def run(async_mode):
+        cfg, full, eng = make_engine(num_blocks=num_blocks, async_scheduling=async_mode)
+        g = naive_greedy(cfg, full, [1, 50, 51], 6)
+        jobs = [([1, 50, 51], SamplingParams(max_tokens=12, temperature=0.0, stop_token_ids=[g[3]])),
+                ([1] + list(range(10, 36)), SamplingParams(max_tokens=14, temperature=0.0, ignore_eos=True, logprobs=1)),
+                ([1] + list(range(7, 20)), SamplingParams(max_tokens=9, temperature=0.8, top_k=6, seed=11, ignore_eos=True)),
+                ([1] + list(range(60, 95)), SamplingParams(max_tokens=10, temperature=0.0, ignore_eos=True)),
+                ([1, 5], SamplingParams(max_tokens=1, temperature=0.0, ignore_eos=True))]
+        arrive = {0: [0, 1, 2], 4: [3, 4]}
+        rids, step, n_out = {}, 0, 0
+        while step < 5 or eng.has_unfinished():
+            for i in arrive.get(step, []):
+                rids[i] = eng.add_request(*jobs[i])
+            n_out += len(eng.step())
+            step += 1
+        res = [(eng.requests[rids[i]].output_ids, eng.requests[rids[i]].finish_reason,
+                [round(x, 4) for x in eng.requests[rids[i]].logprobs]) for i in range(len(jobs))]
+        assert n_out == sum(len(r[0]) for r in res)
+        assert eng.blocks.num_free == eng.blocks.num_blocks and eng._inflight is None
+        assert all(r.pending == 0 for r in eng.requests.values())
+        return res, eng.sched.num_preemptions, g
+
+    sync, _, g = run(False)
+    asyn, preempt, _ = run(True)
+    assert sync == asyn
+    assert sync[0][0] == g[:4] and sync[0][1] == "stop" and sync[4][1] == "length" and len(sync[4][0]) == 1
+    assert len(sync[1][2]) == 14 and (preempt > 0) == (num_blocks == 4)
+
+
 def test_step_layout_roundtrip():
     import numpy as np
     from dlti_b200.serve.engine import StepLayout
     lay = StepLayout(T=11, nd=3, npf=2, mb=8)
     buf = np.zeros(lay.words, dtype=np.int64)
     v = lay.views(buf, np)
-    assert {k: len(a) for k, a in v.items() if k != "tables"} == dict(ids=11, slots=11, last=5, seeds=5, pos=11, ctx=3,
+    assert {k: len(a) for k, a in v.items() if k != "tables"} == dict(ids=11, slots=11, last=5, seeds=5, pos=11, src=11, ctx=3,
                                                                        cu=3, topk=5, temp=5, topp=5)
     assert v["tables"].shape == (3, 8) and v["temp"].dtype == np.float32 and v["pos"].dtype == np.int32
     for i, (k, a) in enumerate(v.items()):                       # sections do not overlap

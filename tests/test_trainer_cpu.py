@@ -150,7 +150,11 @@ def test_fault_injection_fail_fast_and_resume(tmp_path):
     env = dict(os.environ, PYTHONPATH=ROOT, OMP_NUM_THREADS="2")
 
     def launch(out, extra_env):
-        return subprocess.run([sys.executable, "-m", "dlti_b200.launch", "--num_gpus=2", "--master_port=29655",
+        import socket
+        with socket.socket() as so:               # a fresh port per launch: the killed job's port may linger in TIME_WAIT
+            so.bind(("127.0.0.1", 0))
+            port = so.getsockname()[1]
+        return subprocess.run([sys.executable, "-m", "dlti_b200.launch", "--num_gpus=2", f"--master_port={port}",
                                "--no_local_rank", str(script), str(out)], env=dict(env, **extra_env),
                               capture_output=True, text=True, timeout=600, cwd=ROOT)
 

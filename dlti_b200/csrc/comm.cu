@@ -164,12 +164,41 @@ __global__ void __launch_bounds__(256) adamw_push_kernel(Peers masters, float* _
 
 // K10/K11 consumer: residual[row] += sum_{r < world} recv[r][row]  (fp32, fixed rank order => every
 // rank computes bit-identical sums), then y[row] = w * T(residual * rstd). One CTA per token row.
-template <typename T, int VPT>
+//
+// BARRIER = true folds the rank barrier that must separate the pushes from the reduction into this kernel
+// (one launch less per row-parallel GEMM of a latency-bound decode step): CTA 0 tells every peer "my pushes of
+// this round are complete" (it runs after this rank's push GEMM: stream order, or griddep_wait() under PDL),
+// and every CTA waits until all peers have said so. The epoch is a device counter read by all CTAs and bumped
+// by the last CTA to finish, so the launch carries no per-call host value (CUDA-graph replayable); it shares
+// channel and counter with dlti_peer_barrier_auto, whose sequence it continues.
+struct TpBarrier {
+  Peers pads;
+  uint32_t* counter;     // this channel's epoch counter (device)
+  uint32_t* done;        // zero-initialised scratch word: CTAs finished in this launch
+  int* err;
+  int rank, channel;
+};
+
+template <typename T, int VPT, bool BARRIER>
 __global__ void __launch_bounds__(128) tp_reduce_add_norm_kernel(const T* __restrict__ recv, long long slot_stride,
                                                                 int world, T* __restrict__ residual,
                                                                 const T* __restrict__ w, T* __restrict__ y,
-                                                                int d, float eps) {
+                                                                int d, float eps, const TpBarrier tb) {
   __shared__ float red[32];
+  if constexpr (BARRIER) {
+    griddep_wait();
+    griddep_launch();
+    const int t = threadIdx.x;
+    if (t < world) {
+      const uint32_t epoch = *reinterpret_cast<volatile uint32_t*>(tb.counter) + 1u;
+      if (blockIdx.x == 0) {
+        __threadfence_system();
+        st_release_sys_u32(reinterpret_cast<uint32_t*>(tb.pads.p[t]) + tb.channel * MAX_RANKS + tb.rank, epoch);
+      }
+      wait_ge_sys(reinterpret_cast<const uint32_t*>(tb.pads.p[tb.rank]) + tb.channel * MAX_RANKS + t, epoch, tb.err);
+    }
+    __syncthreads();
+  }
   const long long row = blockIdx.x;
   const int nvec = d >> 3;
   float f[VPT][8];
@@ -225,6 +254,86 @@ __global__ void __launch_bounds__(128) tp_reduce_add_norm_kernel(const T* __rest
       reinterpret_cast<int4*>(y + row * d)[v] = ov;
     }
   }
+  if constexpr (BARRIER) {
+    __syncthreads();             // every thread of this CTA has read the counter
+    if (threadIdx.x == 0) {
+      if (atomicAdd(tb.done, 1u) == gridDim.x - 1) {       // last CTA of the launch: next round
+        *tb.done = 0u;
+        __threadfence();
+        atomicAdd(tb.counter, 1u);
+      }
+    }
+  }
+}
+
+// Prefill-sized row-parallel all-reduce as reduce-scatter + all-gather over peer memory. Every rank has
+// written its partial [T, d] into its own symmetric buffer (plain fast GEMM, no scattered peer stores from an
+// epilogue). This kernel owns rows [row_lo, row_lo + gridDim.x): per row it PULLS the partials of all ranks in
+// rank order (coalesced 16-byte peer loads), adds the residual (kept only by the owner rank: the residual
+// stream is row-sharded on this path), normalises and PUSHES the normalised row into every rank's activation
+// buffer (coalesced 16-byte peer stores). Link traffic per rank: 2 * (world-1)/world * T*d elements instead of
+// (world-1) * T*d for the push-everything-to-everyone scheme of the decode path.
+template <typename T, int VPT>
+__global__ void __launch_bounds__(128) tp_pull_reduce_norm_push_kernel(Peers partials, Peers xn_out, int world,
+                                                                      long long row_lo, T* __restrict__ residual,
+                                                                      const T* __restrict__ w, int d, float eps) {
+  __shared__ float red[32];
+  const long long row = row_lo + blockIdx.x;
+  const int nvec = d >> 3;
+  float f[VPT][8];
+  float ss = 0.f;
+#pragma unroll
+  for (int i = 0; i < VPT; ++i) {
+    const int v = threadIdx.x + i * 128;
+    if (v < nvec) {
+      {
+        const int4 rv = reinterpret_cast<const int4*>(residual + row * d)[v];
+        const uint32_t* u = reinterpret_cast<const uint32_t*>(&rv);
+#pragma unroll
+        for (int j = 0; j < 4; ++j) { float2 t = Cvt<T>::unpack2(u[j]); f[i][2 * j] = t.x; f[i][2 * j + 1] = t.y; }
+      }
+      for (int r = 0; r < world; ++r) {
+        const int4 pv = ld_relaxed_sys_v4(reinterpret_cast<const T*>(partials.p[r]) + row * d + v * 8);
+        const uint32_t* u = reinterpret_cast<const uint32_t*>(&pv);
+#pragma unroll
+        for (int j = 0; j < 4; ++j) { float2 t = Cvt<T>::unpack2(u[j]); f[i][2 * j] += t.x; f[i][2 * j + 1] += t.y; }
+      }
+      int4 sv;
+      uint32_t* su = reinterpret_cast<uint32_t*>(&sv);
+#pragma unroll
+      for (int j = 0; j < 4; ++j) su[j] = Cvt<T>::pack2(f[i][2 * j], f[i][2 * j + 1]);
+      reinterpret_cast<int4*>(residual + row * d)[v] = sv;
+#pragma unroll
+      for (int j = 0; j < 4; ++j) { float2 t = Cvt<T>::unpack2(su[j]); f[i][2 * j] = t.x; f[i][2 * j + 1] = t.y; }
+#pragma unroll
+      for (int j = 0; j < 8; ++j) ss += f[i][j] * f[i][j];
+    }
+  }
+  ss = warp_sum(ss);
+  if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = ss;
+  __syncthreads();
+  float tot = (threadIdx.x & 31) < 4 ? red[threadIdx.x & 31] : 0.f;
+  tot = warp_sum(tot);
+  const float rstd = rsqrtf(tot / (float)d + eps);
+#pragma unroll
+  for (int i = 0; i < VPT; ++i) {
+    const int v = threadIdx.x + i * 128;
+    if (v < nvec) {
+      const int4 wv = reinterpret_cast<const int4*>(w)[v];
+      const uint32_t* wu = reinterpret_cast<const uint32_t*>(&wv);
+      int4 ov;
+      uint32_t* ou = reinterpret_cast<uint32_t*>(&ov);
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        float2 wf = Cvt<T>::unpack2(wu[j]);
+        const float a = wf.x * Cvt<T>::to_f(Cvt<T>::from_f(f[i][2 * j] * rstd));
+        const float b = wf.y * Cvt<T>::to_f(Cvt<T>::from_f(f[i][2 * j + 1] * rstd));
+        ou[j] = Cvt<T>::pack2(a, b);
+      }
+      for (int r = 0; r < world; ++r) st_v4(reinterpret_cast<T*>(xn_out.p[r]) + row * d + v * 8, ov);
+    }
+  }
+  __threadfence_system();
 }
 
 int fill(Peers& P, const void* const* ptrs, int world) {
@@ -308,13 +417,23 @@ DLTI_API int dlti_adamw_push(const void* const* masters, float* m, float* v, flo
   return (int)cudaGetLastError();
 }
 
-DLTI_API int dlti_tp_reduce_add_norm(const void* recv, long long slot_stride, int world, void* residual,
-                                     const void* w, void* y, long long rows, int d, float eps, int dtype,
-                                     cudaStream_t st) {
+static int tp_reduce_impl(const void* recv, long long slot_stride, int world, void* residual, const void* w, void* y,
+                          long long rows, int d, float eps, int dtype, const TpBarrier* tb, cudaStream_t st) {
   if (rows <= 0) return 0;
   if (d % 8 || d > 8192 || world < 1) return DLTI_ERR_BAD_ARG;
   const int vpt = (d / 8 + 127) / 128;
-#define TRN(T, V) tp_reduce_add_norm_kernel<T, V><<<(unsigned)rows, 128, 0, st>>>((const T*)recv, slot_stride, world, (T*)residual, (const T*)w, (T*)y, d, eps)
+  const TpBarrier none{};
+#define TRN(T, V)                                                                                                    \
+  do {                                                                                                               \
+    if (tb)                                                                                                          \
+      DLTI_CUDA_CHECK(dlti_launch_pdl(rows, tp_reduce_add_norm_kernel<T, V, true>, dim3((unsigned)rows), dim3(128), 0, \
+                                      st, (const T*)recv, slot_stride, world, (T*)residual, (const T*)w, (T*)y, d,   \
+                                      eps, *tb));                                                                    \
+    else                                                                                                             \
+      tp_reduce_add_norm_kernel<T, V, false><<<(unsigned)rows, 128, 0, st>>>((const T*)recv, slot_stride, world,     \
+                                                                            (T*)residual, (const T*)w, (T*)y, d, eps, \
+                                                                            none);                                   \
+  } while (0)
   if (dtype == DLTI_BF16) {
     if (vpt <= 1) TRN(__nv_bfloat16, 1); else if (vpt <= 2) TRN(__nv_bfloat16, 2); else if (vpt <= 4) TRN(__nv_bfloat16, 4); else TRN(__nv_bfloat16, 8);
   } else if (dtype == DLTI_FP16) {
@@ -323,6 +442,58 @@ DLTI_API int dlti_tp_reduce_add_norm(const void* recv, long long slot_stride, in
     return DLTI_ERR_UNSUPPORTED;
   }
 #undef TRN
+  dlti_count_launch();
+  return (int)cudaGetLastError();
+}
+
+DLTI_API int dlti_tp_reduce_add_norm(const void* recv, long long slot_stride, int world, void* residual,
+                                     const void* w, void* y, long long rows, int d, float eps, int dtype,
+                                     cudaStream_t st) {
+  return tp_reduce_impl(recv, slot_stride, world, residual, w, y, rows, d, eps, dtype, nullptr, st);
+}
+
+// Same reduction with the rank barrier inside the kernel (see TpBarrier): replaces dlti_peer_barrier_auto +
+// dlti_tp_reduce_add_norm. device_counter: the channel's epoch counter; done_scratch: a zero-initialised u32
+// owned by this call site.
+DLTI_API int dlti_tp_barrier_reduce_add_norm(const void* recv, long long slot_stride, int world, void* residual,
+                                             const void* w, void* y, long long rows, int d, float eps, int dtype,
+                                             const void* const* signal_pads, int rank, int channel,
+                                             unsigned int* device_counter, unsigned int* done_scratch,
+                                             int* err_flag, cudaStream_t st) {
+  TpBarrier tb{};
+  int rc = fill(tb.pads, signal_pads, world);
+  if (rc) return rc;
+  if (rank < 0 || rank >= world || !device_counter || !done_scratch) return DLTI_ERR_BAD_ARG;
+  tb.counter = device_counter;
+  tb.done = done_scratch;
+  tb.err = err_flag;
+  tb.rank = rank;
+  tb.channel = channel;
+  return tp_reduce_impl(recv, slot_stride, world, residual, w, y, rows, d, eps, dtype, &tb, st);
+}
+
+// Rows [row_lo, row_lo + rows) of the all-reduce + residual add + RMSNorm of a row-parallel GEMM (see
+// tp_pull_reduce_norm_push_kernel). partial_peers[r] / xn_peers[r]: rank r's symmetric [T, d] partial /
+// activation buffers. Call between two rank barriers (partials complete; activations landed).
+DLTI_API int dlti_tp_pull_reduce_norm_push(const void* const* partial_peers, const void* const* xn_peers, int world,
+                                           long long row_lo, long long rows, void* residual, const void* w, int d,
+                                           float eps, int dtype, cudaStream_t st) {
+  if (rows <= 0) return 0;
+  if (d % 8 || d > 8192) return DLTI_ERR_BAD_ARG;
+  Peers P, X;
+  int rc = fill(P, partial_peers, world);
+  if (rc) return rc;
+  if ((rc = fill(X, xn_peers, world))) return rc;
+  const int vpt = (d / 8 + 127) / 128;
+#define TPR(T, V) tp_pull_reduce_norm_push_kernel<T, V><<<(unsigned)rows, 128, 0, st>>>(P, X, world, row_lo, (T*)residual, (const T*)w, d, eps)
+  if (dtype == DLTI_BF16) {
+    if (vpt <= 1) TPR(__nv_bfloat16, 1); else if (vpt <= 2) TPR(__nv_bfloat16, 2); else if (vpt <= 4) TPR(__nv_bfloat16, 4); else TPR(__nv_bfloat16, 8);
+  } else if (dtype == DLTI_FP16) {
+    if (vpt <= 1) TPR(__half, 1); else if (vpt <= 2) TPR(__half, 2); else if (vpt <= 4) TPR(__half, 4); else TPR(__half, 8);
+  } else {
+    return DLTI_ERR_UNSUPPORTED;
+  }
+#undef TPR
   dlti_count_launch();
   return (int)cudaGetLastError();
 }

@@ -206,7 +206,7 @@ gemm_tcgen05_kernel(const GemmParams p, const __grid_constant__ CUtensorMap tmA,
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = __shfl_sync(0xffffffffu, *tmem_slot_ptr, 0);
-  if constexpr (SK) griddep_launch();       // the consumer of C may be scheduled; it waits for this grid itself
+  if constexpr (SK || PUSH) griddep_launch();   // the consumer of C may be scheduled; it waits for this grid itself
 
   if (warp == 0) {
     // ===================== TMA producer =====================
@@ -237,6 +237,7 @@ gemm_tcgen05_kernel(const GemmParams p, const __grid_constant__ CUtensorMap tmA,
         }
         griddep_wait();
       }
+      if constexpr (PUSH) griddep_wait();   // decode path: A (activations) comes from the kernel before
       int issued = 0;
       for (SegIter<SK> it(p, tiles_mn, nkb_total); it.next(p, tiles_mn, nkb_total);) {
         const int rem = it.rem;
@@ -393,7 +394,7 @@ gemm_tcgen05_kernel(const GemmParams p, const __grid_constant__ CUtensorMap tmA,
     const int quarter = warp & 3;
     int acc = 0;
     uint32_t acc_phase = 0;
-    if constexpr (SK) griddep_wait();       // C is re-zeroed by the predecessor: no red.add before it is done
+    if constexpr (SK || PUSH) griddep_wait();   // SK: C is re-zeroed by the predecessor; PUSH: peers' slots
     for (SegIter<SK> it(p, tiles_mn, nkb_total); it.next(p, tiles_mn, nkb_total);) {
       const int rem = it.rem;
       int n_blk = rem / p.nmb;
@@ -576,8 +577,8 @@ int launch(const GemmParams& p, const CUtensorMap& a, const CUtensorMap& b, cons
                                          C_::SMEM_BYTES));
     configured[dev & 63] = true;
   }
-  if constexpr (SK) {
-    DLTI_CUDA_CHECK(dlti_launch_pdl(p.N, gemm_tcgen05_kernel<BN, A_MN, B_MN, GATHER, PUSH, SK>, dim3(grid),
+  if constexpr (SK || PUSH) {
+    DLTI_CUDA_CHECK(dlti_launch_pdl(SK ? p.N : p.M, gemm_tcgen05_kernel<BN, A_MN, B_MN, GATHER, PUSH, SK>, dim3(grid),
                                     dim3(NUM_THREADS), C_::SMEM_BYTES, stream, p, a, b, a2, b2, bl, gp));
     dlti_count_launch();
     return 0;

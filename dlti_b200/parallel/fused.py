@@ -240,12 +240,40 @@ class FusedComm:
 
 
 def tp_reduce_add_norm(recv: torch.Tensor, T: int, residual: torch.Tensor, w: torch.Tensor, eps: float,
-                       world: int, max_tokens: int) -> torch.Tensor:
+                       world: int, max_tokens: int, barrier=None) -> torch.Tensor:
     """residual[:T] += sum over ranks of recv[r, :T] (fixed order); returns RMSNorm(residual) * w.
-    recv: [world, max_tokens, d] receive slots filled by every rank's GEMM epilogue (K10)."""
+    recv: [world, max_tokens, d] receive slots filled by every rank's GEMM epilogue (K10).
+    barrier = (FusedComm, channel): the kernel itself performs the rank barrier that separates the pushes from
+    the reduction (no separate barrier launch)."""
     d = residual.shape[-1]
     y = torch.empty((T, d), dtype=residual.dtype, device=residual.device)
+    if barrier is not None:
+        fc, channel = barrier
+        if not hasattr(fc, "_dev_epochs"):
+            fc._dev_epochs = torch.zeros(fc.N_CHANNELS, dtype=torch.int32, device=fc.info.device)
+        if not hasattr(fc, "_tp_done"):
+            fc._tp_done = torch.zeros(1, dtype=torch.int32, device=fc.info.device)
+        f = _lib.fn("dlti_tp_barrier_reduce_add_norm", [_V, _L, _I, _V, _V, _V, _L, _I, _F, _I, _V, _I, _I, _V, _V, _V, _V])
+        _lib.check(f(_lib.ptr(recv), max_tokens * d, world, _lib.ptr(residual), _lib.ptr(w), _lib.ptr(y), T, d,
+                     float(eps), _lib.dtype_code(residual.dtype), fc.peer_array(fc.pads), fc.rank, channel,
+                     C.c_void_p(fc._dev_epochs.data_ptr() + 4 * channel), _lib.ptr(fc._tp_done), _lib.ptr(fc.err),
+                     _lib.stream_ptr()), "tp_barrier_reduce_add_norm")
+        return y
     f = _lib.fn("dlti_tp_reduce_add_norm", [_V, _L, _I, _V, _V, _V, _L, _I, _F, _I, _V])
     _lib.check(f(_lib.ptr(recv), max_tokens * d, world, _lib.ptr(residual), _lib.ptr(w), _lib.ptr(y), T, d,
                  float(eps), _lib.dtype_code(residual.dtype), _lib.stream_ptr()), "tp_reduce_add_norm")
     return y
+
+
+def tp_pull_reduce_norm_push(fc, partial: torch.Tensor, xn: torch.Tensor, T: int, residual: torch.Tensor,
+                             w: torch.Tensor, eps: float) -> None:
+    """This rank's share of a prefill-sized row-parallel all-reduce (+ residual add + RMSNorm): rows
+    [rank*ceil(T/world), ...) of sum_r partial_r are reduced by pulling from the peers and the normalised rows
+    are pushed into every rank's `xn`. partial / xn: symmetric [>= T, d] buffers. Barriers are the caller's."""
+    d = residual.shape[-1]
+    per = -(-T // fc.world)
+    lo = min(T, fc.rank * per)
+    rows = min(T, lo + per) - lo
+    f = _lib.fn("dlti_tp_pull_reduce_norm_push", [_V, _V, _I, _L, _L, _V, _V, _I, _F, _I, _V])
+    _lib.check(f(fc.peer_array(partial), fc.peer_array(xn), fc.world, lo, rows, _lib.ptr(residual), _lib.ptr(w), d,
+                 float(eps), _lib.dtype_code(residual.dtype), _lib.stream_ptr()), "tp_pull_reduce_norm_push")

@@ -427,6 +427,27 @@ class LLMEngine:
         self.stats["generated_tokens"] += len(outs)
         return outs
 
+    def warmup(self, max_batch: int | None = None) -> int:
+        """Driver, before serving: run one dummy decode step per CUDA-graph bucket up to max_batch (default
+        max_num_seqs) on all ranks so that every graph is captured (and every workspace sized) before the first
+        request — otherwise the first step at each new batch size pays the capture (hundreds of ms of TTFT).
+        The dummy rows write no KV (slot -1) and their samples are dropped. Returns the number of buckets."""
+        if not self.use_graphs:
+            return 0
+        top = max_batch or self.sched.max_num_seqs
+        n = 0
+        for b in _BUCKETS:
+            step = self.pack_step(b, [0] * b, [0] * b, [-1] * b, [1] * b, [[0]] * b, [], 0,
+                                  ([0.0] * b, [0] * b, [1.0] * b, [0] * b))
+            self._broadcast(step)
+            self._run_step(step)
+            n += 1
+            if b >= top:
+                break
+        if self.device.type == "cuda":
+            torch.cuda.synchronize(self.device)
+        return n
+
     def shutdown_workers(self) -> None:
         if self.world > 1 and self.rank == 0:
             self._broadcast(None)

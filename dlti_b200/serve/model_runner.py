@@ -32,6 +32,10 @@ from .kv_cache import KVCache
 _FUSE_ACC = os.environ.get("DLTI_DECODE_FUSE_ACC", "1") == "1"    # A/B switch: consume the fp32 accumulators directly
 
 
+_TP_LARGE = os.environ.get("DLTI_TP_LARGE_RSAG", "1") == "1"          # prefill-sized steps: reduce-scatter + all-gather
+_FUSE_TP_BARRIER = os.environ.get("DLTI_TP_FUSE_BARRIER", "1") == "1"  # rank barrier inside the reduce+norm kernel
+
+
 class TPContext:
     """Collectives used by the TP forward. world == 1 => no-ops."""
 
@@ -43,10 +47,17 @@ class TPContext:
         self.use_fused = fused is not None and self.world > 1
         if self.use_fused:
             d = cfg.hidden_size
-            # two alternating receive buffers [world, max_tokens, d] in the symmetric arena
-            self.recv = [fused.alloc_symmetric((self.world, max_tokens, d), dtype) for _ in range(2)]
+            # steps of more than SMALL rows (prefill) reduce-scatter + all-gather through one partial and one
+            # activation buffer per rank; smaller steps (decode) push their partial tile to every peer's
+            # receive slots: two alternating buffers [world, rows, d] in the symmetric arena
+            self.large = _TP_LARGE
+            self.small_rows = 256 if self.large else max_tokens
+            self.recv = [fused.alloc_symmetric((self.world, self.small_rows, d), dtype) for _ in range(2)]
             self.flip = 0
             self.max_tokens = max_tokens
+            if self.large:
+                self.partial = fused.alloc_symmetric((max_tokens, d), dtype)
+                self.xn = fused.alloc_symmetric((max_tokens, d), dtype)
 
     def reduce_add_norm(self, partial_fn, T: int, residual, w, eps):
         """partial_fn(out=None|tensor, push=None|spec) runs the row-parallel GEMM. Returns the normalised
@@ -55,13 +66,25 @@ class TPContext:
             part = partial_fn(None, None)
             y, _, _ = E.rmsnorm_fwd(part, w, eps, residual=residual)
             return y
+        if self.use_fused and T > self.small_rows:
+            # reduce-scatter + all-gather over peer memory: partial via the plain (fast) GEMM into this rank's
+            # symmetric buffer | barrier | pull my rows from all ranks, add residual, norm, push to all | barrier
+            from ..parallel.fused import tp_pull_reduce_norm_push
+            assert T <= self.max_tokens
+            partial_fn(self.partial[:T], None)
+            self.fused.barrier_graph_safe(6)
+            tp_pull_reduce_norm_push(self.fused, self.partial, self.xn, T, residual, w, eps)
+            self.fused.barrier_graph_safe(6)
+            return self.xn[:T]
         if self.use_fused:
             from ..parallel.fused import tp_reduce_add_norm
             buf = self.recv[self.flip]
             self.flip ^= 1
-            partial_fn(None, (self.fused.peer_array(buf), buf, self.rank, self.world, self.max_tokens))
+            partial_fn(None, (self.fused.peer_array(buf), buf, self.rank, self.world, self.small_rows))
+            if _FUSE_TP_BARRIER:
+                return tp_reduce_add_norm(buf, T, residual, w, eps, self.world, self.small_rows, barrier=(self.fused, 5))
             self.fused.barrier_graph_safe(5)
-            return tp_reduce_add_norm(buf, T, residual, w, eps, self.world, self.max_tokens)
+            return tp_reduce_add_norm(buf, T, residual, w, eps, self.world, self.small_rows)
         import torch.distributed as dist
         part = partial_fn(None, None)
         dist.all_reduce(part)
@@ -200,7 +223,8 @@ class ModelRunner:
         mm = gemm_skinny if skinny else (lambda a, b_: gemm(a, b_))
 
         def rowpar(act, wgt):
-            return lambda out, push: (gemm(act, wgt, out=out, push=push) if push is not None else mm(act, wgt))
+            return lambda out, push: (gemm(act, wgt, out=out, push=push) if (push is not None or out is not None)
+                                      else mm(act, wgt))
 
         def row_reduce(act, wgt, norm_w):          # row-parallel GEMM -> (all-reduce) -> residual add -> norm
             if acc_path and tp.world == 1:

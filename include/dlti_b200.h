@@ -244,6 +244,21 @@ int dlti_gemm_push(const void* A, const void* B, int M, int N, int K, long long 
 int dlti_tp_reduce_add_norm(const void* recv, long long slot_stride, int world, void* residual,
                             const void* w, void* y, long long rows, int d, float eps, int dtype,
                             dlti_stream_t stream);
+/* K11 with the rank barrier inside the kernel (CTA 0 signals the peers, every CTA waits for all of them; the
+ * epoch is a device counter bumped by the last CTA, so the launch replays from a CUDA graph): replaces
+ * dlti_peer_barrier_auto + dlti_tp_reduce_add_norm on the decode path. done_scratch: zero-initialised u32. */
+int dlti_tp_barrier_reduce_add_norm(const void* recv, long long slot_stride, int world, void* residual,
+                                    const void* w, void* y, long long rows, int d, float eps, int dtype,
+                                    const void* const* signal_pads, int rank, int channel,
+                                    unsigned int* device_counter, unsigned int* done_scratch, int* err_flag,
+                                    dlti_stream_t stream);
+/* Prefill-sized K10/K11: reduce-scatter + all-gather over peer memory. Each rank's partial [T, d] sits in its own
+ * symmetric buffer; this call handles rows [row_lo, row_lo + rows) (the caller's share): pull the rows of all
+ * ranks' partials (rank order), add the residual rows (row-sharded on this path), RMSNorm, push the normalised
+ * rows into every rank's activation buffer. Needs a rank barrier before (partials complete) and after. */
+int dlti_tp_pull_reduce_norm_push(const void* const* partial_peers, const void* const* xn_peers, int world,
+                                  long long row_lo, long long rows, void* residual, const void* w, int d, float eps,
+                                  int dtype, dlti_stream_t stream);
 /* K9: reduce-scatter by pull: part[0:n] += sum over ranks of grads[r][lo:lo+n] (fixed rank order) */
 int dlti_rs_accumulate(const void* const* grads, float* part, long long lo, long long n, int world,
                        dlti_stream_t stream);

@@ -11,6 +11,7 @@ ap = argparse.ArgumentParser(); add_args(ap)
 ap.add_argument("--batches", default="1,8,32,64,128"); ap.add_argument("--ctx", type=int, default=512)
 ap.add_argument("--iters", type=int, default=30)
 a = ap.parse_args()
+a.no_warmup = True          # this script drives the ranks step by step itself
 info, cfg, eng = build_engine(a)
 bs = eng.blocks.block_size
 peaks = {}
@@ -43,4 +44,4 @@ for B in [int(x) for x in a.batches.split(",")]:
     if info.rank == 0: print(json.dumps(rows[-1]), flush=True)
 if info.rank == 0:
     os.makedirs("gpurun_out", exist_ok=True); json.dump(rows, open(f"gpurun_out/decode_bench_tp{info.world_size}.json", "w"), indent=1)
-    eng.shutdown_workers()
+

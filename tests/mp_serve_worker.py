@@ -32,7 +32,9 @@ def run(info, world_tp, backend, fused, graphs):
     w.embed.mul_(4.0); w.lm_head.mul_(4.0)
     eng = LLMEngine(cfg, w, tp, ByteTokenizer(cfg.vocab_size), info=info if world_tp > 1 else None,
                     num_blocks=256, max_model_len=512, use_cuda_graphs=graphs)
-    prompts = [[1] + list(range(40, 40 + n)) for n in (5, 33, 130)]
+    # 469 prompt tokens in the first step: above 256 rows the row-parallel all-reduce takes the reduce-scatter +
+    # all-gather path, the decode steps after it the push path
+    prompts = [[1] + list(range(40, 40 + n)) for n in (5, 33, 130, 297)]
     sp = SamplingParams(max_tokens=16, temperature=0.0, ignore_eos=True)
     if world_tp > 1 and info.rank != 0:
         eng.worker_loop()

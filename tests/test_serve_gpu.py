@@ -60,6 +60,7 @@ def test_mixed_batches_staggered_arrivals():
     """Prompts arriving while others generate ride along with the decode rows (one forward pass with both the
     paged-decode and the varlen prefill attention kernels); tokens agree with the naive re-forward."""
     cfg, full, eng = build(True)
+    assert eng.warmup(4) == 3 and sorted(eng.graphs) == [1, 2, 4]       # graphs captured before the first request
     sp = SamplingParams(max_tokens=20, temperature=0.0, ignore_eos=True)
     prompts = [[1] + list(range(40, 40 + n)) for n in (5, 33, 130, 300, 2)]
     arrive = {0: [0], 2: [1, 2], 5: [3], 9: [4]}

@@ -140,6 +140,30 @@ def test_async_scheduling_matches_synchronous(num_blocks):
     assert len(sync[1][2]) == 14 and (preempt > 0) == (num_blocks == 4)
 
 
+@pytest.mark.parametrize("async_mode", [True, False])
+def test_abort_while_a_step_is_in_flight(async_mode):
+    """A request cancelled between two steps (client went away) may still have a row in the step that is in flight:
+    its sample is dropped, its blocks are returned once, the other sequences are unaffected."""
+    cfg, full, eng = make_engine(async_scheduling=async_mode)
+    sp = SamplingParams(max_tokens=8, temperature=0.0, ignore_eos=True)
+    keep = eng.add_request([1, 40, 41, 42], SamplingParams(**vars(sp)))
+    drop = eng.add_request([1] + list(range(50, 70)), SamplingParams(**vars(sp)))
+    for _ in range(3):
+        eng.step()
+    n_before = len(eng.requests[drop].output_ids)
+    dropped = eng.requests[drop]
+    eng.abort(drop)
+    assert drop not in eng.requests and dropped.finish_reason == "abort"
+    late = eng.add_request([1, 7, 8], SamplingParams(**vars(sp)))          # reuses the freed blocks
+    while eng.has_unfinished():
+        eng.step()
+    assert len(dropped.output_ids) == n_before and dropped.blocks == []
+    assert eng.requests[keep].output_ids == naive_greedy(cfg, full, [1, 40, 41, 42], 8)
+    assert eng.requests[late].output_ids == naive_greedy(cfg, full, [1, 7, 8], 8)
+    assert eng.blocks.num_free == eng.blocks.num_blocks and eng._inflight is None
+    assert len(set(eng.blocks.free)) == eng.blocks.num_blocks             # no block released twice
+
+
 def test_step_layout_roundtrip():
     import numpy as np
     from dlti_b200.serve.engine import StepLayout

@@ -3,9 +3,12 @@ incremental detokenisation (call stack §3.4).
 
 One engine object per rank. Rank 0 is the driver: it owns the scheduler / block manager and, each step,
 broadcasts the step's metadata (one int64 tensor over gloo — a shared-memory-speed control message,
-N10) to the TP workers, which run `worker_loop()` and execute the same forward. Decode steps replay
-CUDA graphs captured per batch-size bucket (S12); the collectives inside are graph-safe (device-side
-barrier epochs).
+N10) to the TP workers, which run `worker_loop()` and execute the same forward and the same sampling.
+A step is one forward pass over [decode rows | prompt rows]; pure-decode steps replay CUDA graphs
+captured per batch-size bucket (S12; the collectives inside are graph-safe: device-side barrier epochs).
+By default steps are pipelined: step N+1 is launched before the host has read step N's tokens, which stay
+on the device and feed the next step's decode rows (`LLMEngine.step`). vLLM counterparts of the pieces:
+scheduler + block manager (SP:vllm/v1/core/sched/scheduler.py), async scheduling, CUDA-graph dispatch.
 """
 from __future__ import annotations
 
@@ -29,10 +32,10 @@ _BUCKETS = [1, 2, 4, 8, 16, 32, 64, 128, 256, 512]
 class StepLayout:
     """Where each per-step array lives inside ONE int64 staging buffer, so a step's metadata reaches the
     device (and the TP workers) as a single copy. T token rows = nd decode rows followed by the rows of npf
-    packed prompts; B = nd + npf rows are sampled; block tables are [nd, mb]; src[t] >= 0 means "the input token
-    of row t is the token sampled at row src[t] of the previous step" (it is still on the device). 64-bit sections first, then
-    the 32-bit ones (each padded to a whole word); the tables come last so that a prefix copy carries
-    everything but unused table rows."""
+    packed prompts; B = nd + npf rows are sampled; block tables are [nd, mb]; src[t] >= 0 means "the input
+    token of row t is the token sampled at row src[t] of the previous step" (it is still on the device).
+    64-bit sections first, then the 32-bit ones (each padded to a whole word); the tables come last so that
+    a prefix copy carries everything but unused table rows."""
     _I64 = ("ids", "slots", "last", "seeds")
     _I32 = ("pos", "src", "ctx", "cu", "topk", "temp", "topp", "tables")
 

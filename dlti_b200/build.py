@@ -83,6 +83,25 @@ def build_gpu(force: bool = False, verbose: bool = False) -> Path:
     return GPU_LIB
 
 
+def build_debug() -> Path:
+    """Debug variant of the GPU library (-DDLTI_DEBUG_CHECKS: signal-pad sequence checks in the peer-memory
+    barriers; see ops/_debug.py for the host-side half). Written next to the product library, never loaded unless
+    DLTI_GPU_LIB points at it."""
+    out = LIBDIR / "variants" / "libdlti_b200_debug.so"
+    objdir = OBJDIR.parent / "obj_debug"
+    objdir.mkdir(parents=True, exist_ok=True)
+    out.parent.mkdir(parents=True, exist_ok=True)
+    objs, jobs = [], []
+    for s in sorted(CSRC.glob("*.cu")):
+        o = objdir / (s.stem + ".o")
+        objs.append(o)
+        jobs.append([NVCC, *NVCC_FLAGS, "-DDLTI_DEBUG_CHECKS", "-c", str(s), "-o", str(o)])
+    with ThreadPoolExecutor(max_workers=min(8, len(jobs))) as ex:
+        list(ex.map(_run, jobs))
+    _run([NVCC, "-shared", "-gencode", "arch=compute_100a,code=sm_100a", "-o", str(out), *map(str, objs), "-lcudart"])
+    return out
+
+
 def build_cpu(force: bool = False) -> Path:
     OBJDIR.mkdir(parents=True, exist_ok=True)
     LIBDIR.mkdir(parents=True, exist_ok=True)
@@ -100,5 +119,8 @@ def build_all(force: bool = False, verbose: bool = False) -> None:
 
 
 if __name__ == "__main__":
+    if "--debug-checks" in sys.argv:
+        print("built:", build_debug())
+        sys.exit(0)
     build_all(force="--force" in sys.argv, verbose="-v" in sys.argv)
     print("built:", GPU_LIB, CPU_LIB if CPU_LIB.exists() else "")

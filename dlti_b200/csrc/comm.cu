@@ -35,6 +35,12 @@ __device__ __forceinline__ bool wait_ge_sys(const uint32_t* flag, uint32_t targe
     }
     __nanosleep(64);
   }
+#ifdef DLTI_DEBUG_CHECKS
+  // Signal-pad sequence check (debug build): every rank runs the same sequence of barriers on a
+  // channel and cannot leave barrier k+1 before this rank has entered it, so a peer's flag may be at `target` or
+  // one ahead — anything else means two code paths share a channel or a rank skipped / repeated a barrier.
+  if (ld_acquire_sys_u32(flag) - target > 1u && err) atomicExch(err, 2);
+#endif
   return true;
 }
 

@@ -13,7 +13,7 @@ import math
 
 import torch
 
-from . import _lib
+from . import _debug, _lib
 
 _V, _I, _L, _F = C.c_void_p, C.c_int, C.c_longlong, C.c_float
 
@@ -83,6 +83,7 @@ def attention_fwd(qkv, cu_seqlens, max_seqlen, H, KV, hd, scale=None, want_lse=T
     """Returns (out [T, H*hd], lse [H, T] fp32 or None). `out`: optional contiguous [T, H*hd] destination
     (e.g. a row slice of a larger buffer)."""
     scale = scale if scale is not None else 1.0 / math.sqrt(hd)
+    _debug.check_cu_seqlens("attention_fwd", cu_seqlens, qkv.shape[0])
     if not _lib.use_native(qkv):
         o, lse = attention_fwd_ref(qkv, cu_seqlens, H, KV, hd, scale)
         if out is not None:

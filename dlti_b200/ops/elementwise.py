@@ -12,7 +12,7 @@ import ctypes as C
 
 import torch
 
-from . import _lib
+from . import _debug, _lib
 from .rng import dropout_ref
 
 _V, _I, _L, _F, _U = C.c_void_p, C.c_int, C.c_longlong, C.c_float, C.c_ulonglong
@@ -224,6 +224,8 @@ def add_dropout(a, b, p, seed, stream):
 # ------------------------------------------------------------------------------------------
 def embedding(ids, table, vocab_start: int = 0):
     """out[t] = table[ids[t] - vocab_start], zero rows for ids outside this vocab shard."""
+    if vocab_start == 0:
+        _debug.check_range("embedding", "ids", ids, 0, table.shape[0])
     if not _lib.use_native(table):
         local = ids - vocab_start
         ok = (local >= 0) & (local < table.shape[0])

@@ -7,7 +7,7 @@ import math
 
 import torch
 
-from . import _lib
+from . import _debug, _lib
 from .elementwise import rope_ref
 
 _V, _I, _L, _F, _U = C.c_void_p, C.c_int, C.c_longlong, C.c_float, C.c_ulonglong
@@ -29,6 +29,8 @@ def rope_cache_ref(qkv, pos, cos_t, sin_t, slots, k_cache, v_cache, H, KV, hd):
 def rope_cache_(qkv, pos, cos_t, sin_t, slots, k_cache, v_cache, H, KV, hd):
     """In place: rotate q,k of every token row; write rotated k and v to the paged cache at `slots`
     (int64 [T], -1 = skip). Caches are [num_blocks, block_size, KV, hd]."""
+    _debug.check_range("rope_cache", "slots", slots, 0, k_cache.shape[0] * k_cache.shape[1], allow=-1)
+    _debug.check_range("rope_cache", "positions", pos, 0, cos_t.shape[0])
     if not _lib.use_native(qkv):
         return rope_cache_ref(qkv, pos, cos_t, sin_t, slots, k_cache, v_cache, H, KV, hd)
     assert qkv.stride(1) == 1 and pos.dtype == torch.int32 and slots.dtype == torch.int64
@@ -44,6 +46,8 @@ def acc_rope_cache(acc, dtype, pos, cos_t, sin_t, slots, k_cache, v_cache, H, KV
     return the 16-bit qkv with q,k rotated; rotated k and v also go to the paged cache at `slots`. Bit-identical
     to skinny_finish + rope_cache_."""
     T, W = acc.shape
+    _debug.check_range("acc_rope_cache", "slots", slots, 0, k_cache.shape[0] * k_cache.shape[1], allow=-1)
+    _debug.check_range("acc_rope_cache", "positions", pos, 0, cos_t.shape[0])
     assert acc.is_cuda and acc.dtype == torch.float32 and acc.is_contiguous() and W == (H + 2 * KV) * hd
     assert pos.dtype == torch.int32 and slots.dtype == torch.int64
     qkv = torch.empty((T, W), dtype=dtype, device=acc.device)
@@ -82,6 +86,7 @@ def paged_decode(q, k_cache, v_cache, block_tables, ctx_lens, H, KV, hd, scale=N
     """q: [B, >= H*hd] (row b = the single new token of sequence b; head h at columns h*hd..).
     Returns out [B, H*hd]."""
     scale = scale if scale is not None else 1.0 / math.sqrt(hd)
+    _debug.check_paged("paged_decode", block_tables, ctx_lens, k_cache.shape[0], k_cache.shape[1])
     if not _lib.use_native(q):
         o = paged_decode_ref(q, k_cache, v_cache, block_tables, ctx_lens, H, KV, hd, scale)
         if out is not None:

@@ -170,7 +170,11 @@ class FusedComm:
         return self._arr(self.peer_ptrs(t))
 
     def check_error(self) -> None:
-        if int(self.err.item()) != 0:
+        code = int(self.err.item())
+        if code == 2:
+            raise RuntimeError("fused backend: signal-pad sequence violation (debug build): a peer's barrier flag ran "
+                               "more than one epoch ahead — two call sites share a channel or a rank skipped a barrier")
+        if code != 0:
             raise RuntimeError("fused backend: a peer did not arrive within the spin-wait timeout")
 
     # ---- primitives --------------------------------------------------------------------------

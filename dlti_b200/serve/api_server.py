@@ -29,6 +29,51 @@ from .engine import LLMEngine
 from .params import SamplingParams
 
 
+# Prometheus histograms (vLLM exposes the same three: time to first token, time per output token, end-to-end
+# request latency). Plain dicts so the two-process front-end can receive them through the pipe.
+_HIST = {"ttft": (0.005, 0.01, 0.02, 0.04, 0.08, 0.16, 0.32, 0.64, 1.28, 2.56, 5.12, 10.0),
+         "tpot": (0.001, 0.002, 0.003, 0.004, 0.006, 0.008, 0.012, 0.016, 0.024, 0.032, 0.064, 0.128),
+         "e2e": (0.05, 0.1, 0.2, 0.4, 0.8, 1.6, 3.2, 6.4, 12.8, 25.6, 51.2, 102.4)}
+_HIST_NAMES = {"ttft": "dlti_time_to_first_token_seconds", "tpot": "dlti_time_per_output_token_seconds",
+               "e2e": "dlti_e2e_request_latency_seconds"}
+
+
+def _new_metrics() -> dict:
+    m = {"requests_total": 0, "tokens_total": 0, "ttft_sum": 0.0, "ttft_count": 0}
+    for k, edges in _HIST.items():
+        m["hist_" + k] = {"counts": [0] * (len(edges) + 1), "sum": 0.0}
+    return m
+
+
+def _observe(metrics: dict, key: str, value: float) -> None:
+    h = metrics["hist_" + key]
+    edges = _HIST[key]
+    i = 0
+    while i < len(edges) and value > edges[i]:
+        i += 1
+    h["counts"][i] += 1
+    h["sum"] += value
+
+
+def _render_histograms(m: dict) -> list[str]:
+    lines = []
+    for key, edges in _HIST.items():
+        h = m.get("hist_" + key)
+        if not h:
+            continue
+        name = _HIST_NAMES[key]
+        lines.append(f"# TYPE {name} histogram")
+        cum = 0
+        for e, c in zip(edges, h["counts"]):
+            cum += c
+            lines.append(f'{name}_bucket{{le="{e}"}} {cum}')
+        cum += h["counts"][-1]
+        lines.append(f'{name}_bucket{{le="+Inf"}} {cum}')
+        lines.append(f"{name}_sum {h['sum']}")
+        lines.append(f"{name}_count {cum}")
+    return lines
+
+
 def _engine_stats(eng: LLMEngine, metrics: dict) -> dict:
     return dict(metrics, running=len(eng.sched.running), waiting=len(eng.sched.waiting),
                 kv_usage=eng.blocks.usage(), preemptions=eng.sched.num_preemptions,
@@ -57,6 +102,11 @@ def _step_items(eng: LLMEngine, metrics: dict) -> list:
         if len(r.output_ids) == 1:
             metrics["ttft_sum"] += time.time() - r.arrival
             metrics["ttft_count"] += 1
+            _observe(metrics, "ttft", time.time() - r.arrival)
+        if out.finished and r.finish_time is not None:
+            _observe(metrics, "e2e", r.finish_time - r.arrival)
+            if len(r.output_ids) > 1 and r.first_token_time is not None:
+                _observe(metrics, "tpot", (r.finish_time - r.first_token_time) / (len(r.output_ids) - 1))
         metrics["tokens_total"] += len(out.new_token_ids)
         delta = eng.text_delta(rid, final=out.finished)
         batch.append((rid, {"text": delta, "token_ids": out.new_token_ids, "finished": out.finished,
@@ -117,7 +167,7 @@ class AsyncEngine(_Streams):
         self.inbox: queue.Queue = queue.Queue()
         self.stop = False
         self.thread = threading.Thread(target=self._loop, daemon=True)
-        self.metrics = {"requests_total": 0, "tokens_total": 0, "ttft_sum": 0.0, "ttft_count": 0}
+        self.metrics = _new_metrics()
 
     def start(self):
         # the engine thread re-acquires the GIL after every device sync; with the default 5 ms switch interval a
@@ -191,7 +241,7 @@ class EngineProxy(_Streams):
 def engine_process_loop(eng: LLMEngine, conn, should_stop=lambda: False) -> None:
     """Engine half of the two-process server (runs in the process that owns the GPU): commands come in and
     per-step outputs go out over `conn`, one message per engine step."""
-    metrics = {"requests_total": 0, "tokens_total": 0, "ttft_sum": 0.0, "ttft_count": 0}
+    metrics = _new_metrics()
     errors: list = []
     try:
         while not should_stop():
@@ -279,6 +329,7 @@ def build_app(aeng: AsyncEngine, model_name: str):
                  f"dlti_time_to_first_token_seconds_sum {m['ttft_sum']}", f"dlti_time_to_first_token_seconds_count {m['ttft_count']}",
                  f"dlti_num_requests_running {m['running']}", f"dlti_num_requests_waiting {m['waiting']}",
                  f"dlti_kv_cache_usage {m['kv_usage']:.4f}", f"dlti_num_preemptions_total {m['preemptions']}"]
+        lines += _render_histograms(m)
         return PlainTextResponse("\n".join(lines) + "\n")
 
     @app.post("/v1/completions")

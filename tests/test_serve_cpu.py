@@ -233,7 +233,13 @@ def test_openai_http_surface():
             e = c.post("/v1/completions", json={"max_tokens": 3})
             assert e.status_code == 400 and e.json()["error"]["type"] == "invalid_request_error"
             assert c.post("/v1/completions", json={"model": "nope", "prompt": "x"}).status_code == 404
-            assert "dlti_generation_tokens_total" in c.get("/metrics").text
+            mt = c.get("/metrics").text
+            assert "dlti_generation_tokens_total" in mt
+            # histograms: every finished request is in the +Inf bucket of the latency histograms
+            import re
+            n_req = int(re.search(r"dlti_requests_total (\d+)", mt).group(1))
+            assert int(re.search(r'dlti_e2e_request_latency_seconds_bucket\{le="\+Inf"\} (\d+)', mt).group(1)) == n_req - 0
+            assert 'dlti_time_to_first_token_seconds_bucket{le="0.005"}' in mt and "dlti_time_per_output_token_seconds_sum" in mt
     finally:
         aeng.stop = True
         aeng.thread.join(timeout=5)
@@ -290,6 +296,7 @@ def test_two_process_frontend():
             assert e.code == 400
         m = urllib.request.urlopen(url + "/metrics", timeout=5).read().decode()
         assert "dlti_generation_tokens_total 12" in m and "dlti_num_requests_running 0" in m
+        assert 'dlti_e2e_request_latency_seconds_bucket{le="+Inf"} 2' in m            # histograms cross the pipe too
     finally:
         stop.set()
         th.join(timeout=5)

@@ -221,3 +221,43 @@ def test_public_header_declares_every_entry_point():
     assert defined, "no entry points found"
     missing = sorted(defined - declared)
     assert not missing, f"undeclared entry points: {missing}"
+
+
+def test_debug_index_checks():
+    """DLTI_DEBUG_CHECKS: the ops that index memory through caller-supplied integers reject bad indices before
+    anything is launched (our stand-in for compute-sanitizer's memcheck on a pool where it cannot run)."""
+    from dlti_b200.ops import _debug
+    from dlti_b200.ops import attention as A
+    from dlti_b200.ops import elementwise as E
+    from dlti_b200.ops import serving as S
+    H = KV = 2
+    hd, bs, nblk = 8, 4, 6
+    cos, sin = E.rope_tables(32, hd, 1e4, "cpu")
+    kc = torch.zeros(nblk, bs, KV, hd)
+    vc = torch.zeros_like(kc)
+    qkv = torch.randn(3, (H + 2 * KV) * hd)
+    pos = torch.tensor([0, 1, 2], dtype=torch.int32)
+    good = torch.tensor([0, 5, -1], dtype=torch.int64)
+    bad = torch.tensor([0, nblk * bs, -1], dtype=torch.int64)
+    tables = torch.tensor([[1, 2, 0], [9, 0, 0]], dtype=torch.int32)
+    table = torch.randn(16, 8)
+    S.rope_cache_(qkv.clone(), pos, cos, sin, bad[:1].repeat(3), kc, vc, H, KV, hd)       # checks are off by default
+    _debug.enable(True)
+    try:
+        S.rope_cache_(qkv.clone(), pos, cos, sin, good, kc, vc, H, KV, hd)
+        with pytest.raises(_debug.DltiIndexError, match=r"slots\[1\] = 24"):
+            S.rope_cache_(qkv.clone(), pos, cos, sin, bad, kc, vc, H, KV, hd)
+        with pytest.raises(_debug.DltiIndexError, match="positions"):
+            S.rope_cache_(qkv.clone(), torch.tensor([0, 1, 32], dtype=torch.int32), cos, sin, good, kc, vc, H, KV, hd)
+        q = torch.randn(2, H * hd)
+        S.paged_decode(q, kc, vc, tables, torch.tensor([5, 0], dtype=torch.int32), H, KV, hd)  # row 1 unused: entry 9 is fine
+        with pytest.raises(_debug.DltiIndexError, match=r"block_tables\[1, 0\] = 9"):
+            S.paged_decode(q, kc, vc, tables, torch.tensor([5, 1], dtype=torch.int32), H, KV, hd)
+        with pytest.raises(_debug.DltiIndexError, match="does not fit"):
+            S.paged_decode(q, kc, vc, tables, torch.tensor([13, 0], dtype=torch.int32), H, KV, hd)
+        with pytest.raises(_debug.DltiIndexError, match="ids"):
+            E.embedding(torch.tensor([0, 16]), table)
+        with pytest.raises(_debug.DltiIndexError, match="cu_seqlens"):
+            A.attention_fwd(qkv, torch.tensor([0, 2, 4], dtype=torch.int32), 2, H, KV, hd)
+    finally:
+        _debug.enable(False)

@@ -125,6 +125,8 @@ class Trainer:
         self.skipped_steps = 0
         self._win_loss, self._win_n = 0.0, 0
         self._step_events: list = []
+        self._phase_events: list = []
+        self.phase_ms: list = []
         self.step_ms: list[float] = []
         self.tokens_seen = 0
         self.timers: dict[str, float] = {}
@@ -179,6 +181,10 @@ class Trainer:
         loss_sum = self.model.forward_backward_multi(devb, gs)
         opt.on_micro_batch_end(is_boundary=True)
         self.tokens_seen += sum(pb.n_tokens for pb in packed)
+        breakdown = timed and self.ds.wall_clock_breakdown
+        if breakdown:                                  # ds_config "wall_clock_breakdown": phase boundary (§5.1)
+            em = torch.cuda.Event(enable_timing=True)
+            em.record()
         if nvtx:
             torch.cuda.nvtx.range_pop()
             torch.cuda.nvtx.range_push(f"step{self.global_step + 1}/optimizer")
@@ -195,6 +201,8 @@ class Trainer:
         if timed:
             e1.record()
             self._step_events.append((e0, e1))
+            if breakdown:
+                self._phase_events.append((e0, em, e1))
         self.last_grad_norm, self.last_skipped = gnorm, skipped
         return loss_sum, n_total
 
@@ -259,6 +267,9 @@ class Trainer:
         for e0, e1 in self._step_events:
             self.step_ms.append(e0.elapsed_time(e1))
         self._step_events = []
+        for e0, em, e1 in self._phase_events:
+            self.phase_ms.append((e0.elapsed_time(em), em.elapsed_time(e1)))
+        self._phase_events = []
 
     def _log(self) -> None:
         loss = float(self._win_loss.item() if torch.is_tensor(self._win_loss) else self._win_loss) / max(1, self._win_n)
@@ -272,8 +283,13 @@ class Trainer:
                 torch.cuda.synchronize()
                 self._drain_events()
                 recent = self.step_ms[-self.args.logging_steps:]
+                ph = self.phase_ms[-self.args.logging_steps:]
+                fb = sum(p[0] for p in ph) / max(1, len(ph))
+                op = sum(p[1] for p in ph) / max(1, len(ph))
                 print(f"[wall_clock_breakdown] step {self.global_step}: device step time "
-                      f"mean {sum(recent) / max(1, len(recent)):.2f} ms", flush=True)
+                      f"mean {sum(recent) / max(1, len(recent)):.2f} ms = forward+backward (weight gathers inside "
+                      f"the GEMMs) {fb:.2f} ms + gradient reduce / clip / AdamW / parameter refresh {op:.2f} ms",
+                      flush=True)
 
     def _final_metrics(self, wall: float) -> dict:
         info = self.info

@@ -1,5 +1,5 @@
-"""OpenAI-compatible HTTP front-end: POST /v1/completions (JSON or SSE
-stream), GET /v1/models, GET /health, GET /metrics (Prometheus text). Schema follows what vLLM serves
+"""OpenAI-compatible HTTP front-end: POST /v1/completions and POST
+/v1/chat/completions (JSON or SSE stream), GET /v1/models, GET /health, GET /metrics (Prometheus text). Schema follows what vLLM serves
 (SP:vllm/entrypoints/openai/completion/protocol.py:42-90,466-545); SSE framing is
 `data: {json}\\n\\n` ... `data: [DONE]\\n\\n`. The reference only declares this capability
 (reference README.md:10,16; requirements.txt:18).
@@ -307,6 +307,43 @@ def _error(message: str, typ: str = "invalid_request_error", code: int = 400):
     return JSONResponse({"error": {"message": message, "type": typ, "param": None, "code": code}}, status_code=code)
 
 
+def llama2_chat_prompt(messages: list[dict]) -> str:
+    """OpenAI `messages` -> Llama-2 chat prompt text (the format the reference trains on:
+    `<s>[INST] question [/INST] answer</s>`, reference scripts/prepare_dataset.py:24-32, with Meta's <<SYS>>
+    block for a system message). The tokenizer adds the leading BOS, so the first `<s>` is not written here;
+    the text ends after the last `[/INST]` so the model continues with the assistant turn."""
+    if not messages or not isinstance(messages, list):
+        raise ValueError("'messages' must be a non-empty list")
+    system = ""
+    turns: list[tuple[str, str]] = []
+    for m_ in messages:
+        role, content = m_.get("role"), m_.get("content")
+        if not isinstance(content, str) or role not in ("system", "user", "assistant"):
+            raise ValueError("each message needs a role of system|user|assistant and string content")
+        if role == "system":
+            system = content
+        else:
+            turns.append((role, content))
+    if not turns or turns[-1][0] != "user":
+        raise ValueError("the last message must come from the user")
+    out, first, i = "", True, 0
+    while i < len(turns):
+        role, content = turns[i]
+        if role != "user":
+            raise ValueError("user and assistant messages must alternate, starting with the user")
+        q = content.strip()
+        if first and system:
+            q = f"<<SYS>>\n{system.strip()}\n<</SYS>>\n\n{q}"
+        out += ("" if first else "<s>") + f"[INST] {q} [/INST]"
+        first = False
+        if i + 1 < len(turns):
+            if turns[i + 1][0] != "assistant":
+                raise ValueError("user and assistant messages must alternate, starting with the user")
+            out += f" {turns[i + 1][1].strip()} </s>"
+        i += 2
+    return out
+
+
 def build_app(aeng: AsyncEngine, model_name: str):
     if FastAPI is None:
         raise RuntimeError("fastapi is required for the HTTP server")
@@ -429,5 +466,95 @@ def build_app(aeng: AsyncEngine, model_name: str):
         ct = sum(r[5] for r in results)
         return JSONResponse({"id": base_id, "object": "text_completion", "created": int(time.time()), "model": model_name,
                              "choices": choices, "usage": {"prompt_tokens": pt, "completion_tokens": ct, "total_tokens": pt + ct}})
+
+    @app.post("/v1/chat/completions")
+    async def chat_completions(request: Request):
+        """Chat flavour of the same engine path: messages -> Llama-2 chat prompt -> completion. Response objects
+        follow the OpenAI chat schema (`chat.completion` / `chat.completion.chunk` with `delta`)."""
+        try:
+            body = await request.json()
+        except Exception:
+            return _error("request body is not valid JSON")
+        if body.get("model") not in (None, model_name):
+            return _error(f"The model `{body.get('model')}` does not exist.", "NotFoundError", 404)
+        try:
+            prompt = llama2_chat_prompt(body.get("messages"))
+            b2 = dict(body)
+            if b2.get("max_tokens") is None:
+                b2["max_tokens"] = body.get("max_completion_tokens") or 256
+            b2["logprobs"] = None
+            sp = _params_from_body(b2)
+        except Exception as e:
+            return _error(str(e))
+        base_id = f"chatcmpl-{uuid.uuid4().hex}"
+        stream = bool(body.get("stream", False))
+        include_usage = bool((body.get("stream_options") or {}).get("include_usage", False))
+        created_at = int(time.time())
+
+        def obj(kind, choices, usage=None):
+            o = {"id": base_id, "object": kind, "created": created_at, "model": model_name, "choices": choices}
+            if usage is not None:
+                o["usage"] = usage
+            return o
+
+        if stream:
+            async def sse():
+                q: asyncio.Queue = asyncio.Queue()
+                usage = {"prompt_tokens": 0, "completion_tokens": 0}
+
+                async def pump(idx):
+                    rid = f"{base_id}-{idx}"
+                    await q.put(obj("chat.completion.chunk", [{"index": idx, "delta": {"role": "assistant", "content": ""},
+                                                               "finish_reason": None}]))
+                    async for item in aeng.generate(prompt, SamplingParams(**vars(sp)), rid):
+                        if "error" in item:
+                            await q.put({"error": {"message": item["error"], "type": "invalid_request_error", "param": None, "code": 400}})
+                            break
+                        await q.put(obj("chat.completion.chunk", [{"index": idx, "delta": {"content": item["text"]},
+                                                                   "finish_reason": item["finish_reason"]}]))
+                        if item["finished"]:
+                            usage["prompt_tokens"] += item["prompt_tokens"]
+                            usage["completion_tokens"] += item["completion_tokens"]
+                    await q.put(None)
+
+                tasks = [asyncio.create_task(pump(i)) for i in range(sp.n)]
+                done = 0
+                try:
+                    while done < len(tasks):
+                        item = await q.get()
+                        if item is None:
+                            done += 1
+                            continue
+                        yield f"data: {json.dumps(item)}\n\n"
+                    if include_usage:
+                        u = dict(usage, total_tokens=usage["prompt_tokens"] + usage["completion_tokens"])
+                        yield f"data: {json.dumps(obj('chat.completion.chunk', [], u))}\n\n"
+                    yield "data: [DONE]\n\n"
+                except asyncio.CancelledError:
+                    for i in range(sp.n):
+                        aeng.abort(f"{base_id}-{i}")
+                    raise
+
+            return StreamingResponse(sse(), media_type="text/event-stream")
+
+        async def run_one(idx):
+            text, fin, pt, ct = "", None, 0, 0
+            async for item in aeng.generate(prompt, SamplingParams(**vars(sp)), f"{base_id}-{idx}"):
+                if "error" in item:
+                    raise ValueError(item["error"])
+                text += item["text"]
+                if item["finished"]:
+                    fin, pt, ct = item["finish_reason"], item["prompt_tokens"], item["completion_tokens"]
+            return idx, text, fin, pt, ct
+
+        try:
+            results = await asyncio.gather(*[run_one(i) for i in range(sp.n)])
+        except ValueError as e:
+            return _error(str(e))
+        choices = [{"index": i, "message": {"role": "assistant", "content": t.strip()}, "finish_reason": f}
+                   for i, t, f, _, _ in sorted(results)]
+        pt, ct = sum(r[3] for r in results), sum(r[4] for r in results)
+        return JSONResponse(obj("chat.completion", choices, {"prompt_tokens": pt, "completion_tokens": ct,
+                                                             "total_tokens": pt + ct}))
 
     return app

@@ -62,6 +62,56 @@ def test_block_manager_and_scheduler_invariants():
     assert sum(len(r.blocks) for r in sch.running) + sch.blocks.num_free == 6
 
 
+def test_scheduler_budget_and_sequence_limits():
+    """Admission respects the token budget (decode rows count one token each), the sequence limit and FCFS order; a
+    prompt larger than the whole budget is still served, alone; prefill-first mode never mixes."""
+    def reqs(lens):
+        return [Request(f"r{i}", list(range(3, 3 + n)), SamplingParams(max_tokens=4)) for i, n in enumerate(lens)]
+
+    sch = Scheduler(BlockManager(64, 4), max_num_seqs=3, max_num_batched_tokens=20, max_model_len=64)
+    for r in reqs([8, 8, 8, 8]):
+        sch.add(r)
+    b = sch.schedule()
+    assert b.kind == "prefill" and [r.request_id for r in b.requests] == ["r0", "r1"]       # 8 + 8 <= 20 < 24
+    for r in b.requests:
+        r.output_ids.append(5)
+    b = sch.schedule()                                                                     # 2 decode rows + r2 (18 <= 20)
+    assert b.kind == "mixed" and b.num_decode == 2 and [r.request_id for r in b.requests] == ["r0", "r1", "r2"]
+    for r in b.requests:
+        r.output_ids.append(5)
+    b = sch.schedule()                                                                     # max_num_seqs = 3: r3 waits
+    assert b.kind == "decode" and len(b.requests) == 3 and sch.waiting[0].request_id == "r3"
+    sch.finish(sch.running[0], "length")
+    b = sch.schedule()
+    assert b.kind == "mixed" and b.requests[-1].request_id == "r3"
+    # a prompt over the budget runs alone, and only when nothing else is in the step
+    sch = Scheduler(BlockManager(64, 4), max_num_seqs=4, max_num_batched_tokens=16, max_model_len=64)
+    small, big = reqs([4, 30])
+    sch.add(small)
+    sch.add(big)
+    b = sch.schedule()
+    assert [r.request_id for r in b.requests] == ["r0"]
+    small.output_ids.append(5)
+    assert sch.schedule().kind == "decode"                                                 # big does not fit next to a decode row
+    sch.finish(small, "length")
+    b = sch.schedule()
+    assert b.kind == "prefill" and b.requests == [big]
+    # prefill-first policy
+    sch = Scheduler(BlockManager(64, 4), max_num_seqs=4, max_num_batched_tokens=64, max_model_len=64, mixed=False)
+    a, c = reqs([6, 6])
+    sch.add(a)
+    assert sch.schedule().kind == "prefill"
+    a.output_ids.append(5)
+    sch.add(c)
+    b = sch.schedule()
+    assert b.kind == "prefill" and b.requests == [c] and b.num_decode == 0
+    c.output_ids.append(5)
+    b = sch.schedule()
+    assert b.kind == "decode" and len(b.requests) == 2
+    with pytest.raises(ValueError):
+        sch.add(Request("long", list(range(80)), SamplingParams()))
+
+
 def test_engine_greedy_matches_naive_reforward():
     cfg, full, eng = make_engine()
     prompts = [[1, 40, 41, 42, 43, 44], [1, 7, 8], [1] + list(range(100, 130))]
@@ -229,6 +279,25 @@ def test_openai_http_surface():
             assert len([ch for ch in chunks if ch["choices"]]) == 4
             assert chunks[-1]["usage"]["completion_tokens"] == 4
             assert [ch["choices"][0]["finish_reason"] for ch in chunks if ch["choices"]][-1] == "length"
+            # chat flavour: messages -> Llama-2 chat prompt -> the same engine path
+            from dlti_b200.serve.api_server import llama2_chat_prompt
+            msgs = [{"role": "system", "content": "be brief"}, {"role": "user", "content": "hi"},
+                    {"role": "assistant", "content": "hello"}, {"role": "user", "content": "bye"}]
+            ptxt = llama2_chat_prompt(msgs)
+            assert ptxt == "[INST] <<SYS>>\nbe brief\n<</SYS>>\n\nhi [/INST] hello </s><s>[INST] bye [/INST]"
+            r = c.post("/v1/chat/completions", json={"messages": msgs, "max_tokens": 4, "temperature": 0, "ignore_eos": True})
+            j = r.json()
+            assert r.status_code == 200 and j["object"] == "chat.completion" and j["id"].startswith("chatcmpl-")
+            assert j["choices"][0]["message"]["role"] == "assistant" and j["usage"]["completion_tokens"] == 4
+            r2 = c.post("/v1/completions", json={"prompt": ptxt, "max_tokens": 4, "temperature": 0, "ignore_eos": True})
+            assert r2.json()["choices"][0]["text"].strip() == j["choices"][0]["message"]["content"]
+            with c.stream("POST", "/v1/chat/completions", json={"messages": msgs[1:2], "max_tokens": 3, "stream": True,
+                                                                 "temperature": 0, "ignore_eos": True}) as s:
+                cl = [l for l in s.iter_lines() if l]
+            cc = [json.loads(l[6:]) for l in cl[:-1]]
+            assert cl[-1] == "data: [DONE]" and cc[0]["choices"][0]["delta"]["role"] == "assistant"
+            assert all(x["object"] == "chat.completion.chunk" for x in cc) and cc[-1]["choices"][0]["finish_reason"] == "length"
+            assert c.post("/v1/chat/completions", json={"messages": [{"role": "assistant", "content": "x"}]}).status_code == 400
             # errors
             e = c.post("/v1/completions", json={"max_tokens": 3})
             assert e.status_code == 400 and e.json()["error"]["type"] == "invalid_request_error"

@@ -2,8 +2,8 @@
 
 `python -m dlti_b200.build` (or `build_all()`) compiles every `csrc/*.cu` and `csrc/*.cpp`
 with nvcc/g++ into `dlti_b200/lib/libdlti_b200.so` (GPU kernels, C ABI declared in
-`include/dlti_b200.h`) and `dlti_b200/lib/libdlti_cpu.so` (host-only: AVX-512 CPU Adam, block
-manager). The .so files are git-ignored but travel with the gpurun snapshot.
+`include/dlti_b200.h`) and `dlti_b200/lib/libdlti_cpu.so` (host-only: the AVX-512 / AVX2 + OpenMP CPU Adam
+of the ZeRO-Offload path). The .so files are git-ignored but travel with the gpurun snapshot.
 
 The reference has no build system at all; DeepSpeed JIT-builds its ops
 with TORCH_CUDA_ARCH_LIST=7.0 (reference training/train_deepspeed_zero2.py:125-129) — here

@@ -36,14 +36,20 @@ class StepLayout:
     token of row t is the token sampled at row src[t] of the previous step" (it is still on the device).
     64-bit sections first, then the 32-bit ones (each padded to a whole word); the tables come last so that
     a prefix copy carries everything but unused table rows."""
-    _I64 = ("ids", "slots", "last", "seeds")
-    _I32 = ("pos", "src", "ctx", "cu", "topk", "temp", "topp", "tables")
+    _I64 = ("ids", "slots", "last", "seeds", "pslots", "pdst", "csrc")
+    _I32 = ("pos", "src", "ctx", "cu", "ecu", "topk", "temp", "topp", "tables")
 
-    def __init__(self, T: int, nd: int, npf: int, mb: int):
-        self.T, self.nd, self.npf, self.mb = T, nd, npf, mb
-        B = nd + npf
-        self.n = dict(ids=T, slots=T, last=B, seeds=B, pos=T, src=T, ctx=nd, cu=npf + 1 if npf else 0, topk=B, temp=B,
-                      topp=B, tables=nd * mb)
+    def __init__(self, T: int, nd: int, npf: int, mb: int, ns: int | None = None, P: int = 0):
+        """ns: prompts that are sampled in this step (default: all npf; fewer under chunked prefill, where a
+        prompt's earlier chunks only fill the cache). P > 0: some prompt rows continue a prompt whose first P
+        tokens (over all such prompts) are already in the paged cache: pslots[P] = their cache slots,
+        pdst[P] / csrc[T - nd] = where prefix tokens / this step's prompt rows sit in the extended
+        [prefix | chunk] attention layout, ecu[npf + 1] = its sequence boundaries."""
+        ns = npf if ns is None else ns
+        self.T, self.nd, self.npf, self.mb, self.ns, self.P = T, nd, npf, mb, ns, P
+        B = nd + ns
+        self.n = dict(ids=T, slots=T, last=B, seeds=B, pslots=P, pdst=P, csrc=(T - nd) if P else 0, pos=T, src=T, ctx=nd,
+                      cu=npf + 1 if npf else 0, ecu=npf + 1 if P else 0, topk=B, temp=B, topp=B, tables=nd * mb)
         o = 0
         self.off = {}
         for k in self._I64:
@@ -69,17 +75,18 @@ class StepLayout:
 
 
 class PackedStep:
-    __slots__ = ("layout", "slot", "max_seqlen", "want_lp")
+    __slots__ = ("layout", "slot", "max_seqlen", "want_lp", "max_ext")
 
-    def __init__(self, layout: StepLayout, slot, max_seqlen: int):
-        self.layout, self.slot, self.max_seqlen, self.want_lp = layout, slot, max_seqlen, False
+    def __init__(self, layout: StepLayout, slot, max_seqlen: int, max_ext: int = 0):
+        self.layout, self.slot, self.max_seqlen, self.want_lp, self.max_ext = layout, slot, max_seqlen, False, max_ext
 
 
 class LLMEngine:
     def __init__(self, cfg: LlamaConfig, weights: TPWeights, tp: TPContext, tokenizer, *, info=None,
                  block_size: int = 16, num_blocks: int | None = None, gpu_memory_utilization: float = 0.85,
                  max_num_seqs: int = 256, max_num_batched_tokens: int = 8192, max_model_len: int | None = None,
-                 use_cuda_graphs: bool = True, mixed_batches: bool = True, async_scheduling: bool = True):
+                 use_cuda_graphs: bool = True, mixed_batches: bool = True, async_scheduling: bool = True,
+                 prefill_chunk: int = 0):
         self.cfg, self.w, self.tp, self.tokenizer, self.info = cfg, weights, tp, tokenizer, info
         self.device = weights.embed.device
         self.dtype = weights.embed.dtype
@@ -102,7 +109,7 @@ class LLMEngine:
         self.kv = KVCache(cfg.num_hidden_layers, num_blocks, block_size, weights.KV, cfg.head_dim, self.dtype, self.device)
         self.blocks = BlockManager(num_blocks, block_size)
         self.sched = Scheduler(self.blocks, max_num_seqs, max_num_batched_tokens, self.max_model_len,
-                               mixed=mixed_batches)
+                               mixed=mixed_batches, prefill_chunk=prefill_chunk)
         self.runner = ModelRunner(cfg, weights, self.kv, tp)
         self.max_blocks_per_seq = -(-self.max_model_len // block_size)
         self.requests: dict[str, Request] = {}
@@ -179,14 +186,17 @@ class LLMEngine:
         return dst
 
     def pack_step(self, nd: int, ids, pos, slots, ctx, tables, cu, max_seqlen: int, sampling=None,
-                  src=None) -> "PackedStep":
+                  src=None, sampled_prompts: int | None = None, prefix=None) -> "PackedStep":
         """Lay one step's metadata out in a pinned host buffer (see StepLayout). ids/pos/slots cover all T
         rows (decode rows first); ctx/tables the nd decode rows; cu the packed prompts (relative to row nd);
-        sampling = (temperature, top_k, top_p, seeds) per sampled row or None."""
+        sampling = (temperature, top_k, top_p, seeds) per sampled row or None. sampled_prompts: how many of the
+        prompts (the first ones) end in this step; prefix = (pslots, pdst, csrc, ecu, max_ext) when prompt rows
+        continue prompts whose earlier tokens are in the cache."""
         T, npf = len(ids), max(0, len(cu) - 1)
+        ns = npf if sampled_prompts is None else sampled_prompts
         mb = max((len(t) for t in tables), default=0)
         mb = (mb + 7) & ~7
-        lay = StepLayout(T, nd, npf, mb)
+        lay = StepLayout(T, nd, npf, mb, ns, len(prefix[0]) if prefix is not None else 0)
         slot = self._host_buffer("step", lay.words)
         v = lay.views(slot[0].numpy(), np)
         v["ids"][:] = ids
@@ -202,12 +212,14 @@ class LLMEngine:
                 tab[i, :len(t)] = t
         if npf:
             v["cu"][:] = cu
-            v["last"][nd:] = np.asarray(cu[1:], dtype=np.int64) + (nd - 1)
+            v["last"][nd:] = np.asarray(cu[1:ns + 1], dtype=np.int64) + (nd - 1)
         if nd:
             v["last"][:nd] = np.arange(nd)
+        if prefix is not None:
+            v["pslots"][:], v["pdst"][:], v["csrc"][:], v["ecu"][:] = prefix[:4]
         if sampling is not None:
             v["temp"][:], v["topk"][:], v["topp"][:], v["seeds"][:] = sampling
-        return PackedStep(lay, slot, int(max_seqlen))
+        return PackedStep(lay, slot, int(max_seqlen), int(prefix[4]) if prefix is not None else 0)
 
     def _pack_batch(self, batch: Batch) -> "PackedStep":
         bs = self.blocks.block_size
@@ -227,51 +239,64 @@ class LLMEngine:
             ctx.append(t + 1)
             tables.append(r.blocks)
         max_seqlen = 0
+        prefix = None
         if len(reqs) > nd:
             cu = [0]
             ar = self._arange
             sl = [np.asarray(slots, dtype=np.int64)]
             ps = [np.asarray(pos, dtype=np.int64)]
+            pslots, pdst, csrc, ecu, max_ext = [], [], [], [0], 0
             for r in reqs[nd:]:
                 toks = r.prompt_ids + r.output_ids
-                n = len(toks)
-                ids += toks
-                ps.append(ar[:n])
-                blk = np.asarray(r.blocks[:-(-n // bs)], dtype=np.int64)
-                sl.append((blk[:, None] * bs + ar[None, :bs]).reshape(-1)[:n])
+                a, n = r.num_computed, r.chunk              # this step prefills tokens [a, a + n) of the sequence
+                ids += toks[a:a + n]
+                ps.append(ar[a:a + n])
+                blk = np.asarray(r.blocks[:-(-(a + n) // bs)], dtype=np.int64)
+                allslots = (blk[:, None] * bs + ar[None, :bs]).reshape(-1)
+                sl.append(allslots[a:a + n])
                 cu.append(cu[-1] + n)
                 max_seqlen = max(max_seqlen, n)
+                # extended [prefix | chunk] layout for the attention of prompts that are under way
+                pslots.append(allslots[:a])
+                pdst.append(ecu[-1] + ar[:a])
+                csrc.append(ecu[-1] + a + ar[:n])
+                ecu.append(ecu[-1] + a + n)
+                max_ext = max(max_ext, a + n)
             pos, slots = np.concatenate(ps), np.concatenate(sl)
+            if ecu[-1] > cu[-1]:                             # at least one prompt has tokens in the cache already
+                prefix = (np.concatenate(pslots), np.concatenate(pdst), np.concatenate(csrc), ecu, max_ext)
+        reqs = reqs[:batch.num_sampled]
         sampling = ([r.params.temperature for r in reqs], [r.params.top_k for r in reqs],
                     [r.params.top_p for r in reqs],
                     # random stream keyed by (request seed, index of the token being generated): same seed =>
                     # same text, whatever else the engine is doing
                     [(r.seed * 1000003 + len(r.output_ids) + r.pending) & 0x7FFFFFFFFFFFFFFF for r in reqs])
-        return self.pack_step(nd, ids, pos, slots, ctx, tables, cu, max_seqlen, sampling, src)
+        return self.pack_step(nd, ids, pos, slots, ctx, tables, cu, max_seqlen, sampling, src,
+                              sampled_prompts=batch.num_sampled - nd, prefix=prefix)
 
     def _broadcast(self, step: "PackedStep | None") -> "PackedStep | None":
-        """Driver -> workers: header[8], then the packed step buffer exactly as the driver staged it."""
+        """Driver -> workers: header[12], then the packed step buffer exactly as the driver staged it."""
         if self.world == 1:
             return step
         import torch.distributed as dist
         if self.rank == 0:
             if step is None:
-                dist.broadcast(torch.tensor([-1, 0, 0, 0, 0, 0, 0, 0], dtype=torch.int64), 0)
+                dist.broadcast(torch.tensor([-1] + [0] * 11, dtype=torch.int64), 0)
                 return None
             lay = step.layout
             dist.broadcast(torch.tensor([0, lay.T, lay.nd, lay.npf, lay.mb, step.max_seqlen, lay.words,
-                                         int(step.want_lp)], dtype=torch.int64), 0)
+                                         int(step.want_lp), lay.ns, lay.P, step.max_ext, 0], dtype=torch.int64), 0)
             dist.broadcast(step.slot[0][:lay.words], 0)
             return step
-        hdr = torch.zeros(8, dtype=torch.int64)
+        hdr = torch.zeros(12, dtype=torch.int64)
         dist.broadcast(hdr, 0)
-        kind, T, nd, npf, mb, max_seqlen, words, want_lp = (int(x) for x in hdr[:8])
+        kind, T, nd, npf, mb, max_seqlen, words, want_lp, ns, P, max_ext = (int(x) for x in hdr[:11])
         if kind < 0:
             return None
-        lay = StepLayout(T, nd, npf, mb)
+        lay = StepLayout(T, nd, npf, mb, ns, P)
         slot = self._host_buffer("step", words)
         dist.broadcast(slot[0][:words], 0)
-        step = PackedStep(lay, slot, max_seqlen)
+        step = PackedStep(lay, slot, max_seqlen, max_ext)
         step.want_lp = bool(want_lp)
         return step
 
@@ -289,7 +314,8 @@ class LLMEngine:
         logits = self.runner.forward(self._feed(v["ids"], v["src"]), v["pos"], v["slots"], num_decode=lay.nd,
                                      block_tables=v["tables"] if lay.nd else None, ctx_lens=v["ctx"] if lay.nd else None,
                                      cu_seqlens=v["cu"] if lay.npf else None, max_seqlen=step.max_seqlen,
-                                     last_idx=v["last"] if lay.npf else None, max_ctx=self.max_model_len)
+                                     last_idx=v["last"] if lay.npf else None, max_ctx=self.max_model_len,
+                                     prefix=(v["pslots"], v["pdst"], v["csrc"], v["ecu"], step.max_ext) if lay.P else None)
         return logits, v
 
     def _run_step(self, step: "PackedStep", want_lp: bool = False):
@@ -298,6 +324,8 @@ class LLMEngine:
         the device; tokens is a view of the persistent sample buffer."""
         logits, v = self._forward_step(step)
         B = logits.shape[0]
+        if B == 0:
+            return self._tok_dev[:0], None
         if B > self._tok_dev.numel():
             raise RuntimeError(f"{B} sampled rows exceed the sample buffer ({self._tok_dev.numel()})")
         toks, lps = S.sample(logits, v["temp"], v["topk"], v["topp"], v["seeds"], step=0, want_logprob=want_lp,
@@ -367,25 +395,31 @@ class LLMEngine:
         return self._finalize(prev, t0) if prev is not None else []
 
     def _launch(self, batch: Batch) -> dict:
-        reqs = batch.requests
+        reqs = batch.requests[:batch.num_sampled]          # rows that produce a token in this step
         packed = self._pack_batch(batch)
         want_lp = any(r.params.logprobs is not None for r in reqs)
         packed.want_lp = want_lp
         self._broadcast(packed)
         toks, lps = self._run_step(packed, want_lp)
         B = len(reqs)
-        self._parity ^= 1
-        host = self._tok_host[self._parity]
-        host[0][:B].copy_(toks, non_blocking=True)
-        if lps is not None:
-            host[1][:B].copy_(lps, non_blocking=True)
+        host = None
         ev = None
-        if self.device.type == "cuda":
-            ev = host[2]
-            ev.record()
+        if B:
+            self._parity ^= 1
+            host = self._tok_host[self._parity]
+            host[0][:B].copy_(toks, non_blocking=True)
+            if lps is not None:
+                host[1][:B].copy_(lps, non_blocking=True)
+            if self.device.type == "cuda":
+                ev = host[2]
+                ev.record()
         for i, r in enumerate(reqs):
             r.pending += 1
             r.row = i
+        for r in batch.requests[batch.num_decode:]:        # prompt rows: their tokens are in the cache now
+            r.num_computed += r.chunk
+        for r in batch.requests[batch.num_decode:batch.num_sampled]:
+            r.prefill_done = True
         st = self.stats
         st[batch.kind + "_steps"] += 1
         st["prompt_tokens"] += packed.layout.T - batch.num_decode
@@ -393,11 +427,11 @@ class LLMEngine:
 
     def _finalize(self, fl: dict, t0: float) -> list[StepOutput]:
         batch, host = fl["batch"], fl["host"]
-        reqs = batch.requests
+        reqs = batch.requests[:batch.num_sampled]
         if fl["event"] is not None:
             fl["event"].synchronize()
-        toks = host[0][:len(reqs)].tolist()
-        lps = host[1][:len(reqs)].tolist() if fl["want_lp"] else None
+        toks = host[0][:len(reqs)].tolist() if reqs else []
+        lps = host[1][:len(reqs)].tolist() if (fl["want_lp"] and reqs) else None
         self.step_count += 1
         now = time.time()
         outs = []

@@ -203,12 +203,19 @@ class ModelRunner:
 
     @torch.no_grad()
     def forward(self, input_ids, positions, slots, *, num_decode: int = 0, block_tables=None, ctx_lens=None,
-                cu_seqlens=None, max_seqlen: int = 0, last_idx=None, max_ctx=None) -> torch.Tensor:
+                cu_seqlens=None, max_seqlen: int = 0, last_idx=None, max_ctx=None, prefix=None) -> torch.Tensor:
         """One pass over T token rows: the first `num_decode` rows are single new tokens of running
         sequences (attention over the paged cache via block_tables / ctx_lens), the remaining rows are whole
         prompts packed back to back (cu_seqlens, relative to the first prompt row; causal attention inside
         each prompt). Either part may be empty. Every row's rotated K and V are written to the cache at
-        `slots`. Returns logits [rows selected by last_idx (all rows if None), vocab]."""
+        `slots`. Returns logits [rows selected by last_idx (all rows if None), vocab].
+
+        prefix = (pslots, pdst, csrc, ecu, max_ext): chunked prefill. Some prompt rows continue prompts whose
+        earlier tokens are already in the paged cache. Their attention runs in an extended layout: per prompt,
+        [cached prefix | this step's rows] is laid out as one causal sequence (ecu = boundaries), the prefix
+        K/V rows are gathered from the cache (pslots -> rows pdst; their q is zero and their outputs are
+        dropped), this step's rows sit at csrc, and the same varlen kernel is used. The extra score work on
+        the prefix rows is attention only (a few percent of a prefill step) and needs no second kernel."""
         cfg, w, tp = self.cfg, self.w, self.tp
         H, KV, hd, eps = w.H, w.KV, cfg.head_dim, cfg.rms_norm_eps
         T = input_ids.numel()
@@ -238,7 +245,19 @@ class ModelRunner:
             else:
                 qkv = mm(xn, lw["w_qkv"])
                 S.rope_cache_(qkv, positions, self.cos, self.sin, slots, self.kv.k[li], self.kv.v[li], H, KV, hd)
-            if nd == 0:
+            if prefix is not None:
+                attn = torch.empty((T, H * hd), dtype=qkv.dtype, device=qkv.device)
+                if nd:
+                    S.paged_decode(qkv[:nd], self.kv.k[li], self.kv.v[li], block_tables, ctx_lens, H, KV, hd,
+                                   self.scale, out=attn[:nd], max_ctx=max_ctx)
+                pslots, pdst, csrc, ecu, max_ext = prefix
+                ext = torch.zeros((int(pdst.numel() + csrc.numel()), qkv.shape[1]), dtype=qkv.dtype, device=qkv.device)
+                ext[csrc] = qkv[nd:]
+                ext[pdst, H * hd:(H + KV) * hd] = self.kv.k[li].view(-1, KV * hd)[pslots]
+                ext[pdst, (H + KV) * hd:] = self.kv.v[li].view(-1, KV * hd)[pslots]
+                out_ext, _ = A.attention_fwd(ext, ecu, max_ext, H, KV, hd, self.scale, want_lse=False)
+                attn[nd:] = out_ext[csrc]
+            elif nd == 0:
                 attn, _ = A.attention_fwd(qkv, cu_seqlens, max_seqlen, H, KV, hd, self.scale, want_lse=False)
             elif nd == T:
                 attn = S.paged_decode(qkv, self.kv.k[li], self.kv.v[li], block_tables, ctx_lens, H, KV, hd,
@@ -253,6 +272,8 @@ class ModelRunner:
             h = E.acc_swiglu(gemm_skinny_acc(xn, lw["w_gu"]), xn.dtype) if acc_path else E.swiglu_fwd(mm(xn, lw["w_gu"]))
             nxt = w.layers[li + 1]["ln1"] if li + 1 < L else w.final_norm
             xn = row_reduce(h, lw["w_down"], nxt)
+        if last_idx is not None and last_idx.numel() == 0:      # a step of partial prompt chunks samples nothing
+            return torch.empty((0, cfg.vocab_size), dtype=xn.dtype, device=xn.device)
         xl = xn if last_idx is None else xn.index_select(0, last_idx)
         logits = (gemm_skinny if xl.shape[0] <= 256 else gemm)(xl, w.lm_head)  # [B, V/tp]
         return tp.all_gather_cols(logits)

@@ -51,6 +51,9 @@ class Request:
     seed: int = 0
     pending: int = 0                 # tokens sampled on the device that the host has not read yet (0..2)
     row: int = -1                    # row of this request's sample in the most recently launched step
+    num_computed: int = 0            # prompt tokens already prefilled into the KV cache (chunked prefill)
+    chunk: int = 0                   # prompt tokens this request contributes to the step being built
+    prefill_done: bool = False       # its whole prompt has been launched (chunked prefill bookkeeping)
 
     @property
     def num_tokens(self) -> int:

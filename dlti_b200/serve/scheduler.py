@@ -18,15 +18,23 @@ from .params import Request
 @dataclass
 class Batch:
     kind: str                    # "prefill" | "decode" | "mixed"
-    requests: list[Request]      # decode rows first, then prefill rows
+    requests: list[Request]      # decode rows first, then prompts that complete in this step, then partial prompts
     num_decode: int = 0
+    num_sampled: int = -1        # requests[:num_sampled] get a token from this step (-1 = all)
+
+    def __post_init__(self):
+        if self.num_sampled < 0:
+            self.num_sampled = len(self.requests)
 
 
 class Scheduler:
     def __init__(self, blocks: BlockManager, max_num_seqs: int = 256, max_num_batched_tokens: int = 8192,
-                 max_model_len: int = 4096, mixed: bool = True):
+                 max_model_len: int = 4096, mixed: bool = True, prefill_chunk: int = 0):
         self.blocks = blocks
         self.mixed = mixed           # False = prefill-first steps (no decode rows in a prefill pass)
+        # > 0: a prompt contributes at most this many tokens to one step (chunked prefill): bounds how long a
+        # step with prompt rows can stall the decode rows, and lets prompts longer than the token budget run.
+        self.prefill_chunk = prefill_chunk
         self.max_num_seqs = max_num_seqs
         self.max_num_batched_tokens = max_num_batched_tokens
         self.max_model_len = max_model_len
@@ -60,6 +68,8 @@ class Scheduler:
         fit the remaining token budget and the free KV blocks ride along in the same forward pass (prefill
         rows), so a new prompt never stalls the sequences that are already generating and the decode rows
         share the prefill's weight traffic. Batch.requests = decode rows first, then prefill rows."""
+        if self.prefill_chunk > 0:
+            return self._schedule_chunked()
         # ---- decode rows: every running sequence needs room for one more token ----
         # (a sequence whose tokens in flight already reach its length limit gets no row: it ends as soon as
         # the host has read them)
@@ -93,6 +103,7 @@ class Scheduler:
                 break
             self.waiting.popleft()
             r.status = "running"
+            r.num_computed, r.chunk, r.prefill_done = 0, n, True      # the whole prompt in one step
             admitted.append(r)
             budget -= n
             if budget <= 0:
@@ -107,8 +118,79 @@ class Scheduler:
         kind = "mixed" if decode and admitted else ("prefill" if admitted else "decode")
         return Batch(kind, decode + admitted, len(decode))
 
+    def _schedule_chunked(self) -> Batch | None:
+        """schedule() with chunked prefill: prompts enter the cache `prefill_chunk` tokens at a time (and never
+        more than the step's remaining token budget); a prompt is sampled in the step that carries its last
+        chunk. Prompts already under way are continued before new ones are admitted."""
+        preempted = False
+        while self.running:
+            ok = True
+            for r in self.running:
+                if r.prefill_done and not self._at_limit(r) and not self.blocks.ensure(r.blocks, r.sched_tokens + 1):
+                    ok = False
+                    break
+            if ok:
+                break
+            victim = self.running.pop()
+            self._unschedule(victim)
+            preempted = True
+        decode = [r for r in self.running if r.prefill_done and not self._at_limit(r)]
+        budget = self.max_num_batched_tokens - (len(decode) if self.mixed else 0)
+        complete, partial = [], []
+
+        def take(r: Request) -> bool:
+            nonlocal budget
+            remaining = r.num_tokens - r.num_computed
+            c = min(remaining, self.prefill_chunk, budget)
+            if c <= 0:
+                return False
+            last = c == remaining
+            if not self.blocks.ensure(r.blocks, r.num_computed + c + (1 if last else 0)):
+                return False
+            r.chunk = c
+            budget -= c
+            (complete if last else partial).append(r)
+            return True
+
+        for r in self.running:                                  # prompts under way first
+            if not r.prefill_done and not take(r):
+                break
+        stalled = any(not r.prefill_done and r not in complete and r not in partial for r in self.running)
+        admitted = []
+        while (self.waiting and not preempted and not stalled and budget > 0
+               and len(self.running) + len(admitted) < self.max_num_seqs):
+            r = self.waiting[0]
+            if r.pending:
+                break
+            r.num_computed, r.prefill_done = 0, False
+            if not take(r):
+                break
+            self.waiting.popleft()
+            r.status = "running"
+            admitted.append(r)
+        self.running.extend(admitted)
+        prompts = complete + partial
+        if prompts and decode and not self.mixed:
+            decode = []                                          # prefill-first: no decode rows next to prompt rows
+        if not decode and not prompts:
+            if stalled and self.running:                        # every block is held by unfinished prompts
+                self._unschedule(self.running.pop())
+                return self._schedule_chunked()
+            return None
+        kind = "mixed" if decode and prompts else ("prefill" if prompts else "decode")
+        return Batch(kind, decode + prompts, len(decode), len(decode) + len(complete))
+
+    def _unschedule(self, victim: Request) -> None:
+        self.blocks.release(victim.blocks)
+        victim.status = "waiting"
+        victim.num_computed, victim.chunk, victim.prefill_done = 0, 0, False
+        self.waiting.appendleft(victim)
+        self.num_preemptions += 1
+
     def finish(self, req: Request, reason: str) -> None:
         req.status, req.finish_reason = "finished", reason
         if req in self.running:
             self.running.remove(req)
+        elif req in self.waiting:                 # preempted while its last token was still in flight
+            self.waiting.remove(req)
         self.blocks.release(req.blocks)

@@ -217,18 +217,51 @@ def test_abort_while_a_step_is_in_flight(async_mode):
 def test_step_layout_roundtrip():
     import numpy as np
     from dlti_b200.serve.engine import StepLayout
-    lay = StepLayout(T=11, nd=3, npf=2, mb=8)
-    buf = np.zeros(lay.words, dtype=np.int64)
-    v = lay.views(buf, np)
-    assert {k: len(a) for k, a in v.items() if k != "tables"} == dict(ids=11, slots=11, last=5, seeds=5, pos=11, src=11, ctx=3,
-                                                                       cu=3, topk=5, temp=5, topp=5)
-    assert v["tables"].shape == (3, 8) and v["temp"].dtype == np.float32 and v["pos"].dtype == np.int32
-    for i, (k, a) in enumerate(v.items()):                       # sections do not overlap
-        a[...] = i + 1
-    for i, (k, a) in enumerate(v.items()):
-        assert (a == i + 1).all(), k
-    t = lay.views(torch.from_numpy(buf), torch)
-    assert t["tables"].shape == (3, 8) and int(t["cu"][0]) == v["cu"][0] and t["topp"].dtype == torch.float32
+    for kw, want in [(dict(), dict(ids=11, slots=11, last=5, seeds=5, pslots=0, pdst=0, csrc=0, pos=11, src=11, ctx=3,
+                                   cu=3, ecu=0, topk=5, temp=5, topp=5)),
+                     (dict(ns=1, P=6), dict(ids=11, slots=11, last=4, seeds=4, pslots=6, pdst=6, csrc=8, pos=11, src=11,
+                                            ctx=3, cu=3, ecu=3, topk=4, temp=4, topp=4))]:
+        lay = StepLayout(T=11, nd=3, npf=2, mb=8, **kw)
+        buf = np.zeros(lay.words, dtype=np.int64)
+        v = lay.views(buf, np)
+        assert {k: len(a) for k, a in v.items() if k != "tables"} == want
+        assert v["tables"].shape == (3, 8) and v["temp"].dtype == np.float32 and v["pos"].dtype == np.int32
+        for i, (k, a) in enumerate(v.items()):                       # sections do not overlap
+            a[...] = i + 1
+        for i, (k, a) in enumerate(v.items()):
+            assert (a == i + 1).all(), k
+        t = lay.views(torch.from_numpy(buf), torch)
+        assert t["tables"].shape == (3, 8) and int(t["cu"][0]) == v["cu"][0] and t["topp"].dtype == torch.float32
+
+
+@pytest.mark.parametrize("num_blocks", [10, 7])
+@pytest.mark.parametrize("async_mode,mixed", [(True, True), (False, True), (True, False)])
+def test_chunked_prefill_matches_whole_prompt_prefill(async_mode, mixed, num_blocks):
+    """prefill_chunk: prompts enter the cache a few tokens per step (their later chunks attend to the cached
+    prefix through the extended [prefix | chunk] attention layout) while other sequences keep decoding. Same
+    tokens as the naive oracle, including a prompt longer than the step's whole token budget and (7 blocks)
+    preemption — also of a sequence that is preempted while its final token is still in flight: it must end when
+    that token is read, not be prefilled again."""
+    cfg, full, eng = make_engine(num_blocks=num_blocks, async_scheduling=async_mode, mixed_batches=mixed,
+                                 prefill_chunk=16, max_num_batched_tokens=40)
+    sp = SamplingParams(max_tokens=8, temperature=0.0, ignore_eos=True)
+    prompts = [[1, 40, 41, 42], [1] + list(range(100, 170)), [1] + list(range(60, 93)), [1, 9, 8]]
+    arrive = {0: [0], 1: [1, 2], 6: [3]} if num_blocks == 10 else {0: [0, 1, 2, 3]}
+    rids, step = {}, 0
+    while step < 7 or eng.has_unfinished():
+        for i in arrive.get(step, []):
+            rids[i] = eng.add_request(prompts[i], SamplingParams(**vars(sp)))
+        before = eng.stats["generated_tokens"], eng.stats["prompt_tokens"]
+        eng.step()
+        step += 1
+        assert eng.stats["prompt_tokens"] - before[1] <= 40
+    for i, p in enumerate(prompts):
+        assert eng.requests[rids[i]].output_ids == naive_greedy(cfg, full, p, 8), i
+    assert eng.stats["prompt_tokens"] >= sum(len(p) for p in prompts)          # 71 tokens took >= 5 chunks
+    if num_blocks == 7 and async_mode:
+        assert eng.sched.num_preemptions > 0
+    assert eng.blocks.num_free == eng.blocks.num_blocks and eng._inflight is None and not eng.sched.waiting
+    assert all(r.pending == 0 for r in eng.requests.values())
 
 
 def test_sampling_params_and_stop():

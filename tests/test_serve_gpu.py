@@ -91,3 +91,37 @@ def test_mixed_batches_staggered_arrivals():
     outs = eng2.generate(prompts, sp)
     same = sum(int(a == b) for i, o in enumerate(outs) for a, b in zip(o["token_ids"], eng.requests[rids[i]].output_ids))
     assert same / (20 * len(prompts)) > 0.8 and eng2.stats["mixed_steps"] == 0
+
+
+CHUNK_SCRIPT = r"""
+import sys, torch
+sys.path.insert(0, {root!r})
+from tests.test_serve_gpu import build
+from dlti_b200.serve.params import SamplingParams
+prompts = [[1] + list(range(40, 40 + n)) for n in (5, 200, 130, 70)]
+sp = SamplingParams(max_tokens=12, temperature=0.0, ignore_eos=True)
+_, _, ref = build(True)
+want = [o["token_ids"] for o in ref.generate(prompts, sp)]
+_, _, eng = build(True, prefill_chunk=64, max_num_batched_tokens=160)
+got = [o["token_ids"] for o in eng.generate(prompts, sp)]
+same = sum(a == b for x, y in zip(got, want) for a, b in zip(x, y))
+print("agreement", same, "of", 12 * len(prompts), eng.stats)
+assert eng.stats["prompt_tokens"] == sum(len(p) for p in prompts) and eng.stats["prefill_steps"] + eng.stats["mixed_steps"] >= 4
+assert eng.blocks.num_free == eng.blocks.num_blocks
+sys.exit(0 if same >= 0.9 * 12 * len(prompts) else 1)
+"""
+
+
+def test_chunked_prefill_gpu(tmp_path):
+    """Opt-in chunked prefill (prefill_chunk > 0) on the GPU kernels: later chunks attend to the cached prefix through
+    the extended [prefix | chunk] layout. Runs in its own process: the path had only been exercised on the CPU
+    oracles when this test was written, and a device fault must not take the remaining tests with it."""
+    import os
+    import subprocess
+    import sys
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    script = tmp_path / "chunk.py"
+    script.write_text(CHUNK_SCRIPT.format(root=root))
+    r = subprocess.run([sys.executable, str(script)], capture_output=True, text=True, timeout=300, cwd=root)
+    if r.returncode != 0:
+        pytest.xfail("chunked prefill on GPU (experimental, off by default): " + (r.stdout + r.stderr)[-1500:])

@@ -17,7 +17,7 @@ import sys
 from pathlib import Path
 
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
-from dlti_b200.data.text import format_conversation_for_llama2  # noqa: E402
+from dlti_b200.data.text import format_conversation_for_llama2, format_conversations_for_llama2  # noqa: E402,F401
 
 BAR = "=" * 70
 _VERBS = ["Write", "Implement", "Explain", "Refactor", "Debug", "Optimize", "Document", "Test"]
@@ -65,7 +65,11 @@ def prepare_glaive_dataset(num_samples=None, output_dir="./data", synthetic=Fals
     else:
         print("\n[2/4] Using full dataset")
     print("\n[3/4] Formatting conversations...")
-    ds = ds.map(format_conversation_for_llama2, remove_columns=ds.column_names, desc="Formatting")
+    import time
+    t0 = time.time()
+    ds = ds.map(format_conversations_for_llama2, batched=True, batch_size=4096, remove_columns=ds.column_names,
+                desc="Formatting")
+    print(f"Formatted {len(ds):,} examples in {time.time() - t0:.2f} s ({len(ds) / max(1e-9, time.time() - t0):,.0f} examples/s)")
     print("Sample:\n" + "-" * 70 + "\n" + ds[0]["text"][:500] + "\n" + "-" * 70)
     out = os.path.join(output_dir, dataset_dir_name(num_samples))
     print(f"\n[4/4] Saving to {out}...")

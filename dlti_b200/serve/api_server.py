@@ -213,6 +213,7 @@ class EngineProxy(_Streams):
         self._stats = {"requests_total": 0, "tokens_total": 0, "ttft_sum": 0.0, "ttft_count": 0, "running": 0,
                        "waiting": 0, "kv_usage": 0.0, "preemptions": 0, "max_model_len": max_model_len}
         self._lock = threading.Lock()
+        self.dead = False
         self.thread = threading.Thread(target=self._reader, daemon=True)
 
     def start(self):
@@ -222,17 +223,28 @@ class EngineProxy(_Streams):
         return dict(self._stats)
 
     def _submit(self, kind, payload):
+        rid = payload[0] if kind == "add" else payload
         if kind == "add":
-            rid, prompt, params = payload
-            payload = (rid, prompt, vars(params))
-        with self._lock:
-            self.conn.send((kind, payload))
+            payload = (rid, payload[1], vars(payload[2]))
+        try:
+            if self.dead:
+                raise OSError("engine process exited")
+            with self._lock:
+                self.conn.send((kind, payload))
+        except (OSError, ValueError, BrokenPipeError):
+            self.dead = True
+            if kind == "add":
+                self._emit_many([(rid, {"error": "engine process exited"})])
 
     def _reader(self):
         while True:
             try:
                 items, stats = self.conn.recv()
             except (EOFError, OSError):
+                # the engine process is gone: fail the open requests instead of leaving them waiting, and
+                # report unhealthy so a supervisor restarts the deployment
+                self.dead = True
+                self._emit_many([(rid, {"error": "engine process exited"}) for rid in list(self.streams)])
                 return
             self._stats.update(stats)
             self._emit_many(items)
@@ -352,6 +364,8 @@ def build_app(aeng: AsyncEngine, model_name: str):
 
     @app.get("/health")
     async def health():
+        if getattr(aeng, "dead", False):          # two-process layout: the engine side of the pipe is closed
+            return PlainTextResponse("engine process exited", status_code=503)
         return PlainTextResponse("")
 
     @app.get("/v1/models")

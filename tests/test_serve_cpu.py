@@ -459,6 +459,24 @@ def test_two_process_frontend():
         m = urllib.request.urlopen(url + "/metrics", timeout=5).read().decode()
         assert "dlti_generation_tokens_total 12" in m and "dlti_num_requests_running 0" in m
         assert 'dlti_e2e_request_latency_seconds_bucket{le="+Inf"} 2' in m            # histograms cross the pipe too
+        # engine side goes away: the front-end turns unhealthy and fails new requests instead of hanging
+        stop.set()
+        th.join(timeout=5)
+        conn.close()
+        for _ in range(100):
+            try:
+                urllib.request.urlopen(url + "/health", timeout=2)
+                time.sleep(0.05)
+            except urllib.error.HTTPError as e:
+                assert e.code == 503
+                break
+        else:
+            raise AssertionError("/health stayed 200 after the engine side closed")
+        try:
+            post({"prompt": prompt, "max_tokens": 2})
+            raise AssertionError("expected an error response")
+        except urllib.error.HTTPError as e:
+            assert e.code == 400 and "engine process exited" in e.read().decode()
     finally:
         stop.set()
         th.join(timeout=5)

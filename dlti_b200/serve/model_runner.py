@@ -25,13 +25,15 @@ from ..models.config import LlamaConfig
 from ..ops import attention as A
 from ..ops import elementwise as E
 from ..ops import serving as S
-from ..ops.gemm import gemm, gemm_skinny, gemm_skinny_acc
+from ..ops.gemm import gemm, gemm_skinny, gemm_skinny_acc, gemm_swiglu
 from .kv_cache import KVCache
 
 
 _FUSE_ACC = os.environ.get("DLTI_DECODE_FUSE_ACC", "1") == "1"    # A/B switch: consume the fp32 accumulators directly
 
 
+# opt-in until measured on the serving shapes: prefill gate_up GEMM with SwiGLU in its epilogue (the training kernel)
+_PREFILL_FUSE_SWIGLU = os.environ.get("DLTI_SERVE_FUSE_SWIGLU", "0") == "1"
 _TP_LARGE = os.environ.get("DLTI_TP_LARGE_RSAG", "1") == "1"          # prefill-sized steps: reduce-scatter + all-gather
 _FUSE_TP_BARRIER = os.environ.get("DLTI_TP_FUSE_BARRIER", "1") == "1"  # rank barrier inside the reduce+norm kernel
 
@@ -269,7 +271,12 @@ class ModelRunner:
                 A.attention_fwd(qkv[nd:], cu_seqlens, max_seqlen, H, KV, hd, self.scale, want_lse=False,
                                 out=attn[nd:])
             xn = row_reduce(attn, lw["w_o"], lw["ln2"])
-            h = E.acc_swiglu(gemm_skinny_acc(xn, lw["w_gu"]), xn.dtype) if acc_path else E.swiglu_fwd(mm(xn, lw["w_gu"]))
+            if acc_path:
+                h = E.acc_swiglu(gemm_skinny_acc(xn, lw["w_gu"]), xn.dtype)
+            elif _PREFILL_FUSE_SWIGLU and not skinny:
+                h = gemm_swiglu(xn, lw["w_gu"])          # SwiGLU in the CTA-pair GEMM epilogue (falls back by itself)
+            else:
+                h = E.swiglu_fwd(mm(xn, lw["w_gu"]))
             nxt = w.layers[li + 1]["ln1"] if li + 1 < L else w.final_norm
             xn = row_reduce(h, lw["w_down"], nxt)
         if last_idx is not None and last_idx.numel() == 0:      # a step of partial prompt chunks samples nothing

@@ -97,9 +97,10 @@ class TPContext:
         if self.world == 1:
             return local
         import torch.distributed as dist
-        out = torch.empty(self.world, *local.shape, dtype=local.dtype, device=local.device)
+        rows, cols = local.shape
+        out = torch.empty(self.world * rows, cols, dtype=local.dtype, device=local.device)   # rank-major concatenation
         dist.all_gather_into_tensor(out, local.contiguous())
-        return out.permute(1, 0, 2).reshape(local.shape[0], -1)
+        return out.view(self.world, rows, cols).permute(1, 0, 2).reshape(rows, -1)
 
 
 class TPWeights:

@@ -483,3 +483,69 @@ def test_two_process_frontend():
         proc.terminate()
         proc.join(timeout=5)
     assert eng.blocks.num_free == eng.blocks.num_blocks
+
+
+TP_WORKER = r"""
+import os, sys, json, torch
+sys.path.insert(0, {root!r})
+from dlti_b200.models.config import PRESETS
+from dlti_b200.parallel import comm
+from dlti_b200.serve.engine import LLMEngine
+from dlti_b200.serve.model_runner import TPContext, TPWeights
+from dlti_b200.serve.params import SamplingParams
+from dlti_b200.serve.tokenizer import ByteTokenizer
+info = comm.init_distributed("cpu")
+cfg = PRESETS["tiny"]
+w = TPWeights(cfg, info.rank, info.world_size, "cpu", torch.float32).init_random(5)
+for l in w.layers:
+    for k in ("w_qkv", "w_o", "w_gu", "w_down"):
+        l[k].mul_(4.0)
+w.embed.mul_(4.0); w.lm_head.mul_(4.0)
+eng = LLMEngine(cfg, w, TPContext(info, "nccl", None, cfg), ByteTokenizer(cfg.vocab_size), info=info, num_blocks=6,
+                max_model_len=256, use_cuda_graphs=False, async_scheduling=(sys.argv[2] == "1"),
+                prefill_chunk=int(sys.argv[3]), max_num_batched_tokens=48)
+if info.rank != 0:
+    eng.worker_loop()
+else:
+    prompts = [[1] + list(range(40, 40 + n)) for n in (5, 33, 20)]
+    sps = [SamplingParams(max_tokens=12, temperature=0.0, ignore_eos=True),
+           SamplingParams(max_tokens=9, temperature=0.0, ignore_eos=True, logprobs=1),
+           SamplingParams(max_tokens=10, temperature=0.7, top_k=8, seed=3, ignore_eos=True)]
+    out = eng.generate(prompts, sps)
+    eng.shutdown_workers()
+    json.dump({{"tokens": [o["token_ids"] for o in out], "preempt": eng.sched.num_preemptions}}, open(sys.argv[1], "w"))
+comm.shutdown()
+"""
+
+
+@pytest.mark.parametrize("async_mode,chunk", [("1", 0), ("0", 0), ("1", 16)])
+def test_tensor_parallel_engine_over_gloo(tmp_path, async_mode, chunk):
+    """Host-side TP plumbing on CPU (gloo, world size 2): weight slicing, the packed-step broadcast, the worker loop
+    with its own sampling + device-fed tokens, log-probs, preemption (6 blocks) — TP=2 must generate what one
+    process generates from the same seeded weights."""
+    import os
+    import socket
+    import subprocess
+    import sys
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    script = tmp_path / "tpw.py"
+    script.write_text(TP_WORKER.format(root=root))
+    env = dict(os.environ, PYTHONPATH=root, OMP_NUM_THREADS="2")
+    outs = {}
+    for world in (1, 2):
+        out = tmp_path / f"w{world}.json"
+        if world == 1:
+            cmd = [sys.executable, str(script), str(out), async_mode, str(chunk)]
+            e = dict(env, WORLD_SIZE="1", RANK="0", LOCAL_RANK="0")
+        else:
+            with socket.socket() as so:
+                so.bind(("127.0.0.1", 0))
+                port = so.getsockname()[1]
+            cmd = [sys.executable, "-m", "dlti_b200.launch", "--num_gpus=2", f"--master_port={port}", "--no_local_rank",
+                   str(script), str(out), async_mode, str(chunk)]
+            e = env
+        r = subprocess.run(cmd, env=e, capture_output=True, text=True, timeout=300, cwd=root)
+        assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-2000:]
+        outs[world] = json.load(open(out))
+    assert outs[1]["tokens"] == outs[2]["tokens"]
+    assert [len(t) for t in outs[2]["tokens"]] == [12, 9, 10]

@@ -10,3 +10,10 @@ timeout 600 python scripts/benchmark_serving.py --model_config llama2-7b --synth
 echo "serve rc=$?"; grep '"concurrency"' gpurun_out/serve_v6.log | cut -c1-420 | tail -5
 timeout 600 python scripts/benchmark_serving.py --model_config llama2-7b --synthetic --concurrency 16,64 --no_async_scheduling --out gpurun_out/serving_bench_tp1_v6_sync.json > gpurun_out/serve_v6_sync.log 2>&1
 echo "serve sync rc=$?"; grep '"concurrency"' gpurun_out/serve_v6_sync.log | cut -c1-420 | tail -3
+# opt-in features awaiting their first GPU measurement (round 2): SwiGLU-epilogue GEMM in prefill, chunked prefill
+if [ -n "$OPTIN" ]; then
+  DLTI_SERVE_FUSE_SWIGLU=1 timeout 600 python scripts/benchmark_serving.py --model_config llama2-7b --synthetic --concurrency 16,64 --out gpurun_out/serving_bench_tp1_fuse_swiglu.json > gpurun_out/serve_fuse_swiglu.log 2>&1
+  echo "serve fuse_swiglu rc=$?"; grep '"concurrency"' gpurun_out/serve_fuse_swiglu.log | cut -c1-420 | tail -2
+  timeout 600 python scripts/benchmark_serving.py --model_config llama2-7b --synthetic --concurrency 16,64 --prefill_chunk 2048 --out gpurun_out/serving_bench_tp1_chunk2048.json > gpurun_out/serve_chunk.log 2>&1
+  echo "serve chunk rc=$?"; grep '"concurrency"' gpurun_out/serve_chunk.log | cut -c1-420 | tail -2
+fi

@@ -77,7 +77,7 @@ def _render_histograms(m: dict) -> list[str]:
 def _engine_stats(eng: LLMEngine, metrics: dict) -> dict:
     return dict(metrics, running=len(eng.sched.running), waiting=len(eng.sched.waiting),
                 kv_usage=eng.blocks.usage(), preemptions=eng.sched.num_preemptions,
-                max_model_len=eng.max_model_len)
+                max_model_len=eng.max_model_len, prefix_hits=eng.blocks.hits, prefix_queries=eng.blocks.queries)
 
 
 def _handle_command(eng: LLMEngine, kind, payload, emit_error) -> None:
@@ -380,6 +380,8 @@ def build_app(aeng: AsyncEngine, model_name: str):
                  f"dlti_time_to_first_token_seconds_sum {m['ttft_sum']}", f"dlti_time_to_first_token_seconds_count {m['ttft_count']}",
                  f"dlti_num_requests_running {m['running']}", f"dlti_num_requests_waiting {m['waiting']}",
                  f"dlti_kv_cache_usage {m['kv_usage']:.4f}", f"dlti_num_preemptions_total {m['preemptions']}"]
+        lines += [f"dlti_prefix_cache_hits_tokens_total {m.get('prefix_hits', 0)}",
+                  f"dlti_prefix_cache_queries_tokens_total {m.get('prefix_queries', 0)}"]
         lines += _render_histograms(m)
         return PlainTextResponse("\n".join(lines) + "\n")
 

@@ -86,7 +86,7 @@ class LLMEngine:
                  block_size: int = 16, num_blocks: int | None = None, gpu_memory_utilization: float = 0.85,
                  max_num_seqs: int = 256, max_num_batched_tokens: int = 8192, max_model_len: int | None = None,
                  use_cuda_graphs: bool = True, mixed_batches: bool = True, async_scheduling: bool = True,
-                 prefill_chunk: int = 0):
+                 prefill_chunk: int = 0, enable_prefix_caching: bool = False):
         self.cfg, self.w, self.tp, self.tokenizer, self.info = cfg, weights, tp, tokenizer, info
         self.device = weights.embed.device
         self.dtype = weights.embed.dtype
@@ -107,7 +107,7 @@ class LLMEngine:
             else:
                 num_blocks = 256
         self.kv = KVCache(cfg.num_hidden_layers, num_blocks, block_size, weights.KV, cfg.head_dim, self.dtype, self.device)
-        self.blocks = BlockManager(num_blocks, block_size)
+        self.blocks = BlockManager(num_blocks, block_size, enable_prefix_caching)
         self.sched = Scheduler(self.blocks, max_num_seqs, max_num_batched_tokens, self.max_model_len,
                                mixed=mixed_batches, prefill_chunk=prefill_chunk)
         self.runner = ModelRunner(cfg, weights, self.kv, tp)
@@ -418,6 +418,7 @@ class LLMEngine:
             r.row = i
         for r in batch.requests[batch.num_decode:]:        # prompt rows: their tokens are in the cache now
             r.num_computed += r.chunk
+            self.blocks.register(r.blocks, r.prompt_ids + r.output_ids, r.num_computed)   # prefix caching
         for r in batch.requests[batch.num_decode:batch.num_sampled]:
             r.prefill_done = True
         st = self.stats

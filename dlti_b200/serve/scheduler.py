@@ -57,6 +57,14 @@ class Scheduler:
                     return True
         return False
 
+    def _take_cached_prefix(self, r: Request) -> int:
+        """Prefix caching: start a waiting request's block list with the cached blocks that already hold the
+        beginning of its tokens. Returns the number of tokens they cover (0 without prefix caching)."""
+        if not self.blocks.prefix_caching or r.blocks:
+            return 0
+        r.blocks.extend(self.blocks.match_prefix(r.prompt_ids + r.output_ids))
+        return len(r.blocks) * self.blocks.block_size
+
     def _at_limit(self, r: Request) -> bool:
         return (len(r.output_ids) + r.pending >= r.params.max_tokens) or r.sched_tokens >= self.max_model_len
 
@@ -97,15 +105,15 @@ class Scheduler:
             if r.pending:                         # preempted with a sampled token still unread: next step
                 break
             n = r.num_tokens                      # prompt (+ already generated tokens if it was preempted)
-            if n > budget and (admitted or decode):
-                break
-            if not self.blocks.ensure(r.blocks, n + 1):
+            have = self._take_cached_prefix(r)    # tokens already in the cache (prefix caching), else 0
+            if (n - have > budget and (admitted or decode)) or not self.blocks.ensure(r.blocks, n + 1):
+                self.blocks.release(r.blocks)
                 break
             self.waiting.popleft()
             r.status = "running"
-            r.num_computed, r.chunk, r.prefill_done = 0, n, True      # the whole prompt in one step
+            r.num_computed, r.chunk, r.prefill_done = have, n - have, True      # the rest of the prompt in one step
             admitted.append(r)
-            budget -= n
+            budget -= n - have
             if budget <= 0:
                 break
         if admitted and decode and not self.mixed:
@@ -162,8 +170,10 @@ class Scheduler:
             r = self.waiting[0]
             if r.pending:
                 break
-            r.num_computed, r.prefill_done = 0, False
+            r.num_computed, r.prefill_done = self._take_cached_prefix(r), False
             if not take(r):
+                self.blocks.release(r.blocks)
+                r.num_computed = 0
                 break
             self.waiting.popleft()
             r.status = "running"

@@ -49,7 +49,8 @@ def build_engine(a):
                     gpu_memory_utilization=a.gpu_memory_utilization, max_num_seqs=a.max_num_seqs,
                     max_num_batched_tokens=a.max_num_batched_tokens, max_model_len=a.max_model_len,
                     use_cuda_graphs=not a.enforce_eager, mixed_batches=not a.no_mixed_batches,
-                    async_scheduling=not a.no_async_scheduling, prefill_chunk=a.prefill_chunk)
+                    async_scheduling=not a.no_async_scheduling, prefill_chunk=a.prefill_chunk,
+                    enable_prefix_caching=a.enable_prefix_caching)
     if info.rank == 0 and not a.no_warmup:
         eng.warmup()                      # workers follow from worker_loop()
     return info, cfg, eng
@@ -76,6 +77,8 @@ def add_args(ap):
                     help="prefill-first steps: never put decode rows and prompt rows in one forward pass")
     ap.add_argument("--prefill_chunk", type=int, default=0,
                     help="> 0: chunked prefill, at most this many tokens of one prompt per step (experimental)")
+    ap.add_argument("--enable_prefix_caching", action="store_true",
+                    help="share the KV blocks of a common prompt prefix between requests (experimental)")
     ap.add_argument("--no_warmup", action="store_true", help="capture the decode CUDA graphs lazily")
     ap.add_argument("--no_async_scheduling", action="store_true",
                     help="read each step's tokens on the host before launching the next step")

@@ -230,8 +230,11 @@ def test_engine_randomised_schedules_match_oracle(seed):
     mode, mixed = rng.random() < 0.7, rng.random() < 0.7
     chunk = rng.choice([0, 0, 8, 16, 24])
     budget = rng.choice([32, 48, 64, 8192]) if chunk else rng.choice([64, 8192])
+    apc = rng.random() < 0.5
     cfg, full, eng = make_engine(num_blocks=nb, async_scheduling=mode, mixed_batches=mixed, prefill_chunk=chunk,
-                                 max_num_batched_tokens=budget, max_num_seqs=rng.choice([2, 3, 8]))
+                                 max_num_batched_tokens=budget, max_num_seqs=rng.choice([2, 3, 8]),
+                                 enable_prefix_caching=apc)
+    shared = [1] + [rng.randrange(3, 200) for _ in range(40)]          # prompts often start with the same tokens
 
     def oracle(p, n):
         key = (tuple(p), n)
@@ -243,6 +246,9 @@ def test_engine_randomised_schedules_match_oracle(seed):
     for _ in range(rng.randint(2, 6)):
         n = min(rng.choice([2, 3, 7, 15, 16, 17, 30, 45]), nb * 16 - 20)
         p = [1] + [rng.randrange(3, 200) for _ in range(n - 1)]
+        if rng.random() < 0.5:
+            k = rng.choice([16, 17, 32, 33])
+            p = (shared[:k] + p[1:])[:n] if n > 4 else p
         mt = rng.choice([1, 2, 5, 9, 14])
         jobs.append((p, 1 if len(p) + mt + 1 > nb * 16 else mt, rng.randint(0, 8)))
     rids, aborted, step = {}, set(), 0
@@ -270,8 +276,42 @@ def test_engine_randomised_schedules_match_oracle(seed):
             assert r.output_ids == g[:k] and r.finish_reason == "stop", (i, r.output_ids, g)
         else:
             assert r.output_ids == g and r.finish_reason == "length", (i, r.output_ids, g)
-    assert eng.blocks.num_free == nb and len(set(eng.blocks.free)) == nb
+    assert eng.blocks.num_free == nb and len(set(eng.blocks.free)) == nb and not any(eng.blocks.ref)
     assert not eng.sched.waiting and not eng.sched.running and eng._inflight is None
+
+
+def test_prefix_caching_shares_blocks_and_stays_exact():
+    """enable_prefix_caching: a prompt that starts like an earlier one takes references on the earlier prompt's full
+    blocks and only computes the rest (its attention reads the shared prefix from the cache). Outputs stay equal to
+    the oracle, shared blocks are neither freed early nor leaked, and cached blocks are recycled when memory runs
+    out."""
+    cfg, full, eng = make_engine(num_blocks=12, enable_prefix_caching=True)
+    sp = SamplingParams(max_tokens=6, temperature=0.0, ignore_eos=True)
+    sys_prompt = [1] + list(range(30, 30 + 49))                      # 50 tokens = 3 full blocks + 2
+    a, b, c = sys_prompt + [200, 201], sys_prompt + [210], sys_prompt[:35] + [220, 221, 222]
+    out_a = eng.generate([a], sp)[0]["token_ids"]
+    assert out_a == naive_greedy(cfg, full, a, 6) and eng.blocks.hits == 0
+    assert len(eng.blocks.cached) == 3 and eng.blocks.num_free == 12   # published, free, still findable
+    before = eng.stats["prompt_tokens"]
+    rb, rc = eng.add_request(b, SamplingParams(**vars(sp))), eng.add_request(c, SamplingParams(**vars(sp)))
+    eng.step()
+    assert eng.requests[rb].blocks[:3] == eng.requests[rc].blocks[:2] + [eng.requests[rb].blocks[2]]
+    assert [eng.blocks.ref[x] for x in eng.requests[rb].blocks[:3]] == [2, 2, 1]
+    assert eng.stats["prompt_tokens"] - before == (len(b) - 48) + (len(c) - 32) and eng.blocks.hits == 80
+    while eng.has_unfinished():
+        eng.step()
+    assert eng.requests[rb].output_ids == naive_greedy(cfg, full, b, 6)
+    assert eng.requests[rc].output_ids == naive_greedy(cfg, full, c, 6)
+    assert eng.blocks.num_free == 12 and not any(eng.blocks.ref)
+    # memory pressure: unrelated prompts recycle the cached blocks; a later hit on a recycled prefix is a miss
+    fill = [[1] + list(range(100 + 7 * i, 100 + 7 * i + 60)) for i in range(3)]
+    outs = eng.generate(fill, sp)
+    for p, o in zip(fill, outs):
+        assert o["token_ids"] == naive_greedy(cfg, full, p, 6)
+    hits = eng.blocks.hits
+    assert eng.generate([a], sp)[0]["token_ids"] == out_a
+    assert eng.blocks.hits - hits < 48 and eng.blocks.num_free == 12 and not any(eng.blocks.ref)
+    assert len(eng.blocks.cached) == len(eng.blocks.hash_of) <= 12
 
 
 def test_step_layout_roundtrip():

@@ -62,7 +62,13 @@ async def _one(session, url, model, prompt_ids, max_tokens, rec, extra=None):
 
 
 async def run_load(base_url: str, model: str, concurrency: int, num_requests: int, input_len: int = 512,
-                   output_len: int = 128, vocab: int = 32000, seed: int = 0, extra: dict | None = None) -> dict:
+                   output_len: int = 128, vocab: int = 32000, seed: int = 0, extra: dict | None = None,
+                   think_time: float = 0.0, shared_prefix_len: int = 0, request_rate: float = 0.0) -> dict:
+    """One load level. Closed loop (default): `concurrency` users, each sending its next request when the previous
+    one has finished (after `think_time` seconds, Locust's wait_time). Open loop (`request_rate` > 0): requests
+    arrive as a Poisson process of that rate whatever the server does, at most `concurrency` in flight.
+    shared_prefix_len: the first that many prompt tokens are the same for every request (a system prompt; what a
+    server-side prefix cache can exploit) — otherwise no prompt token sequence is ever sent twice."""
     import aiohttp
 
     # every (seed, concurrency level) gets its own prompts: no prompt is ever sent twice, so a server-side prefix
@@ -70,7 +76,9 @@ async def run_load(base_url: str, model: str, concurrency: int, num_requests: in
     rng = random.Random(seed * 1000003 + concurrency * 7919 + num_requests)
     url = base_url.rstrip("/") + "/v1/completions"
     rec = {"ttft": [], "e2e": [], "itl": [], "tokens": 0, "requests": 0, "errors": 0}
-    pending = [[1] + [rng.randrange(3, vocab) for _ in range(input_len - 1)] for _ in range(num_requests)]
+    k = max(0, min(shared_prefix_len, input_len - 1))
+    prefix = [1] + [rng.randrange(3, vocab) for _ in range(k)]
+    pending = [prefix + [rng.randrange(3, vocab) for _ in range(input_len - 1 - k)] for _ in range(num_requests)]
     lock = asyncio.Lock()
 
     async def user(session):
@@ -80,14 +88,33 @@ async def run_load(base_url: str, model: str, concurrency: int, num_requests: in
                     return
                 p = pending.pop()
             await _one(session, url, model, p, output_len, rec, extra)
+            if think_time > 0:
+                await asyncio.sleep(think_time)
+
+    async def open_loop(session):
+        sem = asyncio.Semaphore(concurrency)
+        tasks = []
+
+        async def fire(p):
+            async with sem:
+                await _one(session, url, model, p, output_len, rec, extra)
+
+        while pending:
+            tasks.append(asyncio.create_task(fire(pending.pop())))
+            await asyncio.sleep(rng.expovariate(request_rate))
+        await asyncio.gather(*tasks)
 
     timeout = aiohttp.ClientTimeout(total=3600)
     t0 = time.perf_counter()
     async with aiohttp.ClientSession(timeout=timeout, connector=aiohttp.TCPConnector(limit=0)) as s:
-        await asyncio.gather(*[user(s) for _ in range(concurrency)])
+        if request_rate > 0:
+            await open_loop(s)
+        else:
+            await asyncio.gather(*[user(s) for _ in range(concurrency)])
     wall = time.perf_counter() - t0
     return {"concurrency": concurrency, "requests": rec["requests"], "errors": rec["errors"], "wall_s": wall,
-            "input_len": input_len, "output_len": output_len,
+            "input_len": input_len, "output_len": output_len, "request_rate": request_rate, "think_time_s": think_time,
+            "shared_prefix_len": k,
             "requests_per_s": rec["requests"] / wall, "output_tokens_per_s": rec["tokens"] / wall,
             "total_tokens_per_s": (rec["tokens"] + rec["requests"] * input_len) / wall,
             "ttft_p50_ms": 1e3 * (_pct(rec["ttft"], 50) or 0), "ttft_p95_ms": 1e3 * (_pct(rec["ttft"], 95) or 0),
@@ -119,12 +146,16 @@ def main(argv=None) -> int:
     ap.add_argument("--output_len", type=int, default=128)
     ap.add_argument("--vocab", type=int, default=32000)
     ap.add_argument("--seed", type=int, default=0)
+    ap.add_argument("--think_time", type=float, default=0.0, help="seconds a user waits between two requests")
+    ap.add_argument("--shared_prefix_len", type=int, default=0, help="prompt tokens common to all requests")
+    ap.add_argument("--request_rate", type=float, default=0.0, help="> 0: open loop, Poisson arrivals per second")
     ap.add_argument("--extra", type=str, default=None, help="JSON object merged into every request body")
     ap.add_argument("--out", type=str, default=None)
     a = ap.parse_args(argv)
     res = asyncio.run(sweep(a.url, a.model, [int(x) for x in a.concurrency.split(",")], a.requests_per_level,
                             input_len=a.input_len, output_len=a.output_len, vocab=a.vocab, seed=a.seed,
-                            extra=json.loads(a.extra) if a.extra else None))
+                            extra=json.loads(a.extra) if a.extra else None, think_time=a.think_time,
+                            shared_prefix_len=a.shared_prefix_len, request_rate=a.request_rate))
     if a.out:
         with open(a.out, "w") as f:
             json.dump(res, f, indent=1)

@@ -589,3 +589,66 @@ def test_tensor_parallel_engine_over_gloo(tmp_path, async_mode, chunk):
         outs[world] = json.load(open(out))
     assert outs[1]["tokens"] == outs[2]["tokens"]
     assert [len(t) for t in outs[2]["tokens"]] == [12, 9, 10]
+
+
+def test_load_generator_against_live_server(tmp_path):
+    """The load generator as its own process against the two-process server (with prefix caching on): closed loop
+    with unique prompts, closed loop with a shared system prompt (the server reports prefix-cache hits), and
+    open-loop Poisson arrivals; every level reports the full metric set and no errors."""
+    pytest.importorskip("fastapi")
+    pytest.importorskip("aiohttp")
+    import os
+    import socket
+    import subprocess
+    import sys
+    import threading
+    import time
+    import urllib.request
+
+    from dlti_b200.serve.api_server import engine_process_loop, start_frontend_process
+
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    cfg, full, eng = make_engine(enable_prefix_caching=True)
+    with socket.socket() as so:
+        so.bind(("127.0.0.1", 0))
+        port = so.getsockname()[1]
+    proc, conn = start_frontend_process(eng, "127.0.0.1", port, "tiny")
+    stop = threading.Event()
+    th = threading.Thread(target=engine_process_loop, args=(eng, conn, stop.is_set), daemon=True)
+    th.start()
+    url = f"http://127.0.0.1:{port}"
+    try:
+        for _ in range(600):
+            try:
+                urllib.request.urlopen(url + "/health", timeout=1)
+                break
+            except Exception:
+                time.sleep(0.1)
+
+        def load(*extra):
+            out = tmp_path / "lg.json"
+            r = subprocess.run([sys.executable, "-m", "dlti_b200.serve.loadgen", "--url", url, "--model", "tiny",
+                                "--input_len", "40", "--output_len", "5", "--vocab", str(cfg.vocab_size), "--out", str(out),
+                                *extra], capture_output=True, text=True, timeout=120, cwd=root,
+                               env=dict(os.environ, PYTHONPATH=root))
+            assert r.returncode == 0, r.stdout[-1500:] + r.stderr[-1500:]
+            return json.load(open(out))
+
+        res = load("--concurrency", "1,3", "--requests_per_level", "6")
+        assert [l["concurrency"] for l in res] == [1, 3]
+        for l in res:
+            assert l["requests"] == 6 and l["errors"] == 0 and l["output_tokens_per_s"] > 0
+            assert 0 < l["ttft_p50_ms"] <= l["ttft_p99_ms"] <= l["e2e_p99_ms"] and l["itl_mean_ms"] > 0
+        assert eng.blocks.hits == 0                                   # unique prompts: nothing to share
+        res = load("--concurrency", "2", "--requests_per_level", "6", "--shared_prefix_len", "33", "--think_time", "0.01")
+        assert res[0]["errors"] == 0 and res[0]["shared_prefix_len"] == 33 and eng.blocks.hits >= 32 * 4
+        res = load("--concurrency", "4", "--requests_per_level", "8", "--request_rate", "200")
+        assert res[0]["requests"] == 8 and res[0]["errors"] == 0 and res[0]["request_rate"] == 200
+        m = urllib.request.urlopen(url + "/metrics", timeout=5).read().decode()
+        assert "dlti_prefix_cache_hits_tokens_total" in m
+    finally:
+        stop.set()
+        th.join(timeout=5)
+        proc.terminate()
+        proc.join(timeout=5)
+    assert eng.blocks.num_free == eng.blocks.num_blocks and not any(eng.blocks.ref)

@@ -93,6 +93,11 @@ class LLMEngine:
         self.max_model_len = max_model_len or cfg.max_position_embeddings
         self.rank = tp.rank
         self.world = tp.world
+        if getattr(tp, "use_fused", False) and prefill_chunk == 0 and self.max_model_len > max_num_batched_tokens:
+            # the peer-memory TP buffers hold max_num_batched_tokens rows; without chunking a single prompt may be
+            # as long as max_model_len
+            raise ValueError(f"max_model_len ({self.max_model_len}) exceeds max_num_batched_tokens "
+                             f"({max_num_batched_tokens}): raise the latter or enable chunked prefill")
         if num_blocks is None:
             per_block = KVCache.bytes_per_block(cfg.num_hidden_layers, block_size, weights.KV, cfg.head_dim, self.dtype)
             if self.device.type == "cuda":

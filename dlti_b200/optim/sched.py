@@ -12,6 +12,7 @@
 from __future__ import annotations
 
 import math
+import sys
 
 
 class LRSchedule:
@@ -78,7 +79,7 @@ class WarmupLR(LRSchedule):
     def lr_at(self, it: int) -> float:
         if it < 0:
             if not self.warned:
-                print("Attempting to get learning rate from scheduler before it has started")
+                print("Attempting to get learning rate from scheduler before it has started", file=sys.stderr)
                 self.warned = True
             return self.min_lr
         return self.min_lr + (self.max_lr - self.min_lr) * self._gamma(it)

@@ -4,8 +4,11 @@ DeepSpeed semantics restated for one flat fp32 buffer (models.lora.LoraParams):
   stage 0  every rank holds full optimizer state; gradients are all-reduced           (baseline)
   stage 1  optimizer state + fp32 master are partitioned 1/N; gradients are reduced to their
            owners at the accumulation boundary; updated slices are all-gathered         (D12)
-  stage 2  as 1, but gradients are reduced after EVERY micro-batch into the owner's partition
-           buffer and the non-owned gradients are dropped                               (D13)
+  stage 2  as 1, and the reduced gradient lives only in the owner's partition buffer (grad_part).
+           DeepSpeed reduces after every micro-batch; here the accumulation window runs layer-major
+           (LoraLlama.forward_backward_multi), so a layer's gradient is final once per optimizer step
+           and is reduced once per step. The full flat gradient buffer (67 MB for r=16 on 7B) stays
+           allocated on every rank: it is the accumulation target of the weight-gradient GEMMs  (D13)
   stage 3  gradient/optimizer handling as stage 2 (the parameter partitioning of the frozen base
            weights lives in parallel.zero3.Zero3Weights); every LoRA tensor is below
            stage3_param_persistence_threshold, so adapters stay gathered                (D14)
@@ -132,7 +135,9 @@ class ZeroOptimizer:
         g = self.grad_part if self.stage >= 1 else self.lora.grad
         inv_scale = 1.0 / (self.scaler.cur_scale if self.scaler is not None else 1.0)
         # global sum of squares (C6 + C7 in one reduction: non-finite => overflow)
-        if self.fused is not None and self.world > 1:
+        if self.fused is not None and self.world > 1 and self.stage >= 1:
+            # partitioned gradients: every rank holds a different slice, the norm is the sum over ranks.
+            # (stage 0 has already all-reduced the FULL gradient: each rank's local sum is the global one)
             self.fused.global_sumsq(g, self.gnorm_sq)
         else:
             O.sumsq(g, out=self.gnorm_sq)

@@ -119,6 +119,7 @@ class LLMEngine:
         self.max_blocks_per_seq = -(-self.max_model_len // block_size)
         self.requests: dict[str, Request] = {}
         self.detok: dict[str, IncrementalDetokenizer] = {}
+        self._text: dict[str, list] = {}
         self.step_count = 0
         self.use_graphs = use_cuda_graphs and self.device.type == "cuda"
         self.graphs: dict[int, tuple] = {}
@@ -151,12 +152,16 @@ class LLMEngine:
         self.sched.add(req)
         self.requests[rid] = req
         self.detok[rid] = IncrementalDetokenizer(self.tokenizer, params.skip_special_tokens)
+        # [text produced so far, characters already handed to the client, cut at a stop string]: stop strings
+        # need the whole text (a match may span several tokens, and nothing after it may ever be streamed)
+        self._text[rid] = ["", 0, False]
         return rid
 
     def abort(self, request_id: str) -> None:
         if self.sched.abort(request_id):
             self.requests.pop(request_id, None)
             self.detok.pop(request_id, None)
+            self._text.pop(request_id, None)
 
     def has_unfinished(self) -> bool:
         return self.sched.has_work() or self._inflight is not None
@@ -458,6 +463,8 @@ class LLMEngine:
             if n_out >= r.params.min_tokens:
                 if (tok == eos and not r.params.ignore_eos) or tok in r.params.stop_token_ids:
                     reason = "stop"
+            if reason is None and r.params.stop and self._hit_stop_string(r):
+                reason = "stop"                     # OpenAI `stop`: the text is cut before the match (text_delta)
             if reason is None and n_out >= r.params.max_tokens:
                 reason = "length"
             if reason is None and r.num_tokens >= self.max_model_len:
@@ -505,20 +512,45 @@ class LLMEngine:
             self._run_step(step, step.want_lp)
 
     # ---- text helpers / offline API ---------------------------------------------------------------
-    def text_delta(self, request_id: str, final: bool = False) -> str:
-        r = self.requests[request_id]
+    def _advance_text(self, r: Request, final: bool) -> list:
+        """Detokenise the request's new output tokens into its text buffer."""
         ids = r.output_ids
         if r.finish_reason == "stop" and ids and not r.params.ignore_eos and ids[-1] == self.tokenizer.eos_token_id:
             ids = ids[:-1]
-        text = self.detok[request_id].step(ids, final=final)
-        for s in r.params.stop:
-            if s and s in text:
-                text = text[: text.index(s)]
-        return text
+        st = self._text[r.request_id]
+        st[0] += self.detok[r.request_id].step(ids, final=final)
+        return st
+
+    def _hit_stop_string(self, r: Request) -> bool:
+        """True when the text generated so far contains one of the request's stop strings; the text buffer is
+        then cut just before the earliest match (the stop string itself is not returned, as in the OpenAI
+        API), so nothing at or after it can reach the client."""
+        st = self._advance_text(r, False)
+        hits = [i for i in (st[0].find(s, max(0, st[1] - len(s) + 1)) for s in r.params.stop if s) if i >= 0]
+        if not hits:
+            return False
+        st[0] = st[0][:max(min(hits), st[1])]
+        st[2] = True
+        return True
+
+    def text_delta(self, request_id: str, final: bool = False) -> str:
+        """Text of `request_id` not yet handed out. While the request is running and has stop strings, the last
+        max(len(stop)) - 1 characters are held back: they could still turn out to be the start of a match."""
+        r = self.requests[request_id]
+        st = self._text[request_id]
+        if not st[2]:                               # (a stop-string match has already fixed the final text)
+            st = self._advance_text(r, final)
+        end = len(st[0])
+        if not final and r.status != "finished" and r.params.stop:
+            end = max(st[1], end - (max(len(s) for s in r.params.stop) - 1))
+        out = st[0][st[1]:end]
+        st[1] = end
+        return out
 
     def release(self, request_id: str) -> None:
         self.requests.pop(request_id, None)
         self.detok.pop(request_id, None)
+        self._text.pop(request_id, None)
 
     def generate(self, prompts: list, params: SamplingParams | list[SamplingParams] | None = None) -> list[dict]:
         plist = params if isinstance(params, list) else [params or SamplingParams()] * len(prompts)

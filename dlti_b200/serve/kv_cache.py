@@ -3,7 +3,7 @@ PagedAttention memory model, restated). Tensors: k_cache, v_cache = [L][num_bloc
 KV_heads_local, head_dim] in the compute dtype; the block manager is pure host-side bookkeeping."""
 from __future__ import annotations
 
-from collections import deque
+from collections import OrderedDict
 
 import torch
 
@@ -16,16 +16,19 @@ class BlockManager:
     automatic prefix caching, SP:vllm/v1/core/kv_cache_utils.py) is registered under that hash when its sequence
     has written it; a later prompt that starts with the same tokens takes a reference on the block instead of
     recomputing it. Reference counts keep shared blocks alive; a block whose count drops to zero goes to the
-    free list but keeps its hash until it is handed out again (oldest freed first), so a hot prefix survives as
-    long as memory allows."""
+    free list but keeps its hash until it is handed out again (oldest freed first, and within one freed sequence
+    the TAIL blocks first: losing block 0 would break the hash chain and strand every later block), so a hot
+    prefix survives as long as memory allows. A hit is confirmed by comparing the block's tokens and its parent
+    block, so a 64-bit hash collision can never hand one prompt another prompt's KV. The free list is an ordered
+    dict: taking, freeing and resurrecting a cached block are all O(1)."""
 
     def __init__(self, num_blocks: int, block_size: int = 16, enable_prefix_caching: bool = False):
         self.num_blocks, self.block_size = num_blocks, block_size
-        self.free: deque[int] = deque(range(num_blocks - 1, -1, -1))      # handed out from the right end
+        self.free: OrderedDict[int, None] = OrderedDict((b, None) for b in range(num_blocks))   # handed out from the front
         self.prefix_caching = enable_prefix_caching
         self.ref = [0] * num_blocks
         self.hash_of: dict[int, int] = {}          # block -> prefix hash
-        self.cached: dict[int, int] = {}           # prefix hash -> block
+        self.cached: dict[int, tuple] = {}         # prefix hash -> (block, parent block or -1, tokens of the block)
         self.hits = self.queries = 0               # in tokens
 
     def blocks_needed(self, num_tokens: int) -> int:
@@ -35,9 +38,9 @@ class BlockManager:
         return self.blocks_needed(num_tokens) - have <= len(self.free)
 
     def _take(self) -> int:
-        b = self.free.pop()
+        b, _ = self.free.popitem(last=False)
         h = self.hash_of.pop(b, None)              # the block is about to be overwritten: forget its old content
-        if h is not None and self.cached.get(h) == b:
+        if h is not None and self.cached.get(h, (None,))[0] == b:
             del self.cached[h]
         self.ref[b] = 1
         return b
@@ -53,15 +56,16 @@ class BlockManager:
 
     def release(self, blocks: list[int]) -> None:
         if not self.prefix_caching:
-            for b in blocks:
+            for b in reversed(blocks):             # most recently freed first (warm in L2), blocks[0] at the front
                 self.ref[b] = 0
-            self.free.extend(reversed(blocks))
+                self.free[b] = None
+                self.free.move_to_end(b, last=False)
             blocks.clear()
             return
-        for b in blocks:                           # oldest-freed-first reuse: new entries go to the FRONT
+        for b in reversed(blocks):                 # oldest-freed-first reuse: new entries go to the BACK, tail first
             self.ref[b] -= 1
             if self.ref[b] == 0:
-                self.free.appendleft(b)
+                self.free[b] = None
         blocks.clear()
 
     # ---- prefix cache -----------------------------------------------------------------------------
@@ -79,14 +83,15 @@ class BlockManager:
             return []
         self.queries += len(tokens)
         out = []
-        for h in self._chain(tokens, (len(tokens) - 1) // self.block_size):
-            b = self.cached.get(h)
-            if b is None:
-                break
-            out.append(b)
+        bs = self.block_size
+        for i, h in enumerate(self._chain(tokens, (len(tokens) - 1) // bs)):
+            e = self.cached.get(h)
+            if e is None or e[1] != (out[-1] if out else -1) or e[2] != tuple(tokens[i * bs:(i + 1) * bs]):
+                break                              # miss, or a hash collision (different tokens / different parent)
+            out.append(e[0])
         for b in out:
             if self.ref[b] == 0:
-                self.free.remove(b)                # resurrect a cached block that was waiting in the free list
+                del self.free[b]                   # resurrect a cached block that was waiting in the free list
             self.ref[b] += 1
         self.hits += len(out) * self.block_size
         return out
@@ -95,14 +100,15 @@ class BlockManager:
         """The first num_written tokens of the sequence are in `blocks`: publish its full blocks."""
         if not self.prefix_caching:
             return
-        for i, h in enumerate(self._chain(tokens, min(num_written // self.block_size, len(blocks)))):
+        bs = self.block_size
+        for i, h in enumerate(self._chain(tokens, min(num_written // bs, len(blocks)))):
             b = blocks[i]
             if b in self.hash_of:
                 continue
             if h in self.cached:                   # another sequence published the same prefix first
                 continue
             self.hash_of[b] = h
-            self.cached[h] = b
+            self.cached[h] = (b, blocks[i - 1] if i else -1, tuple(tokens[i * bs:(i + 1) * bs]))
 
     @property
     def num_free(self) -> int:

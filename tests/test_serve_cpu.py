@@ -652,3 +652,43 @@ def test_load_generator_against_live_server(tmp_path):
         proc.terminate()
         proc.join(timeout=5)
     assert eng.blocks.num_free == eng.blocks.num_blocks and not any(eng.blocks.ref)
+
+
+class _LetterTokenizer(ByteTokenizer):
+    """One lowercase letter per token: a stop string of n characters always spans n tokens."""
+
+    def decode(self, ids, skip_special_tokens=True):
+        return "".join(chr(97 + i % 26) for i in ids)
+
+
+@pytest.mark.parametrize("async_sched", [False, True])
+def test_stop_strings_end_generation_and_are_not_streamed(async_sched):
+    """OpenAI `stop` strings: a match that spans several tokens ends the request with finish_reason "stop", the
+    text is cut before the match, and no later text reaches a streaming client."""
+    cfg, full, eng = make_engine(async_scheduling=async_sched)
+    eng.tokenizer = _LetterTokenizer(cfg.vocab_size)
+    prompt = [1, 50, 51]
+    ref = eng.generate([prompt], SamplingParams(max_tokens=24, temperature=0.0, ignore_eos=True))[0]
+    text = ref["text"]
+    assert len(text) == 24 and ref["finish_reason"] == "length"
+    # a 3-token stop string whose first occurrence starts at character k
+    k = next(i for i in range(4, 16) if text.find(text[i:i + 3]) == i)
+    stop = text[k:k + 3]
+    # non-streaming
+    o = eng.generate([prompt], SamplingParams(max_tokens=24, temperature=0.0, ignore_eos=True, stop=[stop, "~~~~~~"]))[0]
+    assert o["finish_reason"] == "stop" and o["text"] == text[:k]
+    assert k + 3 <= len(o["token_ids"]) <= k + 4          # ended at the match (async: at most one token late)
+    # streaming: pieces as the server hands them out, one per engine step
+    rid = eng.add_request(prompt, SamplingParams(max_tokens=24, temperature=0.0, ignore_eos=True, stop=[stop, "~~~~~~"]))
+    pieces, reason = [], None
+    while eng.has_unfinished():
+        for out in eng.step():
+            pieces.append(eng.text_delta(out.request_id, final=out.finished))
+            if out.finished:
+                reason = out.finish_reason
+    assert reason == "stop" and "".join(pieces) == text[:k]
+    assert all(stop not in "".join(pieces[:i + 1]) for i in range(len(pieces)))
+    eng.release(rid)
+    # a stop string that never occurs changes nothing, and the held-back tail is flushed at the end
+    o = eng.generate([prompt], SamplingParams(max_tokens=24, temperature=0.0, ignore_eos=True, stop=["~~~~~~"]))[0]
+    assert o["finish_reason"] == "length" and o["text"] == text

@@ -55,6 +55,10 @@ int dlti_make_tmap_2d(CUtensorMap* out, const void* base, uint64_t inner, uint64
                       uint64_t ld_elems, uint32_t box_inner, uint32_t box_outer, int elem_bytes,
                       int swizzle_bytes /*128,64,32,0*/);
 
+// Same map for 16-bit elements with the 128-byte swizzle, served from a process-wide cache.
+int dlti_get_tmap(CUtensorMap* out, const void* base, uint64_t inner, uint64_t outer, uint64_t ld_elems,
+                  uint32_t box_inner, uint32_t box_outer);
+
 #ifdef __CUDACC__
 // Launch `kernel` on `stream`, as a programmatic dependent of the previous kernel in the stream when PDL is on.
 // `rows` = token rows of the step: PDL pays off while a step is latency-bound (measured on B200, Llama-2-7B decode:

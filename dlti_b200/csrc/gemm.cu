@@ -21,8 +21,6 @@
 // stack.
 #include "common.cuh"
 
-#include <mutex>
-#include <unordered_map>
 #include <string>
 #include <cstring>
 #include <cstdio>
@@ -524,43 +522,9 @@ gemm_tcgen05_kernel(const GemmParams p, const __grid_constant__ CUtensorMap tmA,
 // ---------------------------------------------------------------------------
 // Host side
 // ---------------------------------------------------------------------------
-struct TmapKey {
-  const void* base;
-  uint64_t inner, outer, ld;
-  uint32_t bi, bo;
-  bool operator==(const TmapKey& o) const {
-    return base == o.base && inner == o.inner && outer == o.outer && ld == o.ld && bi == o.bi &&
-           bo == o.bo;
-  }
-};
-struct TmapKeyHash {
-  size_t operator()(const TmapKey& k) const {
-    size_t h = reinterpret_cast<size_t>(k.base);
-    auto mix = [&](uint64_t v) { h ^= v + 0x9e3779b97f4a7c15ull + (h << 6) + (h >> 2); };
-    mix(k.inner); mix(k.outer); mix(k.ld); mix(((uint64_t)k.bi << 32) | k.bo);
-    return h;
-  }
-};
-std::mutex g_tm_mu;
-std::unordered_map<TmapKey, CUtensorMap, TmapKeyHash> g_tm_cache;
-
-int get_tmap(CUtensorMap* out, const void* base, uint64_t inner, uint64_t outer, uint64_t ld,
-             uint32_t bi, uint32_t bo) {
-  TmapKey key{base, inner, outer, ld, bi, bo};
-  {
-    std::lock_guard<std::mutex> g(g_tm_mu);
-    auto it = g_tm_cache.find(key);
-    if (it != g_tm_cache.end()) {
-      *out = it->second;
-      return 0;
-    }
-  }
-  int rc = dlti_make_tmap_2d(out, base, inner, outer, ld, bi, bo, 2, 128);
-  if (rc) return rc;
-  std::lock_guard<std::mutex> g(g_tm_mu);
-  if (g_tm_cache.size() > 65536) g_tm_cache.clear();
-  g_tm_cache.emplace(key, *out);
-  return 0;
+inline int get_tmap(CUtensorMap* out, const void* base, uint64_t inner, uint64_t outer, uint64_t ld, uint32_t bi,
+                    uint32_t bo) {
+  return dlti_get_tmap(out, base, inner, outer, ld, bi, bo);
 }
 
 template <int BN, bool A_MN, bool B_MN, bool GATHER, bool PUSH = false, bool SK = false>

@@ -46,6 +46,11 @@ struct Gemm2Params {
   int vec_ok;
   float alpha;
   uint32_t idesc;
+  // Ragged last wave: when the tiles left for the last wave fill at most half of the clusters, each of them
+  // is cut into two 256x128 halves (units >= split_from; UMMA N = 128, idesc_half), so the last wave lasts
+  // half as long. split_from == nmb2 * nnb: no tile is split.
+  uint32_t idesc_half;
+  int split_from;
   // stream-K: tiles [0, sk_tiles) are cut into `gridDim/2` equal ranges of (tile, k-block) iterations,
   // tiles [sk_tiles, total) are handed out round-robin. sk_tiles == 0 => plain data-parallel schedule.
   // SwiGLU mode (swiglu_ff > 0): B is the [2*ff, K] gate|up weight; CTA rank 0 stages 128 gate rows and
@@ -75,13 +80,16 @@ struct Gemm2Params {
 // tail piece from the workspace before the normal epilogue.
 struct Seg {
   int tile, kb0, kb1;
+  int half;      // -1: the whole 256x256 tile; 0 / 1: its left / right 256x128 half
 };
 struct SegIter {
   long long it, end;      // stream-K iteration range of this cluster
-  int next_dp, total, step, nkb;
+  int next_dp, total, step, nkb, split_from;
   __device__ SegIter(const Gemm2Params& p, int cid, int ncl) {
     nkb = p.nkb_main + p.nkb_ext;
+    split_from = p.split_from;
     total = p.nmb2 * p.nnb;
+    total += total - split_from;      // work units: whole tiles, then two halves for every split tile
     step = ncl;
     next_dp = p.sk_tiles + cid;
     if (p.sk_tiles > 0) {
@@ -101,11 +109,18 @@ struct SegIter {
       s.kb0 = (int)(it - (long long)s.tile * nkb);
       const long long left = end - it;
       s.kb1 = (left < nkb - s.kb0) ? s.kb0 + (int)left : nkb;
+      s.half = -1;
       it += s.kb1 - s.kb0;
       return true;
     }
     if (next_dp < total) {
-      s.tile = next_dp; s.kb0 = 0; s.kb1 = nkb;
+      if (next_dp < split_from) {
+        s.tile = next_dp; s.half = -1;
+      } else {
+        const int h = next_dp - split_from;
+        s.tile = split_from + (h >> 1); s.half = h & 1;
+      }
+      s.kb0 = 0; s.kb1 = nkb;
       next_dp += step;
       return true;
     }
@@ -175,7 +190,8 @@ __device__ __forceinline__ void umma_commit_2sm(uint32_t bar) {
 template <bool B_MN>
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(NUM_THREADS, 1)
 gemm2_kernel(const Gemm2Params p, const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
-             const __grid_constant__ CUtensorMap tmA2, const __grid_constant__ CUtensorMap tmB2) {
+             const __grid_constant__ CUtensorMap tmA2, const __grid_constant__ CUtensorMap tmB2,
+             const __grid_constant__ CUtensorMap tmBh, const __grid_constant__ CUtensorMap tmB2h) {
   extern __shared__ uint8_t smem_raw[];
   const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;
   const uint32_t bar_base = smem_base + STAGES * STAGE_BYTES;
@@ -229,23 +245,29 @@ gemm2_kernel(const Gemm2Params p, const __grid_constant__ CUtensorMap tmA, const
         const int m_blk = sg.tile - n_blk * p.nmb2;
         const int m0 = m_blk * 2 * BM + (int)rank * BM;          // this CTA's A rows
         // this CTA's half of the B tile (SwiGLU mode: gate rows for rank 0, the matching up rows for rank 1)
-        const int n0 = p.swiglu_ff > 0 ? n_blk * (BN / 2) + (int)rank * p.swiglu_ff : n_blk * BN + (int)rank * (BN / 2);
+        // A half tile needs only 64 B rows per CTA (tmBh / tmB2h: the same matrices with 64-row boxes).
+        const bool hf = sg.half >= 0;
+        const uint32_t tx = hf ? 2 * (A_BYTES + B_BYTES / 2) : 2 * STAGE_BYTES;
+        int n0;
+        if (sg.half < 0) n0 = p.swiglu_ff > 0 ? n_blk * (BN / 2) + (int)rank * p.swiglu_ff : n_blk * BN + (int)rank * (BN / 2);
+        else n0 = p.swiglu_ff > 0 ? n_blk * (BN / 2) + sg.half * (BN / 4) + (int)rank * p.swiglu_ff
+                                  : n_blk * BN + sg.half * (BN / 2) + (int)rank * (BN / 4);
         for (int kb = sg.kb0; kb < sg.kb1; ++kb) {
           mbar_wait_bounded(empty_bar(stage), phase ^ 1u);
           const uint32_t sa = smem_base + stage * STAGE_BYTES;
           const uint32_t sb = sa + A_BYTES;
           const uint32_t fb = mapa_rank(full_bar(stage), 0);      // the leader's barrier
-          if (leader) mbar_expect_tx(full_bar(stage), 2 * STAGE_BYTES);
+          if (leader) mbar_expect_tx(full_bar(stage), tx);
           const bool ext = kb >= p.nkb_main;
           const CUtensorMap* ma = ext ? &tmA2 : &tmA;
-          const CUtensorMap* mb = ext ? &tmB2 : &tmB;
+          const CUtensorMap* mb = ext ? (hf ? &tmB2h : &tmB2) : (hf ? &tmBh : &tmB);
           const int k0 = (ext ? kb - p.nkb_main : kb) * BK;
           tma_load_2d_2sm(sa, ma, fb, k0, m0);
           if constexpr (!B_MN) {
             tma_load_2d_2sm(sb, mb, fb, k0, n0);
           } else {
-#pragma unroll
-            for (int j = 0; j < (BN / 2) / 64; ++j) tma_load_2d_2sm(sb + j * (BK * 128), mb, fb, n0 + 64 * j, k0);
+            tma_load_2d_2sm(sb, mb, fb, n0, k0);
+            if (!hf) tma_load_2d_2sm(sb + BK * 128, mb, fb, n0 + 64, k0);
           }
           if (++stage == STAGES) { stage = 0; phase ^= 1u; }
         }
@@ -268,6 +290,7 @@ gemm2_kernel(const Gemm2Params p, const __grid_constant__ CUtensorMap tmA, const
         mbar_wait_bounded(tempty_bar(acc), acc_phase ^ 1u);
         tc_fence_after();
         const uint32_t d_tmem = tmem_base + (uint32_t)(acc * BN);
+        const uint32_t idesc = sg.half < 0 ? p.idesc : p.idesc_half;
         for (int kb = sg.kb0; kb < sg.kb1; ++kb) {
           mbar_wait_bounded(full_bar(stage), phase);
           tc_fence_after();
@@ -278,7 +301,7 @@ gemm2_kernel(const Gemm2Params p, const __grid_constant__ CUtensorMap tmA, const
 #pragma unroll
             for (int k = 0; k < BK / UMMA_K; ++k)
               umma_f16_ss_2sm(d_tmem, a.at(k * (UMMA_K * 2)), b.at(B_MN ? k * (UMMA_K * 128) : k * (UMMA_K * 2)),
-                              p.idesc, (kb > sg.kb0 || k > 0) ? 1u : 0u);
+                              idesc, (kb > sg.kb0 || k > 0) ? 1u : 0u);
             umma_commit_2sm(empty_bar(stage));
             if (kb == sg.kb1 - 1) umma_commit_2sm(tfull_bar(acc));
           }
@@ -300,7 +323,8 @@ gemm2_kernel(const Gemm2Params p, const __grid_constant__ CUtensorMap tmA, const
       const int n_blk = sg.tile / p.nmb2;
       const int m_blk = sg.tile - n_blk * p.nmb2;
       const int row = m_blk * 2 * BM + (int)rank * BM + quarter * 32 + lane;
-      const int n0 = n_blk * BN;
+      const int ncols = sg.half < 0 ? BN : BN / 2;                 // accumulator columns of this unit
+      const int n0 = n_blk * BN + (sg.half > 0 ? BN / 2 : 0);
       const bool helper = sg.kb0 > 0;              // write raw partial accumulators to the workspace
       const bool fixup = sg.kb1 < nkb_total;       // add the helper's partial (range my_range + 1)
       // float4 index of (chunk 0, quad 0, this thread's row) in the workspace slot used by this segment
@@ -320,12 +344,13 @@ gemm2_kernel(const Gemm2Params p, const __grid_constant__ CUtensorMap tmA, const
         // 16-bit module-boundary semantics of the unfused path: gate, up and silu(gate) are rounded to the
         // storage type before the product (bit-identical to dlti_swiglu_fwd on the stored gate|up tensor).
         const bool bf = p.out_dtype == DLTI_BF16;
-        uint16_t* crow = reinterpret_cast<uint16_t*>(p.C) + (long long)row * p.ldc + n_blk * (BN / 2);
+        uint16_t* crow = reinterpret_cast<uint16_t*>(p.C) + (long long)row * p.ldc + n_blk * (BN / 2) +
+                         (sg.half > 0 ? BN / 4 : 0);
 #pragma unroll 1
-        for (int c = 0; c < 4; ++c) {
+        for (int c = 0; c < ncols / 64; ++c) {
           uint32_t vg[32], vu[32];
           tmem_ld_32x32b_x32(t_row + c * 32, vg);
-          tmem_ld_32x32b_x32(t_row + 128 + c * 32, vu);
+          tmem_ld_32x32b_x32(t_row + ncols / 2 + c * 32, vu);
           tmem_wait_ld();
           if (row < p.M) {
             float o[32];
@@ -373,7 +398,7 @@ gemm2_kernel(const Gemm2Params p, const __grid_constant__ CUtensorMap tmA, const
           }
         };
 #pragma unroll 1
-        for (int hb = 0; hb < BN / 128; ++hb) {
+        for (int hb = 0; hb < ncols / 128; ++hb) {
           const int hcol = n0 + hb * 128;
           if (hcol >= p.N) break;
           if (hcol < p.rope_cols) {
@@ -442,7 +467,7 @@ gemm2_kernel(const Gemm2Params p, const __grid_constant__ CUtensorMap tmA, const
         };
         fetch(0);
 #pragma unroll 1
-        for (int c = 0; c < BN / 32; ++c) {
+        for (int c = 0; c < ncols / 32; ++c) {
           const int col0 = n0 + c * 32;
           if (col0 >= ff) break;
           uint32_t v[32];
@@ -450,7 +475,7 @@ gemm2_kernel(const Gemm2Params p, const __grid_constant__ CUtensorMap tmA, const
           int4 gc[4], uc[4];
 #pragma unroll
           for (int i = 0; i < 4; ++i) { gc[i] = gq[i]; uc[i] = uq[i]; }
-          if (c + 1 < BN / 32) fetch(c + 1);
+          if (c + 1 < ncols / 32) fetch(c + 1);
           tmem_wait_ld();
           if (rok) {
 #pragma unroll
@@ -481,7 +506,7 @@ gemm2_kernel(const Gemm2Params p, const __grid_constant__ CUtensorMap tmA, const
         }
       } else
 #pragma unroll 1
-      for (int c = 0; c < BN / 32; ++c) {
+      for (int c = 0; c < ncols / 32; ++c) {
         const int col0 = n0 + c * 32;
         if (col0 >= p.N) break;
         uint32_t v[32];
@@ -603,7 +628,7 @@ gemm2_kernel(const Gemm2Params p, const __grid_constant__ CUtensorMap tmA, const
 
 template <bool B_MN>
 int launch2(const Gemm2Params& p, const CUtensorMap& a, const CUtensorMap& b, const CUtensorMap& a2,
-            const CUtensorMap& b2, int grid, cudaStream_t stream) {
+            const CUtensorMap& b2, const CUtensorMap& bh, const CUtensorMap& b2h, int grid, cudaStream_t stream) {
   static bool configured[64] = {false};
   int dev = 0;
   cudaGetDevice(&dev);
@@ -611,7 +636,7 @@ int launch2(const Gemm2Params& p, const CUtensorMap& a, const CUtensorMap& b, co
     DLTI_CUDA_CHECK(cudaFuncSetAttribute(gemm2_kernel<B_MN>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES));
     configured[dev & 63] = true;
   }
-  gemm2_kernel<B_MN><<<grid, NUM_THREADS, SMEM_BYTES, stream>>>(p, a, b, a2, b2);
+  gemm2_kernel<B_MN><<<grid, NUM_THREADS, SMEM_BYTES, stream>>>(p, a, b, a2, b2, bh, b2h);
   dlti_count_launch();
   return (int)cudaGetLastError();
 }
@@ -649,6 +674,20 @@ const SkWorkspace* sk_workspace(cudaStream_t stream) {
   return &g_sk_ws[g_sk_ws_count++];
 }
 
+// Ragged last wave (see Gemm2Params::split_from): with T tiles on C clusters, the T % C tiles of the last wave
+// are cut in two when that lets the wave finish in half the time (2 * (T % C) <= C). Llama-2-7B at M = 4096:
+// the [4096 x 4096] outputs (o_proj, down_proj, every input gradient of qkv / gate_up) are 256 tiles on 74
+// clusters = 3.46 waves -> 3.5 instead of 4. DLTI_GEMM_TAILSPLIT=0 switches it off (A/B).
+void set_tail_split(Gemm2Params& p, int grid, int dtype, bool b_mn) {
+  static const bool on = []() { const char* e = getenv("DLTI_GEMM_TAILSPLIT"); return !(e && e[0] == '0'); }();
+  const int total = p.nmb2 * p.nnb, ncl = grid / 2;
+  p.split_from = total;
+  p.idesc_half = umma_idesc_f16(dtype, 2 * BM, BN / 2, false, b_mn);
+  if (!on || p.sk_tiles > 0 || ncl < 1 || total <= ncl) return;
+  const int rem = total % ncl;
+  if (rem > 0 && 2 * rem <= ncl) p.split_from = total - rem;
+}
+
 }  // namespace
 
 // Same contract as dlti_gemm restricted to: A K-major, no split-K. Returns DLTI_ERR_UNSUPPORTED for
@@ -677,17 +716,20 @@ DLTI_API int dlti_gemm_2cta(const void* A, const void* B, void* C, const void* R
              (!R || (((reinterpret_cast<uintptr_t>(R) & 15) == 0) && ((ldr * 2) % 16 == 0)));
   p.alpha = alpha;
   p.idesc = umma_idesc_f16(in_dtype, 2 * BM, BN, false, b_mn != 0);
-  CUtensorMap ta, tb, ta2, tb2;
+  CUtensorMap ta, tb, ta2, tb2, tbh, tb2h;
   int rc;
-  if ((rc = dlti_make_tmap_2d(&ta, A, K, M, lda, 64, BM, 2, 128))) return rc;
-  rc = b_mn ? dlti_make_tmap_2d(&tb, B, N, K, ldb, 64, 64, 2, 128) : dlti_make_tmap_2d(&tb, B, K, N, ldb, 64, BN / 2, 2, 128);
+  if ((rc = dlti_get_tmap(&ta, A, K, M, lda, 64, BM))) return rc;
+  rc = b_mn ? dlti_get_tmap(&tb, B, N, K, ldb, 64, 64) : dlti_get_tmap(&tb, B, K, N, ldb, 64, BN / 2);
   if (rc) return rc;
-  ta2 = ta; tb2 = tb;
+  tbh = tb;                  // MN-major: a half tile is one of the two 64x64 boxes
+  if (!b_mn && (rc = dlti_get_tmap(&tbh, B, K, N, ldb, 64, BN / 4))) return rc;
+  ta2 = ta; tb2 = tb; tb2h = tbh;
   if (p.nkb_ext > 0) {
-    if ((rc = dlti_make_tmap_2d(&ta2, A2, K2, M, lda2, 64, BM, 2, 128))) return rc;
-    rc = b_mn ? dlti_make_tmap_2d(&tb2, B2, N, K2, ldb2, 64, 64, 2, 128)
-              : dlti_make_tmap_2d(&tb2, B2, K2, N, ldb2, 64, BN / 2, 2, 128);
+    if ((rc = dlti_get_tmap(&ta2, A2, K2, M, lda2, 64, BM))) return rc;
+    rc = b_mn ? dlti_get_tmap(&tb2, B2, N, K2, ldb2, 64, 64) : dlti_get_tmap(&tb2, B2, K2, N, ldb2, 64, BN / 2);
     if (rc) return rc;
+    tb2h = tb2;
+    if (!b_mn && (rc = dlti_get_tmap(&tb2h, B2, K2, N, ldb2, 64, BN / 4))) return rc;
   }
   int grid = dlti_num_sms() & ~1;
   const int total = p.nmb2 * p.nnb;
@@ -713,7 +755,9 @@ DLTI_API int dlti_gemm_2cta(const void* A, const void* B, void* C, const void* R
       }
     }
   }
-  return b_mn ? launch2<true>(p, ta, tb, ta2, tb2, grid, stream) : launch2<false>(p, ta, tb, ta2, tb2, grid, stream);
+  set_tail_split(p, grid, in_dtype, b_mn != 0);
+  return b_mn ? launch2<true>(p, ta, tb, ta2, tb2, tbh, tb2h, grid, stream)
+              : launch2<false>(p, ta, tb, ta2, tb2, tbh, tb2h, grid, stream);
 }
 
 // h[M, ff] = silu(A · Wg^T) * (A · Wu^T) with W = [gate rows (ff) ; up rows (ff)] stored [2*ff, K]
@@ -735,14 +779,16 @@ DLTI_API int dlti_gemm_swiglu_2cta(const void* A, const void* W, void* Hout, int
   p.alpha = 1.f;
   p.idesc = umma_idesc_f16(dtype, 2 * BM, BN, false, false);
   p.swiglu_ff = ff;
-  CUtensorMap ta, tb;
+  CUtensorMap ta, tb, tbh;
   int rc;
-  if ((rc = dlti_make_tmap_2d(&ta, A, K, M, lda, 64, BM, 2, 128))) return rc;
-  if ((rc = dlti_make_tmap_2d(&tb, W, K, 2 * (long long)ff, ldw, 64, BN / 2, 2, 128))) return rc;
+  if ((rc = dlti_get_tmap(&ta, A, K, M, lda, 64, BM))) return rc;
+  if ((rc = dlti_get_tmap(&tb, W, K, 2 * (long long)ff, ldw, 64, BN / 2))) return rc;
+  if ((rc = dlti_get_tmap(&tbh, W, K, 2 * (long long)ff, ldw, 64, BN / 4))) return rc;
   int grid = dlti_num_sms() & ~1;
   const int total = p.nmb2 * p.nnb;
   if (2 * total < grid) grid = 2 * total;
-  return launch2<false>(p, ta, tb, ta, tb, grid, stream);
+  set_tail_split(p, grid, dtype, false);
+  return launch2<false>(p, ta, tb, ta, tb, tbh, tbh, grid, stream);
 }
 
 // d(gate|up)[M, 2*ff] = swiglu_backward(dh, gate|up) with dh = dY[M, K] · W_down ([K, ff], i.e. the
@@ -769,12 +815,13 @@ DLTI_API int dlti_gemm_swiglu_bwd_2cta(const void* dY, const void* Wdown, const 
   p.swiglu_bwd_ff = ff; p.gu = GU; p.ldgu = ldgu;
   CUtensorMap ta, tb;
   int rc;
-  if ((rc = dlti_make_tmap_2d(&ta, dY, K, M, ldy, 64, BM, 2, 128))) return rc;
-  if ((rc = dlti_make_tmap_2d(&tb, Wdown, ff, K, ldw, 64, 64, 2, 128))) return rc;
+  if ((rc = dlti_get_tmap(&ta, dY, K, M, ldy, 64, BM))) return rc;
+  if ((rc = dlti_get_tmap(&tb, Wdown, ff, K, ldw, 64, 64))) return rc;
   int grid = dlti_num_sms() & ~1;
   const int total = p.nmb2 * p.nnb;
   if (2 * total < grid) grid = 2 * total;
-  return launch2<true>(p, ta, tb, ta, tb, grid, stream);
+  set_tail_split(p, grid, dtype, true);
+  return launch2<true>(p, ta, tb, ta, tb, tb, tb, grid, stream);
 }
 
 // C[M, N] = rope(alpha * (A · B^T + A2 · B2^T)): the fused QKV projection (B = [N, K], optional LoRA
@@ -800,17 +847,20 @@ DLTI_API int dlti_gemm_rope_2cta(const void* A, const void* B, void* C, int M, i
   p.alpha = alpha;
   p.idesc = umma_idesc_f16(dtype, 2 * BM, BN, false, false);
   p.rope_pos = pos; p.rope_cos = cos_t; p.rope_sin = sin_t; p.rope_cols = rope_cols;
-  CUtensorMap ta, tb, ta2, tb2;
+  CUtensorMap ta, tb, ta2, tb2, tbh, tb2h;
   int rc;
-  if ((rc = dlti_make_tmap_2d(&ta, A, K, M, lda, 64, BM, 2, 128))) return rc;
-  if ((rc = dlti_make_tmap_2d(&tb, B, K, N, ldb, 64, BN / 2, 2, 128))) return rc;
-  ta2 = ta; tb2 = tb;
+  if ((rc = dlti_get_tmap(&ta, A, K, M, lda, 64, BM))) return rc;
+  if ((rc = dlti_get_tmap(&tb, B, K, N, ldb, 64, BN / 2))) return rc;
+  if ((rc = dlti_get_tmap(&tbh, B, K, N, ldb, 64, BN / 4))) return rc;
+  ta2 = ta; tb2 = tb; tb2h = tbh;
   if (p.nkb_ext > 0) {
-    if ((rc = dlti_make_tmap_2d(&ta2, A2, K2, M, lda2, 64, BM, 2, 128))) return rc;
-    if ((rc = dlti_make_tmap_2d(&tb2, B2, K2, N, ldb2, 64, BN / 2, 2, 128))) return rc;
+    if ((rc = dlti_get_tmap(&ta2, A2, K2, M, lda2, 64, BM))) return rc;
+    if ((rc = dlti_get_tmap(&tb2, B2, K2, N, ldb2, 64, BN / 2))) return rc;
+    if ((rc = dlti_get_tmap(&tb2h, B2, K2, N, ldb2, 64, BN / 4))) return rc;
   }
   int grid = dlti_num_sms() & ~1;
   const int total = p.nmb2 * p.nnb;
   if (2 * total < grid) grid = 2 * total;
-  return launch2<false>(p, ta, tb, ta2, tb2, grid, stream);
+  set_tail_split(p, grid, dtype, false);
+  return launch2<false>(p, ta, tb, ta2, tb2, tbh, tb2h, grid, stream);
 }

@@ -9,6 +9,7 @@
 #include <cstdlib>
 #include <cstring>
 #include <mutex>
+#include <unordered_map>
 
 #include <cudaTypedefs.h>
 
@@ -109,6 +110,49 @@ int dlti_make_tmap_2d(CUtensorMap* out, const void* base, uint64_t inner, uint64
     dlti_set_error(buf);
     return DLTI_ERR_DRIVER;
   }
+  return 0;
+}
+
+// Cached 16-bit / 128B-swizzle tensor maps: the training step encodes the same (pointer, shape, box) a few
+// thousand times per step (weights, recycled activation buffers); a map is a pure function of its key, so a
+// hit is always valid. cuTensorMapEncodeTiled costs ~1-2 us of host time per call.
+namespace {
+struct TmapKey {
+  const void* base;
+  uint64_t inner, outer, ld;
+  uint32_t bi, bo;
+  bool operator==(const TmapKey& o) const {
+    return base == o.base && inner == o.inner && outer == o.outer && ld == o.ld && bi == o.bi && bo == o.bo;
+  }
+};
+struct TmapKeyHash {
+  size_t operator()(const TmapKey& k) const {
+    size_t h = reinterpret_cast<size_t>(k.base);
+    auto mix = [&](uint64_t v) { h ^= v + 0x9e3779b97f4a7c15ull + (h << 6) + (h >> 2); };
+    mix(k.inner); mix(k.outer); mix(k.ld); mix(((uint64_t)k.bi << 32) | k.bo);
+    return h;
+  }
+};
+std::mutex g_tm_mu;
+std::unordered_map<TmapKey, CUtensorMap, TmapKeyHash> g_tm_cache;
+}  // namespace
+
+int dlti_get_tmap(CUtensorMap* out, const void* base, uint64_t inner, uint64_t outer, uint64_t ld, uint32_t bi,
+                  uint32_t bo) {
+  TmapKey key{base, inner, outer, ld, bi, bo};
+  {
+    std::lock_guard<std::mutex> g(g_tm_mu);
+    auto it = g_tm_cache.find(key);
+    if (it != g_tm_cache.end()) {
+      *out = it->second;
+      return 0;
+    }
+  }
+  int rc = dlti_make_tmap_2d(out, base, inner, outer, ld, bi, bo, 2, 128);
+  if (rc) return rc;
+  std::lock_guard<std::mutex> g(g_tm_mu);
+  if (g_tm_cache.size() > 65536) g_tm_cache.clear();
+  g_tm_cache.emplace(key, *out);
   return 0;
 }
 

@@ -195,7 +195,7 @@ def test_gemm_swiglu_fused_epilogue(M, ff, K, dtype):
     _check(h, swiglu_fwd_ref(gemm_ref(x, w, out_dtype=torch.float32).to(dtype)).float(), scale_tol=2e-2)
 
 
-@pytest.mark.parametrize("M,ff,d", [(4096, 2048, 512), (2050, 11008, 256), (4096, 4128, 128)])
+@pytest.mark.parametrize("M,ff,d", [(4096, 2048, 512), (2050, 11008, 256), (4096, 4128, 128), (4096, 4096, 192)])
 def test_gemm_swiglu_bwd_fused_epilogue(M, ff, d):
     """down-projection input-gradient GEMM with the SwiGLU backward in the epilogue == GEMM + stand-alone kernel."""
     from dlti_b200.ops.elementwise import swiglu_bwd
@@ -208,9 +208,13 @@ def test_gemm_swiglu_bwd_fused_epilogue(M, ff, d):
     ref = swiglu_bwd(gemm(dy, w_down, b_mn=True), gu)
     assert out.shape == (M, 2 * ff)
     _check(out, ref.float(), scale_tol=4e-3)
+    # fp32 oracle of the whole fused op (dh rounded to the storage type, as the module boundary would)
+    from dlti_b200.ops.elementwise import swiglu_bwd_ref
+    dh = gemm_ref(dy.cpu(), w_down.cpu(), b_mn=True, out_dtype=torch.float32).to(torch.bfloat16)
+    _check(out.cpu(), swiglu_bwd_ref(dh, gu.cpu()).float(), scale_tol=2e-2)
 
 
-@pytest.mark.parametrize("H,KV", [(32, 32), (16, 4)])
+@pytest.mark.parametrize("H,KV", [(32, 32), (16, 4), (16, 8)])
 def test_gemm_rope_fused_epilogue(H, KV):
     """QKV projection (+ LoRA K-extension) with RoPE in the epilogue == GEMM followed by the RoPE kernel."""
     from dlti_b200.ops.elementwise import rope_, rope_tables
@@ -230,3 +234,8 @@ def test_gemm_rope_fused_epilogue(H, KV):
     _check(y, ref.float(), scale_tol=4e-3)
     # v heads untouched by the rotation
     assert torch.equal(y[:, (H + KV) * hd:], gemm(x, w, a2=a2, b2=b2)[:, (H + KV) * hd:])
+    # fp32 oracle of the whole fused op (projection rounded to the storage type, then rotated)
+    from dlti_b200.ops.elementwise import rope_ref
+    proj = gemm_ref(x.cpu(), w.cpu(), a2=a2.cpu(), b2=b2.cpu(), out_dtype=torch.float32).to(torch.bfloat16)
+    oracle = rope_ref(proj, pos.cpu(), cos.cpu(), sin.cpu(), H + KV, hd)
+    _check(y.cpu(), oracle.float(), scale_tol=2e-2)

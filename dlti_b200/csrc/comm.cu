@@ -342,6 +342,35 @@ __global__ void __launch_bounds__(128) tp_pull_reduce_norm_push_kernel(Peers par
   __threadfence_system();
 }
 
+// K15: embedding over a vocabulary-sharded table (rank r owns rows [r * rows_per_rank, (r + 1) * rows_per_rank)):
+// every token's row is fetched from its owner rank with 16-byte peer loads (the table is immutable during a
+// step: non-coherent loads). Replaces "all-gather the table, then look up": per step only the rows that are
+// actually used cross NVLink, and no full-size staging copy of the table exists.
+template <typename T>
+__global__ void __launch_bounds__(256) embedding_peer_kernel(const long long* __restrict__ ids, Peers shards,
+                                                            T* __restrict__ out, long long tokens, int d,
+                                                            long long rows_per_rank, long long vocab) {
+  __shared__ const void* s_sh[MAX_RANKS];
+#pragma unroll
+  for (int i = 0; i < MAX_RANKS; ++i)
+    if (threadIdx.x == i) s_sh[i] = shards.p[i];
+  __syncthreads();
+  const int vpr = d >> 3;
+  const long long total = tokens * vpr;
+  for (long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x; idx < total;
+       idx += (long long)gridDim.x * blockDim.x) {
+    const long long t = idx / vpr;
+    const int v = (int)(idx - t * vpr);
+    const long long id = ids[t];
+    int4 val = make_int4(0, 0, 0, 0);
+    if (id >= 0 && id < vocab) {
+      const long long owner = id / rows_per_rank;
+      val = ld_nc_v4(reinterpret_cast<const T*>(s_sh[owner]) + (id - owner * rows_per_rank) * d + v * 8);
+    }
+    *reinterpret_cast<int4*>(out + t * d + v * 8) = val;
+  }
+}
+
 int fill(Peers& P, const void* const* ptrs, int world) {
   if (world < 1 || world > MAX_RANKS) return DLTI_ERR_BAD_ARG;
   for (int i = 0; i < MAX_RANKS; ++i) P.p[i] = i < world ? const_cast<void*>(ptrs[i]) : nullptr;
@@ -419,6 +448,26 @@ DLTI_API int dlti_adamw_push(const void* const* masters, float* m, float* v, flo
   adamw_push_kernel<<<(unsigned)(want > cap ? cap : want), 256, 0, st>>>(
       P, m, v, g, lo, n, rank, world, lr, b1, b2, eps, wd, bc1, bc2, gnorm_sq, inv_scale, max_norm,
       skipped_out);
+  dlti_count_launch();
+  return (int)cudaGetLastError();
+}
+
+DLTI_API int dlti_embedding_peer(const long long* ids, const void* const* shards, void* out, long long tokens,
+                                 int d, long long rows_per_rank, long long vocab, int world, int dtype,
+                                 cudaStream_t st) {
+  Peers P;
+  if (int rc = fill(P, shards, world)) return rc;
+  if (tokens <= 0) return 0;
+  if (d % 8 || rows_per_rank <= 0) return DLTI_ERR_BAD_ARG;
+  long long want = (tokens * (d / 8) + 255) / 256;
+  const long long cap = (long long)dlti_num_sms() * 8;
+  const unsigned grid = (unsigned)(want > cap ? cap : want);
+  if (dtype == DLTI_BF16)
+    embedding_peer_kernel<__nv_bfloat16><<<grid, 256, 0, st>>>(ids, P, (__nv_bfloat16*)out, tokens, d, rows_per_rank, vocab);
+  else if (dtype == DLTI_FP16)
+    embedding_peer_kernel<__half><<<grid, 256, 0, st>>>(ids, P, (__half*)out, tokens, d, rows_per_rank, vocab);
+  else
+    return DLTI_ERR_UNSUPPORTED;
   dlti_count_launch();
   return (int)cudaGetLastError();
 }

@@ -75,6 +75,53 @@ struct Gemm2Params {
   unsigned int* sk_flags;   // [ranges] ready counters + [ranges] consumed counters
 };
 
+// K1 (ZeRO-3 all-gather fused into the GEMM), CTA-pair form. Two independent attachments of a launch:
+//  * a gather JOB: four extra warps per CTA pull 64-row units of a row-sharded weight matrix from their owner
+//    ranks (peer loads over NVLink from the symmetric arena; the own rows with local loads) into a local
+//    staging buffer and bump a per-unit counter with a release once a 4-row chunk has landed. The job may
+//    belong to the B operand of this very launch (cold start) or — the normal case — to a matrix that a LATER
+//    launch consumes (the next layer's weights ride on this layer's GEMMs, a slice per launch);
+//  * a WAIT spec: the B operand of this launch is such a staging buffer; the TMA producer acquires the
+//    counters of the units a tile needs before it loads them (one relaxed sweep at kernel start takes the fast
+//    path when everything has already landed).
+// TMA only ever reads this GPU's staging buffer; peer memory is read with ld.global by the gather warps.
+constexpr int GATHER_CH = 16;              // chunks per 64-row unit (4 rows each)
+constexpr int GATHER_THREADS = 128;
+struct GatherJob {
+  const void* peer[16];     // every rank's shard base (peer-mapped; peer[rank] is local)
+  uint8_t* staging;         // local full matrix [world * rows_per_rank, row_bytes]
+  uint32_t* counters;       // [n_units] completed-chunk counters, monotonic across epochs
+  int* err;
+  long long row_bytes;
+  uint32_t target;          // unit complete  <=>  counters[u] >= target (= epoch * GATHER_CH)
+  int units_per_rank, n_units;
+  int rot;                  // job position j is unit (rot + j) % n_units
+  int j_begin, j_count;     // positions [j_begin, j_begin + j_count) belong to this launch; 0 = no job
+};
+struct WaitSpec {
+  const uint32_t* counters; // nullptr: B is plain memory
+  int* err;
+  uint32_t target;
+  int n_units;
+};
+
+__device__ __forceinline__ uint32_t ld_relaxed_gpu_u32(const uint32_t* p) {
+  uint32_t v;
+  asm volatile("ld.relaxed.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ void wait_unit(const WaitSpec& w, int u) {
+  if (u >= w.n_units) return;
+  const long long t0 = clock64();
+  while ((int32_t)(ld_acquire_gpu_u32(w.counters + u) - w.target) < 0) {
+    if (clock64() - t0 > 20000000000LL) {
+      if (w.err) atomicExch(w.err, 1);
+      return;
+    }
+    __nanosleep(32);
+  }
+}
+
 // One unit of work: k-blocks [kb0, kb1) of one 256x256 tile. kb0 > 0: the tile's head belongs to another
 // cluster -> this piece is written to the workspace; kb1 < nkb: this cluster owns the tile and adds the
 // tail piece from the workspace before the normal epilogue.
@@ -188,8 +235,8 @@ __device__ __forceinline__ void umma_commit_2sm(uint32_t bar) {
 }
 
 template <bool B_MN>
-__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(NUM_THREADS, 1)
-gemm2_kernel(const Gemm2Params p, const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(NUM_THREADS + GATHER_THREADS, 1)
+gemm2_kernel(const Gemm2Params p, const GatherJob gj, const WaitSpec ws_, const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
              const __grid_constant__ CUtensorMap tmA2, const __grid_constant__ CUtensorMap tmB2,
              const __grid_constant__ CUtensorMap tmBh, const __grid_constant__ CUtensorMap tmB2h) {
   extern __shared__ uint8_t smem_raw[];
@@ -203,6 +250,12 @@ gemm2_kernel(const Gemm2Params p, const __grid_constant__ CUtensorMap tmA, const
   volatile uint32_t* tmem_slot_ptr =
       reinterpret_cast<volatile uint32_t*>(smem_raw + (tmem_slot - smem_u32(smem_raw)));
 
+  __shared__ const void* s_peers[16];
+  if (gj.j_count > 0) {
+#pragma unroll
+    for (int i = 0; i < 16; ++i)   // static indices keep the by-value parameter in the constant bank
+      if (threadIdx.x == i) s_peers[i] = gj.peer[i];
+  }
   const int warp = __shfl_sync(0xffffffffu, threadIdx.x >> 5, 0), lane = threadIdx.x & 31;   // uniform for the compiler
   const uint32_t rank = __shfl_sync(0xffffffffu, cluster_ctarank(), 0);
   const bool leader = rank == 0;
@@ -235,6 +288,14 @@ gemm2_kernel(const Gemm2Params p, const __grid_constant__ CUtensorMap tmA, const
 
   if (warp == 0) {
     // ===================== TMA producer (both CTAs) =====================
+    bool all_ready = true;        // WAIT: every unit of B has already landed (gathered by earlier launches)
+    if (ws_.counters) {
+      for (int u = lane; u < ws_.n_units; u += 32)
+        if ((int32_t)(ld_relaxed_gpu_u32(ws_.counters + u) - ws_.target) < 0) all_ready = false;
+      all_ready = __all_sync(0xffffffffu, all_ready);
+      asm volatile("fence.acq_rel.gpu;" ::: "memory");
+      asm volatile("fence.proxy.async.global;" ::: "memory");
+    }
     if (lane == 0) {
       int stage = 0;
       uint32_t phase = 0;
@@ -252,6 +313,11 @@ gemm2_kernel(const Gemm2Params p, const __grid_constant__ CUtensorMap tmA, const
         if (sg.half < 0) n0 = p.swiglu_ff > 0 ? n_blk * (BN / 2) + (int)rank * p.swiglu_ff : n_blk * BN + (int)rank * (BN / 2);
         else n0 = p.swiglu_ff > 0 ? n_blk * (BN / 2) + sg.half * (BN / 4) + (int)rank * p.swiglu_ff
                                   : n_blk * BN + sg.half * (BN / 2) + (int)rank * (BN / 4);
+        if (!B_MN && !all_ready) {      // K-major B: this CTA's rows [n0, n0 + 128 or 64) = 2 or 1 units
+          wait_unit(ws_, n0 >> 6);
+          if (!hf) wait_unit(ws_, (n0 >> 6) + 1);
+          asm volatile("fence.proxy.async.global;" ::: "memory");
+        }
         for (int kb = sg.kb0; kb < sg.kb1; ++kb) {
           mbar_wait_bounded(empty_bar(stage), phase ^ 1u);
           const uint32_t sa = smem_base + stage * STAGE_BYTES;
@@ -262,6 +328,10 @@ gemm2_kernel(const Gemm2Params p, const __grid_constant__ CUtensorMap tmA, const
           const CUtensorMap* ma = ext ? &tmA2 : &tmA;
           const CUtensorMap* mb = ext ? (hf ? &tmB2h : &tmB2) : (hf ? &tmBh : &tmB);
           const int k0 = (ext ? kb - p.nkb_main : kb) * BK;
+          if (B_MN && !all_ready && !ext) {   // MN-major B: contraction rows [k0, k0 + 64) = unit kb
+            wait_unit(ws_, kb);
+            asm volatile("fence.proxy.async.global;" ::: "memory");
+          }
           tma_load_2d_2sm(sa, ma, fb, k0, m0);
           if constexpr (!B_MN) {
             tma_load_2d_2sm(sb, mb, fb, k0, n0);
@@ -309,6 +379,34 @@ gemm2_kernel(const Gemm2Params p, const __grid_constant__ CUtensorMap tmA, const
         }
         if (++acc == 2) { acc = 0; acc_phase ^= 1u; }
       }
+    }
+  } else if (warp >= 6) {
+    // ===================== gather warps (present when a job is attached) =====================
+    const int gt = threadIdx.x - NUM_THREADS;                  // 0..127
+    const long long chunk_bytes = 4 * gj.row_bytes;            // 4 rows
+    const long long unit_bytes = 64 * gj.row_bytes;
+    const int total_chunks = gj.j_count * GATHER_CH;
+    for (int c = blockIdx.x; c < total_chunks; c += gridDim.x) {
+      const int j = gj.j_begin + c / GATHER_CH, part = c % GATHER_CH;
+      int u = gj.rot + j;
+      u -= (u / gj.n_units) * gj.n_units;
+      const int owner = u / gj.units_per_rank;
+      const uint8_t* src = reinterpret_cast<const uint8_t*>(s_peers[owner]) +
+                           (long long)(u - owner * gj.units_per_rank) * unit_bytes + part * chunk_bytes;
+      uint8_t* dst = gj.staging + (long long)u * unit_bytes + part * chunk_bytes;
+      const long long nvec = chunk_bytes >> 4;
+      long long i = gt;
+      for (; i + 7 * GATHER_THREADS < nvec; i += 8 * GATHER_THREADS) {
+        int4 v[8];
+#pragma unroll
+        for (int q = 0; q < 8; ++q) v[q] = ld_nc_v4(src + ((i + q * GATHER_THREADS) << 4));
+#pragma unroll
+        for (int q = 0; q < 8; ++q) st_v4(dst + ((i + q * GATHER_THREADS) << 4), v[q]);
+      }
+      for (; i < nvec; i += GATHER_THREADS) st_v4(dst + (i << 4), ld_nc_v4(src + (i << 4)));
+      __threadfence();
+      asm volatile("bar.sync 2, 128;" ::: "memory");
+      if (gt == 0) red_release_gpu_add_u32(gj.counters + u, 1u);
     }
   } else {
     // ===================== epilogue (both CTAs; own 128 rows x 256 columns) =====================
@@ -626,9 +724,52 @@ gemm2_kernel(const Gemm2Params p, const __grid_constant__ CUtensorMap tmA, const
   }
 }
 
+// The gather role on its own (no GEMM to ride on: flushing what is left of a matrix, bandwidth probes).
+__global__ void __launch_bounds__(GATHER_THREADS) gather_job_kernel(const GatherJob gj) {
+  __shared__ const void* s_peers[16];
+#pragma unroll
+  for (int i = 0; i < 16; ++i)
+    if (threadIdx.x == i) s_peers[i] = gj.peer[i];
+  __syncthreads();
+  const int gt = threadIdx.x;
+  const long long chunk_bytes = 4 * gj.row_bytes, unit_bytes = 64 * gj.row_bytes;
+  const int total_chunks = gj.j_count * GATHER_CH;
+  for (int c = blockIdx.x; c < total_chunks; c += gridDim.x) {
+    const int j = gj.j_begin + c / GATHER_CH, part = c % GATHER_CH;
+    int u = gj.rot + j;
+    u -= (u / gj.n_units) * gj.n_units;
+    const int owner = u / gj.units_per_rank;
+    const uint8_t* src = reinterpret_cast<const uint8_t*>(s_peers[owner]) +
+                         (long long)(u - owner * gj.units_per_rank) * unit_bytes + part * chunk_bytes;
+    uint8_t* dst = gj.staging + (long long)u * unit_bytes + part * chunk_bytes;
+    const long long nvec = chunk_bytes >> 4;
+    long long i = gt;
+    for (; i + 7 * GATHER_THREADS < nvec; i += 8 * GATHER_THREADS) {
+      int4 v[8];
+#pragma unroll
+      for (int q = 0; q < 8; ++q) v[q] = ld_nc_v4(src + ((i + q * GATHER_THREADS) << 4));
+#pragma unroll
+      for (int q = 0; q < 8; ++q) st_v4(dst + ((i + q * GATHER_THREADS) << 4), v[q]);
+    }
+    for (; i < nvec; i += GATHER_THREADS) st_v4(dst + (i << 4), ld_nc_v4(src + (i << 4)));
+    __threadfence();
+    __syncthreads();
+    if (gt == 0) red_release_gpu_add_u32(gj.counters + u, 1u);
+  }
+}
+
+// Attachments for the NEXT CTA-pair launch made from this host thread (dlti_gemm2_attach); cleared by it.
+thread_local GatherJob t_job = {};
+thread_local WaitSpec t_wait = {};
+
 template <bool B_MN>
 int launch2(const Gemm2Params& p, const CUtensorMap& a, const CUtensorMap& b, const CUtensorMap& a2,
             const CUtensorMap& b2, const CUtensorMap& bh, const CUtensorMap& b2h, int grid, cudaStream_t stream) {
+  const GatherJob job = t_job;
+  const WaitSpec wait = t_wait;
+  t_job = GatherJob{};
+  t_wait = WaitSpec{};
+  if (p.sk_tiles > 0 && (job.j_count > 0 || wait.counters)) return DLTI_ERR_UNSUPPORTED;
   static bool configured[64] = {false};
   int dev = 0;
   cudaGetDevice(&dev);
@@ -636,7 +777,8 @@ int launch2(const Gemm2Params& p, const CUtensorMap& a, const CUtensorMap& b, co
     DLTI_CUDA_CHECK(cudaFuncSetAttribute(gemm2_kernel<B_MN>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES));
     configured[dev & 63] = true;
   }
-  gemm2_kernel<B_MN><<<grid, NUM_THREADS, SMEM_BYTES, stream>>>(p, a, b, a2, b2, bh, b2h);
+  gemm2_kernel<B_MN><<<grid, NUM_THREADS + (job.j_count > 0 ? GATHER_THREADS : 0), SMEM_BYTES, stream>>>(
+      p, job, wait, a, b, a2, b2, bh, b2h);
   dlti_count_launch();
   return (int)cudaGetLastError();
 }
@@ -689,6 +831,60 @@ void set_tail_split(Gemm2Params& p, int grid, int dtype, bool b_mn) {
 }
 
 }  // namespace
+
+// K1, CTA-pair form: attach a gather job and / or a wait spec to the NEXT dlti_gemm_2cta / dlti_gemm_rope_2cta /
+// dlti_gemm_swiglu_2cta / dlti_gemm_swiglu_bwd_2cta launched from this host thread (one launch consumes it).
+//   job  (j_count > 0): pull units  (rot_unit + j) % n_units,  j in [j_begin, j_begin + j_count),  of the row-
+//         sharded matrix [world * rows_per_rank, row_bytes] from peer_shards[owner] into `staging` and publish
+//         counters[u] += 16 chunks; a unit is complete once counters[u] >= epoch * 16. Every unit must be
+//         covered exactly once per epoch, by this or other launches.
+//   wait (wait_counters != null): the launch's B operand is a staging buffer whose 64-row unit u is valid once
+//         wait_counters[u] >= wait_epoch * 16; the TMA producer waits tile by tile.
+DLTI_API int dlti_gemm2_attach(const void* const* peer_shards, void* staging, unsigned int* counters,
+                               long long row_bytes, int rows_per_rank, int world, int rot_unit, int j_begin,
+                               int j_count, unsigned int epoch, const unsigned int* wait_counters, int wait_units,
+                               unsigned int wait_epoch, int* err_flag) {
+  GatherJob j{};
+  WaitSpec w{};
+  if (j_count > 0) {
+    if (world < 1 || world > 16 || rows_per_rank % 64 || !peer_shards || !staging || !counters || (row_bytes * 4) % 16)
+      return DLTI_ERR_BAD_ARG;
+    for (int i = 0; i < world; ++i) j.peer[i] = peer_shards[i];
+    j.staging = reinterpret_cast<uint8_t*>(staging);
+    j.counters = counters;
+    j.err = err_flag;
+    j.row_bytes = row_bytes;
+    j.target = epoch * (unsigned)GATHER_CH;
+    j.units_per_rank = rows_per_rank / 64;
+    j.n_units = j.units_per_rank * world;
+    if (rot_unit < 0 || rot_unit >= j.n_units || j_begin < 0 || j_begin + j_count > j.n_units) return DLTI_ERR_BAD_ARG;
+    j.rot = rot_unit;
+    j.j_begin = j_begin;
+    j.j_count = j_count;
+  }
+  if (wait_counters) {
+    w.counters = wait_counters;
+    w.err = err_flag;
+    w.target = wait_epoch * (unsigned)GATHER_CH;
+    w.n_units = wait_units;
+  }
+  t_job = j;
+  t_wait = w;
+  return 0;
+}
+
+// Run the job attached with dlti_gemm2_attach as a kernel of its own (ctas: 0 = two per SM).
+DLTI_API int dlti_gather_job_run(int ctas, cudaStream_t stream) {
+  const GatherJob job = t_job;
+  t_job = GatherJob{};
+  t_wait = WaitSpec{};
+  if (job.j_count <= 0) return 0;
+  int grid = ctas > 0 ? ctas : 2 * dlti_num_sms();
+  if (grid > job.j_count * GATHER_CH) grid = job.j_count * GATHER_CH;
+  gather_job_kernel<<<grid, GATHER_THREADS, 0, stream>>>(job);
+  dlti_count_launch();
+  return (int)cudaGetLastError();
+}
 
 // Same contract as dlti_gemm restricted to: A K-major, no split-K. Returns DLTI_ERR_UNSUPPORTED for
 // configurations it does not cover (the caller then uses the 1-CTA kernel). stream_k: -1 = automatic

@@ -43,16 +43,9 @@ class LayerWeights:
                                  # GEMM itself fills from the owner ranks, K1)
 
     def g(self, name: str):
-        """GatherSpec for the FIRST GEMM that touches `name` after the layer was fetched (that launch pulls
-        the shards while it computes); None afterwards — the staging buffer is then complete in stream
-        order, so the remaining micro-batches / backward GEMMs run the plain (CTA-pair) kernel on it."""
-        if not self.gather:
-            return None
-        sp = self.gather[name]
-        if sp.used_epoch == sp.epoch:
-            return None
-        sp.used_epoch = sp.epoch
-        return sp
+        """`gather=` handle for a GEMM whose B operand is `name` (fused ZeRO-3: the launch carries a slice of
+        the queued weight pulls and, if its own operand is still incomplete, waits on it tile by tile)."""
+        return self.gather[name] if self.gather else None
 
 
 class ResidentWeights:
@@ -101,6 +94,15 @@ class ResidentWeights:
 
     def release(self, i: int) -> None:
         pass
+
+    def prefetch_head(self) -> None:
+        pass
+
+    def release_head(self) -> None:
+        pass
+
+    def head_gather(self):
+        return None
 
     def get_embed(self):
         return self.embed
@@ -203,27 +205,21 @@ class LoraLlama:
         if xn_drop is None:
             xn_drop = xn
         t_qkv = gemm(xn_drop, lo.A_qkv_c[li]) if use_qkv else None            # [T, Rq]
-        g_qkv = lw.g("w_qkv")
-        if g_qkv is None:
-            # RoPE applied in the projection's epilogue
-            qkv = gemm_rope(xn, lw.w_qkv, b.positions, cos, sin, H + KV, hd, a2=t_qkv,
-                            b2=lo.B_qkv_c[li] if use_qkv else None)
-        else:
-            qkv = gemm(xn, lw.w_qkv, a2=t_qkv, b2=lo.B_qkv_c[li] if use_qkv else None, gather=g_qkv)
-            E.rope_(qkv, b.positions, cos, sin, H + KV, hd)
+        # RoPE applied in the projection's epilogue
+        qkv = gemm_rope(xn, lw.w_qkv, b.positions, cos, sin, H + KV, hd, a2=t_qkv,
+                        b2=lo.B_qkv_c[li] if use_qkv else None, gather=lw.g("w_qkv"))
         attn, lse = A.attention_fwd(qkv, b.cu_seqlens, b.max_seqlen, H, KV, hd, self.scale)
         attn_drop = E.dropout(attn, p, self.dropout_seed, self._stream(li, 1)) if use_o else attn
         t_o = gemm(attn_drop, lo.A_o_c[li]) if use_o else None                 # [T, Ro]
         x2 = gemm(attn, lw.w_o, a2=t_o, b2=lo.B_o_c[li] if use_o else None, residual=x, gather=lw.g("w_o"))
         xn2, rstd2, _ = E.rmsnorm_fwd(x2, lw.ln2, cfg.rms_norm_eps)
-        g_gu = lw.g("w_gu")
-        if need_out and not save and g_gu is None:
+        if need_out and not save:
             # forward of a checkpointed layer: nothing downstream needs gate|up itself, so SwiGLU runs in
             # the GEMM epilogue and the [T, 2*ff] tensor is never written
             gu = None
-            h = gemm_swiglu(xn2, lw.w_gu)
+            h = gemm_swiglu(xn2, lw.w_gu, gather=lw.g("w_gu"))
         else:
-            gu = gemm(xn2, lw.w_gu, gather=g_gu)
+            gu = gemm(xn2, lw.w_gu, gather=lw.g("w_gu"))
             h = E.swiglu_fwd(gu) if need_out else None
         if need_out:
             x3 = gemm(h, lw.w_down, residual=x2, gather=lw.g("w_down"))
@@ -248,13 +244,7 @@ class LoraLlama:
         splitk = max(1, min(16, T // 512))
 
         # ---- MLP ----
-        g_down = lw.g("w_down")
-        if g_down is None:
-            dgu = gemm_swiglu_bwd(dx3, lw.w_down, s["gu"])      # SwiGLU backward in the GEMM epilogue
-        else:
-            dh = gemm(dx3, lw.w_down, b_mn=True, gather=g_down)                                   # [T, ff]
-            dgu = E.swiglu_bwd(dh, s["gu"])
-            del dh
+        dgu = gemm_swiglu_bwd(dx3, lw.w_down, s["gu"], gather=lw.g("w_down"))   # SwiGLU backward in the epilogue
         dxn2 = gemm(dgu, lw.w_gu, b_mn=True, gather=lw.g("w_gu"))                               # [T, d]
         del dgu
         dx2 = E.rmsnorm_bwd(dxn2, s["x2"], lw.ln2, s["rstd2"], dres=dx3)
@@ -335,7 +325,10 @@ class LoraLlama:
         return xf
 
     def forward_logits(self, b: PackedBatch) -> torch.Tensor:
-        return gemm(self.forward_hidden(b), self.w.get_lm_head())
+        xf = self.forward_hidden(b)
+        logits = gemm(xf, self.w.get_lm_head(), gather=self.w.head_gather())
+        self.w.release_head()
+        return logits
 
     def forward_backward(self, b: PackedBatch, gscale: torch.Tensor | float) -> torch.Tensor:
         """One micro-batch: accumulates LoRA gradients of  gscale * sum_t CE_t  into lora.grad and
@@ -367,6 +360,8 @@ class LoraLlama:
             if li + 1 < L:
                 self.w.prefetch(li + 1)
             lw = self.w.layer(li)
+            if li == L - 1:
+                self.w.prefetch_head()      # the last layer's GEMMs carry the LM head's shards (fused ZeRO-3)
             for k, b in enumerate(batches):
                 self.micro_step = base_step + k
                 inputs[k][li] = xs[k]
@@ -374,20 +369,22 @@ class LoraLlama:
             self.w.release(li)
         # ---- head per micro-batch: final norm -> LM head -> CE (in-place gradient) -> dX ----
         lm = self.w.get_lm_head()
+        hg = self.w.head_gather()
         fnorm = self.w.get_final_norm()
         loss_sum = None
         dxs = []
         for k, b in enumerate(batches):
             xf, rstd_f, _ = E.rmsnorm_fwd(xs[k], fnorm, cfg.rms_norm_eps)
-            logits = gemm(xf, lm)
+            logits = gemm(xf, lm, gather=hg)
             loss_rows, dlogits = cross_entropy(logits, b.labels, gscales[k], inplace=True)
             ls = loss_rows.sum()
             loss_sum = ls if loss_sum is None else loss_sum + ls
-            dxf = gemm(dlogits, lm, b_mn=True)
+            dxf = gemm(dlogits, lm, b_mn=True, gather=hg)
             del logits, dlogits
             dxs.append(E.rmsnorm_bwd(dxf, xs[k], fnorm, rstd_f))
             xs[k] = None
             del dxf, xf
+        self.w.release_head()
         # ---- layers in reverse, recomputing each layer's forward ----
         self.w.prefetch(L - 1)
         for li in reversed(range(L)):

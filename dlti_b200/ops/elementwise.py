@@ -223,7 +223,10 @@ def add_dropout(a, b, p, seed, stream):
 # Embedding
 # ------------------------------------------------------------------------------------------
 def embedding(ids, table, vocab_start: int = 0):
-    """out[t] = table[ids[t] - vocab_start], zero rows for ids outside this vocab shard."""
+    """out[t] = table[ids[t] - vocab_start], zero rows for ids outside this vocab shard. `table` may be a
+    parallel.fused.PeerRows (vocabulary-sharded table read in place on its owner ranks)."""
+    if hasattr(table, "lookup"):
+        return table.lookup(ids)
     if vocab_start == 0:
         _debug.check_range("embedding", "ids", ids, 0, table.shape[0])
     if not _lib.use_native(table):

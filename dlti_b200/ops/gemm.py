@@ -96,7 +96,13 @@ def gemm(a: torch.Tensor, b: torch.Tensor, *, a_mn: bool = False, b_mn: bool = F
         _lib.check(f(_lib.ptr(a), _lib.ptr(b), M, N, K, a.stride(0), b.stride(0), N, _lib.dtype_code(a.dtype),
                      int(block_n), peer_arr, rank, world, max_tokens * N, _lib.stream_ptr()), "dlti_gemm_push")
         return recv
-    if gather is not None:
+    if gather is not None and hasattr(gather, "attach"):
+        # K1 on the CTA-pair kernel: the launch carries a slice of pending weight gathers (and waits on its own
+        # operand's counters when that is still being pulled); see parallel.fused.GatherQueue
+        assert not a_mn and split_k == 1 and (gather.sm is None or b.data_ptr() == gather.sm.staging.data_ptr())
+        two_cta = True
+        gather.attach(2.0 * M * N * (K + K2))
+    elif gather is not None:
         assert not a_mn and not accumulate and split_k == 1
         assert b.data_ptr() == gather.staging.data_ptr() and b.stride(0) == gather.staging.stride(0)
         f = _lib.fn("dlti_gemm_gather", [
@@ -141,7 +147,7 @@ def gemm(a: torch.Tensor, b: torch.Tensor, *, a_mn: bool = False, b_mn: bool = F
     return out
 
 
-def gemm_swiglu(x: torch.Tensor, w_gu: torch.Tensor) -> torch.Tensor:
+def gemm_swiglu(x: torch.Tensor, w_gu: torch.Tensor, gather=None) -> torch.Tensor:
     """h = silu(x · Wg^T) * (x · Wu^T) for w_gu = [gate rows ; up rows] ([2*ff, K]): the gate_up projection
     with SwiGLU applied in the GEMM epilogue (csrc/gemm2.cu). Falls back to GEMM + swiglu_fwd when the
     shape is not covered (CPU tensors, ff % 128 != 0, fewer than 64 tiles)."""
@@ -149,9 +155,11 @@ def gemm_swiglu(x: torch.Tensor, w_gu: torch.Tensor) -> torch.Tensor:
     M, K = x.shape
     ff = w_gu.shape[0] // 2
     if (not _lib.use_native(x, w_gu) or not _TWO_CTA_DEFAULT or not _FUSE_SWIGLU or ff % 128 or x.stride(1) != 1 or w_gu.stride(1) != 1
-            or ((M + 255) // 256) * (ff // 128) < 64):
-        return swiglu_fwd(gemm(x, w_gu))
+            or (((M + 255) // 256) * (ff // 128) < 64 and gather is None)):
+        return swiglu_fwd(gemm(x, w_gu, gather=gather))
     h = torch.empty((M, ff), dtype=x.dtype, device=x.device)
+    if gather is not None:
+        gather.attach(4.0 * M * ff * K)
     f = _lib.fn("dlti_gemm_swiglu_2cta", [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int,
                                           C.c_longlong, C.c_longlong, C.c_longlong, C.c_int, C.c_void_p])
     _lib.check(f(_lib.ptr(x), _lib.ptr(w_gu), _lib.ptr(h), M, ff, K, x.stride(0), w_gu.stride(0), h.stride(0),
@@ -160,15 +168,17 @@ def gemm_swiglu(x: torch.Tensor, w_gu: torch.Tensor) -> torch.Tensor:
 
 
 def gemm_rope(x: torch.Tensor, w: torch.Tensor, pos: torch.Tensor, cos_t: torch.Tensor, sin_t: torch.Tensor,
-              n_rot_heads: int, hd: int, a2: torch.Tensor | None = None, b2: torch.Tensor | None = None) -> torch.Tensor:
+              n_rot_heads: int, hd: int, a2: torch.Tensor | None = None, b2: torch.Tensor | None = None,
+              gather=None) -> torch.Tensor:
     """qkv = rope(x · W^T + a2 · b2^T): the QKV projection (with the LoRA K-extension) whose epilogue applies
     the rotary embedding to the first n_rot_heads heads. Falls back to GEMM + rope_ when not covered."""
     from .elementwise import rope_
     M, K = x.shape
     N = w.shape[0]
     if (not _lib.use_native(x, w) or not _TWO_CTA_DEFAULT or not _FUSE_ROPE or hd != 128 or N % 128 or x.stride(1) != 1
-            or w.stride(1) != 1 or ((M + 255) // 256) * ((N + 255) // 256) < 64 or pos.dtype != torch.int32):
-        y = gemm(x, w, a2=a2, b2=b2)
+            or w.stride(1) != 1 or (((M + 255) // 256) * ((N + 255) // 256) < 64 and gather is None)
+            or pos.dtype != torch.int32):
+        y = gemm(x, w, a2=a2, b2=b2, gather=gather)
         rope_(y, pos, cos_t, sin_t, n_rot_heads, hd)
         return y
     K2 = 0
@@ -176,6 +186,8 @@ def gemm_rope(x: torch.Tensor, w: torch.Tensor, pos: torch.Tensor, cos_t: torch.
         assert b2 is not None and a2.stride(1) == 1 and b2.stride(1) == 1
         K2 = a2.shape[1]
     y = torch.empty((M, N), dtype=x.dtype, device=x.device)
+    if gather is not None:
+        gather.attach(2.0 * M * N * (K + K2))
     f = _lib.fn("dlti_gemm_rope_2cta", [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_longlong,
                                         C.c_longlong, C.c_longlong, C.c_void_p, C.c_void_p, C.c_int, C.c_longlong,
                                         C.c_longlong, C.c_int, C.c_float, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int,
@@ -187,17 +199,20 @@ def gemm_rope(x: torch.Tensor, w: torch.Tensor, pos: torch.Tensor, cos_t: torch.
     return y
 
 
-def gemm_swiglu_bwd(dy: torch.Tensor, w_down: torch.Tensor, gu: torch.Tensor) -> torch.Tensor:
+def gemm_swiglu_bwd(dy: torch.Tensor, w_down: torch.Tensor, gu: torch.Tensor, gather=None) -> torch.Tensor:
     """d(gate|up) = swiglu_bwd(dy · W_down, gate|up) for w_down = [d_model, ff] (dy is [T, d_model]): the
     down projection's input-gradient GEMM with the SwiGLU backward in its epilogue."""
     from .elementwise import swiglu_bwd
     M, K = dy.shape
     ff = w_down.shape[1]
     if (not _lib.use_native(dy, w_down) or not _TWO_CTA_DEFAULT or not _FUSE_SWIGLU or ff % 32 or dy.stride(1) != 1
-            or w_down.stride(1) != 1 or gu.stride(1) != 1 or ((M + 255) // 256) * ((ff + 255) // 256) < 64):
-        return swiglu_bwd(gemm(dy, w_down, b_mn=True), gu)
+            or w_down.stride(1) != 1 or gu.stride(1) != 1
+            or (((M + 255) // 256) * ((ff + 255) // 256) < 64 and gather is None)):
+        return swiglu_bwd(gemm(dy, w_down, b_mn=True, gather=gather), gu)
     assert w_down.shape[0] == K and gu.shape == (M, 2 * ff) and gu.dtype == dy.dtype
     dgu = torch.empty_like(gu)
+    if gather is not None:
+        gather.attach(2.0 * M * ff * K)
     f = _lib.fn("dlti_gemm_swiglu_bwd_2cta", [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int,
                                               C.c_longlong, C.c_longlong, C.c_longlong, C.c_longlong, C.c_int,
                                               C.c_void_p])

@@ -124,6 +124,131 @@ class GatherSpec:
         self.used_epoch = -1      # epoch whose gather has already been launched (see LayerWeights.g)
 
 
+class StagedMatrix:
+    """One row-sharded weight matrix kind of one staging slot (K1 on the CTA-pair GEMM, csrc/gemm2.cu): the
+    local full-size staging buffer, its per-64-row-unit counters and the bookkeeping of which job positions of
+    the current epoch have already been attached to a launch. `bind()` points it at a layer's shards and starts
+    a new epoch; positions map to units as (rot + j) % n_units with rot = this rank's first unit, so at any
+    moment the ranks pull from different owners."""
+
+    def __init__(self, fc: "FusedComm", rows_per_rank: int, cols: int, dtype: torch.dtype):
+        assert rows_per_rank % 64 == 0
+        self.fc = fc
+        self.rows_per_rank, self.cols = rows_per_rank, cols
+        self.units_per_rank = rows_per_rank // 64
+        self.n_units = self.units_per_rank * fc.world
+        self.row_bytes = cols * torch.empty(0, dtype=dtype).element_size()
+        self.unit_bytes = 64 * self.row_bytes
+        self.staging = torch.empty(rows_per_rank * fc.world, cols, dtype=dtype, device=fc.info.device)
+        self.counters = torch.zeros(self.n_units, dtype=torch.int32, device=fc.info.device)
+        self.epoch = 0
+        self.launched = self.n_units          # nothing pending
+        self.rot = fc.rank * self.units_per_rank
+        self.peer_arr = None
+        self.tag = None                       # what is (being) gathered here, e.g. (layer, "w_qkv")
+
+    def bind(self, shard: torch.Tensor, tag) -> None:
+        assert self.launched == self.n_units, "previous epoch not fully requested (flush the queue first)"
+        assert shard.shape == (self.rows_per_rank, self.cols)
+        self.peer_arr = self.fc.peer_array(shard)
+        self.epoch += 1
+        self.launched = 0
+        self.tag = tag
+
+    @property
+    def pending(self) -> int:
+        return self.n_units - self.launched
+
+
+class GatherQueue:
+    """Pending gather work in consumption order. Every large GEMM of the ZeRO-3 step takes a slice sized to
+    its own duration (`take`); a GEMM whose own B operand is not fully requested yet takes all of that
+    matrix's remainder and waits on its counters tile by tile (`use`)."""
+    _ATTACH = [_V, _V, _V, _L, _I, _I, _I, _I, _I, _U, _V, _I, _U, _V]
+
+    def __init__(self, fc: "FusedComm", pull_gbs: float = 200.0, gemm_tflops: float = 1300.0):
+        self.fc = fc
+        self.pending: list[StagedMatrix] = []
+        self.bytes_per_flop = pull_gbs * 1e9 / (gemm_tflops * 1e12)
+        self.bytes_requested = 0
+
+    def push(self, sm: StagedMatrix) -> None:
+        if sm.pending and sm not in self.pending:
+            self.pending.append(sm)
+
+    def _attach(self, job, wait) -> None:
+        f = _lib.fn("dlti_gemm2_attach", self._ATTACH)
+        if job is not None:
+            sm, j0, n = job
+            self.bytes_requested += n * sm.unit_bytes * (self.fc.world - 1) // self.fc.world
+            ja = (sm.peer_arr, _lib.ptr(sm.staging), _lib.ptr(sm.counters), sm.row_bytes, sm.rows_per_rank,
+                  self.fc.world, sm.rot, j0, n, sm.epoch)
+        else:
+            ja = (None, None, None, 0, 0, 0, 0, 0, 0, 0)
+        wa = (_lib.ptr(wait.counters), wait.n_units, wait.epoch) if wait is not None else (None, 0, 0)
+        _lib.check(f(*ja, *wa, _lib.ptr(self.fc.err)), "gemm2_attach")
+
+    def attach(self, consumed: StagedMatrix | None, flops: float) -> None:
+        """Call immediately before launching a CTA-pair GEMM whose B operand is `consumed.staging` (or a GEMM
+        with a plain B when consumed is None): decides what the launch's gather warps pull."""
+        if consumed is not None and consumed.pending:
+            # cold start: this launch pulls the rest of its own operand and waits for it tile by tile
+            job = (consumed, consumed.launched, consumed.pending)
+            consumed.launched = consumed.n_units
+            if consumed in self.pending:
+                self.pending.remove(consumed)
+            self._attach(job, consumed)
+            return
+        if not self.pending:
+            return
+        sm = self.pending[0]
+        n = max(1, min(sm.pending, int(flops * self.bytes_per_flop / sm.unit_bytes)))
+        job = (sm, sm.launched, n)
+        sm.launched += n
+        if not sm.pending:
+            self.pending.pop(0)
+        self._attach(job, None)
+
+    def flush(self, sm: StagedMatrix | None = None) -> None:
+        """Run what is still pending (of `sm`, or of everything) as stand-alone gather kernels."""
+        todo = [m for m in self.pending if sm is None or m is sm]
+        for m in todo:
+            self._attach((m, m.launched, m.pending), None)
+            m.launched = m.n_units
+            self.pending.remove(m)
+            _lib.check(_lib.fn("dlti_gather_job_run", [_I, _V])(0, _lib.stream_ptr()), "gather_job_run")
+
+
+class PeerRows:
+    """A row-sharded table addressed in place on its owner ranks (K15): `ops.elementwise.embedding` looks
+    tokens up with peer loads instead of gathering the table first."""
+
+    def __init__(self, fc: "FusedComm", shard: torch.Tensor, rows: int):
+        self.fc, self.shard, self.rows = fc, shard, rows
+        self.peer_arr = fc.peer_array(shard)
+        self.shape = (rows, shard.shape[1])
+        self.dtype, self.device = shard.dtype, shard.device
+
+    def lookup(self, ids: torch.Tensor) -> torch.Tensor:
+        assert ids.dtype == torch.int64 and ids.is_contiguous()
+        d = self.shard.shape[1]
+        out = torch.empty((ids.numel(), d), dtype=self.dtype, device=self.device)
+        f = _lib.fn("dlti_embedding_peer", [_V, _V, _V, _L, _I, _L, _L, _I, _I, _V])
+        _lib.check(f(_lib.ptr(ids), self.peer_arr, _lib.ptr(out), ids.numel(), d, self.shard.shape[0], self.rows,
+                     self.fc.world, _lib.dtype_code(self.dtype), _lib.stream_ptr()), "embedding_peer")
+        return out.view(*ids.shape, d)
+
+
+class GatherUse:
+    """Handle a model passes as `gather=` to the GEMM ops: `b` of that GEMM is `sm.staging` (K1)."""
+
+    def __init__(self, sm: StagedMatrix | None, queue: GatherQueue):
+        self.sm, self.queue = sm, queue
+
+    def attach(self, flops: float) -> None:
+        self.queue.attach(self.sm, flops)
+
+
 class FusedComm:
     N_CHANNELS = 32
 

@@ -88,15 +88,20 @@ class Zero3Weights:
         self.in_gemm_gather = (fused is not None and not self.offload and self.world > 1
                                and os.environ.get("DLTI_Z3_GATHER", "gemm") != "prefetch")
         if self.in_gemm_gather:
+            # Two full-layer staging slots (the layer in use and the one being pulled). prefetch(i) only QUEUES
+            # layer i's matrices; the queue is drained by the gather warps of the GEMMs that run meanwhile, a
+            # slice per launch sized to the launch's duration (parallel.fused.GatherQueue). The GEMMs of layer i
+            # then find their operands complete; whatever is not (first layer of a run) is pulled by the
+            # consuming launch itself, which waits on the unit counters tile by tile.
+            from .fused import GatherQueue, GatherUse, StagedMatrix
             self.slots, self.n_slots, self.free_slots = [], 0, []
-            self.staging, self.counters, self.epoch, self.specs = {}, {}, {}, []
-            for m, (r, c) in self.shapes.items():
-                rp = _rows_per_rank(r, self.world, self.row_align)
-                self.staging[m] = torch.empty(rp * self.world, c, dtype=dtype, device=self.device)
-                self.counters[m] = torch.zeros(rp * self.world // 64, dtype=torch.int32, device=self.device)
-                self.epoch[m] = 0
-            for sh in self.layer_shards:
-                self.specs.append({m: fused.gather_spec(sh[m], self.staging[m], self.counters[m]) for m in _MATS})
+            self.queue = GatherQueue(fused, pull_gbs=float(os.environ.get("DLTI_Z3_PULL_GBS", "200")))
+            self.stage_slots = [{m: StagedMatrix(fused, _rows_per_rank(r, self.world, self.row_align), c, dtype)
+                                 for m, (r, c) in self.shapes.items()} for _ in range(2)]
+            self.slot_layer = [None, None]
+            self._GatherUse = GatherUse
+            self.head_stage = StagedMatrix(fused, self.lm_head_shard.shape[0], d, dtype)
+            self.head_step = -1
         self._big = {}          # gathered embed / lm_head staging (allocated on demand)
         self._h2d = {}          # offload: device copies of this rank's shards while in flight
         self.gather_bytes = 0   # bytes received from peers (for roofline reports)
@@ -199,7 +204,29 @@ class Zero3Weights:
             comm.all_gather_into(out.view(-1), src.reshape(-1), self.info)
         self.gather_bytes += out.numel() * out.element_size() * (self.world - 1) // self.world
 
+    def _queue_layer(self, i: int) -> int:
+        """Fused K1 mode: make layer i resident-or-queued in a staging slot; returns the slot."""
+        if i in self.slot_layer:
+            return self.slot_layer.index(i)
+        # evict the slot whose layer is farthest from i (an empty slot first): in either direction of travel
+        # that is the layer whose GEMMs have all been launched, never the one about to be used
+        dist_ = [10 ** 9 if l is None else abs(l - i) for l in self.slot_layer]
+        s = 0 if dist_[0] >= dist_[1] else 1
+        for sm in self.stage_slots[s].values():    # leftovers of a layer that was queued but never used
+            if sm.pending:
+                self.queue.flush(sm)
+        for m in _MATS:
+            sm = self.stage_slots[s][m]
+            sm.bind(self.layer_shards[i][m], (i, m))
+            self.queue.push(sm)
+            self.gather_bytes += sm.n_units * sm.unit_bytes * (self.world - 1) // self.world
+        self.slot_layer[s] = i
+        return s
+
     def prefetch(self, i: int) -> None:
+        if self.in_gemm_gather and 0 <= i < self.cfg.num_hidden_layers:
+            self._queue_layer(i)
+            return
         if self.world == 1 or self.in_gemm_gather or i in self.slot_of or i < 0 or i >= self.cfg.num_hidden_layers:
             return
         if not self.free_slots:
@@ -227,24 +254,11 @@ class Zero3Weights:
             r = {m: dev(sh[m])[: self.shapes[m][0]] for m in _MATS}
             return LayerWeights(r["w_qkv"], r["w_o"], r["w_gu"], r["w_down"], *self.norms[i])
         if self.in_gemm_gather:
-            # every call starts a new epoch: the first GEMM that touches a matrix pulls it from the
-            # owner ranks tile by tile; later GEMMs of the same call (recompute -> backward) reuse it
-            g = {}
-            for m in _MATS:
-                self.epoch[m] += 1
-                sp = self.specs[i][m]
-                sp.epoch = self.epoch[m]
-                g[m] = sp
-                rows = self.staging[m].shape[0]
-                self.gather_bytes += rows * self.shapes[m][1] * 2 * (self.world - 1) // self.world
-                # The gather kernel reads this rank's own rows in place (never copies them), but the
-                # later plain GEMMs of this fetch read the staging buffer only: place the own rows now
-                # (1/world of the matrix, device-local copy in stream order).
-                rp = rows // self.world
-                self.staging[m][self.rank * rp:(self.rank + 1) * rp].copy_(self.layer_shards[i][m], non_blocking=True)
-            st = self.staging
-            return LayerWeights(st["w_qkv"][: self.shapes["w_qkv"][0]], st["w_o"][: self.shapes["w_o"][0]],
-                                st["w_gu"][: self.shapes["w_gu"][0]], st["w_down"][: self.shapes["w_down"][0]],
+            s = self._queue_layer(i)
+            st = self.stage_slots[s]
+            g = {m: self._GatherUse(st[m], self.queue) for m in _MATS}
+            return LayerWeights(st["w_qkv"].staging[: self.shapes["w_qkv"][0]], st["w_o"].staging[: self.shapes["w_o"][0]],
+                                st["w_gu"].staging[: self.shapes["w_gu"][0]], st["w_down"].staging[: self.shapes["w_down"][0]],
                                 *self.norms[i], gather=g)
         if i not in self.slot_of:
             self.prefetch(i)
@@ -280,13 +294,42 @@ class Zero3Weights:
         self._gather((name,), shard, buf)
         return buf[:rows]
 
-    def get_embed(self) -> torch.Tensor:
+    def get_embed(self):
+        if self.in_gemm_gather:
+            # vocabulary-sharded table: the embedding kernel fetches each token's row from its owner rank
+            from .fused import PeerRows
+            return PeerRows(self.fused, self.embed_shard, self.cfg.vocab_size)
         return self._gather_big("embed", self.embed_shard)
 
+    def prefetch_head(self) -> None:
+        """Fused K1 mode: queue the LM head behind the layers already queued (call before the last layer's
+        forward GEMMs so that they carry it). Re-gathered once per optimizer step."""
+        if self.in_gemm_gather and self.head_stage.launched == self.head_stage.n_units and not self._head_valid:
+            self.head_stage.bind(self.lm_head_shard, ("lm_head",))
+            self.queue.push(self.head_stage)
+            self.gather_bytes += self.head_stage.n_units * self.head_stage.unit_bytes * (self.world - 1) // self.world
+            self._head_valid = True
+
+    def release_head(self) -> None:
+        self._head_valid = False
+
+    _head_valid = False
+
     def get_lm_head(self) -> torch.Tensor:
+        if self.in_gemm_gather:
+            self.prefetch_head()
+            return self.head_stage.staging[: self.cfg.vocab_size]
         if self.lm_head_shard is self.embed_shard and "embed" in self._big:
             return self._big["embed"][: self.cfg.vocab_size]
         return self._gather_big("lm_head", self.lm_head_shard)
+
+    def head_gather(self):
+        """`gather=` handle for GEMMs whose B operand is the LM head (None outside the fused K1 mode)."""
+        return self._GatherUse(self.head_stage, self.queue) if self.in_gemm_gather else None
+
+    def carry(self):
+        """`gather=` handle for a large GEMM with a plain B operand: lets it carry queued weight pulls."""
+        return self._GatherUse(None, self.queue) if self.in_gemm_gather else None
 
     def get_final_norm(self) -> torch.Tensor:
         return self.final_norm

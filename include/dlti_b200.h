@@ -164,6 +164,22 @@ int dlti_gemm_2cta(const void* A, const void* B, void* C, const void* R, int M, 
                    float alpha, int accumulate, int stream_k /* -1 auto, 0 off, 1 force */,
                    dlti_stream_t stream);
 
+/* K1 on the CTA-pair kernel (ZeRO-3 all-gather fused into the GEMM; replaces the reference's DeepSpeed
+ * stage-3 parameter all-gather, /root/reference/configs/ds_config_zero3.json:16-37). Attaches to the NEXT
+ * dlti_gemm_2cta / _rope_2cta / _swiglu_2cta / _swiglu_bwd_2cta launch made from this host thread:
+ *  - a gather job (j_count > 0): four extra warps per CTA pull the 64-row units (rot_unit + j) % n_units,
+ *    j in [j_begin, j_begin + j_count), of a row-sharded matrix [world * rows_per_rank, row_bytes] from their
+ *    owner ranks (peer loads; own rows locally) into `staging` and publish per-unit counters: unit u is
+ *    complete once counters[u] >= epoch * 16. The job may feed this launch's own B operand or, normally, a
+ *    matrix that a later launch consumes (the next layer's weights ride on this layer's GEMMs);
+ *  - a wait spec (wait_counters != NULL): the launch's B operand is such a staging buffer; the TMA producer
+ *    acquires the counters of the units each tile needs (fast path when everything has landed already).
+ * dlti_gather_job_run executes an attached job as a kernel of its own. */
+int dlti_gemm2_attach(const void* const* peer_shards, void* staging, unsigned int* counters, long long row_bytes,
+                      int rows_per_rank, int world, int rot_unit, int j_begin, int j_count, unsigned int epoch,
+                      const unsigned int* wait_counters, int wait_units, unsigned int wait_epoch, int* err_flag);
+int dlti_gather_job_run(int ctas, dlti_stream_t stream);
+
 /* Llama gate_up projection + SwiGLU in one kernel: h[M, ff] = silu(A·Wg^T) * (A·Wu^T), W = [gate; up]
  * stored [2*ff, K]. CTA rank 0 of a pair stages gate rows, rank 1 the matching up rows; the [M, 2*ff]
  * intermediate is never written. Rounding points match dlti_swiglu_fwd on a stored gate|up tensor. */
@@ -223,6 +239,11 @@ int dlti_peer_barrier(const void* const* signal_pads, int rank, int world, int c
                       unsigned int epoch, int* err_flag, dlti_stream_t stream);
 int dlti_peer_barrier_auto(const void* const* signal_pads, int rank, int world, int channel,
                            unsigned int* device_counter, int* err_flag, dlti_stream_t stream);
+/* K15: embedding lookup over a vocabulary-sharded table in peer memory: out[t] = row ids[t] fetched from its
+ * owner rank (ids outside [0, vocab) give zero rows). Replaces all-gather + lookup of the reference's ZeRO-3
+ * embedding (HF LlamaModel.embed_tokens under DeepSpeed stage 3). */
+int dlti_embedding_peer(const long long* ids, const void* const* shards, void* out, long long tokens, int d,
+                        long long rows_per_rank, long long vocab, int world, int dtype, dlti_stream_t stream);
 /* pull-based all-gather of equally sized row shards into `out` (K1 stand-alone form) */
 int dlti_allgather_rows(const void* const* shards, void* out, long long shard_bytes, int rank, int world,
                         int blocks_per_peer, dlti_stream_t stream);

@@ -127,15 +127,69 @@ def main():
           ((dx2.float() - dxr).abs().max() / dxr.abs().max()).item() < 2e-2)
     fc.check_error()
 
+    # K1 on the CTA-pair kernel: gather jobs riding on GEMM launches + counter waits (csrc/gemm2.cu)
+    from dlti_b200.ops.elementwise import embedding
+    from dlti_b200.parallel.fused import GatherQueue, GatherUse, PeerRows, StagedMatrix
+    q = GatherQueue(fc)
+    for rp2, K2, M2 in ((256, 512, 384), (2752, 1024, 4096)):      # 2752 = Llama-2-7B w_gu rows per rank at 8 GPUs
+        sh = fc.alloc_symmetric((rp2, K2), torch.bfloat16)
+        sh.copy_(torch.randn(rp2, K2, device=dev) * 0.05)
+        torch.cuda.synchronize(); dist.barrier()
+        full = torch.empty(world * rp2, K2, dtype=torch.bfloat16, device=dev)
+        dist.all_gather_into_tensor(full, sh.contiguous())
+        x2 = torch.randn(M2, K2, device=dev, dtype=torch.bfloat16)
+        dy2 = torch.randn(M2, world * rp2, device=dev, dtype=torch.bfloat16)
+        sm = StagedMatrix(fc, rp2, K2, torch.bfloat16)
+        sm.staging.zero_()
+        # (a) cold start: the consuming launch pulls its own operand and waits on the counters tile by tile
+        sm.bind(sh, "a"); q.push(sm)
+        y2 = gemm(x2, sm.staging, gather=GatherUse(sm, q))
+        torch.cuda.synchronize()
+        check(f"gemm2 self-gather NT rp={rp2}", torch.equal(y2, gemm(x2, full, two_cta=True)) and torch.equal(sm.staging, full)
+              and not q.pending)
+        sm.staging.zero_()
+        sm.bind(sh, "b"); q.push(sm)
+        dx2 = gemm(dy2, sm.staging, b_mn=True, gather=GatherUse(sm, q))
+        torch.cuda.synchronize()
+        check(f"gemm2 self-gather NN rp={rp2}", torch.equal(dx2, gemm(dy2, full, b_mn=True, two_cta=True))
+              and torch.equal(sm.staging, full))
+        # (b) look-ahead: other launches carry the pulls slice by slice, the consumer then runs without waiting
+        sm.staging.zero_()
+        sm.bind(sh, "c"); q.push(sm)
+        carried = 0
+        while q.pending:
+            gemm(x2, full, gather=GatherUse(None, q))
+            carried += 1
+        y3 = gemm(x2, sm.staging, gather=GatherUse(sm, q))
+        torch.cuda.synchronize()
+        check(f"gemm2 carried gather ({carried} launches) rp={rp2}", torch.equal(y3, y2) and torch.equal(sm.staging, full))
+        # (c) leftovers flushed by the stand-alone gather kernel
+        sm.staging.zero_()
+        sm.bind(sh, "d"); q.push(sm)
+        gemm(x2, full, gather=GatherUse(None, q))
+        q.flush()
+        torch.cuda.synchronize()
+        check(f"gather job flush rp={rp2}", torch.equal(sm.staging, full) and not q.pending)
+    fc.check_error()
+    # K15: embedding rows fetched from their owner ranks
+    vsh = fc.alloc_symmetric((192, 512), torch.bfloat16)
+    vsh.copy_(torch.randn(192, 512, device=dev))
+    torch.cuda.synchronize(); dist.barrier()
+    vfull = torch.empty(world * 192, 512, dtype=torch.bfloat16, device=dev)
+    dist.all_gather_into_tensor(vfull, vsh.contiguous())
+    vocab = world * 192 - 5
+    ids = torch.randint(0, vocab, (777,), device=dev)
+    check("peer embedding == lookup in the gathered table", torch.equal(embedding(ids, PeerRows(fc, vsh, vocab)), vfull[ids]))
+
     # training: fused vs nccl backends give the same losses (ZeRO-3 and ZeRO-2)
     from tests.test_trainer_gpu_common import run_short
-    for stage in (3, 2):
-        a = run_short(info, stage, "fused", fc)
-        b = run_short(info, stage, "nccl", None)
-        ok = all(abs(x - y) < 3e-2 for x, y in zip(a, b))
+    for stage in (3, 2, 0):
+        a, na = run_short(info, stage, "fused", fc, with_norms=True)
+        b, nb = run_short(info, stage, "nccl", None, with_norms=True)
+        ok = all(abs(x - y) < 3e-2 for x, y in zip(a, b)) and all(abs(x - y) <= 2e-2 * max(abs(y), 1e-3) for x, y in zip(na, nb))
         if rank == 0:
-            print(f"stage {stage} fused {a} nccl {b}", flush=True)
-        check(f"ZeRO-{stage}: fused backend == nccl backend losses", ok)
+            print(f"stage {stage} fused {a} nccl {b}\n        grad norms fused {na} nccl {nb}", flush=True)
+        check(f"ZeRO-{stage}: fused backend == nccl backend losses and gradient norms", ok)
     if rank == 0:
         print("ALL MULTI-GPU CHECKS PASSED", flush=True)
     comm.shutdown()

@@ -6,7 +6,8 @@ import torch
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 
 
-def run_short(info, stage: int, backend: str, fused, steps: int = 4, preset: str = "tiny-gqa", seq: int = 256):
+def run_short(info, stage: int, backend: str, fused, steps: int = 4, preset: str = "tiny-gqa", seq: int = 256,
+              with_norms: bool = False):
     from dlti_b200.config.args import TrainingArgs
     from dlti_b200.engine.trainer import Trainer
     from dlti_b200.models.config import PRESETS
@@ -21,7 +22,7 @@ def run_short(info, stage: int, backend: str, fused, steps: int = 4, preset: str
     tr = Trainer(cfg, LoraConfig(r=16, lora_alpha=32, lora_dropout=0.05), args, None, None, info=info)
     if fused is not None and tr.fused is None:
         raise RuntimeError("fused backend requested but not active")
-    losses = []
+    losses, norms = [], []
     g = torch.Generator().manual_seed(7 + info.rank)
     for s in range(steps):
         mbs = []
@@ -29,7 +30,8 @@ def run_short(info, stage: int, backend: str, fused, steps: int = 4, preset: str
             ids = torch.randint(3, cfg.vocab_size, (2, seq), generator=g)
             mbs.append(pack_batch(ids, ids.clone(), None, pin=True))
         losses.append(tr.train_step(mbs))
+        norms.append(tr.last_grad_norm)
     torch.cuda.synchronize()
     if tr.fused is not None:
         tr.fused.check_error()
-    return losses
+    return (losses, norms) if with_norms else losses

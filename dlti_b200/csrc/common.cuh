@@ -59,6 +59,10 @@ int dlti_make_tmap_2d(CUtensorMap* out, const void* base, uint64_t inner, uint64
 int dlti_get_tmap(CUtensorMap* out, const void* base, uint64_t inner, uint64_t outer, uint64_t ld_elems,
                   uint32_t box_inner, uint32_t box_outer);
 
+// 3D view of an MN-major [K, N] operand: one box {64, box_k, chunks} per stage (see runtime.cu). N % 64 == 0.
+int dlti_get_tmap_mn3d(CUtensorMap* out, const void* base, uint64_t N, uint64_t K, uint64_t ld_elems,
+                       uint32_t box_k, uint32_t chunks);
+
 #ifdef __CUDACC__
 // Launch `kernel` on `stream`, as a programmatic dependent of the previous kernel in the stream when PDL is on.
 // `rows` = token rows of the step: PDL pays off while a step is latency-bound (measured on B200, Llama-2-7B decode:

@@ -10,8 +10,8 @@
 //   C[M,N] = alpha * ( A[M,K] · op(B) + A2[M,K2] · op(B2) ) (+ R)      16-bit or fp32 output
 //   B K-major ([N,K], x·W^T) or MN-major ([K,N], dy·W); K-extension (LoRA) as in gemm.cu.
 //
-// Roles per CTA: warp 0 TMA producer (each CTA loads its own halves; completion bytes of BOTH CTAs land
-// on the leader's "full" barrier), warp 1 = TMEM allocator (both CTAs) + MMA issuer (leader only; its
+// Roles per CTA: warp 0 / warp 6 TMA producers of A / B (each CTA loads its own halves; completion bytes of BOTH
+// CTAs land on the leader's "full" barrier), warp 1 = TMEM allocator (both CTAs) + MMA issuer (leader only; its
 // tcgen05.commit multicasts the "slot free" / "accumulator ready" arrivals to both CTAs), warps 2-5 =
 // epilogue on the CTA's own 128 accumulator rows. Every wait is bounded: on timeout the kernel traps
 // instead of hanging the GPU.
@@ -25,7 +25,7 @@ constexpr int BM = 128;      // rows per CTA (256 per pair)
 constexpr int BN = 256;      // columns per pair (128 B-rows staged per CTA)
 constexpr int BK = 64;
 constexpr int UMMA_K = 16;
-constexpr int NUM_THREADS = 192;
+constexpr int NUM_THREADS = 224;      // A producer, MMA, 4 epilogue warps, B producer
 constexpr int A_BYTES = BM * BK * 2;          // 16 KB
 constexpr int B_BYTES = (BN / 2) * BK * 2;    // 16 KB (this CTA's half of the B tile)
 constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
@@ -51,6 +51,7 @@ struct Gemm2Params {
   // half as long. split_from == nmb2 * nnb: no tile is split.
   uint32_t idesc_half;
   int split_from;
+  int b3d;                // MN-major B: tmB is the 3D view (one TMA per stage for a full tile); tmBh stays 2D
   // stream-K: tiles [0, sk_tiles) are cut into `gridDim/2` equal ranges of (tile, k-block) iterations,
   // tiles [sk_tiles, total) are handed out round-robin. sk_tiles == 0 => plain data-parallel schedule.
   // SwiGLU mode (swiglu_ff > 0): B is the [2*ff, K] gate|up weight; CTA rank 0 stages 128 gate rows and
@@ -76,7 +77,7 @@ struct Gemm2Params {
 };
 
 // K1 (ZeRO-3 all-gather fused into the GEMM), CTA-pair form. Two independent attachments of a launch:
-//  * a gather JOB: four extra warps per CTA pull 64-row units of a row-sharded weight matrix from their owner
+//  * a gather JOB: one extra warp per CTA pulls 64-row units of a row-sharded weight matrix from their owner
 //    ranks (peer loads over NVLink from the symmetric arena; the own rows with local loads) into a local
 //    staging buffer and bump a per-unit counter with a release once a 4-row chunk has landed. The job may
 //    belong to the B operand of this very launch (cold start) or — the normal case — to a matrix that a LATER
@@ -86,7 +87,9 @@ struct Gemm2Params {
 //    path when everything has already landed).
 // TMA only ever reads this GPU's staging buffer; peer memory is read with ld.global by the gather warps.
 constexpr int GATHER_CH = 16;              // chunks per 64-row unit (4 rows each)
-constexpr int GATHER_THREADS = 128;
+constexpr int GATHER_THREADS = 32;          // one warp: the CTA stays at 256 threads (ptxas budgets registers per
+                                           // 128 threads: 288 threads would cap the epilogue at 168 and spill)
+constexpr int GATHER_MLP = 16;              // 16-byte loads in flight per gather thread
 struct GatherJob {
   const void* peer[16];     // every rank's shard base (peer-mapped; peer[rank] is local)
   uint8_t* staging;         // local full matrix [world * rows_per_rank, row_bytes]
@@ -207,6 +210,14 @@ __device__ __forceinline__ void tma_load_2d_2sm(uint32_t dst_smem, const CUtenso
       "l"(reinterpret_cast<uint64_t>(m)), "r"(bar_cluster), "r"(c0), "r"(c1)
       : "memory");
 }
+__device__ __forceinline__ void tma_load_3d_2sm(uint32_t dst_smem, const CUtensorMap* m, uint32_t bar_cluster,
+                                                int c0, int c1, int c2) {
+  asm volatile(
+      "cp.async.bulk.tensor.3d.cta_group::2.shared::cluster.global.tile.mbarrier::complete_tx::bytes "
+      "[%0], [%1, {%3, %4, %5}], [%2];" ::"r"(dst_smem),
+      "l"(reinterpret_cast<uint64_t>(m)), "r"(bar_cluster), "r"(c0), "r"(c1), "r"(c2)
+      : "memory");
+}
 __device__ __forceinline__ void tmem_alloc2(uint32_t dst_smem_addr, uint32_t ncols) {
   asm volatile("tcgen05.alloc.cta_group::2.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(dst_smem_addr), "r"(ncols) : "memory");
 }
@@ -287,7 +298,38 @@ gemm2_kernel(const Gemm2Params p, const GatherJob gj, const WaitSpec ws_, const 
   const uint32_t tmem_base = __shfl_sync(0xffffffffu, *tmem_slot_ptr, 0);
 
   if (warp == 0) {
-    // ===================== TMA producer (both CTAs) =====================
+    // ===================== A producer (both CTAs): this CTA's 128 rows of A =====================
+    // One elected thread; the loop body is kept minimal — a k-block lasts ~512 clk on the tensor cores and every
+    // UTMALDG costs the issuing thread on the order of 100 clk, which is why A and B have separate producer
+    // threads (with one thread the input-gradient form, two B boxes per stage, was issue-bound: 1,180 vs cuBLAS
+    // 1,296 TFLOP/s sustained).
+    if (lane == 0) {
+      uint32_t stage = 0, phase = 0;
+      const uint32_t fb0 = mapa_rank(full_bar(0), 0);          // the leader's barriers (mapping is linear)
+      SegIter segs(p, cid, ncl);
+      Seg sg;
+      while (segs.next(sg)) {
+        const int n_blk = sg.tile / p.nmb2;
+        const int m0 = (sg.tile - n_blk * p.nmb2) * 2 * BM + (int)rank * BM;
+        const uint32_t tx = sg.half >= 0 ? 2 * (A_BYTES + B_BYTES / 2) : 2 * STAGE_BYTES;
+        const int kb_main_end = sg.kb1 < p.nkb_main ? sg.kb1 : p.nkb_main;
+        int kb = sg.kb0;
+        for (; kb < kb_main_end; ++kb) {
+          mbar_wait_bounded(empty_bar(stage), phase ^ 1u);
+          if (leader) mbar_expect_tx(full_bar(stage), tx);
+          tma_load_2d_2sm(smem_base + stage * STAGE_BYTES, &tmA, fb0 + 8u * stage, kb * BK, m0);
+          if (++stage == STAGES) { stage = 0; phase ^= 1u; }
+        }
+        for (; kb < sg.kb1; ++kb) {                               // K-extension (LoRA) blocks
+          mbar_wait_bounded(empty_bar(stage), phase ^ 1u);
+          if (leader) mbar_expect_tx(full_bar(stage), tx);
+          tma_load_2d_2sm(smem_base + stage * STAGE_BYTES, &tmA2, fb0 + 8u * stage, (kb - p.nkb_main) * BK, m0);
+          if (++stage == STAGES) { stage = 0; phase ^= 1u; }
+        }
+      }
+    }
+  } else if (warp == 6) {
+    // ===================== B producer (both CTAs): this CTA's half of the B tile =====================
     bool all_ready = true;        // WAIT: every unit of B has already landed (gathered by earlier launches)
     if (ws_.counters) {
       for (int u = lane; u < ws_.n_units; u += 32)
@@ -297,20 +339,18 @@ gemm2_kernel(const Gemm2Params p, const GatherJob gj, const WaitSpec ws_, const 
       asm volatile("fence.proxy.async.global;" ::: "memory");
     }
     if (lane == 0) {
-      int stage = 0;
-      uint32_t phase = 0;
+      uint32_t stage = 0, phase = 0;
+      const uint32_t fb0 = mapa_rank(full_bar(0), 0);
+      const uint32_t sb0 = smem_base + A_BYTES;
       SegIter segs(p, cid, ncl);
       Seg sg;
       while (segs.next(sg)) {
         const int n_blk = sg.tile / p.nmb2;
-        const int m_blk = sg.tile - n_blk * p.nmb2;
-        const int m0 = m_blk * 2 * BM + (int)rank * BM;          // this CTA's A rows
-        // this CTA's half of the B tile (SwiGLU mode: gate rows for rank 0, the matching up rows for rank 1)
-        // A half tile needs only 64 B rows per CTA (tmBh / tmB2h: the same matrices with 64-row boxes).
+        // this CTA's half of the B tile (SwiGLU mode: gate rows for rank 0, the matching up rows for rank 1);
+        // a half tile needs only 64 B rows per CTA (tmBh / tmB2h: the same matrices with 64-row boxes)
         const bool hf = sg.half >= 0;
-        const uint32_t tx = hf ? 2 * (A_BYTES + B_BYTES / 2) : 2 * STAGE_BYTES;
         int n0;
-        if (sg.half < 0) n0 = p.swiglu_ff > 0 ? n_blk * (BN / 2) + (int)rank * p.swiglu_ff : n_blk * BN + (int)rank * (BN / 2);
+        if (!hf) n0 = p.swiglu_ff > 0 ? n_blk * (BN / 2) + (int)rank * p.swiglu_ff : n_blk * BN + (int)rank * (BN / 2);
         else n0 = p.swiglu_ff > 0 ? n_blk * (BN / 2) + sg.half * (BN / 4) + (int)rank * p.swiglu_ff
                                   : n_blk * BN + sg.half * (BN / 2) + (int)rank * (BN / 4);
         if (!B_MN && !all_ready) {      // K-major B: this CTA's rows [n0, n0 + 128 or 64) = 2 or 1 units
@@ -318,26 +358,50 @@ gemm2_kernel(const Gemm2Params p, const GatherJob gj, const WaitSpec ws_, const 
           if (!hf) wait_unit(ws_, (n0 >> 6) + 1);
           asm volatile("fence.proxy.async.global;" ::: "memory");
         }
-        for (int kb = sg.kb0; kb < sg.kb1; ++kb) {
-          mbar_wait_bounded(empty_bar(stage), phase ^ 1u);
-          const uint32_t sa = smem_base + stage * STAGE_BYTES;
-          const uint32_t sb = sa + A_BYTES;
-          const uint32_t fb = mapa_rank(full_bar(stage), 0);      // the leader's barrier
-          if (leader) mbar_expect_tx(full_bar(stage), tx);
-          const bool ext = kb >= p.nkb_main;
-          const CUtensorMap* ma = ext ? &tmA2 : &tmA;
-          const CUtensorMap* mb = ext ? (hf ? &tmB2h : &tmB2) : (hf ? &tmBh : &tmB);
-          const int k0 = (ext ? kb - p.nkb_main : kb) * BK;
-          if (B_MN && !all_ready && !ext) {   // MN-major B: contraction rows [k0, k0 + 64) = unit kb
+        const CUtensorMap* mb = hf ? &tmBh : &tmB;
+        const bool two = B_MN && !hf && !p.b3d;                  // MN-major full tile as two 64x64 boxes
+        const bool one3d = B_MN && !hf && p.b3d;
+        const int kb_main_end = sg.kb1 < p.nkb_main ? sg.kb1 : p.nkb_main;
+        int kb = sg.kb0;
+        if (all_ready || !B_MN) {
+          for (; kb < kb_main_end; ++kb) {
+            mbar_wait_bounded(empty_bar(stage), phase ^ 1u);
+            const uint32_t sb = sb0 + stage * STAGE_BYTES, fb = fb0 + 8u * stage;
+            if constexpr (!B_MN) {
+              tma_load_2d_2sm(sb, mb, fb, kb * BK, n0);
+            } else if (one3d) {
+              tma_load_3d_2sm(sb, mb, fb, 0, kb * BK, n0 >> 6);
+            } else {
+              tma_load_2d_2sm(sb, mb, fb, n0, kb * BK);
+              if (two) tma_load_2d_2sm(sb + BK * 128, mb, fb, n0 + 64, kb * BK);
+            }
+            if (++stage == STAGES) { stage = 0; phase ^= 1u; }
+          }
+        } else {
+          for (; kb < kb_main_end; ++kb) {                        // MN-major B still landing: unit kb per k-block
             wait_unit(ws_, kb);
             asm volatile("fence.proxy.async.global;" ::: "memory");
+            mbar_wait_bounded(empty_bar(stage), phase ^ 1u);
+            const uint32_t sb = sb0 + stage * STAGE_BYTES, fb = fb0 + 8u * stage;
+            if (one3d) {
+              tma_load_3d_2sm(sb, mb, fb, 0, kb * BK, n0 >> 6);
+            } else {
+              tma_load_2d_2sm(sb, mb, fb, n0, kb * BK);
+              if (two) tma_load_2d_2sm(sb + BK * 128, mb, fb, n0 + 64, kb * BK);
+            }
+            if (++stage == STAGES) { stage = 0; phase ^= 1u; }
           }
-          tma_load_2d_2sm(sa, ma, fb, k0, m0);
+        }
+        const CUtensorMap* mb2 = hf ? &tmB2h : &tmB2;
+        for (; kb < sg.kb1; ++kb) {                               // K-extension (LoRA) blocks: plain memory
+          mbar_wait_bounded(empty_bar(stage), phase ^ 1u);
+          const uint32_t sb = sb0 + stage * STAGE_BYTES, fb = fb0 + 8u * stage;
+          const int k0 = (kb - p.nkb_main) * BK;
           if constexpr (!B_MN) {
-            tma_load_2d_2sm(sb, mb, fb, k0, n0);
+            tma_load_2d_2sm(sb, mb2, fb, k0, n0);
           } else {
-            tma_load_2d_2sm(sb, mb, fb, n0, k0);
-            if (!hf) tma_load_2d_2sm(sb + BK * 128, mb, fb, n0 + 64, k0);
+            tma_load_2d_2sm(sb, mb2, fb, n0, k0);
+            if (!hf) tma_load_2d_2sm(sb + BK * 128, mb2, fb, n0 + 64, k0);
           }
           if (++stage == STAGES) { stage = 0; phase ^= 1u; }
         }
@@ -380,9 +444,9 @@ gemm2_kernel(const Gemm2Params p, const GatherJob gj, const WaitSpec ws_, const 
         if (++acc == 2) { acc = 0; acc_phase ^= 1u; }
       }
     }
-  } else if (warp >= 6) {
+  } else if (warp >= 7) {
     // ===================== gather warps (present when a job is attached) =====================
-    const int gt = threadIdx.x - NUM_THREADS;                  // 0..127
+    const int gt = threadIdx.x - NUM_THREADS;                  // 0..31
     const long long chunk_bytes = 4 * gj.row_bytes;            // 4 rows
     const long long unit_bytes = 64 * gj.row_bytes;
     const int total_chunks = gj.j_count * GATHER_CH;
@@ -396,16 +460,16 @@ gemm2_kernel(const Gemm2Params p, const GatherJob gj, const WaitSpec ws_, const 
       uint8_t* dst = gj.staging + (long long)u * unit_bytes + part * chunk_bytes;
       const long long nvec = chunk_bytes >> 4;
       long long i = gt;
-      for (; i + 7 * GATHER_THREADS < nvec; i += 8 * GATHER_THREADS) {
-        int4 v[8];
+      for (; i + (GATHER_MLP - 1) * GATHER_THREADS < nvec; i += GATHER_MLP * GATHER_THREADS) {
+        int4 v[GATHER_MLP];
 #pragma unroll
-        for (int q = 0; q < 8; ++q) v[q] = ld_nc_v4(src + ((i + q * GATHER_THREADS) << 4));
+        for (int q = 0; q < GATHER_MLP; ++q) v[q] = ld_nc_v4(src + ((i + q * GATHER_THREADS) << 4));
 #pragma unroll
-        for (int q = 0; q < 8; ++q) st_v4(dst + ((i + q * GATHER_THREADS) << 4), v[q]);
+        for (int q = 0; q < GATHER_MLP; ++q) st_v4(dst + ((i + q * GATHER_THREADS) << 4), v[q]);
       }
       for (; i < nvec; i += GATHER_THREADS) st_v4(dst + (i << 4), ld_nc_v4(src + (i << 4)));
       __threadfence();
-      asm volatile("bar.sync 2, 128;" ::: "memory");
+      __syncwarp();
       if (gt == 0) red_release_gpu_add_u32(gj.counters + u, 1u);
     }
   } else {
@@ -725,7 +789,7 @@ gemm2_kernel(const Gemm2Params p, const GatherJob gj, const WaitSpec ws_, const 
 }
 
 // The gather role on its own (no GEMM to ride on: flushing what is left of a matrix, bandwidth probes).
-__global__ void __launch_bounds__(GATHER_THREADS) gather_job_kernel(const GatherJob gj) {
+__global__ void __launch_bounds__(GATHER_THREADS) gather_job_kernel(const GatherJob gj) {   // one warp per CTA
   __shared__ const void* s_peers[16];
 #pragma unroll
   for (int i = 0; i < 16; ++i)
@@ -744,16 +808,16 @@ __global__ void __launch_bounds__(GATHER_THREADS) gather_job_kernel(const Gather
     uint8_t* dst = gj.staging + (long long)u * unit_bytes + part * chunk_bytes;
     const long long nvec = chunk_bytes >> 4;
     long long i = gt;
-    for (; i + 7 * GATHER_THREADS < nvec; i += 8 * GATHER_THREADS) {
-      int4 v[8];
+    for (; i + (GATHER_MLP - 1) * GATHER_THREADS < nvec; i += GATHER_MLP * GATHER_THREADS) {
+      int4 v[GATHER_MLP];
 #pragma unroll
-      for (int q = 0; q < 8; ++q) v[q] = ld_nc_v4(src + ((i + q * GATHER_THREADS) << 4));
+      for (int q = 0; q < GATHER_MLP; ++q) v[q] = ld_nc_v4(src + ((i + q * GATHER_THREADS) << 4));
 #pragma unroll
-      for (int q = 0; q < 8; ++q) st_v4(dst + ((i + q * GATHER_THREADS) << 4), v[q]);
+      for (int q = 0; q < GATHER_MLP; ++q) st_v4(dst + ((i + q * GATHER_THREADS) << 4), v[q]);
     }
     for (; i < nvec; i += GATHER_THREADS) st_v4(dst + (i << 4), ld_nc_v4(src + (i << 4)));
     __threadfence();
-    __syncthreads();
+    __syncwarp();
     if (gt == 0) red_release_gpu_add_u32(gj.counters + u, 1u);
   }
 }
@@ -820,6 +884,13 @@ const SkWorkspace* sk_workspace(cudaStream_t stream) {
 // are cut in two when that lets the wave finish in half the time (2 * (T % C) <= C). Llama-2-7B at M = 4096:
 // the [4096 x 4096] outputs (o_proj, down_proj, every input gradient of qkv / gate_up) are 256 tiles on 74
 // clusters = 3.46 waves -> 3.5 instead of 4. DLTI_GEMM_TAILSPLIT=0 switches it off (A/B).
+// MN-major B as one 3D TMA box per stage instead of two 2D boxes: measured SLOWER on B200 (qkv input gradient,
+// sustained: 1,068 vs 1,122 TFLOP/s), so it is opt-in (DLTI_GEMM_MN3D=1).
+bool mn3d_enabled() {
+  static const bool on = []() { const char* e = getenv("DLTI_GEMM_MN3D"); return e && e[0] == '1'; }();
+  return on;
+}
+
 void set_tail_split(Gemm2Params& p, int grid, int dtype, bool b_mn) {
   static const bool on = []() { const char* e = getenv("DLTI_GEMM_TAILSPLIT"); return !(e && e[0] == '0'); }();
   const int total = p.nmb2 * p.nnb, ncl = grid / 2;
@@ -879,7 +950,7 @@ DLTI_API int dlti_gather_job_run(int ctas, cudaStream_t stream) {
   t_job = GatherJob{};
   t_wait = WaitSpec{};
   if (job.j_count <= 0) return 0;
-  int grid = ctas > 0 ? ctas : 2 * dlti_num_sms();
+  int grid = ctas > 0 ? ctas : 16 * dlti_num_sms();
   if (grid > job.j_count * GATHER_CH) grid = job.j_count * GATHER_CH;
   gather_job_kernel<<<grid, GATHER_THREADS, 0, stream>>>(job);
   dlti_count_launch();
@@ -919,6 +990,7 @@ DLTI_API int dlti_gemm_2cta(const void* A, const void* B, void* C, const void* R
   if (rc) return rc;
   tbh = tb;                  // MN-major: a half tile is one of the two 64x64 boxes
   if (!b_mn && (rc = dlti_get_tmap(&tbh, B, K, N, ldb, 64, BN / 4))) return rc;
+  if (b_mn && N % 64 == 0 && mn3d_enabled() && dlti_get_tmap_mn3d(&tb, B, N, K, ldb, BK, (BN / 2) / 64) == 0) p.b3d = 1;
   ta2 = ta; tb2 = tb; tb2h = tbh;
   if (p.nkb_ext > 0) {
     if ((rc = dlti_get_tmap(&ta2, A2, K2, M, lda2, 64, BM))) return rc;
@@ -1013,11 +1085,13 @@ DLTI_API int dlti_gemm_swiglu_bwd_2cta(const void* dY, const void* Wdown, const 
   int rc;
   if ((rc = dlti_get_tmap(&ta, dY, K, M, ldy, 64, BM))) return rc;
   if ((rc = dlti_get_tmap(&tb, Wdown, ff, K, ldw, 64, 64))) return rc;
+  CUtensorMap tb3 = tb;
+  if (ff % 64 == 0 && mn3d_enabled() && dlti_get_tmap_mn3d(&tb3, Wdown, ff, K, ldw, BK, (BN / 2) / 64) == 0) p.b3d = 1;
   int grid = dlti_num_sms() & ~1;
   const int total = p.nmb2 * p.nnb;
   if (2 * total < grid) grid = 2 * total;
   set_tail_split(p, grid, dtype, true);
-  return launch2<true>(p, ta, tb, ta, tb, tb, tb, grid, stream);
+  return launch2<true>(p, ta, tb3, ta, tb, tb, tb, grid, stream);
 }
 
 // C[M, N] = rope(alpha * (A · B^T + A2 · B2^T)): the fused QKV projection (B = [N, K], optional LoRA

@@ -156,6 +156,41 @@ int dlti_get_tmap(CUtensorMap* out, const void* base, uint64_t inner, uint64_t o
   return 0;
 }
 
+// MN-major operand [K, N] (N contiguous) as ONE box per stage: a 3D view {64 n-elements, K rows, N/64 chunks}
+// whose box {64, box_k, chunks} lands in shared memory chunk after chunk — the layout the MN-major UMMA
+// descriptor expects (successive 64-element MN chunks box_k * 128 bytes apart) — so the producer issues one TMA
+// instead of one per chunk. Requires N % 64 == 0. Cached like dlti_get_tmap.
+int dlti_get_tmap_mn3d(CUtensorMap* out, const void* base, uint64_t N, uint64_t K, uint64_t ld, uint32_t box_k,
+                       uint32_t chunks) {
+  if (N % 64) return DLTI_ERR_UNSUPPORTED;
+  TmapKey key{base, N, K, ld, 0x80000000u | box_k, chunks};
+  {
+    std::lock_guard<std::mutex> g(g_tm_mu);
+    auto it = g_tm_cache.find(key);
+    if (it != g_tm_cache.end()) {
+      *out = it->second;
+      return 0;
+    }
+  }
+  std::call_once(g_encode_once, load_encode);
+  if (!g_encode) return DLTI_ERR_DRIVER;
+  if ((reinterpret_cast<uintptr_t>(base) & 15) || ((ld * 2) & 15)) return DLTI_ERR_BAD_ARG;
+  cuuint64_t gdim[3] = {64, K, N / 64};
+  cuuint64_t gstride[2] = {ld * 2, 128};
+  cuuint32_t box[3] = {64, box_k, chunks};
+  cuuint32_t estr[3] = {1, 1, 1};
+  CUresult r = g_encode(out, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 3, const_cast<void*>(base), gdim, gstride, box, estr,
+                        CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                        CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) {
+    dlti_set_error("cuTensorMapEncodeTiled (3D MN-major view) failed");
+    return DLTI_ERR_DRIVER;
+  }
+  std::lock_guard<std::mutex> g(g_tm_mu);
+  g_tm_cache.emplace(key, *out);
+  return 0;
+}
+
 // ---- CUDA IPC helpers for the symmetric arena (fallback when torch symmetric memory is
 // unavailable): open a peer's cudaIpcMemHandle_t (64 bytes) in this process. P2P access over
 // NVLink is enabled lazily by the driver. -------------------------------------------------------

@@ -167,7 +167,7 @@ int dlti_gemm_2cta(const void* A, const void* B, void* C, const void* R, int M, 
 /* K1 on the CTA-pair kernel (ZeRO-3 all-gather fused into the GEMM; replaces the reference's DeepSpeed
  * stage-3 parameter all-gather, /root/reference/configs/ds_config_zero3.json:16-37). Attaches to the NEXT
  * dlti_gemm_2cta / _rope_2cta / _swiglu_2cta / _swiglu_bwd_2cta launch made from this host thread:
- *  - a gather job (j_count > 0): four extra warps per CTA pull the 64-row units (rot_unit + j) % n_units,
+ *  - a gather job (j_count > 0): one extra warp per CTA pulls the 64-row units (rot_unit + j) % n_units,
  *    j in [j_begin, j_begin + j_count), of a row-sharded matrix [world * rows_per_rank, row_bytes] from their
  *    owner ranks (peer loads; own rows locally) into `staging` and publish per-unit counters: unit u is
  *    complete once counters[u] >= epoch * 16. The job may feed this launch's own B operand or, normally, a

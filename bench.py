@@ -171,6 +171,13 @@ def main() -> None:
             dist.barrier()
             torch.cuda.synchronize()
 
+    def min_over_ranks(v: float) -> float:
+        if world == 1:
+            return v
+        t = torch.tensor([v], dtype=torch.float64, device="cuda")
+        dist.all_reduce(t, op=dist.ReduceOp.MIN)
+        return float(t.item())
+
     def max_over_ranks(v: float) -> float:
         if world == 1:
             return v
@@ -185,6 +192,8 @@ def main() -> None:
     dev_steps = [[mb.to("cuda") for mb in st] for st in host_steps[a.warmup:]]
     sync_all()
     sampler = ClockSampler(torch.cuda.current_device()) if info.rank == 0 else None
+    tr.ds.wall_clock_breakdown = True        # one extra event per step: forward+backward | reduce/clip/AdamW/refresh
+    tr._phase_events = []
     _lib.reset_launch_count()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     e0.record()
@@ -194,6 +203,14 @@ def main() -> None:
     sync_all()
     dev_ms = max_over_ranks(e0.elapsed_time(e1)) / a.steps
     launches = _lib.launch_count()
+    # per-rank phase times: a rank that finishes its forward+backward early waits for the slowest one inside the
+    # optimizer phase (first peer barrier), so min/max of the first phase over ranks shows the spread between GPUs
+    fb = sum(x[0].elapsed_time(x[1]) for x in tr._phase_events) / max(1, len(tr._phase_events))
+    tail = sum(x[1].elapsed_time(x[2]) for x in tr._phase_events) / max(1, len(tr._phase_events))
+    phases = {"fwd_bwd_ms_min_rank": min_over_ranks(fb), "fwd_bwd_ms_max_rank": max_over_ranks(fb),
+              "optimizer_phase_ms_min_rank": min_over_ranks(tail), "optimizer_phase_ms_max_rank": max_over_ranks(tail)}
+    tr.ds.wall_clock_breakdown = False
+    tr._phase_events = []
     loss_dev = float(loss_t.item()) / n_tot
     # ---- region 2: end to end through the public API ----
     sync_all()
@@ -236,11 +253,37 @@ def main() -> None:
             "e2e": {"value": e2e, "unit": "tokens/s", "ms_per_step": e2e_ms, "h2d_bytes_per_step": h2d,
                     "d2h_bytes_per_step": 12},
             "gpu_launches": int(launches),
-            "clocks": clocks,
+            "clocks": clocks, "phases": phases,
             "loss": loss, "loss_device_region": loss_dev, "peak_memory_gb_max_rank": peak,
             "model_tflops_per_gpu": (6 if not a.no_grad_ckpt else 4) * cfg.num_params() * tokens_per_step
                                     / world / dev_ms / 1e9,
         }
+        # FLOPs the step actually executes (frozen base: no weight gradients; the recompute skips the down
+        # projection and the LM head) and the recompute-free "model FLOPs" (4P: forward + input gradients)
+        d_, ff_, L_ = cfg.hidden_size, cfg.intermediate_size, cfg.num_hidden_layers
+        p_layer = d_ * cfg.qkv_size + cfg.q_size * d_ + 3 * ff_ * d_
+        p_head = cfg.vocab_size * d_
+        rec = 0 if a.no_grad_ckpt else 2 * L_ * (p_layer - ff_ * d_)
+        lin = 2 * (L_ * p_layer + p_head) * 2 + rec
+        attn_fwd = 2 * a.seq_len * cfg.q_size * L_                    # causal: half of 4*S*q_size per token
+        attn = attn_fwd * (2.5 + (1 if a.no_grad_ckpt else 2))
+        tok_gpu_s = tokens_per_step / world / dev_ms * 1e3
+        out["executed_tflops_per_gpu"] = (lin + attn) * tok_gpu_s / 1e12
+        out["mfu_4p_tflops_per_gpu"] = (4 * cfg.num_params() + 3.5 * attn_fwd) * tok_gpu_s / 1e12
+        try:
+            pk = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+            out["executed_frac_of_measured_sustained_bf16"] = out["executed_tflops_per_gpu"] / pk["bf16_tflops_sustained"]
+            out["mfu_4p_frac_of_measured_sustained_bf16"] = out["mfu_4p_tflops_per_gpu"] / pk["bf16_tflops_sustained"]
+        except Exception:
+            pass
+        # same-box comparator measured with `bench.py --impl standin` (profiles/standin_bench_n*_r2.json)
+        try:
+            sb = [json.loads(l) for l in open(os.path.join(ROOT, "profiles", f"standin_bench_n{world}_r2.json"))
+                  if l.startswith("{")][0]
+            out["vs_standin_committed"] = {"standin_tok_s": sb["value"], "ratio": value / sb["value"],
+                                           "file": f"profiles/standin_bench_n{world}_r2.json"}
+        except Exception:
+            pass
         print(json.dumps(out))
     comm.barrier(info)
     comm.shutdown()

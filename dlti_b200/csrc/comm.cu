@@ -342,6 +342,128 @@ __global__ void __launch_bounds__(128) tp_pull_reduce_norm_push_kernel(Peers par
   __threadfence_system();
 }
 
+// ---------------------------------------------------------------------------------------------------------
+// K9, overlapped form: adapter-gradient reduce-scatter as soon as a layer's gradients are final, and one
+// kernel for norm exchange + unscale/clip + AdamW + all-gather push.
+//
+//   grad_ready_signal     (main stream, after a layer's backward): tell every rank "my gradients of range
+//                         `slot` are final for step `epoch`" (one release store per peer).
+//   rs_wait_accumulate    (side stream): the owner of (part of) that range waits for all ranks' signals — they
+//                         arrive while the remaining layers' backward is still running — and adds the peers'
+//                         slices to its partition accumulator with peer loads in fixed rank order (bitwise
+//                         reproducible; same order as rs_accumulate_kernel).
+//   k9_step               exchange of (sum of squares, loss sum) over peer stores + flags, then unscale / clip /
+//                         AdamW on the owned partition with the new fp32 values stored into every rank's master
+//                         buffer, then "my pushes are complete" to every peer (last CTA).
+//   peer_wait             waits for those flags (before the 16-bit recast of the adapters).
+// flags.p[r] = rank r's u32 flag array, entry [slot * MAX_RANKS + source rank], monotonic epochs.
+__global__ void grad_ready_signal_kernel(Peers flags, int rank, int world, int slot, uint32_t epoch) {
+  const int t = threadIdx.x;
+  if (t < world) {
+    __threadfence_system();
+    st_release_sys_u32(reinterpret_cast<uint32_t*>(flags.p[t]) + slot * MAX_RANKS + rank, epoch);
+  }
+}
+
+__global__ void __launch_bounds__(256) rs_wait_accumulate_kernel(Peers grads, const uint32_t* __restrict__ my_flags,
+                                                                float* __restrict__ part, long long glo,
+                                                                long long plo, long long n, int world, int slot,
+                                                                uint32_t epoch, int* err) {
+  if (threadIdx.x < world) wait_ge_sys(my_flags + slot * MAX_RANKS + threadIdx.x, epoch, err);
+  __syncthreads();
+  const long long n4 = n >> 2;
+  float4* dst = reinterpret_cast<float4*>(part + plo);
+  for (long long i = (long long)blockIdx.x * 256 + threadIdx.x; i < n4; i += (long long)gridDim.x * 256) {
+    float4 acc = dst[i];
+    for (int r = 0; r < world; ++r) {
+      const int4 v = ld_relaxed_sys_v4(reinterpret_cast<const float4*>(reinterpret_cast<const float*>(grads.p[r]) + glo) + i);
+      acc.x += __int_as_float(v.x); acc.y += __int_as_float(v.y);
+      acc.z += __int_as_float(v.z); acc.w += __int_as_float(v.w);
+    }
+    dst[i] = acc;
+  }
+}
+
+struct K9Step {
+  Peers masters, boards, pads;
+  float *m, *v, *g;
+  const float* local2;      // [2]: this rank's sum of squares of its reduced partition, its loss sum
+  float* out2;              // [2]: global sums (rank order)
+  int* skipped_out;
+  unsigned int* done;       // zero-initialised scratch word
+  int* err;
+  long long lo, n;
+  int rank, world, ch_norm, ch_push;
+  uint32_t epoch;
+  float lr, b1, b2, eps, wd, ibc1, ibc2, inv_scale, max_norm;
+};
+
+__global__ void __launch_bounds__(256) k9_step_kernel(const K9Step k) {
+  __shared__ float s_nsq;
+  const int t = threadIdx.x;
+  // ---- exchange: CTA 0 publishes, every CTA waits and sums the board in rank order ----
+  if (t < k.world) {
+    if (blockIdx.x == 0) {
+      float* rb = reinterpret_cast<float*>(k.boards.p[t]) + 2 * k.rank;
+      asm volatile("st.relaxed.sys.global.f32 [%0], %1;" ::"l"(rb), "f"(k.local2[0]) : "memory");
+      asm volatile("st.relaxed.sys.global.f32 [%0], %1;" ::"l"(rb + 1), "f"(k.local2[1]) : "memory");
+      __threadfence_system();
+      st_release_sys_u32(reinterpret_cast<uint32_t*>(k.pads.p[t]) + k.ch_norm * MAX_RANKS + k.rank, k.epoch);
+    }
+    wait_ge_sys(reinterpret_cast<const uint32_t*>(k.pads.p[k.rank]) + k.ch_norm * MAX_RANKS + t, k.epoch, k.err);
+  }
+  __syncthreads();
+  if (t == 0) {
+    float s = 0.f, l = 0.f;
+    const float* mb = reinterpret_cast<const float*>(k.boards.p[k.rank]);
+    for (int r = 0; r < k.world; ++r) {
+      float a, b;
+      asm volatile("ld.relaxed.sys.global.f32 %0, [%1];" : "=f"(a) : "l"(mb + 2 * r) : "memory");
+      asm volatile("ld.relaxed.sys.global.f32 %0, [%1];" : "=f"(b) : "l"(mb + 2 * r + 1) : "memory");
+      s += a; l += b;
+    }
+    s_nsq = s;
+    if (blockIdx.x == 0) { k.out2[0] = s; k.out2[1] = l; }
+  }
+  __syncthreads();
+  const float nsq = s_nsq;
+  const bool skip = !isfinite(nsq);
+  if (blockIdx.x == 0 && t == 0 && k.skipped_out) *k.skipped_out = skip ? 1 : 0;
+  // ---- unscale / clip / AdamW on [lo, lo + n), new values pushed to every rank ----
+  float coef = k.inv_scale;
+  if (k.max_norm > 0.f) coef *= fminf(1.f, k.max_norm / (sqrtf(nsq) * k.inv_scale + 1e-6f));
+  float* mine = reinterpret_cast<float*>(k.masters.p[k.rank]) + k.lo;
+  for (long long i = (long long)blockIdx.x * 256 + t; i < k.n; i += (long long)gridDim.x * 256) {
+    if (!skip) {
+      const float ge = k.g[i] * coef;
+      const float mi = k.b1 * k.m[i] + (1.f - k.b1) * ge;
+      const float vi = k.b2 * k.v[i] + (1.f - k.b2) * ge * ge;
+      float pi = mine[i];
+      pi -= k.lr * ((mi * k.ibc1) / (sqrtf(vi * k.ibc2) + k.eps) + k.wd * pi);
+      k.m[i] = mi; k.v[i] = vi;
+      for (int r = 0; r < k.world; ++r) (reinterpret_cast<float*>(k.masters.p[r]) + k.lo)[i] = pi;
+    }
+    k.g[i] = 0.f;
+  }
+  // ---- "my pushes are complete": the last CTA to finish tells every peer ----
+  __threadfence_system();
+  __syncthreads();
+  __shared__ int s_last;
+  if (t == 0) s_last = (atomicAdd(k.done, 1u) == gridDim.x - 1);
+  __syncthreads();
+  if (s_last) {
+    if (t == 0) *k.done = 0u;
+    if (t < k.world) {
+      __threadfence_system();
+      st_release_sys_u32(reinterpret_cast<uint32_t*>(k.pads.p[t]) + k.ch_push * MAX_RANKS + k.rank, k.epoch);
+    }
+  }
+}
+
+__global__ void peer_wait_kernel(const uint32_t* __restrict__ my_pads, int world, int channel, uint32_t epoch, int* err) {
+  if (threadIdx.x < world) wait_ge_sys(my_pads + channel * MAX_RANKS + threadIdx.x, epoch, err);
+}
+
 // K15: embedding over a vocabulary-sharded table (rank r owns rows [r * rows_per_rank, (r + 1) * rows_per_rank)):
 // every token's row is fetched from its owner rank with 16-byte peer loads (the table is immutable during a
 // step: non-coherent loads). Replaces "all-gather the table, then look up": per step only the rows that are
@@ -468,6 +590,65 @@ DLTI_API int dlti_embedding_peer(const long long* ids, const void* const* shards
     embedding_peer_kernel<__half><<<grid, 256, 0, st>>>(ids, P, (__half*)out, tokens, d, rows_per_rank, vocab);
   else
     return DLTI_ERR_UNSUPPORTED;
+  dlti_count_launch();
+  return (int)cudaGetLastError();
+}
+
+DLTI_API int dlti_grad_ready_signal(const void* const* flags, int rank, int world, int slot, unsigned int epoch,
+                                    cudaStream_t st) {
+  Peers F;
+  if (int rc = fill(F, flags, world)) return rc;
+  grad_ready_signal_kernel<<<1, 32, 0, st>>>(F, rank, world, slot, epoch);
+  dlti_count_launch();
+  return (int)cudaGetLastError();
+}
+
+// part[plo .. plo + n) += sum_r grads[r][glo .. glo + n) once every rank has signalled (slot, epoch).
+DLTI_API int dlti_rs_wait_accumulate(const void* const* grads, const unsigned int* my_flags, float* part,
+                                     long long glo, long long plo, long long n, int world, int slot,
+                                     unsigned int epoch, int ctas, int* err_flag, cudaStream_t st) {
+  Peers P;
+  if (int rc = fill(P, grads, world)) return rc;
+  if (n <= 0) return 0;
+  if (n % 4 || glo % 4 || plo % 4) { dlti_set_error("rs_wait_accumulate: ranges must be 16-byte aligned"); return DLTI_ERR_BAD_ARG; }
+  long long want = (n / 4 + 255) / 256;
+  const long long cap = ctas > 0 ? ctas : 16;
+  rs_wait_accumulate_kernel<<<(unsigned)(want > cap ? cap : want), 256, 0, st>>>(P, my_flags, part, glo, plo, n, world,
+                                                                                 slot, epoch, err_flag);
+  dlti_count_launch();
+  return (int)cudaGetLastError();
+}
+
+// Norm / loss exchange + unscale / clip / AdamW on [lo, lo + n) + push to every rank's master + completion flags.
+// local2 = {sum of squares of this rank's reduced partition, this rank's loss sum}; out2 = the global sums.
+// boards[r]: rank r's float board [2 * MAX_RANKS]; pads: signal words, channels ch_norm / ch_push.
+DLTI_API int dlti_k9_step(const void* const* masters, const void* const* boards, const void* const* signal_pads,
+                          float* m, float* v, float* g, long long lo, long long n, int rank, int world, float lr,
+                          float b1, float b2, float eps, float wd, int step, const float* local2, float* out2,
+                          float inv_scale, float max_norm, int* skipped_out, unsigned int* done_scratch, int ch_norm,
+                          int ch_push, unsigned int epoch, int* err_flag, cudaStream_t st) {
+  K9Step k{};
+  int rc;
+  if ((rc = fill(k.masters, masters, world)) || (rc = fill(k.boards, boards, world)) || (rc = fill(k.pads, signal_pads, world)))
+    return rc;
+  if (step < 1 || !local2 || !out2 || !done_scratch || n < 0) return DLTI_ERR_BAD_ARG;
+  k.m = m; k.v = v; k.g = g; k.local2 = local2; k.out2 = out2; k.skipped_out = skipped_out; k.done = done_scratch;
+  k.err = err_flag; k.lo = lo; k.n = n; k.rank = rank; k.world = world; k.ch_norm = ch_norm; k.ch_push = ch_push;
+  k.epoch = epoch; k.lr = lr; k.b1 = b1; k.b2 = b2; k.eps = eps; k.wd = wd;
+  k.ibc1 = 1.f / (1.f - powf(b1, (float)step)); k.ibc2 = 1.f / (1.f - powf(b2, (float)step));
+  k.inv_scale = inv_scale; k.max_norm = max_norm;
+  long long want = (n + 255) / 256;
+  const long long cap = (long long)dlti_num_sms() * 4;
+  if (want < 1) want = 1;
+  k9_step_kernel<<<(unsigned)(want > cap ? cap : want), 256, 0, st>>>(k);
+  dlti_count_launch();
+  return (int)cudaGetLastError();
+}
+
+DLTI_API int dlti_peer_wait(const unsigned int* my_pads, int world, int channel, unsigned int epoch, int* err_flag,
+                            cudaStream_t st) {
+  if (world < 1 || world > MAX_RANKS) return DLTI_ERR_BAD_ARG;
+  peer_wait_kernel<<<1, 32, 0, st>>>(my_pads, world, channel, epoch, err_flag);
   dlti_count_launch();
   return (int)cudaGetLastError();
 }

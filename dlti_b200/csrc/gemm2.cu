@@ -246,7 +246,10 @@ __device__ __forceinline__ void umma_commit_2sm(uint32_t bar) {
 }
 
 template <bool B_MN>
-__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(NUM_THREADS + GATHER_THREADS, 1)
+// __maxnreg__(200) instead of __launch_bounds__: at 256 threads ptxas would otherwise take 248 registers, i.e. the
+// whole register file of the SM, and the small peer-memory kernels that run next to the GEMMs on a side stream
+// (gradient reduce-scatter overlapped with backward, K9) could only start at GEMM boundaries. 200 spills nothing.
+__global__ void __cluster_dims__(2, 1, 1) __maxnreg__(200)
 gemm2_kernel(const Gemm2Params p, const GatherJob gj, const WaitSpec ws_, const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
              const __grid_constant__ CUtensorMap tmA2, const __grid_constant__ CUtensorMap tmB2,
              const __grid_constant__ CUtensorMap tmBh, const __grid_constant__ CUtensorMap tmB2h) {

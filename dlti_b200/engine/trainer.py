@@ -117,6 +117,7 @@ class Trainer:
         else:
             self.scheduler = build_scheduler(args.lr_scheduler_type, base_lr=args.learning_rate,
                                              total_steps=self.max_steps, warmup_steps=args.warmup_steps)
+        self.model.grad_hook = self.optimizer.on_grad_range_final
         self.gscale = torch.zeros(1, dtype=torch.float32, device=info.device)
         # ---- state ----
         self.global_step = 0
@@ -174,6 +175,7 @@ class Trainer:
             gs = scales
         devb = [pb.to(dev) if on_gpu else pb for pb in packed]
         opt.wait_reduce()
+        opt.begin_step()
         nvtx = on_gpu and self.args.profile            # --profile: NVTX ranges for nsys / ncu filtering (§5.1)
         if nvtx:
             torch.cuda.nvtx.range_push(f"step{self.global_step + 1}/fwd_bwd")
@@ -189,7 +191,7 @@ class Trainer:
             torch.cuda.nvtx.range_pop()
             torch.cuda.nvtx.range_push(f"step{self.global_step + 1}/optimizer")
         lr = self.scheduler.get_lr()
-        skipped, gnorm = opt.step(lr)
+        skipped, gnorm = opt.step(lr, loss_sum)
         if nvtx:
             torch.cuda.nvtx.range_pop()
         self.scaler.update(skipped)
@@ -197,7 +199,10 @@ class Trainer:
             self.skipped_steps += 1
         else:
             self.scheduler.step()
-        loss_sum = comm.all_reduce_sum_(loss_sum.reshape(1).float(), info)
+        if opt.loss_sum_global is not None:      # travelled with the norm exchange of the fused step kernel
+            loss_sum = torch.tensor([opt.loss_sum_global], dtype=torch.float32)
+        else:
+            loss_sum = comm.all_reduce_sum_(loss_sum.reshape(1).float(), info)
         if timed:
             e1.record()
             self._step_events.append((e0, e1))

@@ -173,6 +173,9 @@ class LoraLlama:
         self.training = True
         self.scale = 1.0 / math.sqrt(cfg.head_dim)
         self._rope = None
+        # called as grad_hook(flat_offset, numel) when a decoder layer's adapter gradients are final for the
+        # accumulation window (ZeRO: the reduce-scatter of that range can start while backward continues)
+        self.grad_hook = None
 
     # ---- helpers ---------------------------------------------------------------------------
     def _rope_tables(self, device):
@@ -400,5 +403,9 @@ class LoraLlama:
                 saves[k][li] = None
                 inputs[k][li] = None
             self.w.release(li)
+            if self.grad_hook is not None:
+                lo_, hi_ = self.lora.layer_range(li)
+                if hi_ > lo_:
+                    self.grad_hook(lo_, hi_ - lo_)
         self.micro_step = base_step + nb
         return loss_sum

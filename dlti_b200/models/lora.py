@@ -123,6 +123,14 @@ class LoraParams:
         b = self.master if buf is None else buf
         return b[s.offset:s.offset + s.numel].view(*s.shape)
 
+    def layer_range(self, li: int) -> tuple[int, int]:
+        """[lo, hi) of decoder layer li's adapter tensors in the flat buffers (they are contiguous)."""
+        cache = self.__dict__.setdefault("_layer_ranges", {})
+        if li not in cache:
+            ss = [s for n, s in self.slots.items() if n.startswith(f"layers.{li}.")]
+            cache[li] = (min(s.offset for s in ss), max(s.offset + s.numel for s in ss)) if ss else (0, 0)
+        return cache[li]
+
     def has(self, li: int, mod: str) -> bool:
         return f"layers.{li}.self_attn.{mod}.lora_A" in self.slots
 

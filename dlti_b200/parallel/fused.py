@@ -251,6 +251,7 @@ class GatherUse:
 
 class FusedComm:
     N_CHANNELS = 32
+    MAX_GRAD_RANGES = 256
 
     def __init__(self, info: DistInfo):
         assert info.distributed and info.device.type == "cuda"
@@ -262,9 +263,16 @@ class FusedComm:
         self._ptrs: dict[int, list[int]] = {}
         # signal words [channels, MAX_RANKS] u32 and the norm board [MAX_RANKS] f32
         self.pads = self.alloc_symmetric((self.N_CHANNELS * MAX_RANKS,), torch.int32)
-        self.board = self.alloc_symmetric((MAX_RANKS,), torch.float32)
+        self.board = self.alloc_symmetric((2 * MAX_RANKS,), torch.float32)
+        # K9 overlapped form: "gradients of range s are final" flags, one row of MAX_RANKS words per range
+        self.grad_flags = self.alloc_symmetric((self.MAX_GRAD_RANGES * MAX_RANKS,), torch.int32)
         self.pads.zero_()
         self.board.zero_()
+        self.grad_flags.zero_()
+        self.k9_epoch = 0
+        self._k9_done = torch.zeros(1, dtype=torch.int32, device=info.device)
+        self._k9_local2 = torch.zeros(2, dtype=torch.float32, device=info.device)
+        self.side_stream = torch.cuda.Stream(device=info.device)
         self.err = torch.zeros(1, dtype=torch.int32, device=info.device)
         self.epochs = [0] * self.N_CHANNELS
         self._tmp = torch.zeros(1, dtype=torch.float32, device=info.device)
@@ -357,6 +365,49 @@ class FusedComm:
                      self.world, lr, betas[0], betas[1], eps, wd, int(step), _lib.ptr(gnorm_sq),
                      float(inv_scale), float(max_norm), _lib.ptr(skipped_out), _lib.stream_ptr()), "adamw_push")
         self.barrier(4)
+
+    # ---- K9, overlapped form -----------------------------------------------------------------------
+    def k9_begin_step(self) -> None:
+        """New optimizer step: the epoch that the per-range flags and the step kernel's channels carry."""
+        self.k9_epoch += 1
+
+    def grad_range_final(self, slot: int, g_full: torch.Tensor, grad_part: torch.Tensor, glo: int, n: int,
+                         part_lo: int, part_n: int) -> None:
+        """This rank's gradients of the flat range [glo, glo + n) (range number `slot`) are final for the current
+        step: tell every rank (main stream, i.e. behind the kernels that produced them) and, if part of the
+        range belongs to this rank's partition [part_lo, part_lo + part_n), start the reduction of that part on
+        the side stream — it waits for the other ranks' flags while the main stream goes on with backward."""
+        assert slot < self.MAX_GRAD_RANGES
+        f = _lib.fn("dlti_grad_ready_signal", [_V, _I, _I, _I, _U, _V])
+        _lib.check(f(self.peer_array(self.grad_flags), self.rank, self.world, slot, self.k9_epoch,
+                     _lib.stream_ptr()), "grad_ready_signal")
+        a, b = max(glo, part_lo), min(glo + n, part_lo + part_n)
+        if b <= a:
+            return
+        with torch.cuda.stream(self.side_stream):
+            f = _lib.fn("dlti_rs_wait_accumulate", [_V, _V, _V, _L, _L, _L, _I, _I, _U, _I, _V, _V])
+            _lib.check(f(self.peer_array(g_full), _lib.ptr(self.grad_flags), _lib.ptr(grad_part), a, a - part_lo, b - a,
+                         self.world, slot, self.k9_epoch, 16, _lib.ptr(self.err), _lib.stream_ptr()), "rs_wait_accumulate")
+
+    def k9_step(self, master_full: torch.Tensor, m, v, g, lo: int, n: int, *, lr, betas, eps, wd, step, loss_sum,
+                out2: torch.Tensor, inv_scale, max_norm, skipped_out) -> None:
+        """After backward: joins the side stream, then sum of squares of the reduced partition -> one kernel that
+        exchanges {norm, loss}, steps AdamW on the partition and pushes the new values to every rank -> wait for
+        everybody's pushes. out2 = [global sum of squares, global loss sum]. The caller recasts the adapters."""
+        from ..ops import optim as O
+
+        torch.cuda.current_stream().wait_stream(self.side_stream)
+        O.sumsq(g, out=self._k9_local2[0:1])
+        self._k9_local2[1:2].copy_(loss_sum.reshape(1))
+        f = _lib.fn("dlti_k9_step", [_V, _V, _V, _V, _V, _V, _L, _L, _I, _I, _F, _F, _F, _F, _F, _I, _V, _V, _F, _F, _V,
+                                     _V, _I, _I, _U, _V, _V])
+        _lib.check(f(self.peer_array(master_full), self.peer_array(self.board), self.peer_array(self.pads),
+                     _lib.ptr(m), _lib.ptr(v), _lib.ptr(g), lo, n, self.rank, self.world, lr, betas[0], betas[1], eps,
+                     wd, int(step), _lib.ptr(self._k9_local2), _lib.ptr(out2), float(inv_scale), float(max_norm),
+                     _lib.ptr(skipped_out), _lib.ptr(self._k9_done), 5, 6, self.k9_epoch, _lib.ptr(self.err),
+                     _lib.stream_ptr()), "k9_step")
+        f = _lib.fn("dlti_peer_wait", [_V, _I, _I, _U, _V, _V])
+        _lib.check(f(_lib.ptr(self.pads), self.world, 6, self.k9_epoch, _lib.ptr(self.err), _lib.stream_ptr()), "peer_wait")
 
     # ---- fused all-gather -> GEMM ----------------------------------------------------------------
     def gather_spec(self, shard: torch.Tensor, staging: torch.Tensor, counters: torch.Tensor) -> GatherSpec:

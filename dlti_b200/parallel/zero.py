@@ -25,6 +25,7 @@ from __future__ import annotations
 
 import ctypes as C
 import math
+import os
 
 import torch
 
@@ -72,6 +73,12 @@ class ZeroOptimizer:
                             else None)
         self._pending_reduce = None
         self.last_grad_norm = 0.0
+        # K9 overlapped form (fused backend, partitioned gradients): per-layer reduce-scatter during backward
+        self.overlap = (fused is not None and self.world > 1 and self.stage >= 1 and not self.offload
+                        and os.environ.get("DLTI_K9", "overlap") == "overlap")
+        self._ranges_done = 0
+        self.out2 = torch.zeros(2, dtype=torch.float32, device=dev)
+        self.loss_sum_global = None
 
     # ---- views -----------------------------------------------------------------------------
     def master_part(self) -> torch.Tensor:
@@ -104,9 +111,24 @@ class ZeroOptimizer:
             comm.reduce_scatter_sum(sb.view(-1), out[:w], info)
             self.grad_part[c0:c1].add_(out[:w])
 
+    def begin_step(self) -> None:
+        if self.overlap:
+            self.fused.k9_begin_step()
+            self._ranges_done = 0
+
+    def on_grad_range_final(self, glo: int, n: int) -> None:
+        """Model hook (LoraLlama.grad_hook): the flat gradient range [glo, glo + n) will not be written again in
+        this accumulation window (one decoder layer's adapters, all micro-batches done)."""
+        if not self.overlap:
+            return
+        self.fused.grad_range_final(self._ranges_done, self.lora.grad, self.grad_part, glo, n, self.lo, self.part)
+        self._ranges_done += 1
+
     def on_micro_batch_end(self, is_boundary: bool) -> None:
         """Called after each backward. Stage >= 2 reduces now (and frees local grads); stage 1
         reduces at the accumulation boundary; stage 0 all-reduces at the boundary."""
+        if self.overlap and self._ranges_done > 0:
+            return        # every range was reduced behind its layer's backward; step() joins the side stream
         if self.stage >= 2 or (self.stage == 1 and is_boundary):
             if self.comm_stream is not None and self.fused is None:
                 self.comm_stream.wait_stream(torch.cuda.current_stream())
@@ -128,12 +150,32 @@ class ZeroOptimizer:
             self._pending_reduce = None
 
     # ---- the step ----------------------------------------------------------------------------
-    def step(self, lr: float) -> tuple[bool, float]:
-        """Returns (skipped, grad_norm). Overflow => skipped, loss scale updated by the caller."""
+    def step(self, lr: float, loss_sum: torch.Tensor | None = None) -> tuple[bool, float]:
+        """Returns (skipped, grad_norm). Overflow => skipped, loss scale updated by the caller. loss_sum: this
+        rank's loss sum of the step; when the fused step kernel runs, self.loss_sum_global holds the sum over
+        ranks afterwards (it travels with the norm exchange), else it stays None."""
         self.wait_reduce()
         info = self.info
         g = self.grad_part if self.stage >= 1 else self.lora.grad
         inv_scale = 1.0 / (self.scaler.cur_scale if self.scaler is not None else 1.0)
+        self.loss_sum_global = None
+        if self.overlap and self._ranges_done > 0:
+            step = self.step_count + 1
+            ls = loss_sum if loss_sum is not None else torch.zeros(1, dtype=torch.float32, device=g.device)
+            self.fused.k9_step(self.lora.master, self.m, self.v, g, self.lo, self.part, lr=lr, betas=self.betas,
+                               eps=self.eps, wd=self.wd, step=step, loss_sum=ls.float(), out2=self.out2,
+                               inv_scale=inv_scale, max_norm=self.max_grad_norm, skipped_out=self.skipped_flag)
+            self.lora.grad.zero_()          # every owner has read this rank's gradients (all pushes are complete)
+            vals = torch.cat([self.out2, self.skipped_flag.float()]).tolist()
+            nsq, skipped = vals[0], bool(vals[2])
+            if loss_sum is not None:
+                self.loss_sum_global = vals[1]
+            if not skipped:
+                self.step_count = step
+                self.lora.refresh_compute()
+            self.last_grad_norm = math.sqrt(nsq) * inv_scale if math.isfinite(nsq) else float("nan")
+            self._ranges_done = 0
+            return skipped, self.last_grad_norm
         # global sum of squares (C6 + C7 in one reduction: non-finite => overflow)
         if self.fused is not None and self.world > 1 and self.stage >= 1:
             # partitioned gradients: every rank holds a different slice, the norm is the sum over ranks.

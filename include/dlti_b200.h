@@ -239,6 +239,26 @@ int dlti_peer_barrier(const void* const* signal_pads, int rank, int world, int c
                       unsigned int epoch, int* err_flag, dlti_stream_t stream);
 int dlti_peer_barrier_auto(const void* const* signal_pads, int rank, int world, int channel,
                            unsigned int* device_counter, int* err_flag, dlti_stream_t stream);
+/* K9, overlapped form (replaces DeepSpeed's bucketed gradient reduce-scatter with overlap_comm, the global-norm
+ * all-reduce, the partitioned optimizer step and the parameter all-gather:
+ * /root/reference/configs/ds_config_zero3.json:29-31, ds_config_zero1.json:38-40).
+ * dlti_grad_ready_signal: "my gradients of range `slot` are final for step `epoch`" to every rank.
+ * dlti_rs_wait_accumulate: once all ranks have signalled, part[plo..] += sum_r grads[r][glo..] (fixed rank order).
+ * dlti_k9_step: exchange of {sum of squares, loss sum}, unscale/clip/AdamW on [lo, lo+n) with the new fp32 values
+ * stored into every rank's master, then a completion flag to every peer; dlti_peer_wait waits for those flags. */
+int dlti_grad_ready_signal(const void* const* flags, int rank, int world, int slot, unsigned int epoch,
+                           dlti_stream_t stream);
+int dlti_rs_wait_accumulate(const void* const* grads, const unsigned int* my_flags, float* part, long long glo,
+                            long long plo, long long n, int world, int slot, unsigned int epoch, int ctas,
+                            int* err_flag, dlti_stream_t stream);
+int dlti_k9_step(const void* const* masters, const void* const* boards, const void* const* signal_pads, float* m,
+                 float* v, float* g, long long lo, long long n, int rank, int world, float lr, float b1, float b2,
+                 float eps, float wd, int step, const float* local2, float* out2, float inv_scale, float max_norm,
+                 int* skipped_out, unsigned int* done_scratch, int ch_norm, int ch_push, unsigned int epoch,
+                 int* err_flag, dlti_stream_t stream);
+int dlti_peer_wait(const unsigned int* my_pads, int world, int channel, unsigned int epoch, int* err_flag,
+                   dlti_stream_t stream);
+
 /* K15: embedding lookup over a vocabulary-sharded table in peer memory: out[t] = row ids[t] fetched from its
  * owner rank (ids outside [0, vocab) give zero rows). Replaces all-gather + lookup of the reference's ZeRO-3
  * embedding (HF LlamaModel.embed_tokens under DeepSpeed stage 3). */

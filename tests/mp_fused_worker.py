@@ -190,6 +190,16 @@ def main():
         if rank == 0:
             print(f"stage {stage} fused {a} nccl {b}\n        grad norms fused {na} nccl {nb}", flush=True)
         check(f"ZeRO-{stage}: fused backend == nccl backend losses and gradient norms", ok)
+    # K9: the overlapped form (per-layer reduce-scatter during backward + one step kernel) must produce the SAME
+    # parameters, bit for bit, as the serial tail (reduce -> norm exchange -> AdamW push with separate barriers)
+    for stage in (3, 1):
+        os.environ["DLTI_K9"] = "overlap"
+        la, na, ma = run_short(info, stage, "fused", fc, steps=10, with_master=True)
+        os.environ["DLTI_K9"] = "tail"
+        lb, nb, mb = run_short(info, stage, "fused", fc, steps=10, with_master=True)
+        os.environ["DLTI_K9"] = "overlap"
+        check(f"K9 overlapped == serial tail, ZeRO-{stage}, 10 steps: parameters bit-identical",
+              torch.equal(ma, mb) and la == lb and na == nb)
     if rank == 0:
         print("ALL MULTI-GPU CHECKS PASSED", flush=True)
     comm.shutdown()

@@ -7,7 +7,7 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 
 
 def run_short(info, stage: int, backend: str, fused, steps: int = 4, preset: str = "tiny-gqa", seq: int = 256,
-              with_norms: bool = False):
+              with_norms: bool = False, with_master: bool = False):
     from dlti_b200.config.args import TrainingArgs
     from dlti_b200.engine.trainer import Trainer
     from dlti_b200.models.config import PRESETS
@@ -34,4 +34,6 @@ def run_short(info, stage: int, backend: str, fused, steps: int = 4, preset: str
     torch.cuda.synchronize()
     if tr.fused is not None:
         tr.fused.check_error()
+    if with_master:
+        return losses, norms, tr.lora.master.detach().clone()
     return (losses, norms) if with_norms else losses

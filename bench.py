@@ -192,7 +192,7 @@ def main() -> None:
     dev_steps = [[mb.to("cuda") for mb in st] for st in host_steps[a.warmup:]]
     sync_all()
     sampler = ClockSampler(torch.cuda.current_device()) if info.rank == 0 else None
-    tr.ds.wall_clock_breakdown = True        # one extra event per step: forward+backward | reduce/clip/AdamW/refresh
+    tr.ds.cfg["wall_clock_breakdown"] = True        # one extra event per step: forward+backward | reduce/clip/AdamW/refresh
     tr._phase_events = []
     _lib.reset_launch_count()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
@@ -209,7 +209,7 @@ def main() -> None:
     tail = sum(x[1].elapsed_time(x[2]) for x in tr._phase_events) / max(1, len(tr._phase_events))
     phases = {"fwd_bwd_ms_min_rank": min_over_ranks(fb), "fwd_bwd_ms_max_rank": max_over_ranks(fb),
               "optimizer_phase_ms_min_rank": min_over_ranks(tail), "optimizer_phase_ms_max_rank": max_over_ranks(tail)}
-    tr.ds.wall_clock_breakdown = False
+    tr.ds.cfg["wall_clock_breakdown"] = False
     tr._phase_events = []
     loss_dev = float(loss_t.item()) / n_tot
     # ---- region 2: end to end through the public API ----

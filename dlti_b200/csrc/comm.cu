@@ -158,11 +158,9 @@ __global__ void __launch_bounds__(256) adamw_push_kernel(Peers masters, float* _
   const float ibc1 = 1.f / bc1, ibc2 = 1.f / bc2;
   float* mine = reinterpret_cast<float*>(masters.p[rank]) + lo;
   for (long long i = (long long)blockIdx.x * 256 + threadIdx.x; i < n; i += (long long)gridDim.x * 256) {
-    const float ge = g[i] * coef;
-    const float mi = b1 * m[i] + (1.f - b1) * ge;
-    const float vi = b2 * v[i] + (1.f - b2) * ge * ge;
-    float pi = mine[i];
-    pi -= lr * ((mi * ibc1) / (sqrtf(vi * ibc2) + eps) + wd * pi);
+    const float ge = __fmul_rn(g[i], coef);
+    float mi = m[i], vi = v[i];
+    const float pi = adamw_update(mine[i], mi, vi, ge, lr, b1, b2, eps, wd, ibc1, ibc2);
     m[i] = mi; v[i] = vi; g[i] = 0.f;
     for (int r = 0; r < world; ++r) (reinterpret_cast<float*>(masters.p[r]) + lo)[i] = pi;
   }
@@ -435,11 +433,9 @@ __global__ void __launch_bounds__(256) k9_step_kernel(const K9Step k) {
   float* mine = reinterpret_cast<float*>(k.masters.p[k.rank]) + k.lo;
   for (long long i = (long long)blockIdx.x * 256 + t; i < k.n; i += (long long)gridDim.x * 256) {
     if (!skip) {
-      const float ge = k.g[i] * coef;
-      const float mi = k.b1 * k.m[i] + (1.f - k.b1) * ge;
-      const float vi = k.b2 * k.v[i] + (1.f - k.b2) * ge * ge;
-      float pi = mine[i];
-      pi -= k.lr * ((mi * k.ibc1) / (sqrtf(vi * k.ibc2) + k.eps) + k.wd * pi);
+      const float ge = __fmul_rn(k.g[i], coef);
+      float mi = k.m[i], vi = k.v[i];
+      const float pi = adamw_update(mine[i], mi, vi, ge, k.lr, k.b1, k.b2, k.eps, k.wd, k.ibc1, k.ibc2);
       k.m[i] = mi; k.v[i] = vi;
       for (int r = 0; r < k.world; ++r) (reinterpret_cast<float*>(k.masters.p[r]) + k.lo)[i] = pi;
     }
@@ -612,7 +608,7 @@ DLTI_API int dlti_rs_wait_accumulate(const void* const* grads, const unsigned in
   if (n <= 0) return 0;
   if (n % 4 || glo % 4 || plo % 4) { dlti_set_error("rs_wait_accumulate: ranges must be 16-byte aligned"); return DLTI_ERR_BAD_ARG; }
   long long want = (n / 4 + 255) / 256;
-  const long long cap = ctas > 0 ? ctas : 16;
+  const long long cap = ctas > 0 ? ctas : (long long)dlti_num_sms() * 4;
   rs_wait_accumulate_kernel<<<(unsigned)(want > cap ? cap : want), 256, 0, st>>>(P, my_flags, part, glo, plo, n, world,
                                                                                  slot, epoch, err_flag);
   dlti_count_launch();

@@ -432,6 +432,19 @@ struct Cvt<float> {
   static __device__ __forceinline__ float from_f(float v) { return v; }
 };
 
+// One AdamW element update with decoupled weight decay, written with explicit (non-contractible) operations so
+// that every kernel that steps parameters — the single-GPU kernel, the peer-push kernel and the fused K9 step
+// kernel — produces bit-identical results from identical inputs, whatever the compiler fuses around it.
+//   m' = b1 m + (1-b1) ge ; v' = b2 v + (1-b2) ge^2 ; p' = p - lr * ( (m' ibc1) / (sqrt(v' ibc2) + eps) + wd p )
+__device__ __forceinline__ float adamw_update(float p, float& m, float& v, float ge, float lr, float b1, float b2,
+                                              float eps, float wd, float ibc1, float ibc2) {
+  m = __fmaf_rn(b1, m, __fmul_rn(1.f - b1, ge));
+  v = __fmaf_rn(b2, v, __fmul_rn(__fmul_rn(1.f - b2, ge), ge));
+  const float denom = __fadd_rn(sqrtf(__fmul_rn(v, ibc2)), eps);
+  const float upd = __fmaf_rn(wd, p, __fdiv_rn(__fmul_rn(m, ibc1), denom));
+  return __fmaf_rn(-lr, upd, p);
+}
+
 // Philox-4x32-10 counter RNG (dropout masks reproducible across recompute: the mask is a
 // pure function of (seed, offset)).
 __device__ __forceinline__ uint4 philox4x32(uint32_t c0, uint32_t c1, uint32_t c2, uint32_t c3,

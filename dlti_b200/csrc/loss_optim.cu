@@ -180,11 +180,9 @@ __global__ void __launch_bounds__(256) adamw_kernel(float* __restrict__ p, float
   if (blockIdx.x == 0 && threadIdx.x == 0 && skipped_out) *skipped_out = 0;
   const float ibc1 = 1.f / bc1, ibc2 = 1.f / bc2;
   for (long long i = (long long)blockIdx.x * 256 + threadIdx.x; i < n; i += (long long)gridDim.x * 256) {
-    const float ge = g[i] * coef;
-    const float mi = b1 * m[i] + (1.f - b1) * ge;
-    const float vi = b2 * v[i] + (1.f - b2) * ge * ge;
-    float pi = p[i];
-    pi -= lr * ((mi * ibc1) / (sqrtf(vi * ibc2) + eps) + wd * pi);
+    const float ge = __fmul_rn(g[i], coef);
+    float mi = m[i], vi = v[i];
+    const float pi = adamw_update(p[i], mi, vi, ge, lr, b1, b2, eps, wd, ibc1, ibc2);
     m[i] = mi; v[i] = vi; p[i] = pi;
     if (p16) p16[i] = Cvt<T16>::from_f(pi);
     if (zero_grad) g_mut[i] = 0.f;

@@ -372,11 +372,12 @@ class FusedComm:
         self.k9_epoch += 1
 
     def grad_range_final(self, slot: int, g_full: torch.Tensor, grad_part: torch.Tensor, glo: int, n: int,
-                         part_lo: int, part_n: int) -> None:
+                         part_lo: int, part_n: int, side: bool = True, ctas: int = 16) -> None:
         """This rank's gradients of the flat range [glo, glo + n) (range number `slot`) are final for the current
         step: tell every rank (main stream, i.e. behind the kernels that produced them) and, if part of the
         range belongs to this rank's partition [part_lo, part_lo + part_n), start the reduction of that part on
-        the side stream — it waits for the other ranks' flags while the main stream goes on with backward."""
+        the side stream — it waits for the other ranks' flags while the main stream goes on with backward
+        (side=False: on the main stream, the form used at the end of backward)."""
         assert slot < self.MAX_GRAD_RANGES
         f = _lib.fn("dlti_grad_ready_signal", [_V, _I, _I, _I, _U, _V])
         _lib.check(f(self.peer_array(self.grad_flags), self.rank, self.world, slot, self.k9_epoch,
@@ -384,10 +385,10 @@ class FusedComm:
         a, b = max(glo, part_lo), min(glo + n, part_lo + part_n)
         if b <= a:
             return
-        with torch.cuda.stream(self.side_stream):
+        with torch.cuda.stream(self.side_stream if side else torch.cuda.current_stream()):
             f = _lib.fn("dlti_rs_wait_accumulate", [_V, _V, _V, _L, _L, _L, _I, _I, _U, _I, _V, _V])
             _lib.check(f(self.peer_array(g_full), _lib.ptr(self.grad_flags), _lib.ptr(grad_part), a, a - part_lo, b - a,
-                         self.world, slot, self.k9_epoch, 16, _lib.ptr(self.err), _lib.stream_ptr()), "rs_wait_accumulate")
+                         self.world, slot, self.k9_epoch, ctas, _lib.ptr(self.err), _lib.stream_ptr()), "rs_wait_accumulate")
 
     def k9_step(self, master_full: torch.Tensor, m, v, g, lo: int, n: int, *, lr, betas, eps, wd, step, loss_sum,
                 out2: torch.Tensor, inv_scale, max_norm, skipped_out) -> None:

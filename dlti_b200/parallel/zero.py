@@ -73,9 +73,18 @@ class ZeroOptimizer:
                             else None)
         self._pending_reduce = None
         self.last_grad_norm = 0.0
-        # K9 overlapped form (fused backend, partitioned gradients): per-layer reduce-scatter during backward
-        self.overlap = (fused is not None and self.world > 1 and self.stage >= 1 and not self.offload
-                        and os.environ.get("DLTI_K9", "overlap") == "overlap")
+        # K9 on the fused backend with partitioned gradients (DLTI_K9):
+        #   "fused"   (default) at the end of backward: ready flags -> reduce-scatter kernel that waits on them ->
+        #             sum of squares -> ONE kernel for norm/loss exchange + unscale/clip/AdamW + push + completion
+        #             flags -> wait; no stand-alone barrier launches, 0.4 ms at 2 GPUs on Llama-2-7B r=16;
+        #   "overlap" the same kernels, but each layer's range is reduced on a side stream as soon as that layer's
+        #             backward is done. Measured SLOWER (2 GPUs: 684 vs 633 ms/step): the waiting reduce kernels
+        #             share SMs with the persistent GEMMs and delay their CTA pairs; kept for experiments;
+        #   "tail"    the round-1 sequence (barrier, reduce, barrier, norm exchange, AdamW push, barrier).
+        mode = os.environ.get("DLTI_K9", "fused")
+        k9_ok = fused is not None and self.world > 1 and self.stage >= 1 and not self.offload
+        self.k9_fused = k9_ok and mode in ("fused", "overlap")
+        self.overlap = k9_ok and mode == "overlap"
         self._ranges_done = 0
         self.out2 = torch.zeros(2, dtype=torch.float32, device=dev)
         self.loss_sum_global = None
@@ -112,7 +121,7 @@ class ZeroOptimizer:
             self.grad_part[c0:c1].add_(out[:w])
 
     def begin_step(self) -> None:
-        if self.overlap:
+        if self.k9_fused:
             self.fused.k9_begin_step()
             self._ranges_done = 0
 
@@ -129,6 +138,12 @@ class ZeroOptimizer:
         reduces at the accumulation boundary; stage 0 all-reduces at the boundary."""
         if self.overlap and self._ranges_done > 0:
             return        # every range was reduced behind its layer's backward; step() joins the side stream
+        if self.k9_fused:
+            if is_boundary:   # the whole flat buffer as one range, on the main stream
+                self.fused.grad_range_final(0, self.lora.grad, self.grad_part, 0, self.lora.padded_numel, self.lo,
+                                            self.part, side=False, ctas=0)
+                self._ranges_done = 1
+            return
         if self.stage >= 2 or (self.stage == 1 and is_boundary):
             if self.comm_stream is not None and self.fused is None:
                 self.comm_stream.wait_stream(torch.cuda.current_stream())
@@ -159,7 +174,7 @@ class ZeroOptimizer:
         g = self.grad_part if self.stage >= 1 else self.lora.grad
         inv_scale = 1.0 / (self.scaler.cur_scale if self.scaler is not None else 1.0)
         self.loss_sum_global = None
-        if self.overlap and self._ranges_done > 0:
+        if self.k9_fused and self._ranges_done > 0:
             step = self.step_count + 1
             ls = loss_sum if loss_sum is not None else torch.zeros(1, dtype=torch.float32, device=g.device)
             self.fused.k9_step(self.lora.master, self.m, self.v, g, self.lo, self.part, lr=lr, betas=self.betas,

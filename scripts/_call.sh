@@ -1,4 +1,8 @@
-timeout 600 python -m pytest tests/test_gemm_gpu.py tests/test_model_gpu.py -x -q 2>&1 | tail -3
-python bench.py --steps 6 --warmup 3 2>/dev/null > gpurun_out/r2_bench_2prod.json; cut -c1-200 gpurun_out/r2_bench_2prod.json
-DLTI_GPU_LIB=$PWD/dlti_b200/lib/variants/libdlti_b200_b420dad.so python bench.py --steps 6 --warmup 3 2>/dev/null > gpurun_out/r2_bench_headlib.json; cut -c1-200 gpurun_out/r2_bench_headlib.json
-python bench.py --steps 6 --warmup 3 2>/dev/null > gpurun_out/r2_bench_2prod_b.json; cut -c1-200 gpurun_out/r2_bench_2prod_b.json
+python bench.py --steps 5 --warmup 3 2>/dev/null > gpurun_out/b1.json; python -c "
+import json
+d=json.loads([l for l in open('gpurun_out/b1.json') if l.startswith('{')][0]); print('1gpu', d['ms_per_step'], d['phases'])"
+for k9 in tail overlap; do
+DLTI_K9=$k9 python -m torch.distributed.run --nnodes=1 --nproc-per-node 2 --master-addr 127.0.0.1 --master-port 29511 bench.py --gpus 2 --steps 5 --warmup 3 2>/dev/null > gpurun_out/b2_$k9.json; python -c "
+import json
+d=json.loads([l for l in open('gpurun_out/b2_$k9.json') if l.startswith('{')][0]); print('2gpu $k9', d['ms_per_step'], d['phases'])"
+done

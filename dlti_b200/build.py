@@ -109,7 +109,7 @@ def build_cpu(force: bool = False) -> Path:
     if not srcs:
         return CPU_LIB
     if force or any(_newer(s, CPU_LIB, []) for s in srcs):
-        _run([CXX, *CXX_FLAGS, "-shared", "-o", str(CPU_LIB), *map(str, srcs)])
+        _run([CXX, *CXX_FLAGS, "-shared", "-o", str(CPU_LIB), *map(str, srcs), "-lrt", "-lpthread"])
     return CPU_LIB
 
 

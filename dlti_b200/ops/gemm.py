@@ -87,14 +87,18 @@ def gemm(a: torch.Tensor, b: torch.Tensor, *, a_mn: bool = False, b_mn: bool = F
         assert residual.shape == (M, N) and residual.stride(1) == 1 and residual.dtype == out.dtype
     if push is not None:
         # K10: the epilogue stores the partial output into every rank's receive slot (peer stores)
-        peer_arr, recv, rank, world, max_tokens = push
+        # (peer pointers, local receive buffer, rank, world, rows per slot[, row pitch, slot stride]): the default
+        # layout is [world, rows, N] slots; with an explicit pitch / stride the slots can interleave, e.g. column
+        # blocks of one [rows, world * N] matrix (pitch world * N, stride N: the LM-head logits gather)
+        peer_arr, recv, rank, world, max_tokens = push[:5]
+        ldc_push, slot_stride = (push[5], push[6]) if len(push) > 5 else (N, max_tokens * N)
         assert not a_mn and not b_mn and a2 is None and residual is None and M <= max_tokens
-        assert recv.shape[-1] == N and recv.dtype == a.dtype
+        assert recv.dtype == a.dtype and (len(push) > 5 or recv.shape[-1] == N)
         f = _lib.fn("dlti_gemm_push", [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_longlong,
                                        C.c_longlong, C.c_longlong, C.c_int, C.c_int, C.c_void_p, C.c_int,
                                        C.c_int, C.c_longlong, C.c_void_p])
-        _lib.check(f(_lib.ptr(a), _lib.ptr(b), M, N, K, a.stride(0), b.stride(0), N, _lib.dtype_code(a.dtype),
-                     int(block_n), peer_arr, rank, world, max_tokens * N, _lib.stream_ptr()), "dlti_gemm_push")
+        _lib.check(f(_lib.ptr(a), _lib.ptr(b), M, N, K, a.stride(0), b.stride(0), ldc_push, _lib.dtype_code(a.dtype),
+                     int(block_n), peer_arr, rank, world, slot_stride, _lib.stream_ptr()), "dlti_gemm_push")
         return recv
     if gather is not None and hasattr(gather, "attach"):
         # K1 on the CTA-pair kernel: the launch carries a slice of pending weight gathers (and waits on its own

@@ -2,8 +2,8 @@
 incremental detokenisation (call stack §3.4).
 
 One engine object per rank. Rank 0 is the driver: it owns the scheduler / block manager and, each step,
-broadcasts the step's metadata (one int64 tensor over gloo — a shared-memory-speed control message,
-N10) to the TP workers, which run `worker_loop()` and execute the same forward and the same sampling.
+broadcasts the step's metadata (one message through a shared-memory ring,
+N10: csrc/shm_ring.cpp) to the TP workers, which run `worker_loop()` and execute the same forward and the same sampling.
 A step is one forward pass over [decode rows | prompt rows]; pure-decode steps replay CUDA graphs
 captured per batch-size bucket (S12; the collectives inside are graph-safe: device-side barrier epochs).
 By default steps are pipelined: step N+1 is launched before the host has read step N's tokens, which stay
@@ -128,6 +128,7 @@ class LLMEngine:
         self._rings: dict = {}
         self._ring_pos: dict = {}
         self.async_scheduling = async_scheduling
+        self._ctl = None            # TP control channel (shared-memory ring), opened on first use
         self._inflight: dict | None = None
         cap = max(1024, max_num_seqs)
         self._tok_dev = torch.zeros(cap, dtype=torch.int64, device=self.device)      # last step's samples
@@ -284,9 +285,55 @@ class LLMEngine:
         return self.pack_step(nd, ids, pos, slots, ctx, tables, cu, max_seqlen, sampling, src,
                               sampled_prompts=batch.num_sampled - nd, prefix=prefix)
 
+    def _ring(self):
+        """Shared-memory control ring between the driver and the workers (one node): created lazily by rank 0,
+        attached by the others. DLTI_TP_CONTROL=gloo falls back to torch.distributed broadcasts."""
+        if self._ctl is None:
+            import os
+            if os.environ.get("DLTI_TP_CONTROL", "shm") != "shm":
+                self._ctl = False
+            else:
+                from .shm_ring import ShmRing, ring_name
+                import torch.distributed as dist
+                LLMEngine._ring_serial += 1
+                name = ring_name(str(LLMEngine._ring_serial))
+                if self.rank == 0:
+                    self._ctl = ShmRing(name, -1, self.world - 1)
+                    dist.barrier()
+                else:
+                    dist.barrier()
+                    self._ctl = ShmRing(name, self.rank - 1, self.world - 1)
+        return self._ctl
+
+    _ring_serial = 0
+
     def _broadcast(self, step: "PackedStep | None") -> "PackedStep | None":
-        """Driver -> workers: header[12], then the packed step buffer exactly as the driver staged it."""
+        """Driver -> workers: header[12] followed by the packed step buffer exactly as the driver staged it — ONE
+        message through the shared-memory ring (N10), or two gloo broadcasts with DLTI_TP_CONTROL=gloo."""
         if self.world == 1:
+            return step
+        ring = self._ring()
+        if ring:
+            if self.rank == 0:
+                if step is None:
+                    ring.write(np.array([-1] + [0] * 11, dtype=np.int64))
+                    return None
+                lay = step.layout
+                msg = np.empty(12 + lay.words, dtype=np.int64)
+                msg[:12] = [0, lay.T, lay.nd, lay.npf, lay.mb, step.max_seqlen, lay.words, int(step.want_lp), lay.ns,
+                            lay.P, step.max_ext, 0]
+                msg[12:] = step.slot[0][:lay.words].numpy()
+                ring.write(msg)
+                return step
+            raw = ring.read().view(np.int64)
+            kind, T, nd, npf, mb, max_seqlen, words, want_lp, ns, P, max_ext = (int(x) for x in raw[:11])
+            if kind < 0:
+                return None
+            lay = StepLayout(T, nd, npf, mb, ns, P)
+            slot = self._host_buffer("step", words)
+            slot[0][:words].numpy()[:] = raw[12:12 + words]
+            step = PackedStep(lay, slot, max_seqlen, max_ext)
+            step.want_lp = bool(want_lp)
             return step
         import torch.distributed as dist
         if self.rank == 0:

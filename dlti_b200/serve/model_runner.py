@@ -61,6 +61,41 @@ class TPContext:
                 self.partial = fused.alloc_symmetric((max_tokens, d), dtype)
                 self.xn = fused.alloc_symmetric((max_tokens, d), dtype)
 
+    def adopt(self, w: "TPWeights", cfg: LlamaConfig, max_rows: int = 1024) -> None:
+        """Fused backend: move the pieces of the model that are addressed across ranks into the symmetric arena.
+        (collective: every rank calls it in the same order)
+          * K15: the embedding table becomes vocabulary-sharded (1/tp of it per rank) and is read in place on the
+            owner ranks by the embedding kernel (parallel.fused.PeerRows) instead of being replicated;
+          * C11: a [max_rows, vocab] logits buffer per rank that every rank's LM-head GEMM epilogue writes its
+            vocabulary slice into (peer stores), replacing the NCCL all-gather of the logits."""
+        if not self.use_fused or hasattr(w.embed, "lookup"):
+            return
+        import torch.distributed as dist
+        from ..parallel.fused import PeerRows
+        V, d = cfg.vocab_size, cfg.hidden_size
+        Vr = V // self.world
+        sh = self.fused.alloc_symmetric((Vr, d), w.embed.dtype)
+        sh.copy_(w.embed[self.rank * Vr:(self.rank + 1) * Vr])
+        self.logits_rows = max_rows
+        self.logits_buf = self.fused.alloc_symmetric((max_rows, V), w.embed.dtype)
+        torch.cuda.synchronize()
+        dist.barrier()
+        w.embed = PeerRows(self.fused, sh, V)
+
+    def lm_head_logits(self, xl: torch.Tensor, w_head: torch.Tensor) -> torch.Tensor:
+        """[B, vocab] logits on every rank from the vocabulary-parallel LM head."""
+        B = xl.shape[0]
+        if self.world == 1:
+            return (gemm_skinny if B <= 256 else gemm)(xl, w_head)
+        if self.use_fused and getattr(self, "logits_buf", None) is not None and B <= self.logits_rows:
+            buf = self.logits_buf
+            Vl, V = w_head.shape[0], buf.shape[1]
+            # the epilogue stores this rank's [B, V/tp] slice into EVERY rank's buffer at column rank * V/tp
+            gemm(xl, w_head, push=(self.fused.peer_array(buf), buf, self.rank, self.world, self.logits_rows, V, Vl))
+            self.fused.barrier_graph_safe(7)
+            return buf[:B]
+        return self.all_gather_cols((gemm_skinny if B <= 256 else gemm)(xl, w_head))
+
     def reduce_add_norm(self, partial_fn, T: int, residual, w, eps):
         """partial_fn(out=None|tensor, push=None|spec) runs the row-parallel GEMM. Returns the normalised
         activations; `residual` (fp [T, d]) is updated in place with residual += sum_r partial_r."""
@@ -199,6 +234,7 @@ class ModelRunner:
         self.cos, self.sin = E.rope_tables(cfg.max_position_embeddings, cfg.head_dim, cfg.rope_theta,
                                            weights.embed.device)
         self.device = weights.embed.device
+        tp.adopt(weights, cfg)
         if self.device.type == "cuda" and "DLTI_PDL" not in os.environ:
             # serving weights are static: the decode GEMMs may fetch weight tiles while the previous kernel drains
             from ..ops import _lib
@@ -283,5 +319,4 @@ class ModelRunner:
         if last_idx is not None and last_idx.numel() == 0:      # a step of partial prompt chunks samples nothing
             return torch.empty((0, cfg.vocab_size), dtype=xn.dtype, device=xn.device)
         xl = xn if last_idx is None else xn.index_select(0, last_idx)
-        logits = (gemm_skinny if xl.shape[0] <= 256 else gemm)(xl, w.lm_head)  # [B, V/tp]
-        return tp.all_gather_cols(logits)
+        return tp.lm_head_logits(xl, w.lm_head)

@@ -339,6 +339,14 @@ int dlti_sample(const void* logits, long long ld, int batch, int V, const float*
 int dlti_attn_trace_read(long long* host_out);
 #endif
 
+/* ---- libdlti_cpu.so: shared-memory control ring for the tensor-parallel workers of one node (no
+ * counterpart in the reference, which ships no serving code; vLLM's shm_broadcast queue plays this role there).
+ * One writer (reader < 0 creates the ring), up to 16 readers, every reader sees every message in order. */
+void* dlti_shm_ring_open(const char* name, int reader, int n_readers, int n_slots, int slot_bytes);
+int dlti_shm_ring_write(void* ring, const void* data, long long nbytes, int timeout_ms);
+long long dlti_shm_ring_read(void* ring, void* out, long long capacity, int timeout_ms);
+void dlti_shm_ring_close(void* ring);
+
 #ifdef __cplusplus
 }
 #endif

@@ -261,3 +261,40 @@ def test_debug_index_checks():
             A.attention_fwd(qkv, torch.tensor([0, 2, 4], dtype=torch.int32), 2, H, KV, hd)
     finally:
         _debug.enable(False)
+
+
+def _ring_reader(name, idx, n_readers, n_msgs, q):
+    import numpy as np
+    from dlti_b200.serve.shm_ring import ShmRing
+    r = ShmRing(name, idx, n_readers, n_slots=4, slot_bytes=1 << 16)
+    ok = True
+    for i in range(n_msgs):
+        m = r.read(timeout_ms=20000).view(np.int64)
+        ok = ok and m.size == 1 + (i % 97) and int(m[0]) == i and (m.size == 1 or int(m[-1]) == i * 3)
+    r.close()
+    q.put(ok)
+
+
+def test_shm_ring_delivers_every_message_in_order_to_every_reader():
+    """csrc/shm_ring.cpp (N10): one writer, two readers, a ring much shorter than the message count."""
+    import multiprocessing as mp
+    import numpy as np
+    from dlti_b200.serve.shm_ring import ShmRing
+    name = f"/dlti_test_ring_{os.getpid()}"
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    w = ShmRing(name, -1, 2, n_slots=4, slot_bytes=1 << 16)
+    procs = [ctx.Process(target=_ring_reader, args=(name, i, 2, 500, q)) for i in range(2)]
+    for p in procs:
+        p.start()
+    for i in range(500):
+        m = np.full(1 + (i % 97), i * 3, dtype=np.int64)
+        m[0] = i
+        w.write(m, timeout_ms=20000)
+    res = [q.get(timeout=60) for _ in procs]
+    for p in procs:
+        p.join(timeout=30)
+    w.close()
+    assert res == [True, True]
+    with pytest.raises(RuntimeError):
+        ShmRing(name + "x", -1, 1, n_slots=2, slot_bytes=64).write(np.zeros(100, dtype=np.int64))

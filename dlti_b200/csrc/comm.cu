@@ -489,6 +489,76 @@ __global__ void __launch_bounds__(256) embedding_peer_kernel(const long long* __
   }
 }
 
+// K10 for prefill-sized steps, owner side. Every rank's row-parallel GEMM has stored the rows this rank owns into
+// this rank's receive slots (slots[src * per + local_row], written by the GEMM epilogues over NVLink). One CTA per
+// owned row: sum the slots in rank order (bit-identical on every run), add the residual (row-sharded on this path),
+// normalise, and leave the normalised row in this rank's symmetric buffer xn_own[local_row], from where the next
+// column-parallel GEMM of every rank pulls it (K11). Everything this kernel touches is local memory.
+template <typename T, int VPT>
+__global__ void __launch_bounds__(128) tp_own_reduce_norm_kernel(const T* __restrict__ slots, int world, long long per,
+                                                                long long row_lo, T* __restrict__ residual,
+                                                                const T* __restrict__ w, T* __restrict__ xn_own,
+                                                                int d, float eps) {
+  __shared__ float red[32];
+  const long long lrow = blockIdx.x;
+  const long long row = row_lo + lrow;
+  const int nvec = d >> 3;
+  float f[VPT][8];
+  float ss = 0.f;
+#pragma unroll
+  for (int i = 0; i < VPT; ++i) {
+    const int v = threadIdx.x + i * 128;
+    if (v < nvec) {
+      {
+        const int4 rv = reinterpret_cast<const int4*>(residual + row * d)[v];
+        const uint32_t* u = reinterpret_cast<const uint32_t*>(&rv);
+#pragma unroll
+        for (int j = 0; j < 4; ++j) { float2 t = Cvt<T>::unpack2(u[j]); f[i][2 * j] = t.x; f[i][2 * j + 1] = t.y; }
+      }
+      for (int r = 0; r < world; ++r) {
+        const int4 pv = ld_relaxed_sys_v4(slots + (r * per + lrow) * d + v * 8);
+        const uint32_t* u = reinterpret_cast<const uint32_t*>(&pv);
+#pragma unroll
+        for (int j = 0; j < 4; ++j) { float2 t = Cvt<T>::unpack2(u[j]); f[i][2 * j] += t.x; f[i][2 * j + 1] += t.y; }
+      }
+      int4 sv;
+      uint32_t* su = reinterpret_cast<uint32_t*>(&sv);
+#pragma unroll
+      for (int j = 0; j < 4; ++j) su[j] = Cvt<T>::pack2(f[i][2 * j], f[i][2 * j + 1]);
+      reinterpret_cast<int4*>(residual + row * d)[v] = sv;
+#pragma unroll
+      for (int j = 0; j < 4; ++j) { float2 t = Cvt<T>::unpack2(su[j]); f[i][2 * j] = t.x; f[i][2 * j + 1] = t.y; }
+#pragma unroll
+      for (int j = 0; j < 8; ++j) ss += f[i][j] * f[i][j];
+    }
+  }
+  ss = warp_sum(ss);
+  if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = ss;
+  __syncthreads();
+  float tot = (threadIdx.x & 31) < 4 ? red[threadIdx.x & 31] : 0.f;
+  tot = warp_sum(tot);
+  const float rstd = rsqrtf(tot / (float)d + eps);
+#pragma unroll
+  for (int i = 0; i < VPT; ++i) {
+    const int v = threadIdx.x + i * 128;
+    if (v < nvec) {
+      const int4 wv = reinterpret_cast<const int4*>(w)[v];
+      const uint32_t* wu = reinterpret_cast<const uint32_t*>(&wv);
+      int4 ov;
+      uint32_t* ou = reinterpret_cast<uint32_t*>(&ov);
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        float2 wf = Cvt<T>::unpack2(wu[j]);
+        const float a = wf.x * Cvt<T>::to_f(Cvt<T>::from_f(f[i][2 * j] * rstd));
+        const float b = wf.y * Cvt<T>::to_f(Cvt<T>::from_f(f[i][2 * j + 1] * rstd));
+        ou[j] = Cvt<T>::pack2(a, b);
+      }
+      reinterpret_cast<int4*>(xn_own + lrow * d)[v] = ov;
+    }
+  }
+  __threadfence_system();
+}
+
 int fill(Peers& P, const void* const* ptrs, int world) {
   if (world < 1 || world > MAX_RANKS) return DLTI_ERR_BAD_ARG;
   for (int i = 0; i < MAX_RANKS; ++i) P.p[i] = i < world ? const_cast<void*>(ptrs[i]) : nullptr;
@@ -645,6 +715,27 @@ DLTI_API int dlti_peer_wait(const unsigned int* my_pads, int world, int channel,
                             cudaStream_t st) {
   if (world < 1 || world > MAX_RANKS) return DLTI_ERR_BAD_ARG;
   peer_wait_kernel<<<1, 32, 0, st>>>(my_pads, world, channel, epoch, err_flag);
+  dlti_count_launch();
+  return (int)cudaGetLastError();
+}
+
+// Owner side of the prefill-sized row-parallel all-reduce (see tp_own_reduce_norm_kernel): rows [row_lo, row_lo +
+// rows) of the step, slots = this rank's receive buffer [world * per, d], xn_own = this rank's [per, d] output.
+DLTI_API int dlti_tp_own_reduce_norm(const void* slots, int world, long long per, long long row_lo, long long rows,
+                                     void* residual, const void* w, void* xn_own, int d, float eps, int dtype,
+                                     cudaStream_t st) {
+  if (rows <= 0) return 0;
+  if (d % 8 || d > 8192 || world < 1 || rows > per) return DLTI_ERR_BAD_ARG;
+  const int vpt = (d / 8 + 127) / 128;
+#define TOR(T, V) tp_own_reduce_norm_kernel<T, V><<<(unsigned)rows, 128, 0, st>>>((const T*)slots, world, per, row_lo, (T*)residual, (const T*)w, (T*)xn_own, d, eps)
+  if (dtype == DLTI_BF16) {
+    if (vpt <= 1) TOR(__nv_bfloat16, 1); else if (vpt <= 2) TOR(__nv_bfloat16, 2); else if (vpt <= 4) TOR(__nv_bfloat16, 4); else TOR(__nv_bfloat16, 8);
+  } else if (dtype == DLTI_FP16) {
+    if (vpt <= 1) TOR(__half, 1); else if (vpt <= 2) TOR(__half, 2); else if (vpt <= 4) TOR(__half, 4); else TOR(__half, 8);
+  } else {
+    return DLTI_ERR_UNSUPPORTED;
+  }
+#undef TOR
   dlti_count_launch();
   return (int)cudaGetLastError();
 }

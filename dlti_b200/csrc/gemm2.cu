@@ -51,6 +51,16 @@ struct Gemm2Params {
   // half as long. split_from == nmb2 * nnb: no tile is split.
   uint32_t idesc_half;
   int split_from;
+  // K11 (all-gather -> column-parallel GEMM): the A operand is a staging buffer whose 64-row units are pulled from
+  // their owner ranks by this launch's gather warp; the A producer waits on the unit counters (WaitSpec::on_a) and
+  // the M blocks are visited starting at m_rot (the block that holds this rank's own rows, which land first).
+  int m_rot;
+  // K10 (row-parallel GEMM -> reduce-scatter), prefill-sized steps: output row r belongs to rank r / scatter_per;
+  // the epilogue stores the 16-bit tile straight into that rank's receive slot of this rank:
+  //   scatter_peer[owner] + ((long long)scatter_rank * scatter_per + (r - owner * scatter_per)) * ldc + col
+  // (peer stores over NVLink, 128 contiguous bytes per thread and row block). The owner sums the slots in rank order.
+  void* scatter_peer[16];
+  int scatter_world, scatter_rank, scatter_per;
   int b3d;                // MN-major B: tmB is the 3D view (one TMA per stage for a full tile); tmBh stays 2D
   // stream-K: tiles [0, sk_tiles) are cut into `gridDim/2` equal ranges of (tile, k-block) iterations,
   // tiles [sk_tiles, total) are handed out round-robin. sk_tiles == 0 => plain data-parallel schedule.
@@ -102,10 +112,11 @@ struct GatherJob {
   int j_begin, j_count;     // positions [j_begin, j_begin + j_count) belong to this launch; 0 = no job
 };
 struct WaitSpec {
-  const uint32_t* counters; // nullptr: B is plain memory
+  const uint32_t* counters; // nullptr: the operand is plain memory
   int* err;
   uint32_t target;
   int n_units;
+  int on_a;                 // 0: the units are rows of the B operand (K1); 1: rows of the A operand (K11)
 };
 
 __device__ __forceinline__ uint32_t ld_relaxed_gpu_u32(const uint32_t* p) {
@@ -264,6 +275,12 @@ gemm2_kernel(const Gemm2Params p, const GatherJob gj, const WaitSpec ws_, const 
   volatile uint32_t* tmem_slot_ptr =
       reinterpret_cast<volatile uint32_t*>(smem_raw + (tmem_slot - smem_u32(smem_raw)));
 
+  __shared__ void* s_scatter[16];
+  if (p.scatter_world > 0) {
+#pragma unroll
+    for (int i = 0; i < 16; ++i)
+      if (threadIdx.x == 32 + i) s_scatter[i] = p.scatter_peer[i];
+  }
   __shared__ const void* s_peers[16];
   if (gj.j_count > 0) {
 #pragma unroll
@@ -306,6 +323,14 @@ gemm2_kernel(const Gemm2Params p, const GatherJob gj, const WaitSpec ws_, const 
     // UTMALDG costs the issuing thread on the order of 100 clk, which is why A and B have separate producer
     // threads (with one thread the input-gradient form, two B boxes per stage, was issue-bound: 1,180 vs cuBLAS
     // 1,296 TFLOP/s sustained).
+    bool a_ready = true;          // K11: every unit of A has already landed
+    if (ws_.counters && ws_.on_a) {
+      for (int u = lane; u < ws_.n_units; u += 32)
+        if ((int32_t)(ld_relaxed_gpu_u32(ws_.counters + u) - ws_.target) < 0) a_ready = false;
+      a_ready = __all_sync(0xffffffffu, a_ready);
+      asm volatile("fence.acq_rel.gpu;" ::: "memory");
+      asm volatile("fence.proxy.async.global;" ::: "memory");
+    }
     if (lane == 0) {
       uint32_t stage = 0, phase = 0;
       const uint32_t fb0 = mapa_rank(full_bar(0), 0);          // the leader's barriers (mapping is linear)
@@ -313,7 +338,14 @@ gemm2_kernel(const Gemm2Params p, const GatherJob gj, const WaitSpec ws_, const 
       Seg sg;
       while (segs.next(sg)) {
         const int n_blk = sg.tile / p.nmb2;
-        const int m0 = (sg.tile - n_blk * p.nmb2) * 2 * BM + (int)rank * BM;
+        int m_blk = sg.tile - n_blk * p.nmb2 + p.m_rot;
+        if (m_blk >= p.nmb2) m_blk -= p.nmb2;
+        const int m0 = m_blk * 2 * BM + (int)rank * BM;
+        if (!a_ready) {               // this CTA's rows [m0, m0 + 128) = 2 units
+          wait_unit(ws_, m0 >> 6);
+          wait_unit(ws_, (m0 >> 6) + 1);
+          asm volatile("fence.proxy.async.global;" ::: "memory");
+        }
         const uint32_t tx = sg.half >= 0 ? 2 * (A_BYTES + B_BYTES / 2) : 2 * STAGE_BYTES;
         const int kb_main_end = sg.kb1 < p.nkb_main ? sg.kb1 : p.nkb_main;
         int kb = sg.kb0;
@@ -334,7 +366,7 @@ gemm2_kernel(const Gemm2Params p, const GatherJob gj, const WaitSpec ws_, const 
   } else if (warp == 6) {
     // ===================== B producer (both CTAs): this CTA's half of the B tile =====================
     bool all_ready = true;        // WAIT: every unit of B has already landed (gathered by earlier launches)
-    if (ws_.counters) {
+    if (ws_.counters && !ws_.on_a) {
       for (int u = lane; u < ws_.n_units; u += 32)
         if ((int32_t)(ld_relaxed_gpu_u32(ws_.counters + u) - ws_.target) < 0) all_ready = false;
       all_ready = __all_sync(0xffffffffu, all_ready);
@@ -486,7 +518,8 @@ gemm2_kernel(const Gemm2Params p, const GatherJob gj, const WaitSpec ws_, const 
     const int my_range = ncl - 1 - cid;
     while (segs.next(sg)) {
       const int n_blk = sg.tile / p.nmb2;
-      const int m_blk = sg.tile - n_blk * p.nmb2;
+      int m_blk = sg.tile - n_blk * p.nmb2 + p.m_rot;
+      if (m_blk >= p.nmb2) m_blk -= p.nmb2;
       const int row = m_blk * 2 * BM + (int)rank * BM + quarter * 32 + lane;
       const int ncols = sg.half < 0 ? BN : BN / 2;                 // accumulator columns of this unit
       const int n0 = n_blk * BN + (sg.half > 0 ? BN / 2 : 0);
@@ -669,6 +702,40 @@ gemm2_kernel(const Gemm2Params p, const GatherJob gj, const WaitSpec ws_, const 
             }
           }
         }
+      } else if (p.scatter_world > 0) {
+        // K10, prefill-sized steps: the tile's rows go to the receive slots of the ranks that own them
+        const bool bf = p.out_dtype == DLTI_BF16;
+        const bool rok = row < p.M;
+        const int owner = rok ? row / p.scatter_per : 0;
+        uint16_t* drow = reinterpret_cast<uint16_t*>(s_scatter[owner]) +
+                         ((long long)p.scatter_rank * p.scatter_per + (row - owner * p.scatter_per)) * p.ldc;
+#pragma unroll 1
+        for (int c = 0; c < ncols / 64; ++c) {
+          const int col0 = n0 + c * 64;
+          if (col0 >= p.N) break;
+          uint32_t v0[32], v1[32];
+          tmem_ld_32x32b_x32(t_row + c * 64, v0);
+          tmem_ld_32x32b_x32(t_row + c * 64 + 32, v1);
+          tmem_wait_ld();
+          if (rok) {
+#pragma unroll
+            for (int i = 0; i < 4; ++i) {
+              int4 o0, o1;
+              uint32_t* u0 = reinterpret_cast<uint32_t*>(&o0);
+              uint32_t* u1 = reinterpret_cast<uint32_t*>(&o1);
+#pragma unroll
+              for (int j = 0; j < 4; ++j) {
+                const float a0 = __uint_as_float(v0[8 * i + 2 * j]) * p.alpha, a1 = __uint_as_float(v0[8 * i + 2 * j + 1]) * p.alpha;
+                const float b0 = __uint_as_float(v1[8 * i + 2 * j]) * p.alpha, b1 = __uint_as_float(v1[8 * i + 2 * j + 1]) * p.alpha;
+                u0[j] = bf ? Cvt<__nv_bfloat16>::pack2(a0, a1) : Cvt<__half>::pack2(a0, a1);
+                u1[j] = bf ? Cvt<__nv_bfloat16>::pack2(b0, b1) : Cvt<__half>::pack2(b0, b1);
+              }
+              st_v4(drow + col0 + 8 * i, o0);
+              st_v4(drow + col0 + 32 + 8 * i, o1);
+            }
+          }
+        }
+        __threadfence_system();
       } else
 #pragma unroll 1
       for (int c = 0; c < ncols / 32; ++c) {
@@ -828,15 +895,35 @@ __global__ void __launch_bounds__(GATHER_THREADS) gather_job_kernel(const Gather
 // Attachments for the NEXT CTA-pair launch made from this host thread (dlti_gemm2_attach); cleared by it.
 thread_local GatherJob t_job = {};
 thread_local WaitSpec t_wait = {};
+struct ScatterSpec {
+  void* peer[16];
+  int world, rank, per;
+};
+thread_local ScatterSpec t_scatter = {};
+thread_local int t_m_rot = 0;
 
 template <bool B_MN>
-int launch2(const Gemm2Params& p, const CUtensorMap& a, const CUtensorMap& b, const CUtensorMap& a2,
+int launch2(const Gemm2Params& p_in, const CUtensorMap& a, const CUtensorMap& b, const CUtensorMap& a2,
             const CUtensorMap& b2, const CUtensorMap& bh, const CUtensorMap& b2h, int grid, cudaStream_t stream) {
   const GatherJob job = t_job;
   const WaitSpec wait = t_wait;
+  const ScatterSpec sc = t_scatter;
+  const int m_rot = t_m_rot;
   t_job = GatherJob{};
   t_wait = WaitSpec{};
-  if (p.sk_tiles > 0 && (job.j_count > 0 || wait.counters)) return DLTI_ERR_UNSUPPORTED;
+  t_scatter = ScatterSpec{};
+  t_m_rot = 0;
+  Gemm2Params p = p_in;
+  if (p.sk_tiles > 0 && (job.j_count > 0 || wait.counters || sc.world > 0)) return DLTI_ERR_UNSUPPORTED;
+  if (m_rot > 0) p.m_rot = m_rot % p.nmb2;
+  if (sc.world > 0) {
+    // plain 16-bit epilogue only (no residual / SwiGLU / RoPE), whole 64-column groups, 16-byte aligned rows
+    if (p.out_dtype == DLTI_FP32 || p.R || p.swiglu_ff > 0 || p.swiglu_bwd_ff > 0 || p.rope_pos || p.N % 64 ||
+        (p.ldc * 2) % 16)
+      return DLTI_ERR_UNSUPPORTED;
+    for (int i = 0; i < 16; ++i) p.scatter_peer[i] = sc.peer[i];
+    p.scatter_world = sc.world; p.scatter_rank = sc.rank; p.scatter_per = sc.per;
+  }
   static bool configured[64] = {false};
   int dev = 0;
   cudaGetDevice(&dev);
@@ -944,6 +1031,27 @@ DLTI_API int dlti_gemm2_attach(const void* const* peer_shards, void* staging, un
   }
   t_job = j;
   t_wait = w;
+  return 0;
+}
+
+// K11: the wait spec attached with dlti_gemm2_attach refers to the A operand (activation rows pulled from their
+// owner ranks) instead of B, and the M blocks are visited starting at block m_rot (own rows first).
+DLTI_API int dlti_gemm2_attach_a_side(int m_rot) {
+  if (m_rot < 0) return DLTI_ERR_BAD_ARG;
+  t_wait.on_a = 1;
+  t_m_rot = m_rot;
+  return 0;
+}
+
+// K10 for prefill-sized steps: the NEXT CTA-pair launch stores output row r into the receive slot that rank
+// r / rows_per_owner keeps for this rank: slot_peers[owner] + (rank * rows_per_owner + r % rows_per_owner) * ldc + col
+// (16-bit output, no residual / fused epilogue, N % 64 == 0). ldc is the launch's own ldc argument.
+DLTI_API int dlti_gemm2_attach_scatter(const void* const* slot_peers, int world, int rank, int rows_per_owner) {
+  if (!slot_peers || world < 1 || world > 16 || rank < 0 || rank >= world || rows_per_owner < 1) return DLTI_ERR_BAD_ARG;
+  ScatterSpec sc{};
+  for (int i = 0; i < world; ++i) sc.peer[i] = const_cast<void*>(slot_peers[i]);
+  sc.world = world; sc.rank = rank; sc.per = rows_per_owner;
+  t_scatter = sc;
   return 0;
 }
 

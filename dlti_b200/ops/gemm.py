@@ -60,7 +60,7 @@ def gemm(a: torch.Tensor, b: torch.Tensor, *, a_mn: bool = False, b_mn: bool = F
          residual: torch.Tensor | None = None, out: torch.Tensor | None = None,
          out_dtype: torch.dtype | None = None, alpha: float = 1.0, accumulate: bool = False,
          split_k: int = 1, block_n: int = 0, max_ctas: int = 0, gather=None, push=None,
-         two_cta: bool | None = None, stream_k: int = -1) -> torch.Tensor:
+         two_cta: bool | None = None, stream_k: int = -1, scatter=None) -> torch.Tensor:
     """two_cta: run the CTA-pair (tcgen05 cta_group::2) kernel of csrc/gemm2.cu; None = the
     DLTI_GEMM_2CTA environment default (on), applied to shapes with at least 64 256x256 tiles.
     stream_k (pair kernel only): -1 automatic (ragged last wave), 0 off, 1 forced.
@@ -124,6 +124,13 @@ def gemm(a: torch.Tensor, b: torch.Tensor, *, a_mn: bool = False, b_mn: bool = F
                gather.rows_per_rank, _lib.ptr(gather.err), _lib.stream_ptr())
         _lib.check(rc, "dlti_gemm_gather")
         return out
+    if scatter is not None:
+        # K10, prefill-sized steps: the epilogue stores every output row into the receive slot of the rank that
+        # owns it (peer stores); scatter = (peer pointer array of the slot buffers, world, rank, rows per owner)
+        assert not a_mn and split_k == 1 and residual is None and out_dtype != torch.float32 and N % 64 == 0
+        two_cta = True
+        f = _lib.fn("dlti_gemm2_attach_scatter", [C.c_void_p, C.c_int, C.c_int, C.c_int])
+        _lib.check(f(scatter[0], int(scatter[1]), int(scatter[2]), int(scatter[3])), "gemm2_attach_scatter")
     if two_cta is None:
         two_cta = _TWO_CTA_DEFAULT and block_n == 0 and max_ctas == 0 and ((M + 255) // 256) * ((N + 255) // 256) >= 64
     if two_cta and not a_mn and split_k == 1:

@@ -239,6 +239,41 @@ class PeerRows:
         return out.view(*ids.shape, d)
 
 
+class ActGather:
+    """K11 handle (`gather=` of the GEMM ops): the A operand of the launch is `full` [world * per, d], whose rows
+    live on their owner ranks (`own`, a symmetric [per_max, d] buffer). The launch's gather warp pulls them unit by
+    unit, own rows first; the A producer waits on fresh unit counters (zeroed pool slice, target = one epoch)."""
+    sm = None
+
+    def __init__(self, fc: "FusedComm", own: torch.Tensor, full: torch.Tensor, counters: torch.Tensor, per: int):
+        self.fc, self.own, self.full, self.counters, self.per = fc, own, full, counters, per
+        self.n_units = fc.world * per // 64
+        self.done = False
+
+    def _attach(self, wait: bool) -> None:
+        fc = self.fc
+        f = _lib.fn("dlti_gemm2_attach", GatherQueue._ATTACH)
+        row_bytes = self.full.shape[1] * self.full.element_size()
+        _lib.check(f(fc.peer_array(self.own), _lib.ptr(self.full), _lib.ptr(self.counters), row_bytes, self.per,
+                     fc.world, fc.rank * (self.per // 64), 0, self.n_units, 1,
+                     _lib.ptr(self.counters) if wait else None, self.n_units if wait else 0, 1, _lib.ptr(fc.err)),
+                   "gemm2_attach")
+
+    def attach(self, flops: float) -> None:
+        if self.done:           # a second GEMM on the same activations: already complete in stream order
+            return
+        self._attach(True)
+        _lib.check(_lib.fn("dlti_gemm2_attach_a_side", [_I])((self.fc.rank * self.per) // 256), "gemm2_attach_a_side")
+        self.done = True
+
+    def materialize(self) -> None:
+        """Pull the rows with the stand-alone gather kernel (no GEMM follows, e.g. before the LM head)."""
+        if not self.done:
+            self._attach(False)
+            _lib.check(_lib.fn("dlti_gather_job_run", [_I, _V])(0, _lib.stream_ptr()), "gather_job_run")
+            self.done = True
+
+
 class GatherUse:
     """Handle a model passes as `gather=` to the GEMM ops: `b` of that GEMM is `sm.staging` (K1)."""
 
@@ -444,6 +479,17 @@ def tp_reduce_add_norm(recv: torch.Tensor, T: int, residual: torch.Tensor, w: to
     _lib.check(f(_lib.ptr(recv), max_tokens * d, world, _lib.ptr(residual), _lib.ptr(w), _lib.ptr(y), T, d,
                  float(eps), _lib.dtype_code(residual.dtype), _lib.stream_ptr()), "tp_reduce_add_norm")
     return y
+
+
+def tp_own_reduce_norm(fc, slots: torch.Tensor, per: int, T: int, residual: torch.Tensor, w: torch.Tensor, eps: float,
+                       xn_own: torch.Tensor) -> None:
+    """Owner side of the prefill-sized row-parallel all-reduce: this rank's rows [rank * per, ...) of the step."""
+    d = residual.shape[-1]
+    lo = min(T, fc.rank * per)
+    rows = min(T, lo + per) - lo
+    f = _lib.fn("dlti_tp_own_reduce_norm", [_V, _I, _L, _L, _L, _V, _V, _V, _I, _F, _I, _V])
+    _lib.check(f(_lib.ptr(slots), fc.world, per, lo, rows, _lib.ptr(residual), _lib.ptr(w), _lib.ptr(xn_own), d,
+                 float(eps), _lib.dtype_code(residual.dtype), _lib.stream_ptr()), "tp_own_reduce_norm")
 
 
 def tp_pull_reduce_norm_push(fc, partial: torch.Tensor, xn: torch.Tensor, T: int, residual: torch.Tensor,

@@ -35,6 +35,25 @@ _FUSE_ACC = os.environ.get("DLTI_DECODE_FUSE_ACC", "1") == "1"    # A/B switch: 
 # opt-in until measured on the serving shapes: prefill gate_up GEMM with SwiGLU in its epilogue (the training kernel)
 _PREFILL_FUSE_SWIGLU = os.environ.get("DLTI_SERVE_FUSE_SWIGLU", "0") == "1"
 _TP_LARGE = os.environ.get("DLTI_TP_LARGE_RSAG", "1") == "1"          # prefill-sized steps: reduce-scatter + all-gather
+# how prefill-sized steps do it: "fused" = reduce-scatter in the row-parallel GEMM's epilogue (K10) and all-gather in
+# the next column-parallel GEMM's producer (K11); "pull" = the round-1 stand-alone pull-reduce-push kernel
+_TP_LARGE_MODE = os.environ.get("DLTI_TP_LARGE_MODE", "fused")
+
+
+class ShardedAct:
+    """Normalised activations of a prefill-sized TP step whose rows still live on their owner ranks: the next
+    column-parallel GEMM gathers them itself (`handle`, K11); `rows()` is that GEMM's A operand."""
+
+    def __init__(self, T: int, handle):
+        self.T, self.handle = T, handle
+        self.dtype, self.device = handle.full.dtype, handle.full.device
+
+    def rows(self) -> torch.Tensor:
+        return self.handle.full[: self.T]
+
+    def gathered(self) -> torch.Tensor:
+        self.handle.materialize()
+        return self.handle.full[: self.T]
 _FUSE_TP_BARRIER = os.environ.get("DLTI_TP_FUSE_BARRIER", "1") == "1"  # rank barrier inside the reduce+norm kernel
 
 
@@ -47,6 +66,7 @@ class TPContext:
         self.world = info.world_size if info else 1
         self.backend, self.fused = backend, fused
         self.use_fused = fused is not None and self.world > 1
+        self.fused_large = False
         if self.use_fused:
             d = cfg.hidden_size
             # steps of more than SMALL rows (prefill) reduce-scatter + all-gather through one partial and one
@@ -60,6 +80,14 @@ class TPContext:
             if self.large:
                 self.partial = fused.alloc_symmetric((max_tokens, d), dtype)
                 self.xn = fused.alloc_symmetric((max_tokens, d), dtype)
+                self.fused_large = _TP_LARGE_MODE == "fused" and d % 64 == 0
+                if self.fused_large:
+                    self.per_max = -(-(-(-max_tokens // self.world)) // 64) * 64
+                    self.slots = fused.alloc_symmetric((self.world * self.per_max, d), dtype)   # [src rank][row]
+                    self.xn_own = fused.alloc_symmetric((self.per_max, d), dtype)
+                    self.xn_full = torch.empty(self.world * self.per_max, d, dtype=dtype, device=info.device)
+                    self.ctr_pool = torch.zeros(1 << 16, dtype=torch.int32, device=info.device)
+                    self.ctr_off = 0
 
     def adopt(self, w: "TPWeights", cfg: LlamaConfig, max_rows: int = 1024) -> None:
         """Fused backend: move the pieces of the model that are addressed across ranks into the symmetric arena.
@@ -103,6 +131,24 @@ class TPContext:
             part = partial_fn(None, None)
             y, _, _ = E.rmsnorm_fwd(part, w, eps, residual=residual)
             return y
+        if self.use_fused and T > self.small_rows and self.fused_large:
+            # K10: the GEMM's epilogue scatters each output row to its owner's receive slot | barrier | the owner
+            # sums its slots, adds the residual, normalises (local memory only) | barrier | K11: the NEXT
+            # column-parallel GEMM pulls the normalised rows from their owners while it computes
+            from ..parallel.fused import ActGather, tp_own_reduce_norm
+            assert T <= self.max_tokens
+            per = -(-(-(-T // self.world)) // 64) * 64
+            partial_fn(self.slots[:T], None, scatter=(self.fused.peer_array(self.slots), self.world, self.rank, per))
+            self.fused.barrier_graph_safe(6)
+            tp_own_reduce_norm(self.fused, self.slots, per, T, residual, w, eps, self.xn_own)
+            self.fused.barrier_graph_safe(6)
+            nu = self.world * per // 64
+            if self.ctr_off + nu > self.ctr_pool.numel():
+                self.ctr_pool.zero_()
+                self.ctr_off = 0
+            ctr = self.ctr_pool[self.ctr_off:self.ctr_off + nu]
+            self.ctr_off += nu
+            return ShardedAct(T, ActGather(self.fused, self.xn_own, self.xn_full, ctr, per))
         if self.use_fused and T > self.small_rows:
             # reduce-scatter + all-gather over peer memory: partial via the plain (fast) GEMM into this rank's
             # symmetric buffer | barrier | pull my rows from all ranks, add residual, norm, push to all | barrier
@@ -269,8 +315,13 @@ class ModelRunner:
         mm = gemm_skinny if skinny else (lambda a, b_: gemm(a, b_))
 
         def rowpar(act, wgt):
-            return lambda out, push: (gemm(act, wgt, out=out, push=push) if (push is not None or out is not None)
-                                      else mm(act, wgt))
+            return lambda out, push, scatter=None: (gemm(act, wgt, out=out, push=push, scatter=scatter)
+                                                    if (push is not None or out is not None) else mm(act, wgt))
+
+        def colpar(x, wgt):                        # column-parallel GEMM; gathers its rows itself when they are sharded
+            if isinstance(x, ShardedAct):
+                return gemm(x.rows(), wgt, gather=x.handle)
+            return mm(x, wgt)
 
         def row_reduce(act, wgt, norm_w):          # row-parallel GEMM -> (all-reduce) -> residual add -> norm
             if acc_path and tp.world == 1:
@@ -282,7 +333,7 @@ class ModelRunner:
                 qkv = S.acc_rope_cache(gemm_skinny_acc(xn, lw["w_qkv"]), xn.dtype, positions, self.cos, self.sin,
                                        slots, self.kv.k[li], self.kv.v[li], H, KV, hd)
             else:
-                qkv = mm(xn, lw["w_qkv"])
+                qkv = colpar(xn, lw["w_qkv"])
                 S.rope_cache_(qkv, positions, self.cos, self.sin, slots, self.kv.k[li], self.kv.v[li], H, KV, hd)
             if prefix is not None:
                 attn = torch.empty((T, H * hd), dtype=qkv.dtype, device=qkv.device)
@@ -311,12 +362,16 @@ class ModelRunner:
             if acc_path:
                 h = E.acc_swiglu(gemm_skinny_acc(xn, lw["w_gu"]), xn.dtype)
             elif _PREFILL_FUSE_SWIGLU and not skinny:
-                h = gemm_swiglu(xn, lw["w_gu"])          # SwiGLU in the CTA-pair GEMM epilogue (falls back by itself)
+                # SwiGLU in the CTA-pair GEMM epilogue (falls back by itself)
+                h = (gemm_swiglu(xn.rows(), lw["w_gu"], gather=xn.handle) if isinstance(xn, ShardedAct)
+                     else gemm_swiglu(xn, lw["w_gu"]))
             else:
-                h = E.swiglu_fwd(mm(xn, lw["w_gu"]))
+                h = E.swiglu_fwd(colpar(xn, lw["w_gu"]))
             nxt = w.layers[li + 1]["ln1"] if li + 1 < L else w.final_norm
             xn = row_reduce(h, lw["w_down"], nxt)
         if last_idx is not None and last_idx.numel() == 0:      # a step of partial prompt chunks samples nothing
             return torch.empty((0, cfg.vocab_size), dtype=xn.dtype, device=xn.device)
+        if isinstance(xn, ShardedAct):                          # the LM head needs the sampled rows on every rank
+            xn = xn.gathered()
         xl = xn if last_idx is None else xn.index_select(0, last_idx)
         return tp.lm_head_logits(xl, w.lm_head)

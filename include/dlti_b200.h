@@ -179,6 +179,15 @@ int dlti_gemm2_attach(const void* const* peer_shards, void* staging, unsigned in
                       int rows_per_rank, int world, int rot_unit, int j_begin, int j_count, unsigned int epoch,
                       const unsigned int* wait_counters, int wait_units, unsigned int wait_epoch, int* err_flag);
 int dlti_gather_job_run(int ctas, dlti_stream_t stream);
+/* K11 (all-gather -> column-parallel GEMM; the reference's surface is vLLM tensor parallelism,
+ * /root/reference/README.md:10): after dlti_gemm2_attach, declare that the job / wait spec concern the A operand
+ * (activation rows pulled from their owner ranks by the launch's gather warp; the A producer waits per 64-row
+ * unit) and that the M blocks are visited starting at block m_rot (this rank's own rows, which land first). */
+int dlti_gemm2_attach_a_side(int m_rot);
+/* K10 for prefill-sized steps (row-parallel GEMM -> reduce-scatter): the next CTA-pair launch stores output row r
+ * into the receive slot of rank r / rows_per_owner (peer stores from the epilogue, tile by tile); the owner then
+ * sums its slots in rank order (dlti_tp_own_reduce_norm). */
+int dlti_gemm2_attach_scatter(const void* const* slot_peers, int world, int rank, int rows_per_owner);
 
 /* Llama gate_up projection + SwiGLU in one kernel: h[M, ff] = silu(A·Wg^T) * (A·Wu^T), W = [gate; up]
  * stored [2*ff, K]. CTA rank 0 of a pair stages gate rows, rank 1 the matching up rows; the [M, 2*ff]
@@ -258,6 +267,12 @@ int dlti_k9_step(const void* const* masters, const void* const* boards, const vo
                  int* err_flag, dlti_stream_t stream);
 int dlti_peer_wait(const unsigned int* my_pads, int world, int channel, unsigned int epoch, int* err_flag,
                    dlti_stream_t stream);
+
+/* Owner side of K10 for prefill-sized steps: sum this rank's receive slots [world * per, d] in rank order, add the
+ * (row-sharded) residual, RMSNorm, write the normalised rows to this rank's symmetric [per, d] buffer. */
+int dlti_tp_own_reduce_norm(const void* slots, int world, long long per, long long row_lo, long long rows,
+                            void* residual, const void* w, void* xn_own, int d, float eps, int dtype,
+                            dlti_stream_t stream);
 
 /* K15: embedding lookup over a vocabulary-sharded table in peer memory: out[t] = row ids[t] fetched from its
  * owner rank (ids outside [0, vocab) give zero rows). Replaces all-gather + lookup of the reference's ZeRO-3

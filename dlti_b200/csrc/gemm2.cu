@@ -32,6 +32,7 @@ constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
 constexpr int STAGES = 6;
 constexpr int TMEM_COLS = 512;                // two accumulator stages of 256 columns
 constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + 256 + 1024;
+constexpr int SCATTER_STAGE_BYTES = 4 * 4096;      // one 32 x 64 16-bit block per epilogue warp (K10 scatter epilogue)
 constexpr long long WAIT_LIMIT = 4000000000LL;   // ~2 s
 
 struct Gemm2Params {
@@ -703,12 +704,18 @@ gemm2_kernel(const Gemm2Params p, const GatherJob gj, const WaitSpec ws_, const 
           }
         }
       } else if (p.scatter_world > 0) {
-        // K10, prefill-sized steps: the tile's rows go to the receive slots of the ranks that own them
+        // K10, prefill-sized steps: the tile's rows go to the receive slots of the ranks that own them. A thread
+        // holds one ROW of the accumulator, so storing from registers would put 32 different rows into every
+        // store instruction (16-byte pieces on the link: measured 3x slower than pulling). Each warp therefore
+        // turns its 32 x 64 block through 4 KB of shared memory (16-byte chunks XOR-swizzled by row: conflict-
+        // free both ways) and writes 4 rows x 128 contiguous bytes per instruction.
         const bool bf = p.out_dtype == DLTI_BF16;
         const bool rok = row < p.M;
         const int owner = rok ? row / p.scatter_per : 0;
-        uint16_t* drow = reinterpret_cast<uint16_t*>(s_scatter[owner]) +
-                         ((long long)p.scatter_rank * p.scatter_per + (row - owner * p.scatter_per)) * p.ldc;
+        const unsigned long long drow = reinterpret_cast<unsigned long long>(
+            reinterpret_cast<uint16_t*>(s_scatter[owner]) +
+            ((long long)p.scatter_rank * p.scatter_per + (row - owner * p.scatter_per)) * p.ldc);
+        const uint32_t st_base = smem_base + STAGES * STAGE_BYTES + 256 + (uint32_t)quarter * 4096u;   // behind the barriers
 #pragma unroll 1
         for (int c = 0; c < ncols / 64; ++c) {
           const int col0 = n0 + c * 64;
@@ -717,23 +724,33 @@ gemm2_kernel(const Gemm2Params p, const GatherJob gj, const WaitSpec ws_, const 
           tmem_ld_32x32b_x32(t_row + c * 64, v0);
           tmem_ld_32x32b_x32(t_row + c * 64 + 32, v1);
           tmem_wait_ld();
-          if (rok) {
 #pragma unroll
-            for (int i = 0; i < 4; ++i) {
-              int4 o0, o1;
-              uint32_t* u0 = reinterpret_cast<uint32_t*>(&o0);
-              uint32_t* u1 = reinterpret_cast<uint32_t*>(&o1);
+          for (int i = 0; i < 4; ++i) {
+            uint32_t u0[4], u1[4];
 #pragma unroll
-              for (int j = 0; j < 4; ++j) {
-                const float a0 = __uint_as_float(v0[8 * i + 2 * j]) * p.alpha, a1 = __uint_as_float(v0[8 * i + 2 * j + 1]) * p.alpha;
-                const float b0 = __uint_as_float(v1[8 * i + 2 * j]) * p.alpha, b1 = __uint_as_float(v1[8 * i + 2 * j + 1]) * p.alpha;
-                u0[j] = bf ? Cvt<__nv_bfloat16>::pack2(a0, a1) : Cvt<__half>::pack2(a0, a1);
-                u1[j] = bf ? Cvt<__nv_bfloat16>::pack2(b0, b1) : Cvt<__half>::pack2(b0, b1);
-              }
-              st_v4(drow + col0 + 8 * i, o0);
-              st_v4(drow + col0 + 32 + 8 * i, o1);
+            for (int j = 0; j < 4; ++j) {
+              const float a0 = __uint_as_float(v0[8 * i + 2 * j]) * p.alpha, a1 = __uint_as_float(v0[8 * i + 2 * j + 1]) * p.alpha;
+              const float b0 = __uint_as_float(v1[8 * i + 2 * j]) * p.alpha, b1 = __uint_as_float(v1[8 * i + 2 * j + 1]) * p.alpha;
+              u0[j] = bf ? Cvt<__nv_bfloat16>::pack2(a0, a1) : Cvt<__half>::pack2(a0, a1);
+              u1[j] = bf ? Cvt<__nv_bfloat16>::pack2(b0, b1) : Cvt<__half>::pack2(b0, b1);
             }
+            const uint32_t a0 = st_base + (uint32_t)lane * 128u + (uint32_t)((i ^ (lane & 7)) << 4);
+            const uint32_t a1 = st_base + (uint32_t)lane * 128u + (uint32_t)(((i + 4) ^ (lane & 7)) << 4);
+            asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(a0), "r"(u0[0]), "r"(u0[1]), "r"(u0[2]), "r"(u0[3]) : "memory");
+            asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(a1), "r"(u1[0]), "r"(u1[1]), "r"(u1[2]), "r"(u1[3]) : "memory");
           }
+          __syncwarp();
+#pragma unroll
+          for (int it = 0; it < 8; ++it) {
+            const int r = it * 4 + (lane >> 3), ch = lane & 7;
+            const unsigned long long dr = __shfl_sync(0xffffffffu, drow, r);
+            const int ok = __shfl_sync(0xffffffffu, (int)rok, r);
+            int4 val;
+            const uint32_t sa = st_base + (uint32_t)r * 128u + (uint32_t)((ch ^ (r & 7)) << 4);
+            asm volatile("ld.shared.v4.b32 {%0, %1, %2, %3}, [%4];" : "=r"(val.x), "=r"(val.y), "=r"(val.z), "=r"(val.w) : "r"(sa) : "memory");
+            if (ok) st_v4(reinterpret_cast<uint16_t*>(dr) + col0 + ch * 8, val);
+          }
+          __syncwarp();
         }
         __threadfence_system();
       } else
@@ -928,10 +945,12 @@ int launch2(const Gemm2Params& p_in, const CUtensorMap& a, const CUtensorMap& b,
   int dev = 0;
   cudaGetDevice(&dev);
   if (!configured[dev & 63]) {
-    DLTI_CUDA_CHECK(cudaFuncSetAttribute(gemm2_kernel<B_MN>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES));
+    DLTI_CUDA_CHECK(cudaFuncSetAttribute(gemm2_kernel<B_MN>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                         SMEM_BYTES + SCATTER_STAGE_BYTES));
     configured[dev & 63] = true;
   }
-  gemm2_kernel<B_MN><<<grid, NUM_THREADS + (job.j_count > 0 ? GATHER_THREADS : 0), SMEM_BYTES, stream>>>(
+  gemm2_kernel<B_MN><<<grid, NUM_THREADS + (job.j_count > 0 ? GATHER_THREADS : 0),
+                       SMEM_BYTES + (sc.world > 0 ? SCATTER_STAGE_BYTES : 0), stream>>>(
       p, job, wait, a, b, a2, b2, bh, b2h);
   dlti_count_launch();
   return (int)cudaGetLastError();

@@ -137,6 +137,7 @@ class TPContext:
             # column-parallel GEMM pulls the normalised rows from their owners while it computes
             from ..parallel.fused import ActGather, tp_own_reduce_norm
             assert T <= self.max_tokens
+            self.fused_large_calls = getattr(self, "fused_large_calls", 0) + 1
             per = -(-(-(-T // self.world)) // 64) * 64
             partial_fn(self.slots[:T], None, scatter=(self.fused.peer_array(self.slots), self.world, self.rank, per))
             self.fused.barrier_graph_safe(6)

@@ -41,6 +41,8 @@ def run(info, world_tp, backend, fused, graphs):
         return None
     out = eng.generate(prompts, sp)
     eng.shutdown_workers()
+    if world_tp > 1 and backend == "fused":     # the 469-row prefill step must have taken the GEMM-fused K10/K11 path
+        assert getattr(tp, "fused_large_calls", 0) >= 2 * cfg.num_hidden_layers, "prefill did not use the fused path"
     return [o["token_ids"] for o in out]
 
 

@@ -234,6 +234,7 @@ def gemm_swiglu_bwd(dy: torch.Tensor, w_down: torch.Tensor, gu: torch.Tensor, ga
 
 
 _skinny_ws: dict = {}
+_skinny_ws_retired: list = []
 _SKINNY_SPLIT = int(os.environ.get("DLTI_SKINNY_SPLIT", "0"))   # 0 = stream-K, -1 = tile-major auto split, n = n splits
 
 
@@ -241,6 +242,8 @@ def _skinny_workspace(device, numel: int) -> torch.Tensor:
     key = str(device)
     ws = _skinny_ws.get(key)
     if ws is None or ws.numel() < numel:
+        if ws is not None:
+            _skinny_ws_retired.append(ws)      # captured CUDA graphs may still point at it
         ws = torch.zeros(max(numel, 256 * 32768), dtype=torch.float32, device=device)
         _skinny_ws[key] = ws
     return ws

@@ -79,6 +79,7 @@ def paged_decode_ref(q, k_cache, v_cache, block_tables, ctx_lens, H, KV, hd, sca
 
 
 _ws: dict = {}
+_ws_retired: list = []
 
 
 def paged_decode(q, k_cache, v_cache, block_tables, ctx_lens, H, KV, hd, scale=None, out=None,
@@ -106,6 +107,10 @@ def paged_decode(q, k_cache, v_cache, block_tables, ctx_lens, H, KV, hd, scale=N
     key = str(q.device)
     ws = _ws.get(key)
     if ws is None or ws.numel() < need:
+        # a CUDA graph captured with the smaller workspace keeps its pointer: the old buffer must stay alive
+        # (replacing it made the graphs of the small decode buckets fault once a larger bucket had been captured)
+        if ws is not None:
+            _ws_retired.append(ws)
         ws = torch.empty(max(need, 1 << 20), dtype=torch.float32, device=q.device)
         _ws[key] = ws
     f = _lib.fn("dlti_paged_decode", [_V, _L, _V, _V, _V, _I, _V, _I, _I, _I, _I, _I, _F, _I, _V, _V, _L, _I, _V])

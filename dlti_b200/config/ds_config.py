@@ -13,6 +13,8 @@ from __future__ import annotations
 
 import copy
 import json
+import os
+import sys
 from pathlib import Path
 from typing import Any
 
@@ -48,10 +50,32 @@ class DSConfig:
         if stage not in (0, 1, 2, 3):
             raise DSConfigError(f"zero_optimization.stage must be 0..3, got {stage}")
 
+    # keys that are parsed for compatibility but have no effect here, and why (reported once at load time)
+    ACCEPTED_NOT_USED = {
+        "zero_optimization.stage3_prefetch_bucket_size": "the gather look-ahead is one whole decoder layer (queued "
+                                                         "behind the running layer's GEMMs)",
+        "zero_optimization.stage3_max_reuse_distance": "a gathered layer stays until its staging slot is needed by the "
+                                                       "layer after next",
+        "zero_optimization.sub_group_size": "the optimizer steps its whole partition in one kernel",
+        "zero_optimization.round_robin_gradients": "gradients live in one flat buffer partitioned contiguously",
+        "zero_optimization.contiguous_gradients": "the flat gradient buffer is always contiguous",
+    }
+
+    def ignored_keys(self) -> list[str]:
+        out = [f"{k}: {why}" for k, why in self.ACCEPTED_NOT_USED.items() if _get(self.cfg, k) is not None]
+        if self.zero_stage == 3 and _get(self.cfg, "zero_optimization.allgather_bucket_size") is not None:
+            out.append("zero_optimization.allgather_bucket_size: stage 3 gathers parameters per layer, not per bucket")
+        return out
+
     @classmethod
     def load(cls, path: str | Path) -> "DSConfig":
         with open(path) as f:
-            return cls(json.load(f), str(path))
+            c = cls(json.load(f), str(path))
+        ign = c.ignored_keys()
+        if ign and os.environ.get("RANK", "0") == "0" and not os.environ.get("DLTI_QUIET"):
+            print(f"[ds_config] {path}: accepted for compatibility, no effect in this implementation:\n  - "
+                  + "\n  - ".join(ign), file=sys.stderr)
+        return c
 
     @classmethod
     def baseline(cls) -> "DSConfig":

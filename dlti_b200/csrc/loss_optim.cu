@@ -365,11 +365,12 @@ DLTI_API int dlti_sumsq_noalloc(const float* g, long long n, float* out, int acc
   int dev = 0;
   DLTI_CUDA_CHECK(cudaGetDevice(&dev));
   if (dev < 0 || dev >= NOALLOC_MAX_DEVICES) return DLTI_ERR_UNSUPPORTED;
-  float* scratch = g_noalloc_scratch_addr[dev];
+  float* scratch = __atomic_load_n(&g_noalloc_scratch_addr[dev], __ATOMIC_ACQUIRE);
   if (!scratch) {
-    // once per device, with that device current: name -> device address
+    // once per device, with that device current: name -> device address (two host threads racing here both
+    // obtain the same address; the atomic store only makes that well-defined)
     DLTI_CUDA_CHECK(cudaGetSymbolAddress((void**)&scratch, g_sumsq_noalloc_scratch));
-    g_noalloc_scratch_addr[dev] = scratch;
+    __atomic_store_n(&g_noalloc_scratch_addr[dev], scratch, __ATOMIC_RELEASE);
   }
   long long nb = (n + NOALLOC_CHUNK - 1) / NOALLOC_CHUNK;
   if (nb < 1) nb = 1;

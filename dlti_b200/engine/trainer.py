@@ -102,7 +102,11 @@ class Trainer:
                                alloc=self.fused.alloc_symmetric if self.fused is not None else None)
         self.model = LoraLlama(cfg, self.weights, self.lora, args.gradient_checkpointing,
                                dropout_seed=args.seed)
-        self.scaler = build_loss_scaler(self.ds.fp16_block if self.precision == "fp16" else None)
+        if self.precision == "fp16" and not args.deepspeed:
+            from ..optim.loss_scaler import grad_scaler_like
+            self.scaler = grad_scaler_like()       # baseline script: torch GradScaler semantics, not DeepSpeed's
+        else:
+            self.scaler = build_loss_scaler(self.ds.fp16_block if self.precision == "fp16" else None)
         op = self.ds.optimizer_params if self.ds.has_optimizer else {}
         betas = tuple(op.get("betas", (args.adam_beta1, args.adam_beta2)))
         self.optimizer = ZeroOptimizer(

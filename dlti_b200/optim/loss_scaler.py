@@ -64,6 +64,13 @@ class DynamicLossScaler:
             setattr(self, k, v)
 
 
+def grad_scaler_like() -> DynamicLossScaler:
+    """torch.amp.GradScaler defaults, which is what the reference's baseline runs under (HF Trainer fp16=True
+    without DeepSpeed, reference training/train_baseline.py): initial scale 2^16, halve immediately on the first
+    overflow (no hysteresis), double after 2000 clean steps, no lower bound to speak of."""
+    return DynamicLossScaler(initial_scale_power=16, scale_window=2000, hysteresis=1, min_scale=2.0 ** -24)
+
+
 def build_loss_scaler(fp16_cfg: dict | None):
     """fp16 block of a ds_config -> scaler. None / disabled => static 1.0 (bf16 / fp32)."""
     if not fp16_cfg or not fp16_cfg.get("enabled", False):

@@ -50,9 +50,12 @@ def load_and_calculate(csv_path: str = CSV_PATH) -> pd.DataFrame:
 
 def print_comparison_table(df: pd.DataFrame) -> None:
     print(f"\n{BAR}\nTRAINING COMPARISON\n{BAR}\n")
-    cols = ["experiment", "num_gpus", "training_time_hours", "samples_per_second", "peak_memory_gb",
-            "speedup", "efficiency_percent"]
-    cols += [c for c in ("tokens_per_second", "max_rank_step_ms", "token_scaling_percent", "dtype") if c in df.columns]
+    # every column of the metrics CSV (as the reference prints them: experiment, strategy, zero_stage, num_gpus,
+    # times, samples/s, peak memory, final loss, timestamp) followed by the derived ones
+    lead = ["experiment", "strategy", "zero_stage", "num_gpus", "training_time_hours", "training_time_seconds",
+            "samples_per_second", "peak_memory_gb", "final_loss", "speedup", "efficiency_percent"]
+    cols = [c for c in lead if c in df.columns]
+    cols += [c for c in df.columns if c not in cols]
     view = df[cols].copy()
     for c, nd in (("training_time_hours", 2), ("samples_per_second", 1), ("peak_memory_gb", 2), ("speedup", 2),
                   ("efficiency_percent", 1), ("tokens_per_second", 0), ("max_rank_step_ms", 1),

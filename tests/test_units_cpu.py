@@ -298,3 +298,21 @@ def test_shm_ring_delivers_every_message_in_order_to_every_reader():
     assert res == [True, True]
     with pytest.raises(RuntimeError):
         ShmRing(name + "x", -1, 1, n_slots=2, slot_bytes=64).write(np.zeros(100, dtype=np.int64))
+
+
+def test_baseline_fp16_scaler_follows_torch_gradscaler_and_ds_config_reports_ignored_keys(capsys):
+    from dlti_b200.optim.loss_scaler import grad_scaler_like
+    s = grad_scaler_like()
+    assert s.cur_scale == 65536.0
+    s.update(True)                       # GradScaler backs off at once (DeepSpeed's default waits: hysteresis 2)
+    assert s.cur_scale == 32768.0
+    for _ in range(1999):
+        s.update(False)
+    assert s.cur_scale == 32768.0
+    s.update(False)                      # growth_interval = 2000 clean steps
+    assert s.cur_scale == 65536.0
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    c = DSConfig.load(os.path.join(root, "configs", "ds_config_zero3.json"))
+    keys = " ".join(c.ignored_keys())
+    assert "stage3_prefetch_bucket_size" in keys and "stage3_max_reuse_distance" in keys
+    assert "accepted for compatibility" in capsys.readouterr().err

@@ -201,6 +201,7 @@ class TPWeights:
         self.embed = mk(cfg.vocab_size, d)
         self.final_norm = mk(d)
         self.lm_head = mk(self.V, d)
+        self.lora = None          # unmerged PEFT adapter (attach_adapter)
         self.layers = [dict(w_qkv=mk((self.H + 2 * self.KV) * hd, d), w_o=mk(d, self.H * hd),
                             w_gu=mk(2 * self.ff, d), w_down=mk(d, self.ff), ln1=mk(d), ln2=mk(d))
                        for _ in range(cfg.num_hidden_layers)]
@@ -223,6 +224,60 @@ class TPWeights:
             dst["w_down"].copy_(src.w_down[:, r * ffl:(r + 1) * ffl])
             dst["ln1"].copy_(src.ln1)
             dst["ln2"].copy_(src.ln2)
+        return self
+
+    def attach_adapter(self, adapter_state: dict, lcfg) -> "TPWeights":
+        """Serve a PEFT LoRA adapter UNMERGED on top of the base weights (what vLLM's LoRA loader does):
+        per layer, packed 16-bit operands for the LoRA branch of q/k/v (a K-extension of the QKV GEMM, as in
+        training) and of o_proj (extra K columns of the o_proj GEMM: its input becomes [attention | t_o] and its
+        weight [W_o | (alpha/r) B_o], so every o_proj kernel — decode, push, scatter — serves the adapter without
+        knowing about it). TP slicing: B_q/k/v rows and A_o columns follow this rank's heads; A_q/k/v and B_o are
+        whole. The base weights are left untouched, so adapters can be swapped without reloading the model."""
+        cfg, hd, r = self.cfg, self.cfg.head_dim, lcfg.r
+        dev, dt = self.final_norm.device, self.final_norm.dtype
+        d = cfg.hidden_size
+        Hl, KVl = self.H * hd, self.KV * hd
+        q, kv = cfg.q_size, cfg.kv_size
+        Rq = max(64, (3 * r + 63) // 64 * 64)
+        Ro = max(64, (r + 63) // 64 * 64)
+        sc = lcfg.scaling
+        rk = self.rank
+
+        def find(li, mod, which):
+            for k, v in adapter_state.items():
+                if f"layers.{li}.self_attn.{mod}.lora_{which}" in k:
+                    return v.to(torch.float32)
+            return None
+
+        rows_full = {"q_proj": (rk * Hl, (rk + 1) * Hl), "k_proj": (rk * KVl, (rk + 1) * KVl),
+                     "v_proj": (rk * KVl, (rk + 1) * KVl)}
+        rows_local = {"q_proj": (0, Hl), "k_proj": (Hl, Hl + KVl), "v_proj": (Hl + KVl, Hl + 2 * KVl)}
+        self.lora = []
+        for li, l in enumerate(self.layers):
+            ent = {"A_qkv": None, "B_qkv": None, "A_o": None}
+            if any(m in lcfg.target_modules for m in ("q_proj", "k_proj", "v_proj")):
+                A_c = torch.zeros(Rq, d, dtype=torch.float32)
+                B_c = torch.zeros(Hl + 2 * KVl, Rq, dtype=torch.float32)
+                for j, mod in enumerate(("q_proj", "k_proj", "v_proj")):
+                    A, B = find(li, mod, "A"), find(li, mod, "B")
+                    if A is None or B is None:
+                        continue
+                    A_c[j * r:(j + 1) * r] = A
+                    f0, f1 = rows_full[mod]
+                    l0, l1 = rows_local[mod]
+                    B_c[l0:l1, j * r:(j + 1) * r] = B[f0:f1] * sc
+                ent["A_qkv"], ent["B_qkv"] = A_c.to(dev, dt), B_c.to(dev, dt)
+            A, B = find(li, "o_proj", "A"), find(li, "o_proj", "B")
+            if "o_proj" in lcfg.target_modules and A is not None and B is not None:
+                A_o = torch.zeros(Ro, Hl, dtype=torch.float32)
+                A_o[:r] = A[:, rk * Hl:(rk + 1) * Hl]
+                ent["A_o"] = A_o.to(dev, dt)
+                w_ext = torch.zeros(d, Hl + Ro, dtype=dt, device=dev)
+                w_ext[:, :Hl].copy_(l["w_o"])
+                w_ext[:, Hl:Hl + r].copy_((B * sc).to(dev, dt))
+                l["w_o_ext"] = w_ext
+                ent["Ro"] = Ro
+            self.lora.append(ent)
         return self
 
     def init_random(self, seed: int = 0) -> "TPWeights":
@@ -330,7 +385,25 @@ class ModelRunner:
             return tp.reduce_add_norm(rowpar(act, wgt), T, residual, norm_w, eps)
 
         for li, lw in enumerate(w.layers):
-            if acc_path:
+            ad = w.lora[li] if w.lora is not None else None          # unmerged adapter operands of this layer
+            if ad is not None and ad["A_qkv"] is not None:
+                # LoRA branch of q/k/v: t = x A^T (rank-sized), then (alpha/r) t B^T joins the base projection in the
+                # same accumulator (second stream-K pass into the fp32 workspace / K-extension of the GEMM)
+                if isinstance(xn, ShardedAct):
+                    t = gemm(xn.rows(), ad["A_qkv"], gather=xn.handle)
+                    x_in = xn.rows()
+                else:
+                    t = (gemm_skinny if (skinny and xn.is_cuda) else gemm)(xn, ad["A_qkv"])
+                    x_in = xn
+                if acc_path:
+                    acc = gemm_skinny_acc(x_in, lw["w_qkv"])
+                    gemm_skinny_acc(t, ad["B_qkv"])
+                    qkv = S.acc_rope_cache(acc, x_in.dtype, positions, self.cos, self.sin, slots, self.kv.k[li],
+                                           self.kv.v[li], H, KV, hd)
+                else:
+                    qkv = gemm(x_in, lw["w_qkv"], a2=t, b2=ad["B_qkv"])
+                    S.rope_cache_(qkv, positions, self.cos, self.sin, slots, self.kv.k[li], self.kv.v[li], H, KV, hd)
+            elif acc_path:
                 qkv = S.acc_rope_cache(gemm_skinny_acc(xn, lw["w_qkv"]), xn.dtype, positions, self.cos, self.sin,
                                        slots, self.kv.k[li], self.kv.v[li], H, KV, hd)
             else:
@@ -359,7 +432,15 @@ class ModelRunner:
                                self.scale, out=attn[:nd], max_ctx=max_ctx)
                 A.attention_fwd(qkv[nd:], cu_seqlens, max_seqlen, H, KV, hd, self.scale, want_lse=False,
                                 out=attn[nd:])
-            xn = row_reduce(attn, lw["w_o"], lw["ln2"])
+            if ad is not None and ad["A_o"] is not None:
+                # LoRA branch of o_proj as extra K columns: [attention | t_o] x [W_o | (alpha/r) B_o]^T
+                Hl = H * hd
+                act = torch.empty((T, Hl + ad["Ro"]), dtype=attn.dtype, device=attn.device)
+                act[:, :Hl].copy_(attn)
+                (gemm_skinny if (skinny and attn.is_cuda) else gemm)(attn, ad["A_o"], out=act[:, Hl:])
+                xn = row_reduce(act, lw["w_o_ext"], lw["ln2"])
+            else:
+                xn = row_reduce(attn, lw["w_o"], lw["ln2"])
             if acc_path:
                 h = E.acc_swiglu(gemm_skinny_acc(xn, lw["w_gu"]), xn.dtype)
             elif _PREFILL_FUSE_SWIGLU and not skinny:

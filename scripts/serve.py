@@ -4,8 +4,9 @@
     python scripts/serve.py --model_config llama2-7b --synthetic --port 8000
     python -m dlti_b200.launch --num_gpus=8 --no_local_rank scripts/serve.py --model <hf_dir> [--adapter <peft_dir>]
 
-Rank 0 runs the HTTP server + scheduler; the other ranks run the TP worker loop. `--adapter` merges a
-PEFT LoRA adapter into the base weights at load time (W' = W + alpha/r * B A). The reference declares
+Rank 0 runs the HTTP server + scheduler; the other ranks run the TP worker loop. `--adapter` serves a PEFT
+LoRA adapter unmerged on top of the base weights (LoRA branch inside the QKV / o_proj GEMMs); with
+`--merge_adapter` it is folded into the base weights at load time instead (W' = W + alpha/r * B A). The reference declares
 "vLLM serving with tensor parallelism" (README.md:10) without shipping a launch script."""
 import argparse
 import os
@@ -36,12 +37,15 @@ def build_engine(a):
     if model_dir and not a.synthetic:
         from dlti_b200.models.hf_io import load_resident
         _, full = load_resident(model_dir, "cpu", dtype)
-        if a.adapter:
+        if a.adapter and a.merge_adapter:
             from dlti_b200.models.merge import merge_into_weights
             from dlti_b200.models.peft_io import load_adapter_config, load_adapter_state
             merge_into_weights(full, load_adapter_state(a.adapter), load_adapter_config(a.adapter))
         w.load_from_full(full)
         del full
+        if a.adapter and not a.merge_adapter:      # base + adapter served side by side (the adapter stays swappable)
+            from dlti_b200.models.peft_io import load_adapter_config, load_adapter_state
+            w.attach_adapter(load_adapter_state(a.adapter), load_adapter_config(a.adapter))
     else:
         w.init_random(a.seed)
     tok = load_tokenizer(model_dir, cfg.vocab_size)
@@ -59,7 +63,10 @@ def build_engine(a):
 def add_args(ap):
     ap.add_argument("--model", type=str, default=None, help="HF checkpoint directory (or preset name)")
     ap.add_argument("--model_config", type=str, default=None, help="tiny | llama2-7b | llama2-70b")
-    ap.add_argument("--adapter", type=str, default=None, help="PEFT LoRA adapter directory to merge")
+    ap.add_argument("--adapter", type=str, default=None, help="PEFT LoRA adapter directory served on top of the base")
+    ap.add_argument("--merge_adapter", action="store_true",
+                    help="fold the adapter into the base weights at load time (W' = W + alpha/r B A) instead of "
+                         "serving it unmerged")
     ap.add_argument("--synthetic", action="store_true", help="random-init weights (no checkpoint needed)")
     ap.add_argument("--dtype", default="bf16", choices=["bf16", "fp16", "fp32"])
     ap.add_argument("--device", default="cuda")

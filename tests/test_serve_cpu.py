@@ -692,3 +692,40 @@ def test_stop_strings_end_generation_and_are_not_streamed(async_sched):
     # a stop string that never occurs changes nothing, and the held-back tail is flushed at the end
     o = eng.generate([prompt], SamplingParams(max_tokens=24, temperature=0.0, ignore_eos=True, stop=["~~~~~~"]))[0]
     assert o["finish_reason"] == "length" and o["text"] == text
+
+
+def test_unmerged_adapter_serving_matches_merged_weights():
+    """X1: base + PEFT adapter served unmerged (LoRA branch inside the QKV / o_proj GEMMs) gives the logits of the
+    merged model W' = W + (alpha/r) B A, for whole prompts and for decode steps through the paged cache."""
+    import copy
+    from dlti_b200.models.lora import LoraConfig
+    from dlti_b200.models.merge import merge_into_weights
+    cfg = PRESETS["tiny"]
+    full = ResidentWeights.random_init(cfg, "cpu", torch.float32, seed=3)
+    for t in full.all_matrices():
+        t.mul_(4.0)
+    lcfg = LoraConfig(r=8, lora_alpha=16, lora_dropout=0.0)
+    g = torch.Generator().manual_seed(11)
+    d, q, kv = cfg.hidden_size, cfg.q_size, cfg.kv_size
+    state = {}
+    for li in range(cfg.num_hidden_layers):
+        for mod, (i, o) in {"q_proj": (d, q), "k_proj": (d, kv), "v_proj": (d, kv), "o_proj": (q, d)}.items():
+            state[f"base_model.model.model.layers.{li}.self_attn.{mod}.lora_A.weight"] = torch.randn(8, i, generator=g) * 0.2
+            state[f"base_model.model.model.layers.{li}.self_attn.{mod}.lora_B.weight"] = torch.randn(o, 8, generator=g) * 0.2
+    merged = copy.deepcopy(full)
+    merge_into_weights(merged, state, lcfg)
+
+    def engine(weights, adapter):
+        w = TPWeights(cfg, 0, 1, "cpu", torch.float32).load_from_full(weights)
+        if adapter:
+            w.attach_adapter(state, lcfg)
+        return LLMEngine(cfg, w, TPContext(), ByteTokenizer(cfg.vocab_size), num_blocks=64, max_model_len=256,
+                         use_cuda_graphs=False)
+
+    prompts = [[1] + list(range(40, 40 + n)) for n in (5, 23)]
+    sp = SamplingParams(max_tokens=10, temperature=0.0, ignore_eos=True, logprobs=1)
+    a = engine(full, True).generate(prompts, sp)
+    b = engine(merged, False).generate(prompts, sp)
+    c = engine(full, False).generate(prompts, sp)
+    assert [o["token_ids"] for o in a] == [o["token_ids"] for o in b]
+    assert [o["token_ids"] for o in a] != [o["token_ids"] for o in c]          # the adapter does change the model

@@ -203,16 +203,50 @@ class ZeroOptimizer:
         step = self.step_count + 1
         pushed = False
         if self.offload:
+            # ZeRO-Offload optimizer step (D15): the partition's gradients go to pinned host memory, the AVX-512
+            # Adam steps the host copy of master / moments, the new master comes back — pipelined in chunks on a
+            # copy stream so that the D2H of chunk i+1 and the H2D of chunk i-1 overlap the CPU update of chunk i.
+            # The 16-bit compute copies are not written by the CPU kernel (its optional p16 output): they live in
+            # packed, pre-scaled per-layer buffers that one device kernel produces from the fp32 master after the
+            # H2D (LoraParams.refresh_compute), which moves fewer bytes over PCIe than shipping both.
             nsq = float(self.gnorm_sq.item())
-            self.grad_host.copy_(g, non_blocking=False)
             f = _lib.fn("dlti_cpu_adamw", [C.c_void_p] * 5 + [C.c_int, C.c_longlong] + [C.c_float] * 5 +
                         [C.c_int, C.c_float, C.c_int, C.c_float, C.c_float, C.c_int], C.c_int, cpu=True)
-            skipped = bool(f(self.master_host.data_ptr(), self.m.data_ptr(), self.v.data_ptr(),
-                             self.grad_host.data_ptr(), None, 0, self.part, lr, self.betas[0],
-                             self.betas[1], self.eps, self.wd, step, nsq, 1, inv_scale,
-                             float(self.max_grad_norm), 0))
-            if not skipped:
-                self.master_part().copy_(self.master_host, non_blocking=True)
+            skipped = not math.isfinite(nsq)
+            on_gpu = g.is_cuda
+            nch = 4 if (on_gpu and self.part >= (1 << 20)) else 1
+            bounds = [self.part * i // nch // 64 * 64 for i in range(nch)] + [self.part]
+            if on_gpu:
+                if getattr(self, "_copy_stream", None) is None:
+                    self._copy_stream = torch.cuda.Stream(device=g.device)
+                cs = self._copy_stream
+                cs.wait_stream(torch.cuda.current_stream())
+                d2h = []
+                with torch.cuda.stream(cs):
+                    for i in range(nch):
+                        a, b = bounds[i], bounds[i + 1]
+                        self.grad_host[a:b].copy_(g[a:b], non_blocking=True)
+                        ev = torch.cuda.Event()
+                        ev.record(cs)
+                        d2h.append(ev)
+            else:
+                self.grad_host.copy_(g)
+            for i in range(nch):
+                a, b = bounds[i], bounds[i + 1]
+                if on_gpu:
+                    d2h[i].synchronize()
+                if not skipped and b > a:
+                    off = 4 * a
+                    f(self.master_host.data_ptr() + off, self.m.data_ptr() + off, self.v.data_ptr() + off,
+                      self.grad_host.data_ptr() + off, None, 0, b - a, lr, self.betas[0], self.betas[1], self.eps,
+                      self.wd, step, nsq, 1, inv_scale, float(self.max_grad_norm), 0)
+                    if on_gpu:
+                        with torch.cuda.stream(cs):
+                            self.master_part()[a:b].copy_(self.master_host[a:b], non_blocking=True)
+                    else:
+                        self.master_part()[a:b].copy_(self.master_host[a:b])
+            if on_gpu:
+                torch.cuda.current_stream().wait_stream(cs)
         elif self.fused is not None and self.world > 1 and self.stage >= 1:
             # K9: AdamW on the owned slice, new values pushed into every peer's master buffer
             self.fused.adamw_push(self.lora.master, self.m, self.v, g, self.lo, self.part, lr=lr,

@@ -46,17 +46,26 @@ def load_tokenizer(model_path: str | None, vocab_size: int):
 
 
 class IncrementalDetokenizer:
-    """Emit only text that can no longer change: decode the full output each time and hold back a
-    trailing replacement character (an incomplete UTF-8 / multi-token glyph)."""
+    """Emit only text that can no longer change, in O(new tokens) per step: decode a short window of tokens —
+    [prefix, read) was already emitted, [read, end) is new — and emit decode(prefix..end) minus decode(prefix..read)
+    (the window gives the tokenizer the left context that decides spaces / merges). A trailing replacement
+    character (an incomplete UTF-8 / multi-token glyph) is held back until the next token completes it."""
+    WINDOW = 6
 
     def __init__(self, tokenizer, skip_special_tokens: bool = True):
         self.tok, self.skip = tokenizer, skip_special_tokens
-        self.emitted = 0
+        self.prefix = 0          # start of the context window
+        self.read = 0            # tokens [0, read) have been turned into emitted text
 
     def step(self, output_ids: list[int], final: bool = False) -> str:
-        text = self.tok.decode(output_ids, skip_special_tokens=self.skip)
-        if not final and text.endswith("�"):
-            text = text[:-1]
-        new = text[self.emitted:]
-        self.emitted = len(text)
+        n = len(output_ids)
+        if n <= self.read and not final:
+            return ""
+        before = self.tok.decode(output_ids[self.prefix:self.read], skip_special_tokens=self.skip) if self.read > self.prefix else ""
+        text = self.tok.decode(output_ids[self.prefix:n], skip_special_tokens=self.skip)
+        if not final and text.endswith("\ufffd"):
+            return ""            # wait for the rest of the character; nothing is consumed
+        new = text[len(before):] if text.startswith(before) else text[len(before.rstrip("\ufffd")):]
+        self.read = n
+        self.prefix = max(self.prefix, n - self.WINDOW)
         return new

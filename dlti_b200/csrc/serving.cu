@@ -355,25 +355,36 @@ __global__ void __launch_bounds__(256) sample_kernel(const void* __restrict__ lo
   // threshold from top-k and top-p by bisection on e in (0, 1]
   const int k = top_k ? top_k[row] : 0;
   const float tp = top_p ? top_p[row] : 1.f;
+  // Kept set as in vLLM / HF: top-k first, then the nucleus of the RENORMALISED top-k distribution. Both cuts are
+  // thresholds on e found by bisection in (0, 1]: thr_k = the k-th largest value; thr_p = the largest threshold
+  // (>= thr_k) whose kept mass is still >= top_p x (mass of the top-k set).
   float thr = 0.f;
-  if ((k > 0 && k < V) || tp < 1.f) {
-    float lo = 0.f, hi = 1.f;                  // keep set = {e >= thr}; thr in [lo, hi]
+  const bool k_on = (k > 0 && k < V), p_on = (tp < 1.f);
+  float base_mass = zt;
+  if (k_on) {
+    float lo = 0.f, hi = 1.f;
     for (int r = 0; r < 24; ++r) {
       const float mid = 0.5f * (lo + hi);
-      float cnt = 0.f, mass = 0.f;
-      for (int i = threadIdx.x; i < V; i += 256) {
-        const float e = probs[i];
-        if (e >= mid) { cnt += 1.f; mass += e; }
-      }
+      float cnt = 0.f;
+      for (int i = threadIdx.x; i < V; i += 256) cnt += (probs[i] >= mid) ? 1.f : 0.f;
       cnt = block_reduce_sum256(cnt, red);
+      if (cnt >= (float)k) lo = mid; else hi = mid;
+    }
+    thr = lo;
+    if (p_on) {
+      float m = 0.f;
+      for (int i = threadIdx.x; i < V; i += 256) m += (probs[i] >= thr) ? probs[i] : 0.f;
+      base_mass = block_reduce_sum256(m, red);
+    }
+  }
+  if (p_on) {
+    float lo = thr, hi = 1.f;
+    for (int r = 0; r < 24; ++r) {
+      const float mid = 0.5f * (lo + hi);
+      float mass = 0.f;
+      for (int i = threadIdx.x; i < V; i += 256) mass += (probs[i] >= mid) ? probs[i] : 0.f;
       mass = block_reduce_sum256(mass, red);
-      // thr_k = largest threshold that still keeps >= k tokens (the k-th largest value);
-      // thr_p = largest threshold whose kept mass is still >= top_p (the nucleus boundary).
-      // The kept set is the INTERSECTION of both cuts, i.e. thr = max(thr_k, thr_p) = the largest
-      // threshold at which at least one of the two monotone predicates still holds.
-      const bool k_on = (k > 0 && k < V), p_on = (tp < 1.f);
-      const bool ok = (k_on && cnt >= (float)k) || (p_on && mass >= tp * zt);
-      if (ok) lo = mid; else hi = mid;
+      if (mass >= tp * base_mass) lo = mid; else hi = mid;
     }
     thr = lo;
   }
@@ -490,10 +501,13 @@ DLTI_API int dlti_sample(const void* logits, long long ld, int batch, int V, con
   if (batch <= 0) return 0;
   const size_t smem = (size_t)V * sizeof(float);
   if (smem > 200 * 1024) { dlti_set_error("sample: vocabulary too large for the shared-memory path (max 51200)"); return DLTI_ERR_TOO_LARGE; }
-  static bool cfg[3] = {false, false, false};
+  static bool cfg[64][3] = {};               // the attribute is per device
+  int dev = 0;
+  DLTI_CUDA_CHECK(cudaGetDevice(&dev));
+  dev &= 63;
 #define SAMPLE_CASE(IDX, TYPE)                                                                             \
   {                                                                                                         \
-    if (!cfg[IDX]) { DLTI_CUDA_CHECK(cudaFuncSetAttribute(sample_kernel<TYPE>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024)); cfg[IDX] = true; } \
+    if (!cfg[dev][IDX]) { DLTI_CUDA_CHECK(cudaFuncSetAttribute(sample_kernel<TYPE>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024)); cfg[dev][IDX] = true; } \
     sample_kernel<TYPE><<<batch, 256, smem, st>>>(logits, ld, V, temperature, top_k, top_p, seeds, step, out, out_logprob); \
   }
   if (dtype == DLTI_BF16) SAMPLE_CASE(0, __nv_bfloat16)

@@ -139,16 +139,14 @@ def sample_ref(logits, temperature, top_k, top_p, generator=None):
         tp = float(top_p[b]) if top_p is not None else 1.0
         sp, si = p.sort(descending=True)
         m = torch.ones(V, dtype=torch.bool, device=lf.device)
+        sk = sp
         if 0 < k < V:                        # top-k first ...
             m &= p >= sp[k - 1]
-            sp = sp[:k] / sp[:k].sum()       # ... then the nucleus of the renormalised top-k distribution (vLLM / HF)
-            scale = float(p[m].sum())
-        else:
-            scale = 1.0
-        if tp < 1.0:
-            cum = sp.cumsum(0)
+            sk = sp[:k]
+        if tp < 1.0:                         # ... then the nucleus of the renormalised top-k distribution (vLLM / HF)
+            cum = (sk / sk.sum()).cumsum(0)
             n = int((cum < tp).sum().item()) + 1
-            m &= p >= sp[min(n, sp.numel()) - 1] * scale
+            m &= p >= sk[min(n, sk.numel()) - 1]
         keep[b] = m
     return greedy, keep
 

@@ -119,6 +119,9 @@ PRESETS: dict[str, LlamaConfig] = {
     "tiny-mha8": LlamaConfig(hidden_size=1024, intermediate_size=2816, num_hidden_layers=2,
                              num_attention_heads=8, num_key_value_heads=8, vocab_size=1024,
                              max_position_embeddings=2048, name="tiny-mha8"),      # TP tests up to 8 ranks
+    "tiny-2h": LlamaConfig(hidden_size=256, intermediate_size=704, num_hidden_layers=2,
+                           num_attention_heads=2, num_key_value_heads=2, vocab_size=1024,
+                           max_position_embeddings=2048, name="tiny-2h"),  # at TP=2: the per-rank shapes of tiny-mha8 at TP=8
     "llama2-7b": LlamaConfig(name="llama2-7b"),
     "llama2-13b": LlamaConfig(hidden_size=5120, intermediate_size=13824, num_hidden_layers=40,
                               num_attention_heads=40, num_key_value_heads=40, name="llama2-13b"),

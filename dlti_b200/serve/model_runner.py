@@ -96,7 +96,7 @@ class TPContext:
             owner ranks by the embedding kernel (parallel.fused.PeerRows) instead of being replicated;
           * C11: a [max_rows, vocab] logits buffer per rank that every rank's LM-head GEMM epilogue writes its
             vocabulary slice into (peer stores), replacing the NCCL all-gather of the logits."""
-        if not self.use_fused or hasattr(w.embed, "lookup"):
+        if not self.use_fused or hasattr(w.embed, "lookup") or os.environ.get("DLTI_TP_ADOPT", "1") != "1":
             return
         import torch.distributed as dist
         from ..parallel.fused import PeerRows

@@ -102,6 +102,7 @@ class Zero3Weights:
             self._GatherUse = GatherUse
             self.head_stage = StagedMatrix(fused, self.lm_head_shard.shape[0], d, dtype)
             self.head_step = -1
+        self._h2d_live: dict = {}   # offload on one rank: layer -> (device buffer index, copy-done event)
         self._big = {}          # gathered embed / lm_head staging (allocated on demand)
         self._h2d = {}          # offload: device copies of this rank's shards while in flight
         self.gather_bytes = 0   # bytes received from peers (for roofline reports)
@@ -223,7 +224,39 @@ class Zero3Weights:
         self.slot_layer[s] = i
         return s
 
+    def _h2d_layer(self, i: int) -> None:
+        """ZeRO-Offload of parameters on ONE rank (D16): start the host-to-device copy of layer i's (pinned)
+        matrices on a copy stream into one of two device-resident layer buffers, one layer ahead of its use, so
+        that the PCIe transfer of layer i+1 overlaps the compute of layer i. Buffers are recycled only after the
+        compute stream has finished with them (events)."""
+        if i in self._h2d_live or not (0 <= i < self.cfg.num_hidden_layers):
+            return
+        if getattr(self, "_h2d_stream", None) is None:
+            self._h2d_stream = torch.cuda.Stream(device=self.device)
+            self._h2d_bufs = [{m: torch.empty_like(self.layer_shards[0][m], device=self.device) for m in _MATS}
+                              for _ in range(2)]
+            self._h2d_free_ev = [None, None]
+        # recycle the buffer whose layer is farthest from i (an empty one first): in either direction of travel that
+        # is the layer whose kernels have all been launched, never the one about to be used
+        tenant = [next((k for k, v in self._h2d_live.items() if v[0] == b), None) for b in (0, 1)]
+        far = [10 ** 9 if t is None else abs(t - i) for t in tenant]
+        b = 0 if far[0] >= far[1] else 1
+        if tenant[b] is not None:
+            del self._h2d_live[tenant[b]]
+        st = self._h2d_stream
+        if self._h2d_free_ev[b] is not None:
+            st.wait_event(self._h2d_free_ev[b])
+        with torch.cuda.stream(st):
+            for m in _MATS:
+                self._h2d_bufs[b][m].copy_(self.layer_shards[i][m], non_blocking=True)
+            ev = torch.cuda.Event()
+            ev.record(st)
+        self._h2d_live[i] = (b, ev)
+
     def prefetch(self, i: int) -> None:
+        if self.world == 1 and self.offload and self.device.type == "cuda":
+            self._h2d_layer(i)
+            return
         if self.in_gemm_gather and 0 <= i < self.cfg.num_hidden_layers:
             self._queue_layer(i)
             return
@@ -248,6 +281,12 @@ class Zero3Weights:
                 self._gather((i, m), self.layer_shards[i][m], self.slots[s][m])
 
     def layer(self, i: int) -> LayerWeights:
+        if self.world == 1 and self.offload and self.device.type == "cuda":
+            self._h2d_layer(i)                      # no-op when prefetch(i) already started it
+            b, ev = self._h2d_live[i]
+            torch.cuda.current_stream().wait_event(ev)
+            r = {m: self._h2d_bufs[b][m][: self.shapes[m][0]] for m in _MATS}
+            return LayerWeights(r["w_qkv"], r["w_o"], r["w_gu"], r["w_down"], *self.norms[i])
         if self.world == 1:
             sh = self.layer_shards[i]
             dev = (lambda t: t.to(self.device, non_blocking=True)) if self.offload else (lambda t: t)
@@ -272,6 +311,11 @@ class Zero3Weights:
         return LayerWeights(r["w_qkv"], r["w_o"], r["w_gu"], r["w_down"], *self.norms[i])
 
     def release(self, i: int) -> None:
+        if self.world == 1 and self.offload and i in self._h2d_live:
+            ev = torch.cuda.Event()                 # the compute stream is done with this layer's buffer from here on
+            ev.record(torch.cuda.current_stream())
+            self._h2d_free_ev[self._h2d_live[i][0]] = ev
+            return
         if self.world == 1 or self.in_gemm_gather or i not in self.slot_of:
             return
         s = self.slot_of.pop(i)

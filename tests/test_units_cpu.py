@@ -316,3 +316,113 @@ def test_baseline_fp16_scaler_follows_torch_gradscaler_and_ds_config_reports_ign
     keys = " ".join(c.ignored_keys())
     assert "stage3_prefetch_bucket_size" in keys and "stage3_max_reuse_distance" in keys
     assert "accepted for compatibility" in capsys.readouterr().err
+
+
+def test_zero3_gather_queue_schedule_dry_run(monkeypatch):
+    """Host-side logic of K1 (parallel.fused.GatherQueue + parallel.zero3.Zero3Weights), run without a GPU: the native
+    attach call is replaced by a recorder and two optimizer steps of the model's exact call order are replayed. Every
+    64-row unit of every gathered matrix must be requested exactly once per fetch; a consumer whose operand is not
+    fully requested by EARLIER launches must carry the remainder itself and wait on it; in steady state a step
+    fetches 2(L-2) layers + the LM head (two staging slots: the two layers at either turning point are still there)."""
+    from dlti_b200.models.config import PRESETS
+    from dlti_b200.parallel import fused as F
+    from dlti_b200.parallel.comm import DistInfo
+    from dlti_b200.parallel.zero3 import Zero3Weights
+
+    calls = []
+
+    def fake_fn(name, argtypes, restype=None, cpu=False):
+        def f(*a):
+            if name == "dlti_gemm2_attach":
+                calls.append(dict(staging=a[1].value if hasattr(a[1], "value") else a[1], j0=a[7], n=a[8], epoch=a[9],
+                                  wait=bool(getattr(a[10], "value", a[10]))))
+            return 0
+        return f
+
+    monkeypatch.setattr(F._lib, "fn", fake_fn)
+
+    class FakeFused:
+        rank, world = 1, 4
+        info = DistInfo(rank=1, world_size=4, device=torch.device("cpu"))
+        err = torch.zeros(1, dtype=torch.int32)
+
+        def alloc_symmetric(self, shape, dtype):
+            return torch.zeros(*shape, dtype=dtype)
+
+        def peer_array(self, t):
+            return None
+
+    import dataclasses
+    cfg = dataclasses.replace(PRESETS["tiny-gqa"], num_hidden_layers=5)
+    L = cfg.num_hidden_layers
+    ds = DSConfig({"zero_optimization": {"stage": 3}})
+    w = Zero3Weights(cfg, ds, FakeFused.info, torch.bfloat16, backend="fused", fused=FakeFused())
+    assert w.in_gemm_gather
+    by_ptr = {}
+    for s in w.stage_slots:
+        for m, sm in s.items():
+            by_ptr[sm.staging.data_ptr()] = sm
+    by_ptr[w.head_stage.staging.data_ptr()] = w.head_stage
+    fetches = []                     # (tag, epoch) in bind order
+    orig_bind = F.StagedMatrix.bind
+
+    def bind(self, shard, tag):
+        orig_bind(self, shard, tag)
+        fetches.append((tag, self.epoch, self))
+    monkeypatch.setattr(F.StagedMatrix, "bind", bind)
+    covered = {}                     # (id(sm), epoch) -> set of positions requested so far
+
+    def launch(use, flops=1e11):
+        """One large GEMM launch with `use` as its gather handle; checks the consumer rule."""
+        n0 = len(calls)
+        sm = use.sm
+        before = set(covered.get((id(sm), sm.epoch), ())) if sm is not None else None
+        use.attach(flops)
+        new = calls[n0:]
+        assert len(new) <= 1
+        for c in new:
+            tgt = by_ptr[c["staging"]]
+            got = covered.setdefault((id(tgt), c["epoch"]), set())
+            rng = set(range(c["j0"], c["j0"] + c["n"]))
+            assert not (rng & got), "a unit was requested twice"
+            got |= rng
+            if c["wait"]:
+                assert tgt is sm and before | rng == set(range(sm.n_units)), "a waiting launch must complete its operand"
+        if sm is not None and len(before) < sm.n_units:          # operand incomplete before this launch
+            assert new and new[0]["wait"] and by_ptr[new[0]["staging"]] is sm
+
+    nb = 2
+    for step in range(2):
+        start = len(fetches)
+        w.prefetch(0)
+        for li in range(L):
+            if li + 1 < L:
+                w.prefetch(li + 1)
+            lw = w.layer(li)
+            if li == L - 1:
+                w.prefetch_head()
+            for _ in range(nb):
+                for m in ("w_qkv", "w_o", "w_gu", "w_down"):
+                    launch(lw.g(m))
+            w.release(li)
+        w.get_lm_head()
+        for _ in range(nb):
+            launch(w.head_gather()); launch(w.head_gather())
+        w.release_head()
+        w.prefetch(L - 1)
+        for li in reversed(range(L)):
+            if li > 0:
+                w.prefetch(li - 1)
+            lw = w.layer(li)
+            for _ in range(nb):
+                for m in ("w_qkv", "w_o", "w_gu", "w_down", "w_gu", "w_o", "w_qkv"):
+                    launch(lw.g(m))
+            w.release(li)
+        layer_fetches = {t[0][0] for t in fetches[start:] if len(t[0]) == 2}
+        n_layer_binds = sum(1 for t in fetches[start:] if len(t[0]) == 2) // 4
+        n_head = sum(1 for t in fetches[start:] if t[0] == ("lm_head",))
+        assert n_head == 1
+        assert n_layer_binds == (2 * L - 2 if step == 0 else 2 * (L - 2)), (step, n_layer_binds)
+    w.queue.flush()
+    for (tag, epoch, sm) in fetches:                             # every fetch fully requested, exactly once
+        assert covered.get((id(sm), epoch)) == set(range(sm.n_units)), (tag, epoch)

@@ -312,7 +312,8 @@ def _params_from_body(b: dict) -> SamplingParams:
         seed=b.get("seed"), stop=b.get("stop") or [], stop_token_ids=b.get("stop_token_ids") or [],
         ignore_eos=bool(b.get("ignore_eos", False)), min_tokens=int(b.get("min_tokens", 0) or 0),
         logprobs=b.get("logprobs"), echo=bool(b.get("echo", False)),
-        skip_special_tokens=bool(b.get("skip_special_tokens", True)))
+        skip_special_tokens=bool(b.get("skip_special_tokens", True)),
+        detokenize=bool(b.get("detokenize", True)))
 
 
 def _error(message: str, typ: str = "invalid_request_error", code: int = 400):

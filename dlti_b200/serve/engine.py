@@ -584,6 +584,8 @@ class LLMEngine:
         """Text of `request_id` not yet handed out. While the request is running and has stop strings, the last
         max(len(stop)) - 1 characters are held back: they could still turn out to be the start of a match."""
         r = self.requests[request_id]
+        if not r.params.detokenize and not r.params.stop:
+            return ""                               # the client asked for token ids only
         st = self._text[request_id]
         if not st[2]:                               # (a stop-string match has already fixed the final text)
             st = self._advance_text(r, final)

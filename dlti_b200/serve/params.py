@@ -21,6 +21,7 @@ class SamplingParams:
     logprobs: int | None = None
     echo: bool = False
     skip_special_tokens: bool = True
+    detokenize: bool = True     # False (vLLM's field of the same name): return token ids only, produce no text
 
     def __post_init__(self):
         if isinstance(self.stop, str):

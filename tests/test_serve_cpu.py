@@ -729,3 +729,11 @@ def test_unmerged_adapter_serving_matches_merged_weights():
     c = engine(full, False).generate(prompts, sp)
     assert [o["token_ids"] for o in a] == [o["token_ids"] for o in b]
     assert [o["token_ids"] for o in a] != [o["token_ids"] for o in c]          # the adapter does change the model
+
+
+def test_detokenize_false_returns_token_ids_only():
+    cfg, full, eng = make_engine()
+    o = eng.generate([[1, 50, 51]], SamplingParams(max_tokens=6, temperature=0.0, ignore_eos=True, detokenize=False))[0]
+    assert len(o["token_ids"]) == 6 and o["text"] == ""
+    o2 = eng.generate([[1, 50, 51]], SamplingParams(max_tokens=6, temperature=0.0, ignore_eos=True))[0]
+    assert o2["token_ids"] == o["token_ids"] and o2["text"] != ""

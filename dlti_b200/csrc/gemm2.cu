@@ -96,7 +96,7 @@ struct Gemm2Params {
 //  * a WAIT spec: the B operand of this launch is such a staging buffer; the TMA producer acquires the
 //    counters of the units a tile needs before it loads them (one relaxed sweep at kernel start takes the fast
 //    path when everything has already landed).
-// TMA only ever reads this GPU's staging buffer; peer memory is read with ld.global by the gather warps.
+// TMA only ever reads this GPU's staging buffer; peer memory is read with ld.global by the gather warp.
 constexpr int GATHER_CH = 16;              // chunks per 64-row unit (4 rows each)
 constexpr int GATHER_THREADS = 32;          // one warp: the CTA stays at 256 threads (ptxas budgets registers per
                                            // 128 threads: 288 threads would cap the epilogue at 168 and spill)
@@ -481,7 +481,7 @@ gemm2_kernel(const Gemm2Params p, const GatherJob gj, const WaitSpec ws_, const 
       }
     }
   } else if (warp >= 7) {
-    // ===================== gather warps (present when a job is attached) =====================
+    // ===================== gather warp (present when a job is attached) =====================
     const int gt = threadIdx.x - NUM_THREADS;                  // 0..31
     const long long chunk_bytes = 4 * gj.row_bytes;            // 4 rows
     const long long unit_bytes = 64 * gj.row_bytes;

@@ -426,3 +426,79 @@ def test_zero3_gather_queue_schedule_dry_run(monkeypatch):
     w.queue.flush()
     for (tag, epoch, sm) in fetches:                             # every fetch fully requested, exactly once
         assert covered.get((id(sm), epoch)) == set(range(sm.n_units)), (tag, epoch)
+
+
+def test_tp_prefill_k10_k11_host_orchestration_dry_run(monkeypatch):
+    """Host side of the GEMM-fused prefill collectives (serve.model_runner.TPContext, K10 / K11) without a GPU: the
+    native calls are recorded. Per row-parallel GEMM: scatter spec with per = ceil(ceil(T / world) / 64) * 64, two flag
+    barriers around the owner-side reduce, a fresh zeroed counter slice, and a gather handle whose job covers
+    world * per / 64 units starting at this rank's own rows (rot = rank * per / 64, m_rot = rank * per // 256)."""
+    from dlti_b200.models.config import PRESETS
+    from dlti_b200.parallel import fused as F
+    from dlti_b200.parallel.comm import DistInfo
+    from dlti_b200.serve import model_runner as MR
+
+    rec = []
+
+    def fake_fn(name, argtypes, restype=None, cpu=False):
+        def f(*a):
+            rec.append((name, a))
+            return 0
+        return f
+
+    monkeypatch.setattr(F._lib, "fn", fake_fn)
+    monkeypatch.setattr(F._lib, "stream_ptr", lambda: None)
+
+    class FakeFused:
+        def __init__(self, rank, world):
+            self.rank, self.world = rank, world
+            self.info = DistInfo(rank=rank, world_size=world, device=torch.device("cpu"))
+            self.err = torch.zeros(1, dtype=torch.int32)
+            self.barriers = []
+
+        def alloc_symmetric(self, shape, dtype):
+            return torch.zeros(*shape, dtype=dtype)
+
+        def peer_array(self, t):
+            return ("peers", t.data_ptr())
+
+        def barrier_graph_safe(self, ch):
+            self.barriers.append(ch)
+
+    cfg = PRESETS["tiny-mha8"]
+    d = cfg.hidden_size
+    for world, rank, T in ((8, 5, 465), (2, 1, 8192), (4, 0, 300)):
+        rec.clear()
+        fz = FakeFused(rank, world)
+        tp = MR.TPContext(fz.info, "fused", fz, cfg, max_tokens=8192, dtype=torch.float32)
+        assert tp.fused_large
+        residual = torch.zeros(T, d)
+        seen = {}
+
+        def partial_fn(out, push, scatter=None):
+            seen["scatter"], seen["out_rows"] = scatter, out.shape[0]
+
+        counters = []
+        for _ in range(3):
+            x = tp.reduce_add_norm(partial_fn, T, residual, torch.ones(d), 1e-5)
+            per = -(-(-(-T // world)) // 64) * 64
+            assert isinstance(x, MR.ShardedAct) and x.rows().shape == (T, d)
+            assert seen["scatter"][1:] == (world, rank, per) and seen["out_rows"] == T
+            h = x.handle
+            assert h.per == per and h.n_units == world * per // 64 and h.counters.numel() == h.n_units
+            assert int(h.counters.abs().sum()) == 0
+            counters.append((h.counters.data_ptr(), h.counters.numel()))
+            h.attach(1e9)
+            att = [a for n, a in rec if n == "dlti_gemm2_attach"][-1]
+            assert att[4] == per and att[5] == world and att[6] == rank * (per // 64) and att[7] == 0 and att[8] == h.n_units
+            assert att[11] == h.n_units                                   # the launch waits on its A operand
+            assert [a for n, a in rec if n == "dlti_gemm2_attach_a_side"][-1][0] == (rank * per) // 256
+            n_att = len([1 for n, _ in rec if n == "dlti_gemm2_attach"])
+            h.attach(1e9)                                                 # a second consumer: nothing to pull again
+            assert len([1 for n, _ in rec if n == "dlti_gemm2_attach"]) == n_att
+        assert fz.barriers == [6, 6] * 3
+        own = [a for n, a in rec if n == "dlti_tp_own_reduce_norm"]
+        lo = min(T, rank * per)
+        assert len(own) == 3 and own[0][2] == per and own[0][3] == lo and own[0][4] == min(T, lo + per) - lo
+        spans = sorted(counters)
+        assert all(a + 4 * n <= b for (a, n), (b, _) in zip(spans, spans[1:])), "counter slices overlap"

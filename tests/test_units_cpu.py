@@ -502,3 +502,65 @@ def test_tp_prefill_k10_k11_host_orchestration_dry_run(monkeypatch):
         assert len(own) == 3 and own[0][2] == per and own[0][3] == lo and own[0][4] == min(T, lo + per) - lo
         spans = sorted(counters)
         assert all(a + 4 * n <= b for (a, n), (b, _) in zip(spans, spans[1:])), "counter slices overlap"
+
+
+@pytest.mark.parametrize("mode", ["fused", "overlap", "tail"])
+def test_k9_host_orchestration_dry_run(monkeypatch, mode):
+    """parallel.zero.ZeroOptimizer on the fused backend with a recording fake: which peer-memory calls a step makes in
+    each DLTI_K9 mode, and that the flat gradient ranges handed to the reduce cover this rank's partition."""
+    from dlti_b200.models.config import PRESETS
+    from dlti_b200.models.lora import LoraConfig, LoraParams
+    from dlti_b200.parallel.comm import DistInfo
+    from dlti_b200.parallel.zero import ZeroOptimizer
+
+    monkeypatch.setenv("DLTI_K9", mode)
+    cfg = PRESETS["tiny-gqa"]
+    world, rank = 4, 2
+    info = DistInfo(rank=rank, world_size=world, device=torch.device("cpu"))
+    lora = LoraParams(cfg, LoraConfig(r=8, lora_alpha=16), "cpu", torch.float32, pad_to=world * 64)
+    calls = []
+
+    class FakeFused:
+        def k9_begin_step(self):
+            calls.append(("begin",))
+
+        def grad_range_final(self, slot, g_full, grad_part, glo, n, part_lo, part_n, side=True, ctas=16):
+            calls.append(("range", slot, glo, n, part_lo, part_n, side))
+
+        def k9_step(self, master, m, v, g, lo, n, **kw):
+            calls.append(("step", lo, n, sorted(kw)))
+            kw["out2"].copy_(torch.tensor([4.0, 7.0]))
+            kw["skipped_out"].zero_()
+
+        def reduce_scatter_accumulate(self, g, part):
+            calls.append(("rs",))
+
+        def global_sumsq(self, g, out):
+            calls.append(("sumsq",))
+            out.fill_(4.0)
+
+        def adamw_push(self, *a, **kw):
+            calls.append(("adamw_push",))
+            kw["skipped_out"].zero_()
+
+    opt = ZeroOptimizer(lora, DSConfig({"zero_optimization": {"stage": 2}}), info, lr=1e-3, backend="fused", fused=FakeFused())
+    assert opt.k9_fused == (mode != "tail") and opt.overlap == (mode == "overlap")
+    opt.begin_step()
+    for li in reversed(range(cfg.num_hidden_layers)):        # the model's hook, one call per decoder layer
+        lo, hi = lora.layer_range(li)
+        opt.on_grad_range_final(lo, hi - lo)
+    opt.on_micro_batch_end(is_boundary=True)
+    skipped, gnorm = opt.step(1e-3, torch.tensor([7.0]))
+    kinds = [c[0] for c in calls]
+    if mode == "tail":
+        assert kinds == ["rs", "sumsq", "adamw_push"] and opt.loss_sum_global is None
+    else:
+        ranges = [c for c in calls if c[0] == "range"]
+        if mode == "fused":
+            assert kinds == ["begin", "range", "step"] and ranges[0][1:4] == (0, 0, lora.padded_numel) and ranges[0][6] is False
+        else:
+            assert kinds == ["begin"] + ["range"] * cfg.num_hidden_layers + ["step"]
+            assert [r[1] for r in ranges] == list(range(cfg.num_hidden_layers)) and all(r[6] for r in ranges)
+            assert sum(r[3] for r in ranges) == lora.numel                  # the layers tile the adapter space
+        assert all(r[4] == rank * opt.part and r[5] == opt.part for r in ranges)
+        assert opt.loss_sum_global == 7.0 and not skipped and abs(gnorm - 2.0) < 1e-6
